@@ -1,0 +1,84 @@
+/* b2p -- C-ABI of the B200-native batched physics + OSC backend (libb2p.so).
+ *
+ * Drop-in boundary for the hot path of peterdavidfagan/mujoco_robot_environments:
+ * the calls below replace, with a leading env dimension, what the reference does through
+ * dm_control / mujoco for ONE scene:
+ *
+ *   b2p_step_physics   <- physics.set_control(ctrl); physics.step()           models/robot_arm.py:78-79
+ *   b2p_step_osc       <- RobotArm.run_controller(duration)                   models/robot_arm.py:61-94
+ *                         (OSC.compute_control_output  mujoco_controllers/osc.py:180-238,
+ *                          MinMax.compute_control_output  mujoco_controllers/min_max.py:14-19,
+ *                          OSC.is_converged  osc.py:240-247)
+ *   b2p_settle         <- PropPlacer settle loop under JointStaticIsolator    environment/prop_initializer.py:245-257
+ *   b2p_forward        <- physics.forward() + reads of data.site_xpos / contact / qacc
+ *                                                                           prop_initializer.py:190,221 ; tasks/rearrangement.py:653
+ *   b2p_osc_config     <- config/robots/arm/controller_config/osc.yaml gains / nullspace / convergence
+ *   b2p_set_env_params <- per-scene prop sizes drawn in environment/props.py:277-291 and the per-prop
+ *                         contype/conaffinity toggling of prop_initializer.py:142-162
+ *
+ * Conventions (after the reference's own raw C boundary, madrona_mjx src/bindings.cpp:219-250): the caller owns
+ * every I/O buffer (device pointers, e.g. torch tensors), the handle owns scratch, work is enqueued on the
+ * caller's stream, calls return 0 or a negative error code (no exceptions cross the boundary), a handle is
+ * not thread-safe, one handle per (GPU, model topology).  dtype: 0 = float64, 1 = float32; every "real"
+ * pointer below is of the handle's dtype.  Quaternions are MuJoCo order (w, x, y, z).
+ */
+#ifndef B2P_H
+#define B2P_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef struct b2p_handle_s* b2p_handle;
+
+enum { B2P_F64 = 0, B2P_F32 = 1 };
+enum { B2P_OK = 0, B2P_ERR_ARG = -1, B2P_ERR_MODEL = -2, B2P_ERR_CUDA = -3, B2P_ERR_STATE = -4 };
+
+/* b2p_query ids */
+enum {
+  B2P_Q_NQ = 0, B2P_Q_NV, B2P_Q_NU, B2P_Q_NPROP, B2P_Q_STATE_STRIDE, B2P_Q_OUT_STRIDE, B2P_Q_MAXPROP,
+  B2P_Q_REC_QPOS, B2P_Q_REC_QVEL, B2P_Q_REC_QACC_WARMSTART, B2P_Q_REC_TIME, B2P_Q_LAUNCHES, B2P_Q_SMEM_BYTES,
+  B2P_Q_BLOCKS_PER_SM, B2P_Q_THREADS, B2P_Q_GRID, B2P_Q_MAXCON, B2P_Q_NGEOM
+};
+/* derived-output fields (b2p_get / offsets inside the output record via b2p_out_offset) */
+enum {
+  B2P_O_SITE_XPOS = 0 /* [2][3] attachment_site, pinch */, B2P_O_SITE_XMAT /* [2][9] */, B2P_O_QACC /* [40] */,
+  B2P_O_QFRC_BIAS /* [40] */, B2P_O_CTRL /* [8] */, B2P_O_NCON, B2P_O_NEFC, B2P_O_NITER,
+  B2P_O_CONTACT /* [48][10]: dist,pos3,normal3,geom1,geom2,excluded */, B2P_O_MARM /* [16][16] */,
+  B2P_O_GEOM_XPOS /* [32][3] */, B2P_O_GEOM_XMAT /* [32][9] */, B2P_O_QACC_SMOOTH /* [40] */, B2P_O_EFC_FORCE /* [160] */,
+  B2P_O_NFIELD
+};
+
+int b2p_create(const void* model_blob, size_t nbytes, int n_env, int dtype, int device, b2p_handle* out);
+int b2p_destroy(b2p_handle h);
+int b2p_query(b2p_handle h, int what);
+int b2p_out_offset(int field, int* offset, int* count);
+
+/* state: [n_env][B2P_Q_STATE_STRIDE] reals, one record per env: qpos | qvel | qacc_warmstart | time (see B2P_Q_REC_*) */
+int b2p_bind_state(b2p_handle h, void* state);
+/* optional caller-owned derived-output buffer [n_env][B2P_Q_OUT_STRIDE]; NULL = use the handle's own */
+int b2p_bind_out(b2p_handle h, void* out);
+/* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */
+int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active);
+int b2p_osc_config(b2p_handle h, const double gains6[6], const double nullspace7[7], double pos_thresh, double ori_thresh);
+/* 0 = only solver-active contacts while stepping (default), 1 = list every contact inside geom margin */
+int b2p_set_full_contacts(b2p_handle h, int full);
+
+int b2p_step_physics(b2p_handle h, const void* ctrl /* [n_env][nu] */, int n_steps, void* stream);
+int b2p_step_osc(b2p_handle h, const void* target13 /* [n_env][13] pos vel quat angvel */, const uint8_t* grip /* [n_env] */,
+                 int n_ticks, int control_steps, uint8_t* converged /* [n_env] or NULL */, void* stream);
+int b2p_settle(b2p_handle h, const uint8_t* env_mask /* NULL = all */, int max_steps, int min_steps, double qvel_tol,
+               double qacc_tol, int32_t* steps_done /* [n_env] or NULL */, void* stream);
+int b2p_forward(b2p_handle h, int full_contacts, void* stream);
+int b2p_get(b2p_handle h, int field, void* dst /* [n_env][count] */, void* stream);
+int b2p_status(b2p_handle h, int32_t* flags /* device [n_env] */, int clear, void* stream);
+
+/* micro-benchmark: register-resident FMA chain, returns TFLOP/s of the handle-independent device (dtype 0/1) */
+int b2p_fma_peak(int dtype, int device, double* tflops);
+const char* b2p_last_error(void);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

@@ -1,0 +1,286 @@
+// libb2p.so: sm_100a kernels + the C-ABI of include/b2p.h.
+//
+// Launch shape: persistent grid of one CTA per resident slot (148 SMs x CTAs/SM that fit the shared-memory
+// footprint), each CTA loops over scenes e = blockIdx.x, blockIdx.x + gridDim.x, ...  Model constants
+// (DevModel<T>) are staged into shared memory ONCE per CTA with a 1-D TMA bulk copy (cp.async.bulk ->
+// UBLKCP) completing on an mbarrier; each scene's 128-real state record is TMA-loaded into the head of
+// Scratch<T> and TMA-stored back at the end, so HBM sees exactly one coalesced record read + write per
+// scene per launch, however many physics steps the launch runs.
+#include <cuda_runtime.h>
+
+#include <cstdio>
+#include <cstdlib>
+#include <string>
+
+#include "../../include/b2p.h"
+#include "b2p_core.h"
+
+using namespace b2p;
+
+static thread_local std::string g_err;
+static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(B2P_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
+
+// ------------------------------------------------------------------------------------------ TMA / mbarrier helpers
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase) {
+  unsigned done;
+  do {
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_store_1d(void* dst, const void* src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+constexpr int NT = 128;
+template <typename T> struct Occ { static constexpr int kMinBlocks = 2; };
+template <> struct Occ<float> { static constexpr int kMinBlocks = 4; };
+
+template <typename T>
+struct alignas(16) SmemLayout {
+  DevModel<T> model;
+  alignas(16) Scratch<T> scratch;
+  alignas(8) unsigned long long bar;
+};
+
+template <typename T>
+__global__ void __launch_bounds__(NT, Occ<T>::kMinBlocks) b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int use_tma) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SmemLayout<T>& sm = *reinterpret_cast<SmemLayout<T>*>(smem_raw);
+  const Ctx c = {(int)threadIdx.x, (int)blockDim.x};
+  constexpr unsigned kModelBytes = (unsigned)sizeof(DevModel<T>);
+  constexpr unsigned kRecBytes = REC_SIZE * sizeof(T);
+  static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
+  unsigned phase = 0;
+  if (use_tma) {
+    if (c.tid == 0) { mbar_init(&sm.bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
+    __syncthreads();
+    if (c.tid == 0) { mbar_expect_tx(&sm.bar, kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar); }
+    mbar_wait(&sm.bar, phase); phase ^= 1;
+  } else {
+    const int* src = reinterpret_cast<const int*>(gmodel); int* dst = reinterpret_cast<int*>(&sm.model);
+    for (int i = c.tid; i < (int)(kModelBytes / 4); i += c.nt) dst[i] = src[i];
+    __syncthreads();
+  }
+  for (int env = blockIdx.x; env < a.n_env; env += gridDim.x) {
+    if (a.env_mask && !a.env_mask[env]) continue;
+    T* rec = a.state + (size_t)env * a.state_stride;
+    if (use_tma) {
+      if (c.tid == 0) { fence_async_smem(); mbar_expect_tx(&sm.bar, kRecBytes); tma_load_1d(sm.scratch.qpos, rec, kRecBytes, &sm.bar); }
+      mbar_wait(&sm.bar, phase); phase ^= 1;
+    }
+    run_env(sm.model, g, sm.scratch, a, env, c, use_tma != 0);
+    if (use_tma) {
+      __syncthreads();
+      if (c.tid == 0) { fence_async_smem(); tma_store_1d(rec, sm.scratch.qpos, kRecBytes); }
+    }
+    __syncthreads();
+  }
+}
+
+// register-resident FMA chain for the FP pipe roofline denominator
+template <typename T>
+__global__ void fma_peak_kernel(T* out, int iters) {
+  T a0 = T(threadIdx.x) * T(1e-3), a1 = a0 + 1, a2 = a0 + 2, a3 = a0 + 3, a4 = a0 + 4, a5 = a0 + 5, a6 = a0 + 6, a7 = a0 + 7;
+  const T b = T(0.999), cc = T(1e-4);
+  for (int i = 0; i < iters; i++) {
+    a0 = a0 * b + cc; a1 = a1 * b + cc; a2 = a2 * b + cc; a3 = a3 * b + cc; a4 = a4 * b + cc; a5 = a5 * b + cc; a6 = a6 * b + cc; a7 = a7 * b + cc;
+  }
+  out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
+}
+
+// ------------------------------------------------------------------------------------------ handle
+struct b2p_handle_s {
+  int dtype, device, n_env, grid, blocks_per_sm, smem_bytes, use_tma, full_contacts, nq, nv, nu, nprop, ngeom;
+  long long launches;
+  DevModel<double> hmodel;
+  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr; short *d_g1, *d_g2; void* d_pair_param;
+  void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
+  void* d_zero_ctrl;
+};
+
+template <typename T> static size_t smem_size() { return sizeof(SmemLayout<T>) + 128; }
+
+template <typename T>
+static int upload(b2p_handle_s* h, const HostTables& ht) {
+  DevModel<T> dm; convert_model(h->hmodel, dm);
+  CK(cudaMalloc(&h->d_model, sizeof dm)); CK(cudaMemcpy(h->d_model, &dm, sizeof dm, cudaMemcpyHostToDevice));
+  std::vector<T> mv(ht.mesh_vert.begin(), ht.mesh_vert.end());
+  CK(cudaMalloc(&h->d_mesh_vert, mv.size() * sizeof(T) + 16)); CK(cudaMemcpy(h->d_mesh_vert, mv.data(), mv.size() * sizeof(T), cudaMemcpyHostToDevice));
+  std::vector<PairParam<T>> pp(ht.pair_g1.size()); std::vector<short> g1(pp.size()), g2(pp.size());
+  for (size_t i = 0; i < pp.size(); i++) {
+    const double* q = &ht.pair_param[12 * i];
+    for (int k = 0; k < 3; k++) pp[i].friction[k] = (T)q[k];
+    for (int k = 0; k < 2; k++) pp[i].solref[k] = (T)q[3 + k];
+    for (int k = 0; k < 5; k++) pp[i].solimp[k] = (T)q[5 + k];
+    pp[i].margin = (T)q[10]; pp[i].gap = (T)q[11]; g1[i] = (short)ht.pair_g1[i]; g2[i] = (short)ht.pair_g2[i];
+  }
+  CK(cudaMalloc(&h->d_pair_param, pp.size() * sizeof(PairParam<T>) + 16)); CK(cudaMemcpy(h->d_pair_param, pp.data(), pp.size() * sizeof(PairParam<T>), cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->d_g1, g1.size() * 2 + 16)); CK(cudaMemcpy(h->d_g1, g1.data(), g1.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->d_g2, g2.size() * 2 + 16)); CK(cudaMemcpy(h->d_g2, g2.data(), g2.size() * 2, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->d_nbradr, ht.mesh_nbradr.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbradr, ht.mesh_nbradr.data(), ht.mesh_nbradr.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->d_nbrnum, ht.mesh_nbrnum.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbrnum, ht.mesh_nbrnum.data(), ht.mesh_nbrnum.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->d_nbr, ht.mesh_nbr.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbr, ht.mesh_nbr.data(), ht.mesh_nbr.size() * 4, cudaMemcpyHostToDevice));
+  CK(cudaMalloc(&h->own_out, (size_t)h->n_env * OutLayout::SIZE * sizeof(T))); CK(cudaMemset(h->own_out, 0, (size_t)h->n_env * OutLayout::SIZE * sizeof(T)));
+  CK(cudaMalloc(&h->d_zero_ctrl, (size_t)h->n_env * MAXU * sizeof(T))); CK(cudaMemset(h->d_zero_ctrl, 0, (size_t)h->n_env * MAXU * sizeof(T)));
+  h->out = h->own_out;
+  const size_t smem = smem_size<T>();
+  CK(cudaFuncSetAttribute(b2p_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+  int per_sm = 0, sms = 0;
+  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T>, NT, smem));
+  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
+  if (per_sm < 1) return fail(B2P_ERR_CUDA, "kernel does not fit on an SM (shared memory)");
+  const char* ov = getenv("B2P_BLOCKS_PER_SM");
+  if (ov && atoi(ov) > 0 && atoi(ov) < per_sm) per_sm = atoi(ov);
+  h->blocks_per_sm = per_sm; h->smem_bytes = (int)smem;
+  h->grid = sms * per_sm; if (h->grid > h->n_env) h->grid = h->n_env;
+  return B2P_OK;
+}
+
+template <typename T>
+static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
+  if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
+  a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
+  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE;
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param};
+  b2p_step_kernel<T><<<h->grid, NT, smem_size<T>(), st>>>((const DevModel<T>*)h->d_model, g, a, h->use_tma);
+  h->launches++;
+  CK(cudaGetLastError());
+  return B2P_OK;
+}
+
+template <typename T>
+static int run_mode(b2p_handle h, int mode, int n_steps, int control_steps, int full, const void* ctrl, const void* target, const uint8_t* grip,
+                    const uint8_t* mask, uint8_t* conv, int32_t* steps_done, double vt, double at, int min_steps, void* stream) {
+  StepArgs<T> a; std::memset(&a, 0, sizeof a);
+  a.mode = mode; a.n_steps = n_steps; a.control_steps = control_steps; a.full_contacts = full;
+  a.ctrl = (const T*)(ctrl ? ctrl : h->d_zero_ctrl); a.target = (const T*)target; a.grip = grip; a.env_mask = mask; a.converged = conv; a.steps_done = steps_done;
+  a.settle_qvel_tol = (T)vt; a.settle_qacc_tol = (T)at; a.settle_min_steps = min_steps;
+  return launch<T>(h, a, (cudaStream_t)stream);
+}
+extern "C" {
+
+const char* b2p_last_error(void) { return g_err.c_str(); }
+
+int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device, b2p_handle* out) {
+  if (!blob || !out || n_env < 1 || (dtype != B2P_F64 && dtype != B2P_F32)) return fail(B2P_ERR_ARG, "b2p_create: bad argument");
+  b2p_handle_s* h = new b2p_handle_s(); std::memset((void*)h, 0, sizeof *h);
+  HostTables ht;
+  std::string err = build_model(blob, nbytes, h->hmodel, ht);
+  if (!err.empty()) { delete h; return fail(B2P_ERR_MODEL, "b2p_create: " + err); }
+  h->dtype = dtype; h->device = device; h->n_env = n_env; h->nq = h->hmodel.nq; h->nv = h->hmodel.nv; h->nu = h->hmodel.nu; h->nprop = h->hmodel.nprop; h->ngeom = h->hmodel.ngeom;
+  const char* nt = getenv("B2P_NO_TMA"); h->use_tma = !(nt && nt[0] == '1');
+  CK(cudaSetDevice(device));
+  CK(cudaMalloc(&h->d_status, (size_t)n_env * 4)); CK(cudaMemset(h->d_status, 0, (size_t)n_env * 4));
+  int rc = dtype == B2P_F64 ? upload<double>(h, ht) : upload<float>(h, ht);
+  if (rc != B2P_OK) { delete h; return rc; }
+  *out = h;
+  return B2P_OK;
+}
+int b2p_destroy(b2p_handle h) {
+  if (!h) return B2P_OK;
+  cudaSetDevice(h->device);
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl};
+  for (void* p : ptrs) if (p) cudaFree(p);
+  delete h;
+  return B2P_OK;
+}
+int b2p_query(b2p_handle h, int what) {
+  if (!h) return B2P_ERR_ARG;
+  switch (what) {
+    case B2P_Q_NQ: return h->nq; case B2P_Q_NV: return h->nv; case B2P_Q_NU: return h->nu; case B2P_Q_NPROP: return h->nprop;
+    case B2P_Q_STATE_STRIDE: return REC_SIZE; case B2P_Q_OUT_STRIDE: return OutLayout::SIZE; case B2P_Q_MAXPROP: return MAXP;
+    case B2P_Q_REC_QPOS: return REC_QPOS; case B2P_Q_REC_QVEL: return REC_QVEL; case B2P_Q_REC_QACC_WARMSTART: return REC_QACC; case B2P_Q_REC_TIME: return REC_TIME;
+    case B2P_Q_LAUNCHES: return (int)h->launches; case B2P_Q_SMEM_BYTES: return h->smem_bytes; case B2P_Q_BLOCKS_PER_SM: return h->blocks_per_sm;
+    case B2P_Q_THREADS: return NT; case B2P_Q_GRID: return h->grid; case B2P_Q_MAXCON: return MAXCON; case B2P_Q_NGEOM: return h->ngeom;
+  }
+  return B2P_ERR_ARG;
+}
+int b2p_out_offset(int field, int* offset, int* count) {
+  typedef OutLayout L;
+  static const int off[B2P_O_NFIELD] = {L::SITE_XPOS, L::SITE_XMAT, L::QACC, L::QFRC_BIAS, L::CTRL, L::NCON, L::NEFC, L::NITER, L::CONTACT, L::MARM, L::GPOS, L::GMAT, L::QACC_SMOOTH, L::EFC_FORCE};
+  static const int cnt[B2P_O_NFIELD] = {6, 18, MAXNV, MAXNV, MAXU, 1, 1, 1, MAXCON * L::CONTACT_W, MAXTD * MAXTD, MAXG * 3, MAXG * 9, MAXNV, MAXEFC};
+  if (field < 0 || field >= B2P_O_NFIELD) return fail(B2P_ERR_ARG, "b2p_out_offset: unknown field");
+  if (offset) *offset = off[field];
+  if (count) *count = cnt[field];
+  return B2P_OK;
+}
+int b2p_bind_state(b2p_handle h, void* state) {
+  if (!h || !state) return fail(B2P_ERR_ARG, "b2p_bind_state: null");
+  if (((uintptr_t)state) % 16) return fail(B2P_ERR_ARG, "b2p_bind_state: state must be 16-byte aligned (TMA)");
+  h->state = state; return B2P_OK;
+}
+int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out = out ? out : h->own_out; return B2P_OK; }
+int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
+int b2p_set_full_contacts(b2p_handle h, int full) { if (!h) return B2P_ERR_ARG; h->full_contacts = full; return B2P_OK; }
+int b2p_osc_config(b2p_handle h, const double g[6], const double q0[7], double pt, double ot) {
+  if (!h || !g || !q0) return fail(B2P_ERR_ARG, "b2p_osc_config: null");
+  for (int i = 0; i < 6; i++) h->hmodel.osc_gains[i] = g[i];
+  for (int i = 0; i < 7; i++) h->hmodel.osc_null[i] = q0[i];
+  h->hmodel.osc_pos_thresh = pt; h->hmodel.osc_ori_thresh = ot;
+  CK(cudaSetDevice(h->device));
+  if (h->dtype == B2P_F64) { DevModel<double> dm; convert_model(h->hmodel, dm); CK(cudaMemcpy(h->d_model, &dm, sizeof dm, cudaMemcpyHostToDevice)); }
+  else { DevModel<float> dm; convert_model(h->hmodel, dm); CK(cudaMemcpy(h->d_model, &dm, sizeof dm, cudaMemcpyHostToDevice)); }
+  return B2P_OK;
+}
+
+#define DISPATCH(...) (h->dtype == B2P_F64 ? run_mode<double>(__VA_ARGS__) : run_mode<float>(__VA_ARGS__))
+
+int b2p_step_physics(b2p_handle h, const void* ctrl, int n_steps, void* stream) {
+  if (!h || n_steps < 0) return fail(B2P_ERR_ARG, "b2p_step_physics: bad argument");
+  return DISPATCH(h, MODE_PHYSICS, n_steps, 1, h->full_contacts, ctrl, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, stream);
+}
+int b2p_step_osc(b2p_handle h, const void* target13, const uint8_t* grip, int n_ticks, int control_steps, uint8_t* converged, void* stream) {
+  if (!h || !target13 || n_ticks < 0 || control_steps < 1) return fail(B2P_ERR_ARG, "b2p_step_osc: bad argument");
+  return DISPATCH(h, MODE_OSC, n_ticks, control_steps, h->full_contacts, nullptr, target13, grip, nullptr, converged, nullptr, 0, 0, 0, stream);
+}
+int b2p_settle(b2p_handle h, const uint8_t* mask, int max_steps, int min_steps, double vt, double at, int32_t* steps_done, void* stream) {
+  if (!h || max_steps < 0) return fail(B2P_ERR_ARG, "b2p_settle: bad argument");
+  return DISPATCH(h, MODE_SETTLE, max_steps, 1, h->full_contacts, nullptr, nullptr, nullptr, mask, nullptr, steps_done, vt, at, min_steps, stream);
+}
+int b2p_forward(b2p_handle h, int full_contacts, void* stream) {
+  if (!h) return fail(B2P_ERR_ARG, "b2p_forward: null handle");
+  return DISPATCH(h, MODE_FORWARD, 0, 1, full_contacts, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, stream);
+}
+int b2p_get(b2p_handle h, int field, void* dst, void* stream) {
+  int off, cnt;
+  if (!h || !dst) return fail(B2P_ERR_ARG, "b2p_get: null");
+  if (b2p_out_offset(field, &off, &cnt) != B2P_OK) return B2P_ERR_ARG;
+  const size_t w = h->dtype == B2P_F64 ? 8 : 4;
+  CK(cudaMemcpy2DAsync(dst, cnt * w, (const char*)h->out + off * w, OutLayout::SIZE * w, cnt * w, h->n_env, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  return B2P_OK;
+}
+int b2p_status(b2p_handle h, int32_t* flags, int clear, void* stream) {
+  if (!h) return B2P_ERR_ARG;
+  if (flags) CK(cudaMemcpyAsync(flags, h->d_status, (size_t)h->n_env * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
+  if (clear) CK(cudaMemsetAsync(h->d_status, 0, (size_t)h->n_env * 4, (cudaStream_t)stream));
+  return B2P_OK;
+}
+int b2p_fma_peak(int dtype, int device, double* tflops) {
+  if (!tflops) return B2P_ERR_ARG;
+  CK(cudaSetDevice(device));
+  int sms = 0; CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device));
+  const int blocks = sms * 8, threads = 256, iters = 1 << 16;
+  void* buf; CK(cudaMalloc(&buf, (size_t)blocks * threads * 8));
+  cudaEvent_t e0, e1; CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+  float best = 1e30f;
+  for (int rep = 0; rep < 4; rep++) {
+    CK(cudaEventRecord(e0));
+    if (dtype == B2P_F64) fma_peak_kernel<double><<<blocks, threads>>>((double*)buf, iters); else fma_peak_kernel<float><<<blocks, threads>>>((float*)buf, iters);
+    CK(cudaEventRecord(e1)); CK(cudaEventSynchronize(e1));
+    float ms; CK(cudaEventElapsedTime(&ms, e0, e1)); if (rep > 0 && ms < best) best = ms;
+  }
+  *tflops = 2.0 * 8 * (double)iters * blocks * threads / (best * 1e-3) / 1e12;
+  cudaFree(buf); cudaEventDestroy(e0); cudaEventDestroy(e1);
+  return B2P_OK;
+}
+}  // extern "C"

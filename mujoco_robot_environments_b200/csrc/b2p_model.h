@@ -1,0 +1,231 @@
+// Device-side model constants for the rearrangement model class, specialised:
+//   * one kinematic tree (arm + gripper) whose moving bodies each carry exactly one hinge
+//     (the compiler fuses welded bodies), tree body b <-> dof b-1;
+//   * NP free "prop" bodies with identity inertial frame (box props), 6 dofs each;
+//   * static geoms live on body 0.
+// Unified body ids: 0 static/world, 1..ntb-1 tree bodies, PROP_BODY0+p prop p.
+// DevModel<T> is a POD that the kernel stages into shared memory with one TMA bulk copy;
+// large read-only tables (hull vertices, pair table) stay in global memory.
+#pragma once
+#include <cmath>
+#include <cstdint>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "../../include/b2p_model_layout.h"
+
+namespace b2p {
+
+constexpr int MAXTD = 16;        // tree dofs (15 used)
+constexpr int MAXTB = 16;        // tree bodies incl. world
+constexpr int MAXP = 4;          // props
+constexpr int MAXNV = MAXTD + 6 * MAXP;   // 40
+constexpr int MAXNQ = MAXTD + 7 * MAXP;   // 44
+constexpr int MAXG = 32;         // collidable geoms
+constexpr int MAXCON = 48;       // contacts kept per env
+constexpr int MAXEFC = 160;      // constraint rows per env
+constexpr int MAXCAND = 160;     // narrow-phase candidates per env
+constexpr int MAXEQ = 4;
+constexpr int MAXU = 8;
+constexpr int MAXLEVEL = 12;
+constexpr int PROP_BODY0 = MAXTB;
+constexpr int JW = MAXTD - 1 + 6; // 21: compressed Jacobian row width (15 tree slots + 6 prop slots)
+constexpr int SEGB = MAXTD - 1;   // 15: first slot of segment B
+
+template <typename T>
+struct PairParam {               // per candidate geom pair, mixed contact parameters (App. B item 10)
+  T friction[3]; T solref[2]; T solimp[5]; T margin; T gap;
+};
+
+template <typename T>
+struct alignas(16) DevModel {
+  int nv, nq, ntd, ntb, nprop, ngeom, npair, neq, nu, nlevel;
+  int iterations, ls_iterations, integrator, ccd_iterations, site_body[2], pad_[2];
+  T timestep, gravity[3], impratio, tolerance, ls_tolerance, ccd_tolerance, meaninertia, ref[3];
+  // tree
+  int tb_parent[MAXTB], level_start[MAXLEVEL + 1], level_body[MAXTB], child_start[MAXTB + 1], child_list[MAXTB];
+  unsigned anc_mask[MAXTB];      // bit d set <=> tree dof d is on the chain of body b (incl. its own)
+  T tb_pos[MAXTB][3], tb_quat[MAXTB][4], tb_ipos[MAXTB][3], tb_iquat[MAXTB][4], tb_mass[MAXTB], tb_inertia[MAXTB][3];
+  T tb_invweight0[MAXTB][2];
+  T jnt_pos[MAXTD][3], jnt_axis[MAXTD][3], jnt_stiffness[MAXTD], jnt_range[MAXTD][2], jnt_margin[MAXTD];
+  T jnt_solref[MAXTD][2], jnt_solimp[MAXTD][5], qpos0[MAXTD], qpos_spring[MAXTD];
+  T dof_armature[MAXTD], dof_damping[MAXTD], dof_invweight0[MAXTD];
+  int jnt_limited[MAXTD];
+  // props
+  T prop_mass[MAXP];
+  // geoms
+  int geom_type[MAXG], geom_body[MAXG], geom_vertadr[MAXG], geom_vertnum[MAXG], geom_prop[MAXG];
+  T geom_size[MAXG][3], geom_pos[MAXG][3], geom_quat[MAXG][4], geom_rbound[MAXG], geom_invweight0[MAXG][2];
+  // sites: 0 attachment_site, 1 pinch
+  T site_pos[2][3], site_quat[2][4];
+  // equality
+  int eq_type[MAXEQ], eq_obj1[MAXEQ], eq_obj2[MAXEQ];
+  T eq_data[MAXEQ][6], eq_solref[MAXEQ][2], eq_solimp[MAXEQ][5];
+  // actuators
+  int act_trnnum[MAXU], act_trndof[MAXU][2], act_ctrllimited[MAXU], act_forcelimited[MAXU];
+  T act_trncoef[MAXU][2], act_gain[MAXU], act_bias[MAXU][3], act_ctrlrange[MAXU][2], act_forcerange[MAXU][2];
+  // OSC configuration (config/robots/arm/controller_config/osc.yaml)
+  T osc_gains[6], osc_null[7], osc_pos_thresh, osc_ori_thresh;
+};
+
+// ------------------------------------------------------------------------------------------ host builder
+struct HostTables {              // global-memory tables, always fp64 on host; converted on upload
+  std::vector<double> mesh_vert; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr;
+  std::vector<int> pair_g1, pair_g2; std::vector<double> pair_param;  // 12 doubles per pair
+};
+
+struct BlobView {
+  const unsigned char* p; const int* hdr; const double* opt; const int* tab;
+  explicit BlobView(const void* b) : p((const unsigned char*)b), hdr((const int*)b), opt((const double*)((const unsigned char*)b + B2PM_HEADER_BYTES)), tab((const int*)((const unsigned char*)b + B2PM_TABLE_OFFSET)) {}
+  const int* I(int f) const { return (const int*)(p + tab[2 * f]); }
+  const double* D(int f) const { return (const double*)(p + tab[2 * f]); }
+  int n(int f) const { return tab[2 * f + 1]; }
+  int C(int c) const { return hdr[c]; }
+};
+
+// Returns "" on success, else an error message.  Builds DevModel<double>; cast with convert<T>().
+inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>& m, HostTables& ht) {
+  if (nbytes < 1024) return "blob too small";
+  BlobView b(blob);
+  if ((unsigned)b.hdr[0] != B2PM_MAGIC || b.hdr[1] != B2PM_VERSION) return "bad blob magic/version";
+  std::memset(&m, 0, sizeof m);
+  const int nbody = b.C(B2PM_C_NBODY), nv = b.C(B2PM_C_NV), ngeom = b.C(B2PM_C_NGEOM), nprop = b.C(B2PM_C_NPROP);
+  const int ntd = b.C(B2PM_C_NARM) + b.C(B2PM_C_NGRIP), ntb = nbody - nprop;
+  if (nprop > MAXP || ntd > MAXTD - 1 || ntb > MAXTB || ngeom > MAXG || nv != ntd + 6 * nprop) return "model exceeds kernel maxima";
+  if (b.C(B2PM_C_NEQ) > MAXEQ || b.C(B2PM_C_NU) > MAXU) return "too many equalities / actuators";
+  if ((int)b.opt[B2PM_O_CONE] != B2P_CONE_ELLIPTIC) return "only elliptic cones are implemented";
+  m.nv = nv; m.nq = b.C(B2PM_C_NQ); m.ntd = ntd; m.ntb = ntb; m.nprop = nprop; m.ngeom = ngeom; m.npair = b.C(B2PM_C_NPAIR);
+  m.neq = b.C(B2PM_C_NEQ); m.nu = b.C(B2PM_C_NU);
+  m.timestep = b.opt[B2PM_O_TIMESTEP]; m.gravity[0] = b.opt[B2PM_O_GRAVITY_X]; m.gravity[1] = b.opt[B2PM_O_GRAVITY_Y]; m.gravity[2] = b.opt[B2PM_O_GRAVITY_Z];
+  m.impratio = b.opt[B2PM_O_IMPRATIO]; m.tolerance = b.opt[B2PM_O_TOLERANCE]; m.ls_tolerance = b.opt[B2PM_O_LS_TOLERANCE];
+  m.iterations = (int)b.opt[B2PM_O_ITERATIONS]; m.ls_iterations = (int)b.opt[B2PM_O_LS_ITERATIONS]; m.integrator = (int)b.opt[B2PM_O_INTEGRATOR];
+  m.ccd_iterations = (int)b.opt[B2PM_O_CCD_ITERATIONS]; m.ccd_tolerance = b.opt[B2PM_O_CCD_TOLERANCE]; m.meaninertia = b.opt[B2PM_O_MEANINERTIA];
+  const int *par = b.I(B2PM_F_BODY_PARENTID), *jnum = b.I(B2PM_F_BODY_JNTNUM), *jadr = b.I(B2PM_F_BODY_JNTADR), *jtype = b.I(B2PM_F_JNT_TYPE);
+  const int *dadr = b.I(B2PM_F_BODY_DOFADR), *bprop = b.I(B2PM_F_BODY_PROPID);
+  // body layout check: bodies 1..ntb-1 = tree (one hinge each, dof = body-1), then props (free joint)
+  for (int i = 1; i < nbody; i++) {
+    if (i < ntb) {
+      if (jnum[i] != 1 || jtype[jadr[i]] != B2P_JNT_HINGE || dadr[i] != i - 1 || par[i] >= i) return "tree body without exactly one hinge (compile with fuse=True)";
+    } else {
+      if (jnum[i] != 1 || jtype[jadr[i]] != B2P_JNT_FREE || bprop[i] != i - ntb || par[i] != 0) return "prop body layout unexpected";
+      const double *ip = b.D(B2PM_F_BODY_IPOS) + 3 * i, *iq = b.D(B2PM_F_BODY_IQUAT) + 4 * i;
+      if (std::fabs(ip[0]) + std::fabs(ip[1]) + std::fabs(ip[2]) > 1e-12 || std::fabs(std::fabs(iq[0]) - 1) > 1e-9) return "prop inertial frame must be identity";
+    }
+  }
+  auto cp = [](double* d, const double* s, int n) { for (int i = 0; i < n; i++) d[i] = s[i]; };
+  int depth[MAXTB] = {0}, maxd = 0;
+  for (int i = 0; i < ntb; i++) {
+    m.tb_parent[i] = i ? par[i] : 0;
+    cp(m.tb_pos[i], b.D(B2PM_F_BODY_POS) + 3 * i, 3); cp(m.tb_quat[i], b.D(B2PM_F_BODY_QUAT) + 4 * i, 4);
+    cp(m.tb_ipos[i], b.D(B2PM_F_BODY_IPOS) + 3 * i, 3); cp(m.tb_iquat[i], b.D(B2PM_F_BODY_IQUAT) + 4 * i, 4);
+    m.tb_mass[i] = b.D(B2PM_F_BODY_MASS)[i]; cp(m.tb_inertia[i], b.D(B2PM_F_BODY_INERTIA) + 3 * i, 3);
+    cp(m.tb_invweight0[i], b.D(B2PM_F_BODY_INVWEIGHT0) + 2 * i, 2);
+    if (i) { depth[i] = depth[par[i]] + 1; if (depth[i] > maxd) maxd = depth[i]; m.anc_mask[i] = m.anc_mask[par[i]] | (1u << (i - 1)); }
+  }
+  if (maxd > MAXLEVEL) return "tree too deep";
+  m.nlevel = maxd; int k = 0;
+  for (int l = 1; l <= maxd; l++) { m.level_start[l - 1] = k; for (int i = 1; i < ntb; i++) if (depth[i] == l) m.level_body[k++] = i; }
+  m.level_start[maxd] = k; k = 0;
+  for (int i = 0; i < ntb; i++) { m.child_start[i] = k; for (int c = 1; c < ntb; c++) if (par[c] == i) m.child_list[k++] = c; }
+  m.child_start[ntb] = k;
+  for (int d = 0; d < ntd; d++) {
+    cp(m.jnt_pos[d], b.D(B2PM_F_JNT_POS) + 3 * d, 3); cp(m.jnt_axis[d], b.D(B2PM_F_JNT_AXIS) + 3 * d, 3);
+    m.jnt_stiffness[d] = b.D(B2PM_F_JNT_STIFFNESS)[d]; cp(m.jnt_range[d], b.D(B2PM_F_JNT_RANGE) + 2 * d, 2); m.jnt_margin[d] = b.D(B2PM_F_JNT_MARGIN)[d];
+    cp(m.jnt_solref[d], b.D(B2PM_F_JNT_SOLREF) + 2 * d, 2); cp(m.jnt_solimp[d], b.D(B2PM_F_JNT_SOLIMP) + 5 * d, 5);
+    m.qpos0[d] = b.D(B2PM_F_QPOS0)[d]; m.qpos_spring[d] = b.D(B2PM_F_QPOS_SPRING)[d];
+    m.dof_armature[d] = b.D(B2PM_F_DOF_ARMATURE)[d]; m.dof_damping[d] = b.D(B2PM_F_DOF_DAMPING)[d]; m.dof_invweight0[d] = b.D(B2PM_F_DOF_INVWEIGHT0)[d];
+    m.jnt_limited[d] = b.I(B2PM_F_JNT_LIMITED)[d];
+  }
+  // spatial reference point: the (world-fixed) anchor of dof 0 at qpos0 = parent-chain of static frames
+  cp(m.ref, b.D(B2PM_F_BODY_POS) + 3 * 1, 3);   // body 1's parent is the (fused) world
+  for (int p = 0; p < nprop; p++) m.prop_mass[p] = b.D(B2PM_F_PROP_MASS)[p];
+  const int *gt = b.I(B2PM_F_GEOM_TYPE), *gb = b.I(B2PM_F_GEOM_BODYID), *gm = b.I(B2PM_F_GEOM_MESHID), *gp = b.I(B2PM_F_GEOM_PROPID), *condim = b.I(B2PM_F_GEOM_CONDIM);
+  const int *vadr = b.I(B2PM_F_MESH_VERTADR), *vnum = b.I(B2PM_F_MESH_VERTNUM);
+  for (int g = 0; g < ngeom; g++) {
+    if (condim[g] != 3) return "only condim 3 is implemented";
+    m.geom_type[g] = gt[g]; m.geom_prop[g] = gp[g];
+    m.geom_body[g] = gb[g] < ntb ? gb[g] : PROP_BODY0 + (gb[g] - ntb);
+    m.geom_vertadr[g] = gm[g] >= 0 ? vadr[gm[g]] : 0; m.geom_vertnum[g] = gm[g] >= 0 ? vnum[gm[g]] : 0;
+    cp(m.geom_size[g], b.D(B2PM_F_GEOM_SIZE) + 3 * g, 3); cp(m.geom_pos[g], b.D(B2PM_F_GEOM_POS) + 3 * g, 3); cp(m.geom_quat[g], b.D(B2PM_F_GEOM_QUAT) + 4 * g, 4);
+    m.geom_rbound[g] = b.D(B2PM_F_GEOM_RBOUND)[g]; cp(m.geom_invweight0[g], b.D(B2PM_F_GEOM_INVWEIGHT0) + 2 * g, 2);
+  }
+  const int sid[2] = {b.C(B2PM_C_SITE_ATTACHMENT), b.C(B2PM_C_SITE_PINCH)};
+  for (int s = 0; s < 2; s++) {
+    m.site_body[s] = b.I(B2PM_F_SITE_BODYID)[sid[s]];
+    if (m.site_body[s] >= ntb) return "site not on the arm tree";
+    cp(m.site_pos[s], b.D(B2PM_F_SITE_POS) + 3 * sid[s], 3); cp(m.site_quat[s], b.D(B2PM_F_SITE_QUAT) + 4 * sid[s], 4);
+  }
+  for (int e = 0; e < m.neq; e++) {
+    m.eq_type[e] = b.I(B2PM_F_EQ_TYPE)[e]; m.eq_obj1[e] = b.I(B2PM_F_EQ_OBJ1ID)[e]; m.eq_obj2[e] = b.I(B2PM_F_EQ_OBJ2ID)[e];
+    if (m.eq_type[e] == B2P_EQ_CONNECT && (m.eq_obj1[e] >= ntb || m.eq_obj2[e] >= ntb)) return "connect equality must be on the tree";
+    cp(m.eq_data[e], b.D(B2PM_F_EQ_DATA) + 11 * e, 6); cp(m.eq_solref[e], b.D(B2PM_F_EQ_SOLREF) + 2 * e, 2); cp(m.eq_solimp[e], b.D(B2PM_F_EQ_SOLIMP) + 5 * e, 5);
+    if (m.eq_type[e] == B2P_EQ_JOINT) { const double* c = b.D(B2PM_F_EQ_DATA) + 11 * e; if (c[2] != 0 || c[3] != 0 || c[4] != 0) return "only linear joint equalities are implemented"; }
+  }
+  for (int a = 0; a < m.nu; a++) {
+    m.act_trnnum[a] = b.I(B2PM_F_ACT_TRNNUM)[a];
+    for (int x = 0; x < 2; x++) { m.act_trndof[a][x] = b.I(B2PM_F_ACT_TRNDOF)[2 * a + x]; m.act_trncoef[a][x] = b.D(B2PM_F_ACT_TRNCOEF)[2 * a + x]; if (x < m.act_trnnum[a] && m.act_trndof[a][x] >= ntd) return "actuator on a prop dof"; }
+    m.act_ctrllimited[a] = b.I(B2PM_F_ACT_CTRLLIMITED)[a]; m.act_forcelimited[a] = b.I(B2PM_F_ACT_FORCELIMITED)[a];
+    m.act_gain[a] = b.D(B2PM_F_ACT_GAIN)[a]; cp(m.act_bias[a], b.D(B2PM_F_ACT_BIAS) + 3 * a, 3);
+    cp(m.act_ctrlrange[a], b.D(B2PM_F_ACT_CTRLRANGE) + 2 * a, 2); cp(m.act_forcerange[a], b.D(B2PM_F_ACT_FORCERANGE) + 2 * a, 2);
+  }
+  const double g6[6] = {350, 20, 500, 100, 200, 30}, q0[7] = {0, -0.785, 0, -2.356, 0, 1.571, 0.785};
+  cp(m.osc_gains, g6, 6); cp(m.osc_null, q0, 7); m.osc_pos_thresh = 5e-3; m.osc_ori_thresh = 68e-3;
+  // global tables
+  ht.mesh_vert.assign(b.D(B2PM_F_MESH_VERT), b.D(B2PM_F_MESH_VERT) + b.n(B2PM_F_MESH_VERT));
+  ht.mesh_nbradr.assign(b.I(B2PM_F_MESH_NBRADR), b.I(B2PM_F_MESH_NBRADR) + b.n(B2PM_F_MESH_NBRADR));
+  ht.mesh_nbrnum.assign(b.I(B2PM_F_MESH_NBRNUM), b.I(B2PM_F_MESH_NBRNUM) + b.n(B2PM_F_MESH_NBRNUM));
+  ht.mesh_nbr.assign(b.I(B2PM_F_MESH_NBR), b.I(B2PM_F_MESH_NBR) + b.n(B2PM_F_MESH_NBR));
+  // neighbour indices are mesh-local; make adr/num per global vertex and nbr global
+  {
+    const int nmesh = b.C(B2PM_C_NMESH);
+    for (int me = 0; me < nmesh; me++) for (int v = vadr[me]; v < vadr[me] + vnum[me]; v++)
+      for (int q = ht.mesh_nbradr[v]; q < ht.mesh_nbradr[v] + ht.mesh_nbrnum[v]; q++) ht.mesh_nbr[q] += vadr[me];
+  }
+  const int *p1 = b.I(B2PM_F_PAIR_GEOM1), *p2 = b.I(B2PM_F_PAIR_GEOM2), *prio = b.I(B2PM_F_GEOM_PRIORITY);
+  const double *fr = b.D(B2PM_F_GEOM_FRICTION), *sr = b.D(B2PM_F_GEOM_SOLREF), *si = b.D(B2PM_F_GEOM_SOLIMP), *sm = b.D(B2PM_F_GEOM_SOLMIX);
+  const double *mg = b.D(B2PM_F_GEOM_MARGIN), *gg = b.D(B2PM_F_GEOM_GAP);
+  for (int p = 0; p < m.npair; p++) {
+    int g1 = p1[p], g2 = p2[p]; double pp[12];
+    if (prio[g1] != prio[g2]) {
+      int g = prio[g1] > prio[g2] ? g1 : g2;
+      cp(pp, fr + 3 * g, 3); cp(pp + 3, sr + 2 * g, 2); cp(pp + 5, si + 5 * g, 5);
+    } else {
+      for (int q = 0; q < 3; q++) pp[q] = fr[3 * g1 + q] > fr[3 * g2 + q] ? fr[3 * g1 + q] : fr[3 * g2 + q];
+      double mix;
+      if (sm[g1] >= 1e-15 && sm[g2] >= 1e-15) mix = sm[g1] / (sm[g1] + sm[g2]);
+      else if (sm[g1] < 1e-15 && sm[g2] < 1e-15) mix = 0.5; else mix = sm[g1] < 1e-15 ? 0 : 1;
+      if (sr[2 * g1] > 0 && sr[2 * g2] > 0) for (int q = 0; q < 2; q++) pp[3 + q] = mix * sr[2 * g1 + q] + (1 - mix) * sr[2 * g2 + q];
+      else for (int q = 0; q < 2; q++) pp[3 + q] = sr[2 * g1 + q] < sr[2 * g2 + q] ? sr[2 * g1 + q] : sr[2 * g2 + q];
+      for (int q = 0; q < 5; q++) pp[5 + q] = mix * si[5 * g1 + q] + (1 - mix) * si[5 * g2 + q];
+    }
+    pp[10] = mg[g1] > mg[g2] ? mg[g1] : mg[g2]; pp[11] = gg[g1] > gg[g2] ? gg[g1] : gg[g2];
+    ht.pair_g1.push_back(g1); ht.pair_g2.push_back(g2); ht.pair_param.insert(ht.pair_param.end(), pp, pp + 12);
+  }
+  return "";
+}
+
+template <typename T>
+inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
+  // field-wise cast: both structs share the member order, ints copy, reals cast
+  std::memset(&d, 0, sizeof d);
+#define CI(f) std::memcpy(&d.f, &s.f, sizeof d.f)
+#define CR(f) do { const double* a = (const double*)&s.f; T* o = (T*)&d.f; for (size_t i = 0; i < sizeof(s.f) / sizeof(double); i++) o[i] = (T)a[i]; } while (0)
+  CI(nv); CI(nq); CI(ntd); CI(ntb); CI(nprop); CI(ngeom); CI(npair); CI(neq); CI(nu); CI(nlevel);
+  CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body);
+  CR(timestep); CR(gravity); CR(impratio); CR(tolerance); CR(ls_tolerance); CR(ccd_tolerance); CR(meaninertia); CR(ref);
+  CI(tb_parent); CI(level_start); CI(level_body); CI(child_start); CI(child_list); CI(anc_mask);
+  CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0);
+  CR(jnt_pos); CR(jnt_axis); CR(jnt_stiffness); CR(jnt_range); CR(jnt_margin); CR(jnt_solref); CR(jnt_solimp); CR(qpos0); CR(qpos_spring);
+  CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass);
+  CI(geom_type); CI(geom_body); CI(geom_vertadr); CI(geom_vertnum); CI(geom_prop);
+  CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(site_pos); CR(site_quat);
+  CI(eq_type); CI(eq_obj1); CI(eq_obj2); CR(eq_data); CR(eq_solref); CR(eq_solimp);
+  CI(act_trnnum); CI(act_trndof); CI(act_ctrllimited); CI(act_forcelimited);
+  CR(act_trncoef); CR(act_gain); CR(act_bias); CR(act_ctrlrange); CR(act_forcerange);
+  CR(osc_gains); CR(osc_null); CR(osc_pos_thresh); CR(osc_ori_thresh);
+#undef CI
+#undef CR
+}
+
+}  // namespace b2p

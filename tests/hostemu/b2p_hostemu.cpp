@@ -1,0 +1,74 @@
+// TEST INFRASTRUCTURE ONLY.  Compiles the kernel's per-env templates (csrc/b2p_core.h) for the host with a
+// one-thread "block" so the CPU test-suite can check kernel logic against the oracle without a GPU.
+// The package never loads this library; the product path is the CUDA build and has no CPU fallback.
+#include <cmath>
+#include <cstdlib>
+#include <new>
+using std::sqrt; using std::fabs; using std::sin; using std::cos; using std::pow;
+#include "../../mujoco_robot_environments_b200/csrc/b2p_core.h"
+
+using namespace b2p;
+
+template <typename T>
+struct Emu {
+  DevModel<T> model; HostTables ht;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp;
+  Globals<T> g; Scratch<T>* s;
+};
+
+template <typename T>
+static Emu<T>* make(const void* blob, size_t n) {
+  DevModel<double> md; Emu<T>* e = new Emu<T>();
+  std::string err = build_model(blob, n, md, e->ht);
+  if (!err.empty()) { fprintf(stderr, "hostemu: %s\n", err.c_str()); delete e; return nullptr; }
+  convert_model(md, e->model);
+  e->mesh_vert.assign(e->ht.mesh_vert.begin(), e->ht.mesh_vert.end());
+  for (size_t i = 0; i < e->ht.pair_g1.size(); i++) {
+    e->g1.push_back((short)e->ht.pair_g1[i]); e->g2.push_back((short)e->ht.pair_g2[i]);
+    PairParam<T> p; const double* q = &e->ht.pair_param[12 * i];
+    for (int k = 0; k < 3; k++) p.friction[k] = (T)q[k];
+    for (int k = 0; k < 2; k++) p.solref[k] = (T)q[3 + k];
+    for (int k = 0; k < 5; k++) p.solimp[k] = (T)q[5 + k];
+    p.margin = (T)q[10]; p.gap = (T)q[11]; e->pp.push_back(p);
+  }
+  e->g.mesh_vert = e->mesh_vert.data(); e->g.nbradr = e->ht.mesh_nbradr.data(); e->g.nbrnum = e->ht.mesh_nbrnum.data(); e->g.nbr = e->ht.mesh_nbr.data();
+  e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
+  e->s = new Scratch<T>();
+  return e;
+}
+
+struct EmuArgs {   // mirrors the ctypes struct in tests/hostemu.py
+  int mode, n_env, n_steps, control_steps, state_stride, full_contacts, settle_min_steps, out_stride;
+  double settle_qvel_tol, settle_qacc_tol;
+  void *state, *ctrl, *target, *grip, *prop_size, *prop_active, *env_mask, *converged, *status, *steps_done, *out;
+};
+
+template <typename T>
+static int run(Emu<T>* e, const EmuArgs* a) {
+  StepArgs<T> s; std::memset(&s, 0, sizeof s);
+  s.mode = a->mode; s.n_env = a->n_env; s.n_steps = a->n_steps; s.control_steps = a->control_steps; s.state_stride = a->state_stride; s.full_contacts = a->full_contacts;
+  s.state = (T*)a->state; s.ctrl = (const T*)a->ctrl; s.target = (const T*)a->target; s.grip = (const unsigned char*)a->grip;
+  s.prop_size = (const T*)a->prop_size; s.prop_active = (const unsigned char*)a->prop_active; s.env_mask = (const unsigned char*)a->env_mask;
+  s.converged = (unsigned char*)a->converged; s.status = (int*)a->status; s.steps_done = (int*)a->steps_done;
+  s.settle_qvel_tol = (T)a->settle_qvel_tol; s.settle_qacc_tol = (T)a->settle_qacc_tol; s.settle_min_steps = a->settle_min_steps;
+  s.out = (T*)a->out; s.out_stride = a->out_stride;
+  Ctx c = {0, 1};
+  for (int env = 0; env < a->n_env; env++) {
+    if (s.env_mask && !s.env_mask[env]) continue;
+    run_env(e->model, e->g, *e->s, s, env, c, false);
+  }
+  return 0;
+}
+
+extern "C" {
+void* emu_create(const void* blob, size_t n, int dtype) { return dtype == 0 ? (void*)make<double>(blob, n) : (void*)make<float>(blob, n); }
+int emu_run(void* h, int dtype, const EmuArgs* a) { return dtype == 0 ? run((Emu<double>*)h, a) : run((Emu<float>*)h, a); }
+void emu_osc_config(void* h, int dtype, const double* gains6, const double* null7, double pt, double ot) {
+  if (dtype == 0) { auto* e = (Emu<double>*)h; for (int i = 0; i < 6; i++) e->model.osc_gains[i] = gains6[i]; for (int i = 0; i < 7; i++) e->model.osc_null[i] = null7[i]; e->model.osc_pos_thresh = pt; e->model.osc_ori_thresh = ot; }
+  else { auto* e = (Emu<float>*)h; for (int i = 0; i < 6; i++) e->model.osc_gains[i] = (float)gains6[i]; for (int i = 0; i < 7; i++) e->model.osc_null[i] = (float)null7[i]; e->model.osc_pos_thresh = (float)pt; e->model.osc_ori_thresh = (float)ot; }
+}
+int emu_out_size() { return OutLayout::SIZE; }
+int emu_scratch_bytes(int dtype) { return dtype == 0 ? (int)sizeof(Scratch<double>) : (int)sizeof(Scratch<float>); }
+int emu_model_bytes(int dtype) { return dtype == 0 ? (int)sizeof(DevModel<double>) : (int)sizeof(DevModel<float>); }
+void emu_destroy(void* h, int dtype) { if (dtype == 0) { auto* e = (Emu<double>*)h; delete e->s; delete e; } else { auto* e = (Emu<float>*)h; delete e->s; delete e; } }
+}

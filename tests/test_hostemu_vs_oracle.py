@@ -1,0 +1,88 @@
+"""CPU suite: the kernel's per-env templates compiled for the host (one-thread block; tests/hostemu) against the
+oracle, on the same seeded scenes the GPU parity tests use.  This checks kernel LOGIC without a GPU; it is not a
+product path (the package never loads the host build)."""
+import numpy as np
+import pytest
+
+import scenarios as sc
+from hostemu import MODE_FORWARD, MODE_OSC, MODE_PHYSICS, MODE_SETTLE, HostEmu, out_slices
+from orc import Oracle
+
+S = out_slices()
+
+
+@pytest.fixture(scope="module")
+def blob():
+    return sc.default_blob()
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-9), (np.float32, 2e-4)])
+def test_forward_and_contact_sets(blob, dtype, tol):
+    n = 6
+    st, size, active = sc.make_states(n, seed=7)
+    e = HostEmu(blob, dtype); o = Oracle(blob)
+    r = e.run(MODE_FORWARD, st.astype(dtype), prop_size=size, prop_active=active, full_contacts=True)
+    assert r["status"].max() == 0
+    for i in range(n):
+        out = r["out"][i].astype(np.float64)
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 1); o.forward()
+        assert np.abs(out[S["site_xpos"]][:3] - o.site_xpos[3]).max() < tol
+        assert np.abs(out[S["qfrc_bias"]][:sc.NV] - o.qfrc_bias).max() < tol * max(1, np.abs(o.qfrc_bias).max())
+        assert np.abs(out[S["qacc"]][:sc.NV] - o.qacc).max() < 50 * tol * max(10, np.abs(o.qacc).max())
+        oc = o.contacts(); nc = int(out[S["ncon"]][0])
+        c = out[S["contact"]].reshape(-1, 10)[:nc]
+        assert nc == len(oc["dist"])
+        assert (c[:, 7].astype(int) == oc["geom"][:, 0]).all() and (c[:, 8].astype(int) == oc["geom"][:, 1]).all()
+        assert (c[:, 9].astype(int) == (oc["exclude"] != 0)).all()
+        assert np.abs(c[:, 0] - oc["dist"]).max(initial=0) < 10 * max(tol, 1e-6)
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-8), (np.float32, 5e-3)])
+def test_physics_steps(blob, dtype, tol):
+    n, steps = 3, 100
+    st, size, active = sc.make_states(n, seed=11, settled=False)
+    e = HostEmu(blob, dtype); o = Oracle(blob)
+    sc.oracle_load(o, st[0], size[0], active[0]); o.step1(); bias = o.qfrc_bias[:7].copy()
+    ctrl = sc.halton_ctrl(n, 0, bias)
+    got = st.astype(dtype)
+    r = e.run(MODE_PHYSICS, got, n_steps=steps, ctrl=ctrl, prop_size=size, prop_active=active)
+    assert r["status"].max() == 0
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0); o.ctrl[:] = ctrl[i]
+        for _ in range(steps):
+            o.step()
+        want = sc.oracle_state(o)
+        assert np.abs(got[i, :sc.NQ] - want[:sc.NQ]).max() < tol
+        assert np.abs(got[i, sc.REC_QVEL:sc.REC_QVEL + sc.NV] - want[sc.REC_QVEL:sc.REC_QVEL + sc.NV]).max() < 100 * tol
+
+
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-8), (np.float32, 5e-3)])
+def test_osc_run_controller(blob, dtype, tol):
+    n, ticks = 3, 40
+    st, size, active = sc.make_states(n, seed=5)
+    tg, grip = sc.random_targets(n, seed=3)
+    e = HostEmu(blob, dtype); o = Oracle(blob)
+    got = st.astype(dtype)
+    r = e.run(MODE_OSC, got, n_steps=ticks, target=tg, grip=grip, prop_size=size, prop_active=active)
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0)
+        c = o.run_controller(tg[i], int(grip[i]), ticks)
+        assert np.abs(got[i, :sc.NQ] - o.qpos[:sc.NQ]).max() < tol
+        assert bool(r["converged"][i]) == c
+
+
+def test_settle(blob):
+    st, size, active = sc.make_states(2, seed=21, settled=False)
+    e = HostEmu(blob); o = Oracle(blob)
+    got = st.copy()
+    r = e.run(MODE_SETTLE, got, n_steps=2000, prop_size=size, prop_active=active, settle=(1e-3, 1e-2, 300))
+    assert np.abs(got[:, :15] - st[:, :15]).max() == 0
+    sc.oracle_load(o, st[0], size[0], active[0]); o.set_option("full_contacts", 0)
+    k = 0
+    act = np.repeat(active[0].astype(bool), 6)
+    while k < 2000:
+        o.step_frozen_arm(); k += 1
+        if np.abs(o.qvel[15:39][act]).max() < 1e-3 and np.abs(o.qacc[15:39][act]).max() < 1e-2 and k > 300:
+            break
+    assert 300 < k < 2000 and k == r["steps_done"][0]
+    assert np.abs(got[0, :sc.NQ] - o.qpos[:sc.NQ]).max() < 1e-9

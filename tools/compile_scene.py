@@ -1,0 +1,28 @@
+"""Compile the canonical rearrangement scene(s) from the MJCF sources into B2PM blobs.
+
+The MJCF / mesh inputs are the menagerie files the reference loads (SURVEY.md 0.4:
+MEN-B franka_emika_panda/panda_nohand.xml + robotiq_2f85/2f85.xml); they are third-party
+data that cannot travel to the GPU box, so the compiled blobs (hull vertices, inertias,
+pair table, mj_setConst quantities) are committed under
+mujoco_robot_environments_b200/assets/ together with this generating script.
+
+  python tools/compile_scene.py [--menagerie PATH]
+"""
+import argparse
+import json
+import os
+import sys
+
+sys.path.insert(0, os.path.join(os.path.dirname(__file__), ".."))
+from mujoco_robot_environments_b200.compile import scene  # noqa: E402
+
+ap = argparse.ArgumentParser()
+ap.add_argument("--menagerie", default=scene.DEFAULT_MENAGERIE)
+args = ap.parse_args()
+out = os.path.join(os.path.dirname(__file__), "..", "mujoco_robot_environments_b200", "assets")
+os.makedirs(out, exist_ok=True)
+for tag, fuse in (("rearrangement_n4", True), ("rearrangement_n4_unfused", False)):
+    blob, names = scene.compile_rearrangement(4, fuse=fuse, menagerie=args.menagerie)
+    open(os.path.join(out, tag + ".b2pm"), "wb").write(blob)
+    json.dump(names, open(os.path.join(out, tag + ".names.json"), "w"), indent=0)
+    print(tag, len(blob), "bytes")
