@@ -1,0 +1,96 @@
+"""C-ABI checks that need no GPU: libb2p.so loads, exports every entry point include/b2p.h declares, and the
+Python-side enum mirrors (ffi.Q / ffi.O) agree with the header.  No compute call is made here."""
+import ctypes as C
+import os
+import re
+
+import pytest
+
+from mujoco_robot_environments_b200 import ffi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+HEADER = os.path.join(ROOT, "include", "b2p.h")
+
+
+def _header_text():
+    with open(HEADER) as f:
+        txt = f.read()
+    return re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
+
+
+def _declared_functions():
+    return sorted(set(re.findall(r"\b(b2p_[a-z0-9_]+)\s*\(", _header_text())))
+
+
+def _enum_block(first_name):
+    m = re.search(r"enum\s*\{([^}]*\b%s\b[^}]*)\}" % first_name, _header_text())
+    names, val = [], 0
+    for item in m.group(1).split(","):
+        item = item.strip()
+        if not item:
+            continue
+        if "=" in item:
+            n, v = item.split("=")
+            val = int(v.strip(), 0)
+            item = n.strip()
+        names.append((item, val))
+        val += 1
+    return dict(names)
+
+
+@pytest.fixture(scope="module")
+def lib():
+    if not os.path.exists(ffi.LIB_PATH):
+        ffi.build()
+    return C.CDLL(ffi.LIB_PATH)
+
+
+def test_header_declares_what_ffi_binds():
+    assert _declared_functions() == sorted(ffi.SYMBOLS)
+
+
+def test_library_exports_every_declared_symbol(lib):
+    for name in _declared_functions():
+        assert hasattr(lib, name), name
+
+
+def test_enum_mirrors_match_header():
+    q = _enum_block("B2P_Q_NQ")
+    for k, v in ffi.Q.items():
+        assert q["B2P_Q_" + k] == v, k
+    o = _enum_block("B2P_O_SITE_XPOS")
+    for k, v in ffi.O.items():
+        assert o["B2P_O_" + k] == v, k
+    assert o["B2P_O_NFIELD"] == len(ffi.O)
+
+
+def test_error_paths_without_a_gpu(lib):
+    """Argument validation happens before any CUDA call: bad arguments return B2P_ERR_ARG (-1) and set last_error."""
+    lib.b2p_last_error.restype = C.c_char_p
+    h = C.c_void_p()
+    assert lib.b2p_create(None, 0, 1, 0, 0, C.byref(h)) == -1
+    assert b"b2p_create" in lib.b2p_last_error()
+    assert lib.b2p_query(None, 0) == -1
+    off, cnt = C.c_int(), C.c_int()
+    assert lib.b2p_out_offset(9999, C.byref(off), C.byref(cnt)) == -1
+    assert lib.b2p_out_offset(ffi.O["SITE_XPOS"], C.byref(off), C.byref(cnt)) == 0 and cnt.value == 6
+    assert lib.b2p_step_physics(None, None, 1, None) == -1
+    assert lib.b2p_destroy(None) == 0
+
+
+def test_bad_blob_is_rejected_before_touching_the_device(lib):
+    h = C.c_void_p()
+    junk = bytes(4096)
+    rc = lib.b2p_create(junk, len(junk), 4, 0, 0, C.byref(h))
+    assert rc == -2        # B2P_ERR_MODEL
+    lib.b2p_last_error.restype = C.c_char_p
+    assert b"magic" in lib.b2p_last_error()
+
+
+def test_physics_backend_refuses_to_run_without_cuda():
+    import torch
+    if torch.cuda.is_available():
+        pytest.skip("GPU present")
+    from mujoco_robot_environments_b200.physics import BatchedPhysics
+    with pytest.raises(RuntimeError, match="no CPU fallback"):
+        BatchedPhysics(4)
