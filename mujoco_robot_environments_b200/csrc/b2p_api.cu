@@ -1,11 +1,5 @@
-// libb2p.so: sm_100a kernels + the C-ABI of include/b2p.h.
-//
-// Launch shape: persistent grid of one CTA per resident slot (148 SMs x CTAs/SM that fit the shared-memory
-// footprint), each CTA loops over scenes e = blockIdx.x, blockIdx.x + gridDim.x, ...  Model constants
-// (DevModel<T>) are staged into shared memory ONCE per CTA with a 1-D TMA bulk copy (cp.async.bulk ->
-// UBLKCP) completing on an mbarrier; each scene's 128-real state record is TMA-loaded into the head of
-// Scratch<T> and TMA-stored back at the end, so HBM sees exactly one coalesced record read + write per
-// scene per launch, however many physics steps the launch runs.
+// libb2p.so: the C-ABI of include/b2p.h (handle lifetime, uploads, launches).  The step kernel itself lives in
+// b2p_kernel.cuh and is instantiated per dtype in b2p_kernel_f32.cu / b2p_kernel_f64.cu.
 #include <cuda_runtime.h>
 
 #include <cstdio>
@@ -13,79 +7,13 @@
 #include <string>
 
 #include "../../include/b2p.h"
-#include "b2p_core.h"
+#include "b2p_launch.h"
 
 using namespace b2p;
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(B2P_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
-
-// ------------------------------------------------------------------------------------------ TMA / mbarrier helpers
-__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
-__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
-__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
-__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase) {
-  unsigned done;
-  do {
-    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
-  } while (!done);
-}
-__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
-}
-__device__ __forceinline__ void tma_store_1d(void* dst, const void* src, unsigned bytes) {
-  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
-  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
-}
-__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
-
-constexpr int NT = 128;
-template <typename T> struct Occ { static constexpr int kMinBlocks = 2; };
-template <> struct Occ<float> { static constexpr int kMinBlocks = 4; };
-
-template <typename T>
-struct alignas(16) SmemLayout {
-  DevModel<T> model;
-  alignas(16) Scratch<T> scratch;
-  alignas(8) unsigned long long bar;
-};
-
-template <typename T>
-__global__ void __launch_bounds__(NT, Occ<T>::kMinBlocks) b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int use_tma) {
-  extern __shared__ __align__(128) unsigned char smem_raw[];
-  SmemLayout<T>& sm = *reinterpret_cast<SmemLayout<T>*>(smem_raw);
-  const Ctx c = {(int)threadIdx.x, (int)blockDim.x};
-  constexpr unsigned kModelBytes = (unsigned)sizeof(DevModel<T>);
-  constexpr unsigned kRecBytes = REC_SIZE * sizeof(T);
-  static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
-  unsigned phase = 0;
-  if (use_tma) {
-    if (c.tid == 0) { mbar_init(&sm.bar, 1); asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory"); }
-    __syncthreads();
-    if (c.tid == 0) { mbar_expect_tx(&sm.bar, kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar); }
-    mbar_wait(&sm.bar, phase); phase ^= 1;
-  } else {
-    const int* src = reinterpret_cast<const int*>(gmodel); int* dst = reinterpret_cast<int*>(&sm.model);
-    for (int i = c.tid; i < (int)(kModelBytes / 4); i += c.nt) dst[i] = src[i];
-    __syncthreads();
-  }
-  for (int env = blockIdx.x; env < a.n_env; env += gridDim.x) {
-    if (a.env_mask && !a.env_mask[env]) continue;
-    T* rec = a.state + (size_t)env * a.state_stride;
-    if (use_tma) {
-      if (c.tid == 0) { fence_async_smem(); mbar_expect_tx(&sm.bar, kRecBytes); tma_load_1d(sm.scratch.qpos, rec, kRecBytes, &sm.bar); }
-      mbar_wait(&sm.bar, phase); phase ^= 1;
-    }
-    run_env(sm.model, g, sm.scratch, a, env, c, use_tma != 0);
-    if (use_tma) {
-      __syncthreads();
-      if (c.tid == 0) { fence_async_smem(); tma_store_1d(rec, sm.scratch.qpos, kRecBytes); }
-    }
-    __syncthreads();
-  }
-}
 
 // register-resident FMA chain for the FP pipe roofline denominator
 template <typename T>
@@ -100,15 +28,14 @@ __global__ void fma_peak_kernel(T* out, int iters) {
 
 // ------------------------------------------------------------------------------------------ handle
 struct b2p_handle_s {
-  int dtype, device, n_env, grid, blocks_per_sm, smem_bytes, use_tma, full_contacts, nq, nv, nu, nprop, ngeom;
+  int dtype, device, n_env, full_contacts, nq, nv, nu, nprop, ngeom;
+  LaunchGeom lg;
   long long launches;
   DevModel<double> hmodel;
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
-  void* d_zero_ctrl;
+  void* d_zero_ctrl; int* d_next_env;
 };
-
-template <typename T> static size_t smem_size() { return sizeof(SmemLayout<T>) + 128; }
 
 template <typename T>
 static int upload(b2p_handle_s* h, const HostTables& ht) {
@@ -133,16 +60,8 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   CK(cudaMalloc(&h->own_out, (size_t)h->n_env * OutLayout::SIZE * sizeof(T))); CK(cudaMemset(h->own_out, 0, (size_t)h->n_env * OutLayout::SIZE * sizeof(T)));
   CK(cudaMalloc(&h->d_zero_ctrl, (size_t)h->n_env * MAXU * sizeof(T))); CK(cudaMemset(h->d_zero_ctrl, 0, (size_t)h->n_env * MAXU * sizeof(T)));
   h->out = h->own_out;
-  const size_t smem = smem_size<T>();
-  CK(cudaFuncSetAttribute(b2p_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
-  int per_sm = 0, sms = 0;
-  CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T>, NT, smem));
-  CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, h->device));
-  if (per_sm < 1) return fail(B2P_ERR_CUDA, "kernel does not fit on an SM (shared memory)");
-  const char* ov = getenv("B2P_BLOCKS_PER_SM");
-  if (ov && atoi(ov) > 0 && atoi(ov) < per_sm) per_sm = atoi(ov);
-  h->blocks_per_sm = per_sm; h->smem_bytes = (int)smem;
-  h->grid = sms * per_sm; if (h->grid > h->n_env) h->grid = h->n_env;
+  CK(cudaMalloc(&h->d_next_env, sizeof(int)));
+  CK(sizeof(T) == 8 ? configure_f64(h->device, h->n_env, &h->lg) : configure_f32(h->device, h->n_env, &h->lg));
   return B2P_OK;
 }
 
@@ -152,9 +71,9 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param};
-  b2p_step_kernel<T><<<h->grid, NT, smem_size<T>(), st>>>((const DevModel<T>*)h->d_model, g, a, h->use_tma);
+  if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, h->d_next_env, st));
+  else CK(launch_f32(h->lg, h->d_model, g, a, h->d_next_env, st));
   h->launches++;
-  CK(cudaGetLastError());
   return B2P_OK;
 }
 
@@ -178,7 +97,6 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
   std::string err = build_model(blob, nbytes, h->hmodel, ht);
   if (!err.empty()) { delete h; return fail(B2P_ERR_MODEL, "b2p_create: " + err); }
   h->dtype = dtype; h->device = device; h->n_env = n_env; h->nq = h->hmodel.nq; h->nv = h->hmodel.nv; h->nu = h->hmodel.nu; h->nprop = h->hmodel.nprop; h->ngeom = h->hmodel.ngeom;
-  const char* nt = getenv("B2P_NO_TMA"); h->use_tma = !(nt && nt[0] == '1');
   CK(cudaSetDevice(device));
   CK(cudaMalloc(&h->d_status, (size_t)n_env * 4)); CK(cudaMemset(h->d_status, 0, (size_t)n_env * 4));
   int rc = dtype == B2P_F64 ? upload<double>(h, ht) : upload<float>(h, ht);
@@ -189,7 +107,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;
@@ -200,8 +118,8 @@ int b2p_query(b2p_handle h, int what) {
     case B2P_Q_NQ: return h->nq; case B2P_Q_NV: return h->nv; case B2P_Q_NU: return h->nu; case B2P_Q_NPROP: return h->nprop;
     case B2P_Q_STATE_STRIDE: return REC_SIZE; case B2P_Q_OUT_STRIDE: return OutLayout::SIZE; case B2P_Q_MAXPROP: return MAXP;
     case B2P_Q_REC_QPOS: return REC_QPOS; case B2P_Q_REC_QVEL: return REC_QVEL; case B2P_Q_REC_QACC_WARMSTART: return REC_QACC; case B2P_Q_REC_TIME: return REC_TIME;
-    case B2P_Q_LAUNCHES: return (int)h->launches; case B2P_Q_SMEM_BYTES: return h->smem_bytes; case B2P_Q_BLOCKS_PER_SM: return h->blocks_per_sm;
-    case B2P_Q_THREADS: return NT; case B2P_Q_GRID: return h->grid; case B2P_Q_MAXCON: return MAXCON; case B2P_Q_NGEOM: return h->ngeom;
+    case B2P_Q_LAUNCHES: return (int)h->launches; case B2P_Q_SMEM_BYTES: return h->lg.smem_bytes; case B2P_Q_BLOCKS_PER_SM: return h->lg.blocks_per_sm;
+    case B2P_Q_THREADS: return h->lg.threads; case B2P_Q_GRID: return h->lg.grid; case B2P_Q_MAXCON: return MAXCON; case B2P_Q_NGEOM: return h->ngeom;
   }
   return B2P_ERR_ARG;
 }

@@ -1,0 +1,351 @@
+#pragma once
+#include "b2p_scratch.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------------------------------ collision
+template <typename T>
+struct CObj { const T* pos; const T* mat; const T* size; const T* vert; int type, vadr, vnum, cur; T margin; };
+
+// support point in world direction dir (|dir| = 1), inflated by margin/2.  Meshes: hill climbing over the
+// hull graph with warm start inside one query (what MuJoCo does for meshes with a graph).
+template <typename T>
+B2P_HD void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
+  T ld[3], lp[3];
+  mulmtv(ld, o.mat, dir);
+  if (o.type == B2P_GEOM_BOX) {
+    for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? o.size[k] : -o.size[k];
+  } else {
+    int v = o.cur; T best = dot3(g.mesh_vert + 3 * v, ld);
+    for (int guard = 0; guard < 4096; guard++) {
+      int nb = v; const int a = g.nbradr[v], n = g.nbrnum[v];
+      for (int q = 0; q < n; q++) { const int u = g.nbr[a + q]; const T d = dot3(g.mesh_vert + 3 * u, ld); if (d > best) { best = d; nb = u; } }
+      if (nb == v) break;
+      v = nb;
+    }
+    o.cur = v; cp3(lp, g.mesh_vert + 3 * v);
+  }
+  mulmv(res, o.mat, lp);
+  const T hm = T(0.5) * o.margin;
+  for (int k = 0; k < 3; k++) res[k] += o.pos[k] + hm * dir[k];
+}
+template <typename T> struct Sup { T v[3], v1[3], v2[3]; };
+template <typename T>
+B2P_HD void mink_support(CObj<T>& a, CObj<T>& b, const Globals<T>& g, const T* dir, Sup<T>& s) {
+  T nd[3] = {-dir[0], -dir[1], -dir[2]};
+  support(a, g, dir, s.v1); support(b, g, nd, s.v2);
+  for (int k = 0; k < 3; k++) s.v[k] = s.v1[k] - s.v2[k];
+}
+template <typename T> B2P_HD bool is_zero(T x) { return fabs(x) < Num<T>::eps(); }
+template <typename T> B2P_HD void portal_dir(const Sup<T>* p, T* dir) {
+  T a[3], b[3];
+  for (int k = 0; k < 3; k++) { a[k] = p[2].v[k] - p[1].v[k]; b[k] = p[3].v[k] - p[1].v[k]; }
+  cross3(dir, a, b); normalize3(dir);
+}
+template <typename T> B2P_HD bool portal_reach_tol(const Sup<T>* p, const Sup<T>& v4, const T* dir, T tol) {
+  T dv4 = dot3(v4.v, dir), mn = dv4 - dot3(p[1].v, dir), d2 = dv4 - dot3(p[2].v, dir), d3 = dv4 - dot3(p[3].v, dir);
+  if (d2 < mn) mn = d2;
+  if (d3 < mn) mn = d3;
+  return is_zero(mn - tol) || mn < tol;
+}
+template <typename T> B2P_HD void expand_portal(Sup<T>* p, const Sup<T>& v4) {
+  T cr[3]; cross3(cr, v4.v, p[0].v);
+  if (dot3(p[1].v, cr) > 0) { if (dot3(p[2].v, cr) > 0) p[1] = v4; else p[3] = v4; }
+  else { if (dot3(p[3].v, cr) > 0) p[2] = v4; else p[1] = v4; }
+}
+template <typename T> B2P_HD T point_tri_dist2(const T* a, const T* b, const T* c, T* w) {
+  T ab[3], ac[3], ap[3], bp[3], cpt[3];
+  for (int k = 0; k < 3; k++) { ab[k] = b[k] - a[k]; ac[k] = c[k] - a[k]; ap[k] = -a[k]; bp[k] = -b[k]; cpt[k] = -c[k]; }
+  T d1 = dot3(ab, ap), d2 = dot3(ac, ap), d3 = dot3(ab, bp), d4 = dot3(ac, bp), d5 = dot3(ab, cpt), d6 = dot3(ac, cpt);
+  if (d1 <= 0 && d2 <= 0) { cp3(w, a); }
+  else if (d3 >= 0 && d4 <= d3) { cp3(w, b); }
+  else if (d1 * d4 - d3 * d2 <= 0 && d1 >= 0 && d3 <= 0) { T v = d1 / (d1 - d3); for (int k = 0; k < 3; k++) w[k] = a[k] + v * ab[k]; }
+  else if (d6 >= 0 && d5 <= d6) { cp3(w, c); }
+  else if (d5 * d2 - d1 * d6 <= 0 && d2 >= 0 && d6 <= 0) { T v = d2 / (d2 - d6); for (int k = 0; k < 3; k++) w[k] = a[k] + v * ac[k]; }
+  else if (d3 * d6 - d5 * d4 <= 0 && (d4 - d3) >= 0 && (d5 - d6) >= 0) { T v = (d4 - d3) / ((d4 - d3) + (d5 - d6)); for (int k = 0; k < 3; k++) w[k] = b[k] + v * (c[k] - b[k]); }
+  else {
+    T va = d3 * d6 - d5 * d4, vb = d5 * d2 - d1 * d6, vc = d1 * d4 - d3 * d2, den = 1 / (va + vb + vc);
+    T v = vb * den, u = vc * den;
+    for (int k = 0; k < 3; k++) w[k] = a[k] + ab[k] * v + ac[k] * u;
+  }
+  return dot3(w, w);
+}
+// Minkowski portal refinement (libccd ccdMPRPenetration, what mjc_Convex runs in MuJoCo 3.2.x)
+template <typename T>
+B2P_HDN bool mpr_penetration(CObj<T>& o1, CObj<T>& o2, const Globals<T>& g, int maxiter, T tol, T& depth, T* dir, T* pos) {
+  Sup<T> p[4], v4; T d[3], va[3], vb[3];
+  for (int k = 0; k < 3; k++) { p[0].v1[k] = o1.pos[k]; p[0].v2[k] = o2.pos[k]; p[0].v[k] = p[0].v1[k] - p[0].v2[k]; }
+  if (is_zero(p[0].v[0]) && is_zero(p[0].v[1]) && is_zero(p[0].v[2])) p[0].v[0] += T(1e-5);
+  for (int k = 0; k < 3; k++) d[k] = -p[0].v[k];
+  normalize3(d);
+  mink_support(o1, o2, g, d, p[1]);
+  T dt = dot3(p[1].v, d);
+  if (is_zero(dt) || dt < 0) return false;
+  cross3(d, p[0].v, p[1].v);
+  if (is_zero(dot3(d, d))) {
+    if (is_zero(dot3(p[1].v, p[1].v))) { depth = 0; dir[0] = dir[1] = dir[2] = 0; }
+    else { cp3(dir, p[1].v); depth = normalize3(dir); }
+    for (int k = 0; k < 3; k++) pos[k] = T(0.5) * (p[1].v1[k] + p[1].v2[k]);
+    return true;
+  }
+  normalize3(d);
+  mink_support(o1, o2, g, d, p[2]);
+  dt = dot3(p[2].v, d);
+  if (is_zero(dt) || dt < 0) return false;
+  for (int k = 0; k < 3; k++) { va[k] = p[1].v[k] - p[0].v[k]; vb[k] = p[2].v[k] - p[0].v[k]; }
+  cross3(d, va, vb); normalize3(d);
+  if (dot3(d, p[0].v) > 0) { Sup<T> t = p[1]; p[1] = p[2]; p[2] = t; for (int k = 0; k < 3; k++) d[k] = -d[k]; }
+  for (int guard = 0;; guard++) {
+    if (guard > 100) return false;
+    mink_support(o1, o2, g, d, p[3]);
+    dt = dot3(p[3].v, d);
+    if (is_zero(dt) || dt < 0) return false;
+    bool cont = false;
+    cross3(va, p[1].v, p[3].v);
+    dt = dot3(va, p[0].v);
+    if (dt < 0 && !is_zero(dt)) { p[2] = p[3]; cont = true; }
+    if (!cont) {
+      cross3(va, p[3].v, p[2].v);
+      dt = dot3(va, p[0].v);
+      if (dt < 0 && !is_zero(dt)) { p[1] = p[3]; cont = true; }
+    }
+    if (!cont) break;
+    for (int k = 0; k < 3; k++) { va[k] = p[1].v[k] - p[0].v[k]; vb[k] = p[2].v[k] - p[0].v[k]; }
+    cross3(d, va, vb); normalize3(d);
+  }
+  for (int guard = 0;; guard++) {
+    portal_dir(p, d);
+    dt = dot3(d, p[1].v);
+    if (is_zero(dt) || dt > 0) break;
+    mink_support(o1, o2, g, d, v4);
+    dt = dot3(v4.v, d);
+    if (!(is_zero(dt) || dt > 0) || portal_reach_tol(p, v4, d, tol) || guard > maxiter) return false;
+    expand_portal(p, v4);
+  }
+  for (int it = 0;; it++) {
+    portal_dir(p, d);
+    mink_support(o1, o2, g, d, v4);
+    if (portal_reach_tol(p, v4, d, tol) || it > maxiter) {
+      T pd[3];
+      depth = sqrt(point_tri_dist2(p[1].v, p[2].v, p[3].v, pd));
+      if (is_zero(pd[0]) && is_zero(pd[1]) && is_zero(pd[2])) cp3(pd, d);
+      normalize3(pd); cp3(dir, pd);
+      T b[4], cr[3], sum;
+      cross3(cr, p[1].v, p[2].v); b[0] = dot3(cr, p[3].v);
+      cross3(cr, p[3].v, p[2].v); b[1] = dot3(cr, p[0].v);
+      cross3(cr, p[0].v, p[1].v); b[2] = dot3(cr, p[3].v);
+      cross3(cr, p[2].v, p[1].v); b[3] = dot3(cr, p[0].v);
+      sum = b[0] + b[1] + b[2] + b[3];
+      if (is_zero(sum) || sum < 0) {
+        b[0] = 0;
+        cross3(cr, p[2].v, p[3].v); b[1] = dot3(cr, d);
+        cross3(cr, p[3].v, p[1].v); b[2] = dot3(cr, d);
+        cross3(cr, p[1].v, p[2].v); b[3] = dot3(cr, d);
+        sum = b[1] + b[2] + b[3];
+      }
+      for (int k = 0; k < 3; k++) {
+        T p1 = 0, p2 = 0;
+        for (int i = 0; i < 4; i++) { p1 += b[i] * p[i].v1[k]; p2 += b[i] * p[i].v2[k]; }
+        pos[k] = T(0.5) * (p1 + p2) / sum;
+      }
+      return true;
+    }
+    expand_portal(p, v4);
+  }
+}
+
+template <typename T> struct RawCon { T dist[8]; T pos[8][3]; T normal[3]; };
+
+template <typename T>
+B2P_HD int plane_box(const T* ppos, const T* pmat, const T* bpos, const T* bmat, const T* bsize, T margin, RawCon<T>& out) {
+  T n[3] = {pmat[2], pmat[5], pmat[8]};
+  int cnt = 0;
+  cp3(out.normal, n);
+  for (int i = 0; i < 8 && cnt < 4; i++) {
+    T loc[3] = {(i & 1 ? bsize[0] : -bsize[0]), (i & 2 ? bsize[1] : -bsize[1]), (i & 4 ? bsize[2] : -bsize[2])}, w[3], dif[3];
+    mulmv(w, bmat, loc);
+    for (int k = 0; k < 3; k++) { w[k] += bpos[k]; dif[k] = w[k] - ppos[k]; }
+    const T dist = dot3(dif, n);
+    if (dist > margin) continue;
+    out.dist[cnt] = dist;
+    for (int k = 0; k < 3; k++) out.pos[cnt][k] = w[k] - T(0.5) * dist * n[k];
+    cnt++;
+  }
+  return cnt;
+}
+
+// SAT (15 axes) + reference-face clipping / edge-edge point.  Returns #contacts, or -1 when the boxes are
+// separated by 0 < s <= margin (caller then runs the margin-inflated convex query: one closest-feature contact).
+template <typename T>
+B2P_HDN int box_box(const T* p1, const T* m1, const T* s1, const T* p2, const T* m2, const T* s2, T margin, RawCon<T>& out) {
+  T R[9], aR[9], t[3], dp[3];
+  for (int k = 0; k < 3; k++) dp[k] = p2[k] - p1[k];
+  mulmtv(t, m1, dp);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    R[3 * i + j] = m1[i] * m2[j] + m1[3 + i] * m2[3 + j] + m1[6 + i] * m2[6 + j];
+    aR[3 * i + j] = fabs(R[3 * i + j]) + T(1e-12);
+  }
+  T best = -Num<T>::big(); int code = -1; T bn[3] = {0, 0, 0};
+  for (int i = 0; i < 3; i++) {
+    T s = fabs(t[i]) - (s1[i] + s2[0] * aR[3 * i] + s2[1] * aR[3 * i + 1] + s2[2] * aR[3 * i + 2]);
+    if (s > margin) return 0;
+    if (s > best) { best = s; code = i; }
+  }
+  for (int j = 0; j < 3; j++) {
+    T tj = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
+    T s = fabs(tj) - (s2[j] + s1[0] * aR[j] + s1[1] * aR[3 + j] + s1[2] * aR[6 + j]);
+    if (s > margin) return 0;
+    if (s > best) { best = s; code = 3 + j; }
+  }
+  T best_edge = -Num<T>::big(); int ecode = -1;
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
+    const int i1 = (i + 1) % 3, i2 = (i + 2) % 3, j1 = (j + 1) % 3, j2 = (j + 2) % 3;
+    const T l = sqrt(R[3 * i1 + j] * R[3 * i1 + j] + R[3 * i2 + j] * R[3 * i2 + j]);
+    if (l < T(1e-6)) continue;
+    const T tl = t[i2] * R[3 * i1 + j] - t[i1] * R[3 * i2 + j];
+    const T ra = s1[i1] * aR[3 * i2 + j] + s1[i2] * aR[3 * i1 + j], rb = s2[j1] * aR[3 * i + j2] + s2[j2] * aR[3 * i + j1];
+    const T s = (fabs(tl) - (ra + rb)) / l;
+    if (s > margin) return 0;
+    if (s > best_edge) {
+      best_edge = s; ecode = 6 + 3 * i + j;
+      T a[3] = {m1[i], m1[3 + i], m1[6 + i]}, b[3] = {m2[j], m2[3 + j], m2[6 + j]};
+      cross3(bn, a, b); normalize3(bn);
+      if (dot3(bn, dp) < 0) for (int k = 0; k < 3; k++) bn[k] = -bn[k];
+    }
+  }
+  if (ecode >= 0 && best_edge > best + T(1e-6) * (1 + fabs(best))) { best = best_edge; code = ecode; }
+  if (best > 0) return -1;
+  if (code >= 6) {
+    const int i = (code - 6) / 3, j = (code - 6) % 3;
+    T pa[3], pb[3], ua[3] = {m1[i], m1[3 + i], m1[6 + i]}, ub[3] = {m2[j], m2[3 + j], m2[6 + j]};
+    cp3(pa, p1); cp3(pb, p2);
+    for (int k = 0; k < 3; k++) {
+      if (k != i) { T ax[3] = {m1[k], m1[3 + k], m1[6 + k]}; T sg = dot3(bn, ax) > 0 ? T(1) : T(-1); for (int q = 0; q < 3; q++) pa[q] += sg * s1[k] * ax[q]; }
+      if (k != j) { T ax[3] = {m2[k], m2[3 + k], m2[6 + k]}; T sg = dot3(bn, ax) > 0 ? T(-1) : T(1); for (int q = 0; q < 3; q++) pb[q] += sg * s2[k] * ax[q]; }
+    }
+    T w[3] = {pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]};
+    T uaub = dot3(ua, ub), q1 = dot3(ua, w), q2 = -dot3(ub, w), den = 1 - uaub * uaub;
+    T al = den > T(1e-12) ? (q1 + uaub * q2) / den : T(0), be = den > T(1e-12) ? (uaub * q1 + q2) / den : T(0);
+    for (int k = 0; k < 3; k++) { pa[k] += al * ua[k]; pb[k] += be * ub[k]; }
+    out.dist[0] = best; cp3(out.normal, bn);
+    for (int k = 0; k < 3; k++) out.pos[0][k] = T(0.5) * (pa[k] + pb[k]);
+    return 1;
+  }
+  const T *pa = p1, *ma = m1, *sa = s1, *pb = p2, *mb = m2, *sb = s2; int ai = code; bool flip = false;
+  if (code >= 3) { pa = p2; ma = m2; sa = s2; pb = p1; mb = m1; sb = s1; ai = code - 3; flip = true; }
+  T nref[3] = {ma[ai], ma[3 + ai], ma[6 + ai]}, d[3] = {pb[0] - pa[0], pb[1] - pa[1], pb[2] - pa[2]};
+  if (dot3(nref, d) < 0) for (int k = 0; k < 3; k++) nref[k] = -nref[k];
+  int bj = 0; T bd = -1;
+  for (int j = 0; j < 3; j++) { T ax[3] = {mb[j], mb[3 + j], mb[6 + j]}; T v = fabs(dot3(nref, ax)); if (v > bd) { bd = v; bj = j; } }
+  T nb[3] = {mb[bj], mb[3 + bj], mb[6 + bj]};
+  if (dot3(nb, nref) > 0) for (int k = 0; k < 3; k++) nb[k] = -nb[k];
+  const int k1 = (bj + 1) % 3, k2 = (bj + 2) % 3;
+  T poly[16][3], tmp[16][3]; int np = 4;
+  for (int q = 0; q < 4; q++) {
+    const T sg1 = (q == 0 || q == 3) ? T(1) : T(-1), sg2 = (q < 2) ? T(1) : T(-1);
+    for (int k = 0; k < 3; k++) poly[q][k] = pb[k] + nb[k] * sb[bj] + sg1 * sb[k1] * mb[3 * k + k1] + sg2 * sb[k2] * mb[3 * k + k2];
+  }
+  const int u1 = (ai + 1) % 3, u2 = (ai + 2) % 3;
+  for (int pl = 0; pl < 4; pl++) {
+    const int u = pl < 2 ? u1 : u2; const T sg = (pl & 1) ? T(-1) : T(1);
+    T ax[3] = {sg * ma[u], sg * ma[3 + u], sg * ma[6 + u]}; const T lim = sa[u];
+    int nn = 0;
+    for (int v = 0; v < np; v++) {
+      const T *A = poly[v], *Bp = poly[(v + 1) % np];
+      const T da = (A[0] - pa[0]) * ax[0] + (A[1] - pa[1]) * ax[1] + (A[2] - pa[2]) * ax[2] - lim;
+      const T db = (Bp[0] - pa[0]) * ax[0] + (Bp[1] - pa[1]) * ax[1] + (Bp[2] - pa[2]) * ax[2] - lim;
+      if (da <= 0) { cp3(tmp[nn], A); nn++; }
+      if ((da < 0 && db > 0) || (da > 0 && db < 0)) { const T sx = da / (da - db); for (int k = 0; k < 3; k++) tmp[nn][k] = A[k] + sx * (Bp[k] - A[k]); nn++; }
+    }
+    np = nn;
+    for (int v = 0; v < np; v++) cp3(poly[v], tmp[v]);
+    if (np == 0) break;
+  }
+  int cnt = 0;
+  for (int k = 0; k < 3; k++) out.normal[k] = flip ? -nref[k] : nref[k];
+  for (int v = 0; v < np && cnt < 8; v++) {
+    const T dist = (poly[v][0] - pa[0]) * nref[0] + (poly[v][1] - pa[1]) * nref[1] + (poly[v][2] - pa[2]) * nref[2] - sa[ai];
+    if (dist > margin) continue;
+    out.dist[cnt] = dist;
+    for (int k = 0; k < 3; k++) out.pos[cnt][k] = poly[v][k] - T(0.5) * dist * nref[k];
+    cnt++;
+  }
+  return cnt;
+}
+
+// broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
+template <typename T>
+B2P_HD void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
+  if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
+  for (int q = c.tid; q < m.ngeom; q += c.nt) {
+    const int p = m.geom_prop[q];
+    s.grbound[q] = p >= 0 ? norm3(s.psize[p]) : m.geom_rbound[q];
+  }
+  bsync(c);
+  int base = 0;
+  for (int p0 = 0; p0 < m.npair; p0 += c.nt) {
+    const int p = p0 + c.tid; int flag = 0;
+    if (p < m.npair) {
+      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
+      if (!((pr1 >= 0 && !s.pactive[pr1]) || (pr2 >= 0 && !s.pactive[pr2]))) {
+        const PairParam<T>& pp = g.pair_param[p];
+        const T md = full_contacts ? pp.margin : pp.margin - pp.gap;
+        T dif[3] = {s.gpos[g2][0] - s.gpos[g1][0], s.gpos[g2][1] - s.gpos[g1][1], s.gpos[g2][2] - s.gpos[g1][2]};
+        if (m.geom_type[g1] == B2P_GEOM_PLANE) {
+          T nrm[3] = {s.gmat[g1][2], s.gmat[g1][5], s.gmat[g1][8]};
+          flag = (m.geom_type[g2] == B2P_GEOM_BOX) && !(dot3(dif, nrm) - s.grbound[g2] > md);
+        } else flag = !(norm3(dif) > s.grbound[g1] + s.grbound[g2] + md);
+      }
+    }
+    int tot; const int ofs = block_scan(c, flag, tot);
+    if (flag && base + ofs < MAXCAND) s.cand[base + ofs] = (short)p;
+    base += tot;
+  }
+  if (c.tid == 0) { s.ncand = base < MAXCAND ? base : MAXCAND; if (base > MAXCAND) s.flags |= FLAG_CANDFULL; }
+  bsync(c);
+  const int ncand = s.ncand;
+  const T tol = m.ccd_tolerance > 16 * Num<T>::eps() ? m.ccd_tolerance : 16 * Num<T>::eps();
+  int cbase = 0;
+  for (int c0 = 0; c0 < ncand; c0 += c.nt) {
+    const int ci = c0 + c.tid; int n = 0; RawCon<T> raw; int p = -1; T md = 0;
+    if (ci < ncand) {
+      p = s.cand[ci];
+      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], t1 = m.geom_type[g1], t2 = m.geom_type[g2];
+      const PairParam<T>& pp = g.pair_param[p];
+      md = full_contacts ? pp.margin : pp.margin - pp.gap;
+      const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
+      const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1];
+      const T* sz2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+      if (t1 == B2P_GEOM_PLANE) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
+      else {
+        bool convex = true;
+        if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw); convex = n < 0; if (n < 0) n = 0; }
+        if (convex) {
+          CObj<T> a = {s.gpos[g1], s.gmat[g1], sz1, nullptr, t1, m.geom_vertadr[g1], m.geom_vertnum[g1], m.geom_vertadr[g1], md};
+          CObj<T> b = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], m.geom_vertadr[g2], md};
+          T depth, dir[3], pos[3];
+          if (mpr_penetration(a, b, g, m.ccd_iterations, tol, depth, dir, pos) && depth >= 0) {
+            raw.dist[0] = md - depth; cp3(raw.normal, dir); cp3(raw.pos[0], pos); n = 1;
+          }
+        }
+      }
+      int keep = 0;   // drop points not strictly inside the detection margin
+      for (int i = 0; i < n; i++) if (raw.dist[i] < md) { if (keep != i) { raw.dist[keep] = raw.dist[i]; cp3(raw.pos[keep], raw.pos[i]); } keep++; }
+      n = keep;
+    }
+    int tot; const int ofs = block_scan(c, n, tot);
+    for (int i = 0; i < n; i++) {
+      const int k = cbase + ofs + i;
+      if (k >= MAXCON) break;
+      const PairParam<T>& pp = g.pair_param[p];
+      s.c_dist[k] = raw.dist[i]; cp3(s.c_pos[k], raw.pos[i]); cp3(s.c_frame[k], raw.normal); make_frame(s.c_frame[k]);
+      s.c_pair[k] = (short)p; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k][0] = pp.friction[0]; s.c_fric[k][1] = pp.friction[0]; s.c_row[k] = -1;
+    }
+    cbase += tot;
+  }
+  if (c.tid == 0) { s.ncon = cbase < MAXCON ? cbase : MAXCON; if (cbase > MAXCON) s.flags |= FLAG_CONTACTFULL; }
+  bsync(c);
+}
+
+
+}  // namespace b2p

@@ -1,0 +1,120 @@
+// The sm_100a step kernel (one template, instantiated for float in b2p_kernel_f32.cu and for double in
+// b2p_kernel_f64.cu so the two long compiles run in parallel).
+//
+// Launch shape: persistent grid, one WARP per scene ("warp-per-env").  A CTA holds kWarps warps; model constants
+// (DevModel<T>) are staged into shared memory ONCE per CTA with a 1-D TMA bulk copy (cp.async.bulk -> UBLKCP)
+// completing on an mbarrier and are shared by the CTA's warps.  Each warp owns one Scratch<T> in shared memory,
+// pulls scene indices from a global atomic counter (dynamic load balance: per-scene cost varies with contacts and
+// Newton iterations), TMA-loads the scene's 128-real state record into the head of its Scratch and TMA-stores it
+// back when the requested steps are done.  HBM therefore sees exactly one coalesced record read + write per scene
+// per launch, however many physics steps the launch runs.  Warps never synchronise with each other after staging.
+#pragma once
+#include <cuda_runtime.h>
+
+#include <cstddef>
+
+#include "b2p_core.h"
+#include "b2p_launch.h"
+
+namespace b2p {
+
+
+
+template <typename T> struct KernelCfg { static constexpr int kWarps = 4; static constexpr int kMinBlocks = 1; };
+template <> struct KernelCfg<double> { static constexpr int kWarps = 2; static constexpr int kMinBlocks = 1; };
+
+// ------------------------------------------------------------------------------------------ TMA / mbarrier helpers
+__device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void mbar_init(unsigned long long* bar, int count) { asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count)); }
+__device__ __forceinline__ void mbar_expect_tx(unsigned long long* bar, unsigned bytes) { asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory"); }
+__device__ __forceinline__ void mbar_wait(unsigned long long* bar, unsigned phase) {
+  unsigned done;
+  do {
+    asm volatile("{ .reg .pred p; mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2; selp.u32 %0, 1, 0, p; }" : "=r"(done) : "r"(smem_u32(bar)), "r"(phase) : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_1d(void* dst, const void* src, unsigned bytes, unsigned long long* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(smem_u32(dst)), "l"(src), "r"(bytes), "r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tma_store_1d(void* dst, const void* src, unsigned bytes) {
+  asm volatile("cp.async.bulk.global.shared::cta.bulk_group [%0], [%1], %2;" ::"l"(dst), "r"(smem_u32(src)), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.commit_group;" ::: "memory");
+  asm volatile("cp.async.bulk.wait_group.read 0;" ::: "memory");
+}
+__device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
+
+template <typename T>
+struct alignas(16) SmemLayout {
+  DevModel<T> model;
+  alignas(16) Scratch<T> scratch[KernelCfg<T>::kWarps];
+  alignas(8) unsigned long long bar[1 + KernelCfg<T>::kWarps];
+};
+
+template <typename T>
+__global__ void __launch_bounds__(32 * KernelCfg<T>::kWarps, KernelCfg<T>::kMinBlocks)
+b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int* __restrict__ next_env) {
+  extern __shared__ __align__(128) unsigned char smem_raw[];
+  SmemLayout<T>& sm = *reinterpret_cast<SmemLayout<T>*>(smem_raw);
+  constexpr unsigned kModelBytes = (unsigned)sizeof(DevModel<T>);
+  constexpr unsigned kRecBytes = REC_SIZE * sizeof(T);
+  static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
+  static_assert(offsetof(Scratch<T>, qpos) == 0 && sizeof(Scratch<T>) % 16 == 0, "state record must head a 16-byte aligned Scratch");
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const Ctx c = {lane, 32};
+  if (threadIdx.x == 0) {
+    for (int i = 0; i <= KernelCfg<T>::kWarps; i++) mbar_init(&sm.bar[i], 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  __syncthreads();
+  if (threadIdx.x == 0) { mbar_expect_tx(&sm.bar[0], kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar[0]); }
+  mbar_wait(&sm.bar[0], 0);
+  Scratch<T>& s = sm.scratch[warp];
+  unsigned long long* bar = &sm.bar[1 + warp];
+  unsigned phase = 0;
+  for (;;) {
+    int env = 0;
+    if (lane == 0) env = atomicAdd(next_env, 1);
+    env = __shfl_sync(0xffffffffu, env, 0);
+    if (env >= a.n_env) break;
+    if (a.env_mask && !a.env_mask[env]) continue;
+    T* rec = a.state + (size_t)env * a.state_stride;
+    if (lane == 0) { fence_async_smem(); mbar_expect_tx(bar, kRecBytes); tma_load_1d(s.qpos, rec, kRecBytes, bar); }
+    mbar_wait(bar, phase); phase ^= 1;
+    run_env(sm.model, g, s, a, env, c, true);
+    __syncwarp();
+    if (lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }
+    __syncwarp();
+  }
+}
+
+template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<T>) + 128; }
+
+// occupancy query + attribute setup (once per handle)
+template <typename T>
+static cudaError_t step_configure(int device, int n_env, LaunchGeom* out) {
+  const size_t smem = step_smem_size<T>();
+  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  int per_sm = 0, sms = 0;
+  const int threads = 32 * KernelCfg<T>::kWarps;
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T>, threads, smem);
+  if (e != cudaSuccess) return e;
+  e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
+  if (e != cudaSuccess) return e;
+  if (per_sm < 1) return cudaErrorLaunchOutOfResources;
+  out->threads = threads; out->smem_bytes = (int)smem; out->blocks_per_sm = per_sm; out->warps_per_cta = KernelCfg<T>::kWarps;
+  out->grid = sms * per_sm;
+  const int need = (n_env + KernelCfg<T>::kWarps - 1) / KernelCfg<T>::kWarps;
+  if (out->grid > need) out->grid = need;
+  return cudaSuccess;
+}
+
+template <typename T>
+static cudaError_t step_launch(const LaunchGeom& lg, const void* d_model, const Globals<T>& g, const StepArgs<T>& a, int* next_env, cudaStream_t st) {
+  cudaError_t e = cudaMemsetAsync(next_env, 0, sizeof(int), st);
+  if (e != cudaSuccess) return e;
+  b2p_step_kernel<T><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  return cudaGetLastError();
+}
+
+}  // namespace b2p

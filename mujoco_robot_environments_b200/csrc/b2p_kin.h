@@ -1,0 +1,218 @@
+#pragma once
+#include "b2p_linalg.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------------------------------ mj_kinematics + comPos + comVel + rne (forward sweep)
+template <typename T>
+B2P_HD void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  if (c.tid == 0) {
+    for (int k = 0; k < 3; k++) s.xpos[0][k] = 0;
+    s.xquat[0][0] = 1; s.xquat[0][1] = 0; s.xquat[0][2] = 0; s.xquat[0][3] = 0;
+    quat2mat(s.xmat[0], s.xquat[0]);
+    for (int k = 0; k < 6; k++) { s.cvel[0][k] = 0; s.cacc[0][k] = 0; s.cfrc[0][k] = 0; }
+    for (int k = 0; k < 3; k++) s.cacc[0][3 + k] = -m.gravity[k];
+    for (int k = 0; k < 10; k++) s.crb[0][k] = 0;
+  }
+  for (int p = c.tid; p < m.nprop; p += c.nt) {     // free bodies: xpos = qpos[0:3], xquat = normalize(qpos[3:7])
+    T* q = s.qpos + m.ntd + 7 * p;
+    normquat(q + 3); cp3(s.ppos[p], q); quat2mat(s.pmat[p], q + 3);
+  }
+  bsync(c);
+  for (int l = 0; l < m.nlevel; l++) {
+    for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
+      const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
+      T pos[3], quat[4], a[3];
+      mulmv(pos, s.xmat[p], m.tb_pos[b]);
+      for (int k = 0; k < 3; k++) pos[k] += s.xpos[p][k];
+      mulquat(quat, s.xquat[p], m.tb_quat[b]);
+      T mat[9]; quat2mat(mat, quat);
+      mulmv(a, mat, m.jnt_pos[d]);
+      for (int k = 0; k < 3; k++) s.xanchor[d][k] = pos[k] + a[k];
+      mulmv(s.xaxis[d], mat, m.jnt_axis[d]);
+      const T ang = s.qpos[d] - m.qpos0[d], sn = sin(T(0.5) * ang);
+      T qloc[4] = {cos(T(0.5) * ang), sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
+      mulquat(quat, quat, qloc); normquat(quat);
+      quat2mat(mat, quat);
+      mulmv(a, mat, m.jnt_pos[d]);
+      for (int k = 0; k < 3; k++) { pos[k] = s.xanchor[d][k] - a[k]; s.xpos[b][k] = pos[k]; }
+      for (int k = 0; k < 4; k++) s.xquat[b][k] = quat[k];
+      for (int k = 0; k < 9; k++) s.xmat[b][k] = mat[k];
+      // inertia about the fixed reference point, motion axis
+      T xipos[3], qi[4], ximat[9], off[3];
+      mulmv(xipos, mat, m.tb_ipos[b]);
+      for (int k = 0; k < 3; k++) off[k] = pos[k] + xipos[k] - m.ref[k];
+      mulquat(qi, quat, m.tb_iquat[b]); quat2mat(ximat, qi);
+      inert_com(s.cinert[b], m.tb_inertia[b], ximat, off, m.tb_mass[b]);
+      for (int k = 0; k < 10; k++) s.crb[b][k] = s.cinert[b][k];
+      T* cd = s.cdof[d];
+      cp3(cd, s.xaxis[d]);
+      for (int k = 0; k < 3; k++) off[k] = m.ref[k] - s.xanchor[d][k];
+      cross3(cd + 3, s.xaxis[d], off);
+      // velocity: cdof_dot = cvel_parent x cdof ; cvel = cvel_parent + cdof*qvel
+      T v[6];
+      for (int k = 0; k < 6; k++) v[k] = s.cvel[p][k];
+      cross_motion(s.cdof_dot[d], v, cd);
+      for (int k = 0; k < 6; k++) { v[k] += cd[k] * s.qvel[d]; s.cvel[b][k] = v[k]; }
+      // rne forward: cacc = cacc_parent + cdof_dot*qvel ; cfrc = I*cacc + cvel x* (I*cvel)
+      T acc[6], Ia[6], Iv[6], cf[6];
+      for (int k = 0; k < 6; k++) { acc[k] = s.cacc[p][k] + s.cdof_dot[d][k] * s.qvel[d]; s.cacc[b][k] = acc[k]; }
+      mul_inert_vec(Ia, s.cinert[b], acc); mul_inert_vec(Iv, s.cinert[b], v); cross_force(cf, v, Iv);
+      for (int k = 0; k < 6; k++) s.cfrc[b][k] = Ia[k] + cf[k];
+    }
+    bsync(c);
+  }
+  // geoms + sites
+  for (int g = c.tid; g < m.ngeom; g += c.nt) {
+    const int b = m.geom_body[g];
+    const T *bp, *bm; T bq[4];
+    if (b >= PROP_BODY0) { const int p = b - PROP_BODY0; bp = s.ppos[p]; bm = s.pmat[p]; for (int k = 0; k < 4; k++) bq[k] = s.qpos[m.ntd + 7 * p + 3 + k]; }
+    else { bp = s.xpos[b]; bm = s.xmat[b]; for (int k = 0; k < 4; k++) bq[k] = s.xquat[b][k]; }
+    T t[3], q[4];
+    mulmv(t, bm, m.geom_pos[g]);
+    for (int k = 0; k < 3; k++) s.gpos[g][k] = bp[k] + t[k];
+    mulquat(q, bq, m.geom_quat[g]); quat2mat(s.gmat[g], q);
+  }
+  for (int i = c.tid; i < 2; i += c.nt) {
+    const int b = m.site_body[i]; T t[3], q[4];
+    mulmv(t, s.xmat[b], m.site_pos[i]);
+    for (int k = 0; k < 3; k++) s.site_xpos[i][k] = s.xpos[b][k] + t[k];
+    mulquat(q, s.xquat[b], m.site_quat[i]); quat2mat(s.site_xmat[i], q);
+  }
+  bsync(c);
+}
+
+// backward sweep: composite inertias (mj_crb) and rne force accumulation, parent gathers children
+template <typename T>
+B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  for (int l = m.nlevel - 2; l >= 0; l--) {
+    for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
+      const int b = m.level_body[idx];
+      for (int q = m.child_start[b]; q < m.child_start[b + 1]; q++) {
+        const int ch = m.child_list[q];
+        for (int k = 0; k < 10; k++) s.crb[b][k] += s.crb[ch][k];
+        for (int k = 0; k < 6; k++) s.cfrc[b][k] += s.cfrc[ch][k];
+      }
+    }
+    bsync(c);
+  }
+}
+
+// mass matrix (tree block dense, props diagonal), bias forces, passive forces
+template <typename T>
+B2P_HD void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  const int n = m.ntd;
+  for (int e = c.tid; e < n * n; e += c.nt) {
+    const int i = e / n, j = e % n;
+    if (j > i) continue;
+    T v = 0;
+    if (m.anc_mask[i + 1] & (1u << j)) {
+      T buf[6]; mul_inert_vec(buf, s.crb[i + 1], s.cdof[i]);
+      for (int k = 0; k < 6; k++) v += s.cdof[j][k] * buf[k];
+      if (i == j) v += m.dof_armature[i];
+    }
+    s.Marm[i * MAXTD + j] = v; s.Marm[j * MAXTD + i] = v;
+    s.Larm[i * MAXTD + j] = v; s.Larm[j * MAXTD + i] = v;
+  }
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    if (d < n) {
+      T v = 0;
+      for (int k = 0; k < 6; k++) v += s.cdof[d][k] * s.cfrc[d + 1][k];
+      s.qfrc_bias[d] = v;
+      s.qfrc_passive[d] = -m.dof_damping[d] * s.qvel[d] - m.jnt_stiffness[d] * (s.qpos[d] - m.qpos_spring[d]);
+    } else {
+      const int p = (d - n) / 6, k = (d - n) % 6; const T mass = m.prop_mass[p];
+      if (k < 3) { s.Mdiag[d] = mass; s.qfrc_bias[d] = -mass * m.gravity[k]; }
+      else {
+        const T* w = s.qvel + n + 6 * p + 3; const T* I = s.pinertia[p];
+        T Iw[3] = {I[0] * w[0], I[1] * w[1], I[2] * w[2]}, cr[3];
+        cross3(cr, w, Iw);
+        s.Mdiag[d] = I[k - 3]; s.qfrc_bias[d] = cr[k - 3];
+      }
+      s.qfrc_passive[d] = 0;
+    }
+  }
+  bsync(c);
+  block_cholesky(s.Larm, n, MAXTD, c);
+}
+
+// ------------------------------------------------------------------------------------------ actuation + smooth acceleration
+template <typename T>
+B2P_HD void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  for (int d = c.tid; d < m.nv; d += c.nt) s.qfrc_act[d] = 0;
+  bsync(c);
+  if (c.tid == 0) {
+    for (int a = 0; a < m.nu; a++) {
+      T len = 0, vel = 0;
+      for (int k = 0; k < m.act_trnnum[a]; k++) { const int d = m.act_trndof[a][k]; len += m.act_trncoef[a][k] * s.qpos[d]; vel += m.act_trncoef[a][k] * s.qvel[d]; }
+      T u = s.ctrl[a];
+      if (m.act_ctrllimited[a]) u = clampT(u, m.act_ctrlrange[a][0], m.act_ctrlrange[a][1]);
+      T f = m.act_gain[a] * u + m.act_bias[a][0] + m.act_bias[a][1] * len + m.act_bias[a][2] * vel;
+      if (m.act_forcelimited[a]) f = clampT(f, m.act_forcerange[a][0], m.act_forcerange[a][1]);
+      s.act_force[a] = f;
+      for (int k = 0; k < m.act_trnnum[a]; k++) s.qfrc_act[m.act_trndof[a][k]] += m.act_trncoef[a][k] * f;
+    }
+  }
+  bsync(c);
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    bool active = d < m.ntd || s.pactive[(d - m.ntd) / 6];
+    const T f = active ? s.qfrc_passive[d] - s.qfrc_bias[d] + s.qfrc_act[d] : T(0);
+    s.qfrc_smooth[d] = f;
+    s.qacc_smooth[d] = d < m.ntd ? f : f / s.Mdiag[d];
+  }
+  bsync(c);
+  warp_chol_solve(s.Larm, m.ntd, MAXTD, s.qacc_smooth, c);
+  bsync(c);
+}
+
+// ------------------------------------------------------------------------------------------ integrator (mj_implicit / mj_Euler + mj_advance)
+template <typename T>
+B2P_HD void integrate(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool freeze_tree) {
+  const int n = m.ntd; const T h = m.timestep;
+  for (int e = c.tid; e < n * n; e += c.nt) {
+    const int i = e / n, j = e % n;
+    T v = s.Marm[i * MAXTD + j];
+    if (i == j) {
+      v += h * m.dof_damping[i];
+      if (m.integrator == B2P_INT_IMPLICITFAST)
+        for (int a = 0; a < m.nu; a++) if (m.act_bias[a][2] != 0) for (int x = 0; x < m.act_trnnum[a]; x++) if (m.act_trndof[a][x] == i) v -= h * m.act_trncoef[a][x] * m.act_trncoef[a][x] * m.act_bias[a][2];
+    } else if (m.integrator == B2P_INT_IMPLICITFAST) {
+      // off-diagonal actuator terms only inside M's (ancestor) sparsity pattern
+      const int hi = i > j ? i : j, lo = i > j ? j : i;
+      if (m.anc_mask[hi + 1] & (1u << lo))
+        for (int a = 0; a < m.nu; a++) if (m.act_bias[a][2] != 0 && m.act_trnnum[a] == 2) {
+          const int d0 = m.act_trndof[a][0], d1 = m.act_trndof[a][1];
+          if ((d0 == i && d1 == j) || (d0 == j && d1 == i)) v -= h * m.act_trncoef[a][0] * m.act_trncoef[a][1] * m.act_bias[a][2];
+        }
+    }
+    s.H[i * MAXNV + j] = v;
+  }
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    bool active = d < n || s.pactive[(d - n) / 6];
+    const T f = active ? s.qfrc_smooth[d] + s.qfrc_con[d] : T(0);
+    s.tmpv[d] = d < n ? f : f / s.Mdiag[d];
+  }
+  bsync(c);
+  block_cholesky(s.H, n, MAXNV, c);
+  warp_chol_solve(s.H, n, MAXNV, s.tmpv, c);
+  bsync(c);
+  for (int d = c.tid; d < m.nv; d += c.nt) { s.qvel[d] += h * s.tmpv[d]; s.qacc_ws[d] = s.qacc[d]; }
+  bsync(c);
+  for (int d = c.tid; d < n; d += c.nt) s.qpos[d] += h * s.qvel[d];
+  for (int p = c.tid; p < m.nprop; p += c.nt) {
+    T* q = s.qpos + n + 7 * p; const T* v = s.qvel + n + 6 * p;
+    for (int k = 0; k < 3; k++) q[k] += h * v[k];
+    T w[3] = {v[3], v[4], v[5]}; const T ang = h * normalize3(w), sn = sin(T(0.5) * ang);
+    T qr[4] = {cos(T(0.5) * ang), sn * w[0], sn * w[1], sn * w[2]};
+    mulquat(q + 3, q + 3, qr); normquat(q + 3);
+  }
+  if (c.tid == 0) s.time += h;
+  bsync(c);
+  if (freeze_tree) {   // dm_control JointStaticIsolator: non-prop joints restored after the step (App. B item 18)
+    for (int d = c.tid; d < n; d += c.nt) { s.qpos[d] = s.hold_q[d]; s.qvel[d] = s.hold_v[d]; }
+    bsync(c);
+  }
+}
+
+
+}  // namespace b2p

@@ -1,0 +1,138 @@
+#pragma once
+#include "b2p_scratch.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------------------------------ constraints
+template <typename T>
+B2P_HD T impedance(const T* si, T pos, T margin) {
+  const T d0 = clampT(si[0], T(0.0001), T(0.9999)), d1 = clampT(si[1], T(0.0001), T(0.9999)), w = si[2] > 0 ? si[2] : T(0);
+  const T mid = clampT(si[3], T(0.0001), T(0.9999)), pw = si[4] > 1 ? si[4] : T(1);
+  if (d0 == d1 || w <= Num<T>::minval()) return T(0.5) * (d0 + d1);
+  const T x = fabs((pos - margin) / w); T y;
+  if (x >= 1) return d1;
+  if (x <= 0) return d0;
+  if (pw == 1) y = x;
+  else if (x <= mid) y = pow(x, pw) / pow(mid, pw - 1);
+  else y = 1 - pow(1 - x, pw) / pow(1 - mid, pw - 1);
+  return d0 + y * (d1 - d0);
+}
+// K, B, imp, R for one row (mj_makeImpedance, App. B item 9)
+template <typename T>
+B2P_HD void row_params(const DevModel<T>& m, const T* solref_in, const T* solimp, T pos_imp, T margin, T diag, bool friction_row, T& K, T& B, T& imp, T& R) {
+  T sr0 = solref_in[0], sr1 = solref_in[1];
+  if (sr0 > 0 && sr0 < 2 * m.timestep) sr0 = 2 * m.timestep;
+  imp = impedance(solimp, pos_imp, margin);
+  const T dmax = clampT(solimp[1], T(0.0001), T(0.9999)), mv = Num<T>::minval();
+  if (sr0 > 0) { T a = dmax * dmax * sr0 * sr0 * sr1 * sr1; K = 1 / (a > mv ? a : mv); T bb = dmax * sr0; B = 2 / (bb > mv ? bb : mv); }
+  else { T a = dmax * dmax; K = -sr0 / (a > mv ? a : mv); B = -sr1 / (dmax > mv ? dmax : mv); }
+  if (friction_row) K = 0;
+  R = (1 - imp) / imp * diag; if (R < mv) R = mv;
+}
+// add sign * ax . d(point velocity of unified body `body` at world point pt)/d(qvel) into a compressed row
+template <typename T>
+B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0, int body, const T* pt, const T* ax, T sign) {
+  if (body == 0) return;
+  if (body >= PROP_BODY0) {
+    const int p = body - PROP_BODY0; T r[3] = {pt[0] - s.ppos[p][0], pt[1] - s.ppos[p][1], pt[2] - s.ppos[p][2]};
+    for (int k = 0; k < 3; k++) row[seg0 + k] += sign * ax[k];
+    for (int k = 0; k < 3; k++) { T a[3] = {s.pmat[p][k], s.pmat[p][3 + k], s.pmat[p][6 + k]}, cr[3]; cross3(cr, a, r); row[seg0 + 3 + k] += sign * dot3(ax, cr); }
+  } else {
+    T off[3] = {pt[0] - m.ref[0], pt[1] - m.ref[1], pt[2] - m.ref[2]};
+    const unsigned mask = m.anc_mask[body];
+    for (int d = 0; d < m.ntd; d++) if (mask & (1u << d)) {
+      T cr[3]; cross3(cr, s.cdof[d], off);
+      row[seg0 + d] += sign * (ax[0] * (s.cdof[d][3] + cr[0]) + ax[1] * (s.cdof[d][4] + cr[1]) + ax[2] * (s.cdof[d][5] + cr[2]));
+    }
+  }
+}
+template <typename T>
+B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s, int r) {
+  T v = 0; const int a = s.row_a[r], b = s.row_b[r];
+  if (a >= 0) { const int st = block_start(m, a), n = a == 0 ? m.ntd : 6; for (int k = 0; k < n; k++) v += s.J[r][k] * s.qvel[st + k]; }
+  if (b >= 0) { const int st = block_start(m, b); for (int k = 0; k < 6; k++) v += s.J[r][SEGB + k] * s.qvel[st + k]; }
+  return v;
+}
+template <typename T>
+B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
+  T v = 0; const int a = s.row_a[r], b = s.row_b[r];
+  if (a >= 0) { const int st = block_start(m, a), n = a == 0 ? m.ntd : 6; for (int k = 0; k < n; k++) v += s.J[r][k] * x[st + k]; }
+  if (b >= 0) { const int st = block_start(m, b); for (int k = 0; k < 6; k++) v += s.J[r][SEGB + k] * x[st + k]; }
+  return v;
+}
+
+// mj_makeConstraint + mj_referenceConstraint: equality -> limits -> contacts, rows complete incl. aref
+template <typename T>
+B2P_HD void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
+  const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon;
+  int base = 0;
+  for (int i0 = 0; i0 < nitem; i0 += c.nt) {
+    const int it = i0 + c.tid; int nr = 0, kind = -1, id = 0; T dist = 0;
+    if (it < nitem) {
+      if (it < m.neq) { kind = ROW_EQ; id = it; nr = m.eq_type[it] == B2P_EQ_CONNECT ? 3 : 1; }
+      else if (it < m.neq + nlim) {
+        const int j = (it - m.neq) >> 1, side = ((it - m.neq) & 1) ? 1 : -1;
+        if (m.jnt_limited[j]) { dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]); if (dist < m.jnt_margin[j]) { kind = ROW_LIMIT; id = j * 2 + (side > 0); nr = 1; } }
+      } else { id = it - m.neq - nlim; if (s.c_dist[id] < s.c_incl[id]) { kind = ROW_CONTACT; nr = 3; } }
+    }
+    int tot; const int ofs = block_scan(c, nr, tot);
+    int r0 = base + ofs;
+    if (nr > 0 && r0 + nr > MAXEFC) { nr = 0; if (kind == ROW_CONTACT) s.c_row[id] = -1; s.flags |= FLAG_EFCFULL; }
+    if (nr > 0) {
+      for (int q = 0; q < nr; q++) { for (int k = 0; k < JW; k++) s.J[r0 + q][k] = 0; s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_b[r0 + q] = -1; s.row_a[r0 + q] = 0; }
+      if (kind == ROW_EQ && nr == 3) {
+        const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];
+        mulmv(g1, s.xmat[b1], m.eq_data[id]); mulmv(g2, s.xmat[b2], m.eq_data[id] + 3);
+        for (int k = 0; k < 3; k++) { g1[k] += s.xpos[b1][k]; g2[k] += s.xpos[b2][k]; res[k] = g1[k] - g2[k]; }
+        const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
+        for (int q = 0; q < 3; q++) {
+          T ax[3] = {T(q == 0), T(q == 1), T(q == 2)};
+          add_jac(m, s, s.J[r0 + q], 0, b1, g1, ax, T(1)); add_jac(m, s, s.J[r0 + q], 0, b2, g2, ax, T(-1));
+          T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
+          s.D[r0 + q] = 1 / R; s.aref[r0 + q] = -B * row_vel(m, s, r0 + q) - K * imp * res[q];
+        }
+      } else if (kind == ROW_EQ) {
+        const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
+        const T x = s.qpos[j2] - m.qpos0[j2], pos = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
+        s.J[r0][j1] = 1; s.J[r0][j2] = -cf[1];
+        T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], pos, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
+        s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * pos;
+      } else if (kind == ROW_LIMIT) {
+        const int j = id >> 1, side = (id & 1) ? 1 : -1;
+        s.J[r0][j] = T(-side);
+        T K, B, imp, R; row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
+        s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * (dist - m.jnt_margin[j]);
+      } else {
+        const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
+        const PairParam<T>& pp = g.pair_param[p];
+        // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
+        int ba = -1, bb = -1, seg1 = 0, seg2 = 0;
+        const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
+        if (t1 || t2) ba = 0;
+        if (b1 >= PROP_BODY0) { if (ba < 0) { ba = 1 + b1 - PROP_BODY0; seg1 = 0; } else { bb = 1 + b1 - PROP_BODY0; seg1 = SEGB; } }
+        if (b2 >= PROP_BODY0) { if (ba < 0) { ba = 1 + b2 - PROP_BODY0; seg2 = 0; } else { bb = 1 + b2 - PROP_BODY0; seg2 = SEGB; } }
+        T iw1[2], iw2[2];
+        for (int k = 0; k < 2; k++) { iw1[k] = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][k] : m.geom_invweight0[g1][k]; iw2[k] = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][k] : m.geom_invweight0[g2][k]; }
+        const T tran = iw1[0] + iw2[0];
+        T K, B, imp, R0;
+        row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], tran, false, K, B, imp, R0);
+        const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
+        s.c_mu[id] = s.c_fric[id][0] * sqrt(R1 / R0); s.c_row[id] = (short)r0;
+        for (int q = 0; q < 3; q++) {
+          s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
+          const T* ax = s.c_frame[id] + 3 * q;
+          add_jac(m, s, s.J[r0 + q], seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, s.J[r0 + q], seg1, b1, s.c_pos[id], ax, T(-1));
+          const T vel = row_vel(m, s, r0 + q);
+          if (q == 0) { s.D[r0] = 1 / R0; s.aref[r0] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
+          else { s.D[r0 + q] = 1 / R1; s.aref[r0 + q] = -B * vel; }
+        }
+      }
+    }
+    base += tot;
+  }
+  if (c.tid == 0) s.nefc = base < MAXEFC ? base : MAXEFC;
+  bsync(c);
+}
+
+
+}  // namespace b2p

@@ -1,0 +1,84 @@
+#pragma once
+#include "b2p_math.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------------------------------ per-env scratch
+// HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
+constexpr int REC_QPOS = 0, REC_QVEL = MAXNQ, REC_QACC = MAXNQ + MAXNV, REC_TIME = MAXNQ + 2 * MAXNV, REC_SIZE = 128;
+template <typename T>
+struct Globals {                 // read-only global-memory tables
+  const T* mesh_vert; const int* nbradr; const int* nbrnum; const int* nbr;
+  const short* pair_g1; const short* pair_g2; const PairParam<T>* pair_param;
+};
+
+template <typename T>
+struct alignas(16) Scratch {
+  // persisted state (one HBM record per env: qpos | qvel | qacc_warmstart | time)
+  T qpos[MAXNQ], qvel[MAXNV], qacc_ws[MAXNV], time, rec_pad[REC_SIZE - (MAXNQ + 2 * MAXNV + 1)], ctrl[MAXU];
+  // per-env prop parameters
+  T psize[MAXP][3], pinertia[MAXP][3], pinvw[MAXP][2]; int pactive[MAXP];
+  // tree
+  T xpos[MAXTB][3], xquat[MAXTB][4], xmat[MAXTB][9], xanchor[MAXTD][3], xaxis[MAXTD][3];
+  T cinert[MAXTB][10], crb[MAXTB][10], cdof[MAXTD][6], cdof_dot[MAXTD][6], cvel[MAXTB][6], cacc[MAXTB][6], cfrc[MAXTB][6];
+  T ppos[MAXP][3], pmat[MAXP][9];
+  T gpos[MAXG][3], gmat[MAXG][9], grbound[MAXG], site_xpos[2][3], site_xmat[2][9];
+  // dynamics
+  T Marm[MAXTD * MAXTD], Larm[MAXTD * MAXTD], Mdiag[MAXNV];
+  T qfrc_bias[MAXNV], qfrc_passive[MAXNV], qfrc_act[MAXNV], qfrc_smooth[MAXNV], qacc_smooth[MAXNV], qacc[MAXNV], qfrc_con[MAXNV];
+  T act_force[MAXU];
+  // contacts
+  int ncand, ncon, nefc, flags, niter;
+  short cand[MAXCAND];
+  T c_dist[MAXCON], c_pos[MAXCON][3], c_frame[MAXCON][9], c_mu[MAXCON], c_fric[MAXCON][2], c_incl[MAXCON];
+  short c_pair[MAXCON], c_row[MAXCON];
+  // constraint rows (compressed Jacobian: slots 0..14 segment A, 15..20 segment B)
+  T J[MAXEFC][JW], D[MAXEFC], aref[MAXEFC], Jaref[MAXEFC], Jv[MAXEFC], force[MAXEFC];
+  signed char row_a[MAXEFC], row_b[MAXEFC], row_type[MAXEFC], row_state[MAXEFC];
+  short row_id[MAXEFC];
+  T cW[MAXCON][6];               // per-contact 3x3 symmetric Hessian weight (xx,yy,zz,xy,xz,yz) in row space
+  // solver
+  T H[MAXNV * MAXNV], grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV];
+  // settle / frozen-arm support
+  T hold_q[MAXTD], hold_v[MAXTD];
+};
+
+// block id of a dof: 0 = tree, 1+p = prop p
+template <typename T> B2P_HD int dof_block(const DevModel<T>& m, int d) { return d < m.ntd ? 0 : 1 + (d - m.ntd) / 6; }
+template <typename T> B2P_HD int block_start(const DevModel<T>& m, int blk) { return blk == 0 ? 0 : m.ntd + 6 * (blk - 1); }
+// slot of dof d inside row r, or -1
+template <typename T> B2P_HD int row_slot(const DevModel<T>& m, const Scratch<T>& s, int r, int d) {
+  int blk = dof_block(m, d), a = s.row_a[r], b = s.row_b[r];
+  if (a == blk) return d - block_start(m, blk);
+  if (b == blk) return SEGB + d - block_start(m, blk);
+  return -1;
+}
+
+// HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
+// launch parameters shared by kernel and host emulation
+template <typename T>
+struct StepArgs {
+  int mode, n_env, n_steps, control_steps, state_stride, full_contacts;
+  T* state;                  // [n_env][state_stride]: qpos | qvel | qacc_warmstart | time
+  const T* ctrl;             // MODE_PHYSICS / SETTLE: [n_env][nu]
+  const T* target;           // MODE_OSC: [n_env][13] pos3 vel3 quat4(wxyz) angvel3
+  const unsigned char* grip; // MODE_OSC: [n_env] 0 = min, 1 = max
+  const T* prop_size;        // [n_env][MAXP][3] half sizes
+  const unsigned char* prop_active; // [n_env][MAXP]
+  const unsigned char* env_mask;    // optional [n_env]: 0 = skip env
+  unsigned char* converged;  // MODE_OSC out [n_env]
+  int* status;               // out [n_env] OR-ed flags
+  int* steps_done;           // MODE_SETTLE out [n_env]
+  T settle_qvel_tol, settle_qacc_tol; int settle_min_steps;
+  T* out;                    // MODE_FORWARD / any: optional derived-output record per env (see OutLayout)
+  int out_stride;
+};
+// derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |
+//   contacts[MAXCON] x (dist, pos3, normal3, geom1, geom2, excluded) | Marm[MAXTD*MAXTD] | gpos[MAXG][3] | gmat[MAXG][9]
+struct OutLayout {
+  static constexpr int SITE_XPOS = 0, SITE_XMAT = 6, QACC = 24, QFRC_BIAS = QACC + MAXNV, CTRL = QFRC_BIAS + MAXNV, NCON = CTRL + MAXU, NEFC = NCON + 1,
+                       NITER = NEFC + 1, CONTACT = NITER + 1, CONTACT_W = 10, MARM = CONTACT + MAXCON * CONTACT_W, GPOS = MARM + MAXTD * MAXTD,
+                       GMAT = GPOS + MAXG * 3, QACC_SMOOTH = GMAT + MAXG * 9, EFC_FORCE = QACC_SMOOTH + MAXNV, SIZE = EFC_FORCE + MAXEFC;
+};
+
+}  // namespace b2p

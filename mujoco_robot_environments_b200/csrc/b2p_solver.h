@@ -1,0 +1,238 @@
+#pragma once
+#include "b2p_linalg.h"
+#include "b2p_rows.h"
+
+namespace b2p {
+
+// ------------------------------------------------------------------------------------------ Newton solver
+template <typename T>
+B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, const Ctx& c) {
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    if (d < m.ntd) { T a = 0; for (int j = 0; j < m.ntd; j++) a += s.Marm[d * MAXTD + j] * v[j]; r[d] = a; }
+    else r[d] = s.Mdiag[d] * v[d];
+  }
+}
+// per-item (rows of eq/limit, whole contacts) force/state/cost from s.Jaref; returns this thread's cost part
+template <typename T>
+B2P_HD T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess) {
+  T cost = 0;
+  for (int r = c.tid; r < s.nefc; r += c.nt) {
+    const int tp = s.row_type[r];
+    if (tp == ROW_CONTACT) continue;
+    const T j = s.Jaref[r];
+    if (tp == ROW_EQ || j < 0) { s.force[r] = -s.D[r] * j; s.row_state[r] = ST_QUADRATIC; cost += T(0.5) * s.D[r] * j * j; }
+    else { s.force[r] = 0; s.row_state[r] = ST_SATISFIED; }
+  }
+  for (int k = c.tid; k < s.ncon; k += c.nt) {
+    const int r = s.c_row[k];
+    if (r < 0) continue;
+    const T mu = s.c_mu[k], f1 = s.c_fric[k][0], f2 = s.c_fric[k][1];
+    const T j0 = s.Jaref[r], j1 = s.Jaref[r + 1], j2 = s.Jaref[r + 2];
+    const T N = j0 * mu, U1 = j1 * f1, U2 = j2 * f2, Tt = sqrt(U1 * U1 + U2 * U2);
+    T* W = s.cW[k];
+    if (N >= mu * Tt || (Tt <= 0 && N >= 0)) {
+      for (int q = 0; q < 3; q++) { s.force[r + q] = 0; s.row_state[r + q] = ST_SATISFIED; }
+      if (want_hess) for (int q = 0; q < 6; q++) W[q] = 0;
+    } else if (mu * N + Tt <= 0 || (Tt <= 0 && N < 0)) {
+      for (int q = 0; q < 3; q++) { const T jq = s.Jaref[r + q]; s.force[r + q] = -s.D[r + q] * jq; s.row_state[r + q] = ST_QUADRATIC; cost += T(0.5) * s.D[r + q] * jq * jq; }
+      if (want_hess) { W[0] = s.D[r]; W[1] = s.D[r + 1]; W[2] = s.D[r + 2]; W[3] = W[4] = W[5] = 0; }
+    } else {
+      const T mv = Num<T>::minval(), dn = mu * mu * (1 + mu * mu), Dm = s.D[r] / (dn > mv ? dn : mv), NmT = N - mu * Tt;
+      cost += T(0.5) * Dm * NmT * NmT;
+      const T fn = -Dm * NmT * mu;
+      s.force[r] = fn; s.force[r + 1] = -fn / Tt * U1 * f1; s.force[r + 2] = -fn / Tt * U2 * f2;
+      for (int q = 0; q < 3; q++) s.row_state[r + q] = ST_CONE;
+      if (want_hess) {
+        const T iT = 1 / Tt, a = Dm * mu * mu * iT * iT, b = Dm * mu * NmT, iT3 = iT * iT * iT;
+        const T h00 = Dm, h01 = -Dm * mu * U1 * iT, h02 = -Dm * mu * U2 * iT;
+        const T h11 = a * U1 * U1 - b * (iT - U1 * U1 * iT3), h22 = a * U2 * U2 - b * (iT - U2 * U2 * iT3), h12 = a * U1 * U2 + b * U1 * U2 * iT3;
+        W[0] = h00 * mu * mu; W[1] = h11 * f1 * f1; W[2] = h22 * f2 * f2; W[3] = h01 * mu * f1; W[4] = h02 * mu * f2; W[5] = h12 * f1 * f2;
+      }
+    }
+  }
+  return cost;
+}
+// qfrc_con = J' force
+template <typename T>
+B2P_HD void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    T a = 0;
+    for (int r = 0; r < s.nefc; r++) { const T f = s.force[r]; if (f == 0) continue; const int sl = row_slot(m, s, r, d); if (sl >= 0) a += s.J[r][sl] * f; }
+    s.qfrc_con[d] = a;
+  }
+}
+// H = M + J' W J (lower triangle, dense nv x nv with leading dimension MAXNV)
+template <typename T>
+B2P_HD void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  const int nv = m.nv, cnt = nv * (nv + 1) / 2;
+  for (int e = c.tid; e < cnt; e += c.nt) {
+    int i = (int)((sqrt(T(8) * e + 1) - 1) * T(0.5));
+    while ((i + 1) * (i + 2) / 2 <= e) i++;
+    while (i * (i + 1) / 2 > e) i--;
+    const int j = e - i * (i + 1) / 2;
+    const int bi = dof_block(m, i), bj = dof_block(m, j), oi = i - block_start(m, bi), oj = j - block_start(m, bj);
+    T h = 0;
+    if (bi == 0 && bj == 0) h = s.Marm[i * MAXTD + j]; else if (i == j) h = s.Mdiag[i];
+    for (int r = 0; r < s.nefc; r++) {
+      const int a = s.row_a[r], b = s.row_b[r];
+      const int si = a == bi ? oi : (b == bi ? SEGB + oi : -1);
+      if (si < 0) { if (s.row_type[r] == ROW_CONTACT) r += 2; continue; }
+      const int sj = a == bj ? oj : (b == bj ? SEGB + oj : -1);
+      if (sj < 0) { if (s.row_type[r] == ROW_CONTACT) r += 2; continue; }
+      if (s.row_type[r] != ROW_CONTACT) { if (s.row_state[r] == ST_QUADRATIC) h += s.D[r] * s.J[r][si] * s.J[r][sj]; }
+      else {
+        const int st = s.row_state[r];
+        if (st != ST_SATISFIED) {
+          const T* W = s.cW[s.row_id[r]];
+          const T a0 = s.J[r][si], a1 = s.J[r + 1][si], a2 = s.J[r + 2][si], b0 = s.J[r][sj], b1 = s.J[r + 1][sj], b2 = s.J[r + 2][sj];
+          h += W[0] * a0 * b0 + W[1] * a1 * b1 + W[2] * a2 * b2 + W[3] * (a0 * b1 + a1 * b0) + W[4] * (a0 * b2 + a2 * b0) + W[5] * (a1 * b2 + a2 * b1);
+        }
+        r += 2;
+      }
+    }
+    s.H[i * MAXNV + j] = h;
+  }
+}
+template <typename T> struct LsPt { T alpha, cost, d1, d2; };
+template <typename T>
+B2P_HD LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, const T* qg) {
+  T q0 = 0, q1 = 0, q2 = 0, ec = 0, e1 = 0, e2 = 0;
+  for (int r = c.tid; r < s.nefc; r += c.nt) {
+    const int tp = s.row_type[r];
+    if (tp == ROW_CONTACT) continue;
+    const T D = s.D[r], j0 = s.Jaref[r], jv = s.Jv[r];
+    if (tp == ROW_EQ || j0 + a * jv < 0) { q0 += T(0.5) * D * j0 * j0; q1 += D * j0 * jv; q2 += T(0.5) * D * jv * jv; }
+  }
+  for (int k = c.tid; k < s.ncon; k += c.nt) {
+    const int r = s.c_row[k];
+    if (r < 0) continue;
+    const T mu = s.c_mu[k], f1 = s.c_fric[k][0], f2 = s.c_fric[k][1];
+    T t0 = 0, t1 = 0, t2 = 0;
+    for (int q = 0; q < 3; q++) { const T D = s.D[r + q], j0 = s.Jaref[r + q], jv = s.Jv[r + q]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }
+    const T U0 = s.Jaref[r] * mu, V0 = s.Jv[r] * mu, u1 = s.Jaref[r + 1] * f1, u2 = s.Jaref[r + 2] * f2, v1 = s.Jv[r + 1] * f1, v2 = s.Jv[r + 2] * f2;
+    const T UU = u1 * u1 + u2 * u2, UV = u1 * v1 + u2 * v2, VV = v1 * v1 + v2 * v2;
+    const T N = U0 + a * V0, Tsqr = UU + a * (2 * UV + a * VV);
+    if (Tsqr <= 0) { if (N < 0) { q0 += t0; q1 += t1; q2 += t2; } }
+    else {
+      const T Tt = sqrt(Tsqr);
+      if (N >= mu * Tt) { }
+      else if (mu * N + Tt <= 0) { q0 += t0; q1 += t1; q2 += t2; }
+      else {
+        const T mv = Num<T>::minval(), dn = mu * mu * (1 + mu * mu), Dm = s.D[r] / (dn > mv ? dn : mv);
+        const T N1 = V0, T1 = (UV + a * VV) / Tt, T2 = VV / Tt - (UV + a * VV) * T1 / (Tt * Tt), NmT = N - mu * Tt;
+        ec += T(0.5) * Dm * NmT * NmT; e1 += Dm * NmT * (N1 - mu * T1); e2 += Dm * ((N1 - mu * T1) * (N1 - mu * T1) + NmT * (-mu * T2));
+      }
+    }
+  }
+  T v[3] = {ec + a * a * q2 + a * q1 + q0, e1 + 2 * a * q2 + q1, e2 + 2 * q2};
+  block_sum(c, v);
+  LsPt<T> p; p.alpha = a; p.cost = v[0] + a * a * qg[2] + a * qg[1] + qg[0]; p.d1 = v[1] + 2 * a * qg[2] + qg[1]; p.d2 = v[2] + 2 * qg[2];
+  if (p.d2 < Num<T>::minval()) p.d2 = Num<T>::minval();
+  return p;
+}
+// Jaref = J*x - aref, Ma = M*x, returns total cost (all threads)
+template <typename T>
+B2P_HD T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x) {
+  for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] = row_dot(m, s, r, x) - s.aref[r];
+  mul_M(m, s, s.Ma, x, c);
+  bsync(c);
+  T v[1] = {constraint_update(m, s, c, false)};
+  for (int d = c.tid; d < m.nv; d += c.nt) v[0] += T(0.5) * (s.Ma[d] - s.qfrc_smooth[d]) * (x[d] - s.qacc_smooth[d]);
+  block_sum(c, v);
+  return v[0];
+}
+// cost, gradient, Hessian factor, Newton direction at s.qacc (s.Jaref / s.Ma consistent with it)
+template <typename T>
+B2P_HD T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2) {
+  T v[2] = {constraint_update(m, s, c, true), 0};
+  bsync(c);
+  mul_JT_force(m, s, c);
+  assemble_H(m, s, c);
+  bsync(c);
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    const T gd = s.Ma[d] - s.qfrc_smooth[d] - s.qfrc_con[d];
+    s.grad[d] = gd; s.Mgrad[d] = gd; v[1] += gd * gd;
+    v[0] += T(0.5) * (s.Ma[d] - s.qfrc_smooth[d]) * (s.qacc[d] - s.qacc_smooth[d]);
+  }
+  block_sum(c, v);
+  block_cholesky(s.H, m.nv, MAXNV, c);
+  warp_chol_solve(s.H, m.nv, MAXNV, s.Mgrad, c);
+  bsync(c);
+  gradnorm2 = v[1];
+  return v[0];
+}
+template <typename T>
+B2P_HD T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale) {
+  T v[4] = {0, 0, 0, 0};
+  mul_M(m, s, s.Mv, s.search, c);
+  for (int r = c.tid; r < s.nefc; r += c.nt) s.Jv[r] = row_dot(m, s, r, s.search);
+  bsync(c);
+  for (int d = c.tid; d < m.nv; d += c.nt) {
+    const T sd = s.search[d], res = s.Ma[d] - s.qfrc_smooth[d];
+    v[0] += sd * sd; v[1] += sd * res; v[2] += T(0.5) * sd * s.Mv[d]; v[3] += T(0.5) * res * (s.qacc[d] - s.qacc_smooth[d]);
+  }
+  block_sum(c, v);
+  const T snorm = sqrt(v[0]);
+  if (snorm < Num<T>::minval()) return 0;
+  const T gtol = m.tolerance * m.ls_tolerance * snorm / scale;
+  const T qg[3] = {v[3], v[1], v[2]};
+  LsPt<T> p0 = ls_eval(m, s, c, T(0), qg), p1 = ls_eval(m, s, c, -p0.d1 / p0.d2, qg), p2;
+  if (p0.cost < p1.cost) p1 = p0;
+  if (fabs(p1.d1) < gtol) return p1.alpha;
+  const int dir = p1.d1 < 0 ? 1 : -1; int k = 0;
+  p2 = p1;
+  while (p1.d1 * dir <= -gtol && k < m.ls_iterations) {
+    p2 = p1; p1 = ls_eval(m, s, c, p1.alpha - p1.d1 / p1.d2, qg); k++;
+    if (fabs(p1.d1) < gtol) return p1.alpha;
+  }
+  if (k >= m.ls_iterations) return p1.alpha;
+  LsPt<T> lo = p2, hi = p1, best = p1.cost < p2.cost ? p1 : p2;
+  while (k < m.ls_iterations) {
+    const LsPt<T>& from = fabs(lo.d1) < fabs(hi.d1) ? lo : hi;
+    T a = from.alpha - from.d1 / from.d2; const T amin = lo.alpha < hi.alpha ? lo.alpha : hi.alpha, amax = lo.alpha < hi.alpha ? hi.alpha : lo.alpha;
+    if (!(a > amin && a < amax)) a = T(0.5) * (lo.alpha + hi.alpha);
+    LsPt<T> pm = ls_eval(m, s, c, a, qg); k++;
+    if (pm.cost < best.cost) best = pm;
+    if (fabs(pm.d1) < gtol) return pm.alpha;
+    if (pm.d1 * dir < 0) lo = pm; else hi = pm;
+    if (fabs(hi.alpha - lo.alpha) < 64 * Num<T>::eps() * (1 + fabs(hi.alpha))) break;
+  }
+  return best.alpha;
+}
+template <typename T>
+B2P_HD void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  const int nv = m.nv;
+  if (s.nefc == 0) {
+    for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] = s.qacc_smooth[d]; s.qfrc_con[d] = 0; }
+    if (c.tid == 0) s.niter = 0;
+    bsync(c);
+    return;
+  }
+  const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
+  const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
+  for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
+  bsync(c);
+  cost_at(m, s, c, s.qacc);
+  T gn2, cost = solver_update(m, s, c, gn2);
+  for (int d = c.tid; d < nv; d += c.nt) s.search[d] = -s.Mgrad[d];
+  bsync(c);
+  int it = 0;
+  for (; it < m.iterations; it++) {
+    const T alpha = line_search(m, s, c, scale);
+    if (alpha == 0) break;
+    for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] += alpha * s.search[d]; s.Ma[d] += alpha * s.Mv[d]; }
+    for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] += alpha * s.Jv[r];
+    bsync(c);
+    const T old = cost;
+    cost = solver_update(m, s, c, gn2);
+    const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
+    if (improvement < m.tolerance || gradient < m.tolerance) { it++; break; }
+    for (int d = c.tid; d < nv; d += c.nt) s.search[d] = -s.Mgrad[d];
+    bsync(c);
+  }
+  if (c.tid == 0) { s.niter = it; if (it >= m.iterations) s.flags |= FLAG_SOLVER_MAXITER; }
+  bsync(c);
+}
+
+
+}  // namespace b2p

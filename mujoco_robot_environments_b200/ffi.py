@@ -12,7 +12,8 @@ import subprocess
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libb2p.so")
-NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC", "-shared"]
+NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
+UNITS = ("b2p_api.cu", "b2p_kernel_f32.cu", "b2p_kernel_f64.cu")
 
 # enums of include/b2p.h
 F64, F32 = 0, 1
@@ -26,16 +27,27 @@ SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind
 
 
 def sources():
-    return [os.path.join(CSRC, f) for f in ("b2p_api.cu", "b2p_core.h", "b2p_model.h")] + \
+    return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".h"))] + \
            [os.path.join(_HERE, "..", "include", f) for f in ("b2p.h", "b2p_model_layout.h")]
 
 
 def build(force: bool = False, verbose: bool = False) -> str:
-    """Compile libb2p.so in-tree for sm_100a (nvcc cross-compiles without a GPU)."""
+    """Compile libb2p.so in-tree for sm_100a (nvcc cross-compiles without a GPU).  The translation units are
+    compiled in parallel (the fp32 and fp64 kernel instantiations dominate) and linked into one shared library."""
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(s) for s in sources()):
         return LIB_PATH
-    cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-o", LIB_PATH, os.path.join(CSRC, "b2p_api.cu")]
-    subprocess.check_call(cmd)
+    bdir = os.path.join(CSRC, "build")
+    os.makedirs(bdir, exist_ok=True)
+    procs, objs = [], []
+    for u in UNITS:
+        obj = os.path.join(bdir, u.replace(".cu", ".o"))
+        objs.append(obj)
+        cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, u)]
+        procs.append((cmd, subprocess.Popen(cmd)))
+    for cmd, p in procs:
+        if p.wait() != 0:
+            raise subprocess.CalledProcessError(p.returncode, cmd)
+    subprocess.check_call(["nvcc", "-gencode", "arch=compute_100a,code=sm_100a", "-shared", "-o", LIB_PATH] + objs)
     return LIB_PATH
 
 

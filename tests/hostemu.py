@@ -20,9 +20,8 @@ def lib():
     global _lib
     if _lib is None:
         so = os.path.join(ROOT, "tests", "_hostemu", "libb2p_hostemu.so")
-        srcs = [os.path.join(ROOT, "tests", "hostemu", "b2p_hostemu.cpp"),
-                os.path.join(ROOT, "mujoco_robot_environments_b200", "csrc", "b2p_core.h"),
-                os.path.join(ROOT, "mujoco_robot_environments_b200", "csrc", "b2p_model.h")]
+        csrc = os.path.join(ROOT, "mujoco_robot_environments_b200", "csrc")
+        srcs = [os.path.join(ROOT, "tests", "hostemu", "b2p_hostemu.cpp")] + [os.path.join(csrc, f) for f in sorted(os.listdir(csrc)) if f.endswith(".h")]
         if not os.path.exists(so) or os.path.getmtime(so) < max(os.path.getmtime(s) for s in srcs):
             os.makedirs(os.path.dirname(so), exist_ok=True)
             subprocess.check_call(["g++", "-O2", "-std=c++17", "-fPIC", "-shared", "-ffp-contract=off", "-o", so, srcs[0]])
