@@ -10,7 +10,7 @@ struct CObj { const T* pos; const T* mat; const T* size; const T* vert; int type
 // support point in world direction dir (|dir| = 1), inflated by margin/2.  Meshes: hill climbing over the
 // hull graph with warm start inside one query (what MuJoCo does for meshes with a graph).
 template <typename T>
-B2P_HD void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
+B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
   T ld[3], lp[3];
   mulmtv(ld, o.mat, dir);
   if (o.type == B2P_GEOM_BOX) {
@@ -273,9 +273,29 @@ B2P_HDN int box_box(const T* p1, const T* m1, const T* s1, const T* p2, const T*
   return cnt;
 }
 
+// oriented-bounding-box test along the 6 face normals: true when the boxes (centre c, half extents h in the geom frame)
+// are more than md apart along one of them.  Hull vertices lie inside their box, so this never drops a real contact.
+template <typename T>
+B2P_HD bool obb_separated(const T* p1, const T* m1, const T* c1, const T* h1, const T* p2, const T* m2, const T* c2, const T* h2, T md) {
+  T w1[3], w2[3], t[3], R[9];
+  mulmv(w1, m1, c1); mulmv(w2, m2, c2);
+  for (int k = 0; k < 3; k++) t[k] = (p2[k] + w2[k]) - (p1[k] + w1[k]);
+  for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) R[3 * i + j] = fabs(m1[i] * m2[j] + m1[3 + i] * m2[3 + j] + m1[6 + i] * m2[6 + j]);
+  const T slack = md + T(1e-6);
+  for (int i = 0; i < 3; i++) {
+    const T ti = t[0] * m1[i] + t[1] * m1[3 + i] + t[2] * m1[6 + i];
+    if (fabs(ti) > h1[i] + h2[0] * R[3 * i] + h2[1] * R[3 * i + 1] + h2[2] * R[3 * i + 2] + slack) return true;
+  }
+  for (int j = 0; j < 3; j++) {
+    const T tj = t[0] * m2[j] + t[1] * m2[3 + j] + t[2] * m2[6 + j];
+    if (fabs(tj) > h2[j] + h1[0] * R[j] + h1[1] * R[3 + j] + h1[2] * R[6 + j] + slack) return true;
+  }
+  return false;
+}
+
 // broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
 template <typename T>
-B2P_HD void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
+B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
   if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
   for (int q = c.tid; q < m.ngeom; q += c.nt) {
     const int p = m.geom_prop[q];
@@ -294,7 +314,13 @@ B2P_HD void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
         if (m.geom_type[g1] == B2P_GEOM_PLANE) {
           T nrm[3] = {s.gmat[g1][2], s.gmat[g1][5], s.gmat[g1][8]};
           flag = (m.geom_type[g2] == B2P_GEOM_BOX) && !(dot3(dif, nrm) - s.grbound[g2] > md);
-        } else flag = !(norm3(dif) > s.grbound[g1] + s.grbound[g2] + md);
+        } else {
+          flag = !(norm3(dif) > s.grbound[g1] + s.grbound[g2] + md);
+          if (flag) {   // second filter: the geoms' oriented bounding boxes along their 6 face normals (conservative, so exact)
+            const T* h1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+            flag = !obb_separated(s.gpos[g1], s.gmat[g1], m.geom_aabb_c[g1], h1, s.gpos[g2], s.gmat[g2], m.geom_aabb_c[g2], h2, md);
+          }
+        }
       }
     }
     int tot; const int ofs = block_scan(c, flag, tot);
@@ -339,7 +365,7 @@ B2P_HD void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       if (k >= MAXCON) break;
       const PairParam<T>& pp = g.pair_param[p];
       s.c_dist[k] = raw.dist[i]; cp3(s.c_pos[k], raw.pos[i]); cp3(s.c_frame[k], raw.normal); make_frame(s.c_frame[k]);
-      s.c_pair[k] = (short)p; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k][0] = pp.friction[0]; s.c_fric[k][1] = pp.friction[0]; s.c_row[k] = -1;
+      s.c_pair[k] = (short)p; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k] = pp.friction[0]; s.c_row[k] = -1;
     }
     cbase += tot;
   }

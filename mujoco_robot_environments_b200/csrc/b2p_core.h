@@ -33,7 +33,7 @@ B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   bsync(c);
 }
 template <typename T>
-B2P_HD void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
+B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
   forward_sweep(m, s, c);
   backward_sweep(m, s, c);
   dynamics_terms(m, s, c);
@@ -41,19 +41,22 @@ B2P_HD void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, cons
   make_rows(m, g, s, c);
 }
 template <typename T>
-B2P_HD void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree) {
+B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree) {
   actuation_and_smooth(m, s, c);
   solve_constraints(m, s, c);
-  if (c.tid == 0) {
-    for (int d = 0; d < m.nv; d++) { if (!(fabs(s.qacc[d]) < T(1e10))) s.flags |= FLAG_BADQACC; if (!(fabs(s.qvel[d]) < T(1e10))) s.flags |= FLAG_BADQVEL; }
-    for (int d = 0; d < m.nq; d++) if (!(fabs(s.qpos[d]) < T(1e10))) s.flags |= FLAG_BADQPOS;
+  {   // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
+    unsigned bad = 0;
+    for (int d = c.tid; d < m.nv; d += c.nt) { if (!(fabs(s.qacc[d]) < T(1e10))) bad |= FLAG_BADQACC; if (!(fabs(s.qvel[d]) < T(1e10))) bad |= FLAG_BADQVEL; }
+    for (int d = c.tid; d < m.nq; d += c.nt) if (!(fabs(s.qpos[d]) < T(1e10))) bad |= FLAG_BADQPOS;
+    bad = block_or(c, bad);
+    if (c.tid == 0 && bad) s.flags |= (int)bad;
   }
   if (do_integrate) integrate(m, s, c, freeze_tree);
   else bsync(c);
 }
 
 template <typename T>
-B2P_HD void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, const Ctx& c, T* o) {
+B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, const Ctx& c, T* o) {
   typedef OutLayout L;
   for (int i = c.tid; i < 6; i += c.nt) o[L::SITE_XPOS + i] = s.site_xpos[i / 3][i % 3];
   for (int i = c.tid; i < 18; i += c.nt) o[L::SITE_XMAT + i] = s.site_xmat[i / 9][i % 9];

@@ -5,7 +5,7 @@ namespace b2p {
 
 // ------------------------------------------------------------------------------------------ mj_kinematics + comPos + comVel + rne (forward sweep)
 template <typename T>
-B2P_HD void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   if (c.tid == 0) {
     for (int k = 0; k < 3; k++) s.xpos[0][k] = 0;
     s.xquat[0][0] = 1; s.xquat[0][1] = 0; s.xquat[0][2] = 0; s.xquat[0][3] = 0;
@@ -27,15 +27,16 @@ B2P_HD void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       for (int k = 0; k < 3; k++) pos[k] += s.xpos[p][k];
       mulquat(quat, s.xquat[p], m.tb_quat[b]);
       T mat[9]; quat2mat(mat, quat);
+      T xanchor[3], xaxis[3];
       mulmv(a, mat, m.jnt_pos[d]);
-      for (int k = 0; k < 3; k++) s.xanchor[d][k] = pos[k] + a[k];
-      mulmv(s.xaxis[d], mat, m.jnt_axis[d]);
+      for (int k = 0; k < 3; k++) xanchor[k] = pos[k] + a[k];
+      mulmv(xaxis, mat, m.jnt_axis[d]);
       const T ang = s.qpos[d] - m.qpos0[d], sn = sin(T(0.5) * ang);
       T qloc[4] = {cos(T(0.5) * ang), sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
       mulquat(quat, quat, qloc); normquat(quat);
       quat2mat(mat, quat);
       mulmv(a, mat, m.jnt_pos[d]);
-      for (int k = 0; k < 3; k++) { pos[k] = s.xanchor[d][k] - a[k]; s.xpos[b][k] = pos[k]; }
+      for (int k = 0; k < 3; k++) { pos[k] = xanchor[k] - a[k]; s.xpos[b][k] = pos[k]; }
       for (int k = 0; k < 4; k++) s.xquat[b][k] = quat[k];
       for (int k = 0; k < 9; k++) s.xmat[b][k] = mat[k];
       // inertia about the fixed reference point, motion axis
@@ -43,21 +44,23 @@ B2P_HD void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       mulmv(xipos, mat, m.tb_ipos[b]);
       for (int k = 0; k < 3; k++) off[k] = pos[k] + xipos[k] - m.ref[k];
       mulquat(qi, quat, m.tb_iquat[b]); quat2mat(ximat, qi);
-      inert_com(s.cinert[b], m.tb_inertia[b], ximat, off, m.tb_mass[b]);
-      for (int k = 0; k < 10; k++) s.crb[b][k] = s.cinert[b][k];
+      T cinert[10];
+      inert_com(cinert, m.tb_inertia[b], ximat, off, m.tb_mass[b]);
+      for (int k = 0; k < 10; k++) s.crb[b][k] = cinert[k];
       T* cd = s.cdof[d];
-      cp3(cd, s.xaxis[d]);
-      for (int k = 0; k < 3; k++) off[k] = m.ref[k] - s.xanchor[d][k];
-      cross3(cd + 3, s.xaxis[d], off);
+      cp3(cd, xaxis);
+      for (int k = 0; k < 3; k++) off[k] = m.ref[k] - xanchor[k];
+      cross3(cd + 3, xaxis, off);
       // velocity: cdof_dot = cvel_parent x cdof ; cvel = cvel_parent + cdof*qvel
       T v[6];
       for (int k = 0; k < 6; k++) v[k] = s.cvel[p][k];
-      cross_motion(s.cdof_dot[d], v, cd);
+      T cdof_dot[6];
+      cross_motion(cdof_dot, v, cd);
       for (int k = 0; k < 6; k++) { v[k] += cd[k] * s.qvel[d]; s.cvel[b][k] = v[k]; }
       // rne forward: cacc = cacc_parent + cdof_dot*qvel ; cfrc = I*cacc + cvel x* (I*cvel)
       T acc[6], Ia[6], Iv[6], cf[6];
-      for (int k = 0; k < 6; k++) { acc[k] = s.cacc[p][k] + s.cdof_dot[d][k] * s.qvel[d]; s.cacc[b][k] = acc[k]; }
-      mul_inert_vec(Ia, s.cinert[b], acc); mul_inert_vec(Iv, s.cinert[b], v); cross_force(cf, v, Iv);
+      for (int k = 0; k < 6; k++) { acc[k] = s.cacc[p][k] + cdof_dot[k] * s.qvel[d]; s.cacc[b][k] = acc[k]; }
+      mul_inert_vec(Ia, cinert, acc); mul_inert_vec(Iv, cinert, v); cross_force(cf, v, Iv);
       for (int k = 0; k < 6; k++) s.cfrc[b][k] = Ia[k] + cf[k];
     }
     bsync(c);
@@ -100,7 +103,7 @@ B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
 
 // mass matrix (tree block dense, props diagonal), bias forces, passive forces
 template <typename T>
-B2P_HD void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   const int n = m.ntd;
   for (int e = c.tid; e < n * n; e += c.nt) {
     const int i = e / n, j = e % n;
@@ -112,7 +115,7 @@ B2P_HD void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       if (i == j) v += m.dof_armature[i];
     }
     s.Marm[i * MAXTD + j] = v; s.Marm[j * MAXTD + i] = v;
-    s.Larm[i * MAXTD + j] = v; s.Larm[j * MAXTD + i] = v;
+    s.Larm[tri_idx(i, j)] = v;
   }
   for (int d = c.tid; d < m.nv; d += c.nt) {
     if (d < n) {
@@ -133,12 +136,12 @@ B2P_HD void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
     }
   }
   bsync(c);
-  block_cholesky(s.Larm, n, MAXTD, c);
+  sp_cholesky(s.Larm, m.sp_tree, m.tri, c);
 }
 
 // ------------------------------------------------------------------------------------------ actuation + smooth acceleration
 template <typename T>
-B2P_HD void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) s.qfrc_act[d] = 0;
   bsync(c);
   if (c.tid == 0) {
@@ -161,41 +164,24 @@ B2P_HD void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx&
     s.qacc_smooth[d] = d < m.ntd ? f : f / s.Mdiag[d];
   }
   bsync(c);
-  warp_chol_solve(s.Larm, m.ntd, MAXTD, s.qacc_smooth, c);
-  bsync(c);
+  sp_solve(s.Larm, m.sp_tree, s.qacc_smooth, 0, m.ntd, c);
 }
 
 // ------------------------------------------------------------------------------------------ integrator (mj_implicit / mj_Euler + mj_advance)
 template <typename T>
-B2P_HD void integrate(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool freeze_tree) {
+B2P_HDN void integrate(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool freeze_tree) {
   const int n = m.ntd; const T h = m.timestep;
-  for (int e = c.tid; e < n * n; e += c.nt) {
-    const int i = e / n, j = e % n;
-    T v = s.Marm[i * MAXTD + j];
-    if (i == j) {
-      v += h * m.dof_damping[i];
-      if (m.integrator == B2P_INT_IMPLICITFAST)
-        for (int a = 0; a < m.nu; a++) if (m.act_bias[a][2] != 0) for (int x = 0; x < m.act_trnnum[a]; x++) if (m.act_trndof[a][x] == i) v -= h * m.act_trncoef[a][x] * m.act_trncoef[a][x] * m.act_bias[a][2];
-    } else if (m.integrator == B2P_INT_IMPLICITFAST) {
-      // off-diagonal actuator terms only inside M's (ancestor) sparsity pattern
-      const int hi = i > j ? i : j, lo = i > j ? j : i;
-      if (m.anc_mask[hi + 1] & (1u << lo))
-        for (int a = 0; a < m.nu; a++) if (m.act_bias[a][2] != 0 && m.act_trnnum[a] == 2) {
-          const int d0 = m.act_trndof[a][0], d1 = m.act_trndof[a][1];
-          if ((d0 == i && d1 == j) || (d0 == j && d1 == i)) v -= h * m.act_trncoef[a][0] * m.act_trncoef[a][1] * m.act_bias[a][2];
-        }
-    }
-    s.H[i * MAXNV + j] = v;
-  }
+  // M - h * d(qfrc_passive + qfrc_actuator)/d(qvel): the velocity-derivative part is a model constant (joint damping
+  // on the diagonal; for implicitfast the affine actuator's -bias_vel * moment' moment inside M's sparsity), built on the host
+  for (int e = c.tid; e < (n * (n + 1)) / 2; e += c.nt) { const unsigned t = m.tri[e]; s.H[e] = s.Marm[(t >> 8) * MAXTD + (t & 255u)] + m.impl_hD[e]; }
   for (int d = c.tid; d < m.nv; d += c.nt) {
     bool active = d < n || s.pactive[(d - n) / 6];
     const T f = active ? s.qfrc_smooth[d] + s.qfrc_con[d] : T(0);
     s.tmpv[d] = d < n ? f : f / s.Mdiag[d];
   }
   bsync(c);
-  block_cholesky(s.H, n, MAXNV, c);
-  warp_chol_solve(s.H, n, MAXNV, s.tmpv, c);
-  bsync(c);
+  sp_cholesky(s.H, m.sp_tree, m.tri, c);
+  sp_solve(s.H, m.sp_tree, s.tmpv, 0, n, c);
   for (int d = c.tid; d < m.nv; d += c.nt) { s.qvel[d] += h * s.tmpv[d]; s.qacc_ws[d] = s.qacc[d]; }
   bsync(c);
   for (int d = c.tid; d < n; d += c.nt) s.qpos[d] += h * s.qvel[d];

@@ -1,55 +1,166 @@
+// Warp-level block-sparse Cholesky on packed lower-triangular storage.
+//
+// The Newton Hessian H = M + J' W J of a rearrangement scene is block structured: one dense tree block (arm +
+// gripper, <= 15 dofs) and one 6x6 block per free prop, coupled only where a constraint row touches two blocks
+// (gripper pad <-> prop, prop <-> prop).  At rest on the table every prop block is decoupled, so factoring the
+// dense 39x39 matrix would waste ~10x the work.  Solver order puts the props FIRST and the tree LAST, so
+// eliminating a prop never creates fill between the tree and an unrelated prop.
+//
+// SpStruct lists, per block, the rows that are structurally non-zero below its diagonal (own rows, then the rows of
+// later coupled blocks) and the columns of earlier coupled blocks; the factorisation, the triangular solves and
+// the Hessian assembly all walk those lists, one lane per matrix element, with a __syncwarp() between phases.
 #pragma once
 #include "b2p_scratch.h"
 
 namespace b2p {
 
-// dense Cholesky (lower, in place) of an n x n matrix with leading dimension ld; block-parallel
-template <typename T>
-B2P_HD void block_cholesky(T* A, int n, int ld, const Ctx& c) {
-  for (int k = 0; k < n; k++) {
-    T d = A[k * ld + k];
-    d = d > Num<T>::minval() ? sqrt(d) : sqrt(Num<T>::minval());
-    bsync(c);   // everyone has read the pivot before it is overwritten
-    for (int i = k + c.tid; i < n; i += c.nt) A[i * ld + k] = (i == k) ? d : A[i * ld + k] / d;
-    bsync(c);
-    const int rem = n - k - 1, cnt = rem * (rem + 1) / 2;
-    for (int e = c.tid; e < cnt; e += c.nt) {      // e -> (i >= j) in the trailing block
-      int i = (int)((sqrt(T(8) * e + 1) - 1) * T(0.5));
-      while ((i + 1) * (i + 2) / 2 <= e) i++;
-      while (i * (i + 1) / 2 > e) i--;
-      const int j = e - i * (i + 1) / 2, ii = k + 1 + i, jj = k + 1 + j;
-      A[ii * ld + jj] -= A[ii * ld + k] * A[jj * ld + k];
+B2P_HD int tri_idx(int i, int j) { return ((i * (i + 1)) >> 1) + j; }   // i >= j
+
+// dof index of solver index u (props first, tree last); np6 = 6 * nprop for the full system, 0 for tree-only
+B2P_HD int sp_dof(int u, int np6, int ntd) { return u < np6 ? ntd + u : u - np6; }
+
+// fill-in closure + list construction from the direct coupling bits (cpl[b] = mask of LATER blocks coupled to b).
+// Block ids here are solver blocks: 0..np-1 props, np = tree.  Executed redundantly by every lane, result in smem.
+B2P_HD void sp_build(SpStruct& st, int nprop, int ntd, unsigned direct_pairs, const Ctx& c) {
+  // direct_pairs bit (i * SP_MAXBLK + j), i > j  <=>  blocks i and j share a constraint row
+  if (c.tid == 0) {
+    const int nb = nprop + 1;
+    unsigned char later[SP_MAXBLK];
+    for (int b = 0; b < nb; b++) { later[b] = 0; for (int i = b + 1; i < nb; i++) if (direct_pairs & (1u << (i * SP_MAXBLK + b))) later[b] |= (unsigned char)(1u << i); }
+    for (int b = 0; b < nb; b++)       // eliminating b couples every pair of its later neighbours
+      for (int i = b + 1; i < nb; i++) if (later[b] & (1u << i)) later[i] |= (unsigned char)(later[b] & ~((2u << i) - 1u));
+    st.nblk = nb;
+    for (int b = 0; b < nb; b++) {
+      const int start = b < nprop ? 6 * b : 6 * nprop, len = b < nprop ? 6 : ntd;
+      int n = 0;
+      for (int k = 0; k < len; k++) st.rows[b][n++] = (unsigned char)(start + k);
+      for (int i = b + 1; i < nb; i++) if (later[b] & (1u << i)) {
+        const int s2 = i < nprop ? 6 * i : 6 * nprop, l2 = i < nprop ? 6 : ntd;
+        for (int k = 0; k < l2; k++) st.rows[b][n++] = (unsigned char)(s2 + k);
+      }
+      int np = 0;
+      for (int j = 0; j < b; j++) if (later[j] & (1u << b)) for (int k = 0; k < 6; k++) st.prev[b][np++] = (unsigned char)(6 * j + k);
+      st.blk[b].start = (unsigned char)start; st.blk[b].len = (unsigned char)len; st.blk[b].nrows = (unsigned char)n; st.blk[b].nprev = (unsigned char)np;
+      st.later[b] = later[b];
     }
-    bsync(c);
   }
+  bsync(c);
 }
-// x <- (L L')^-1 x  by the first warp (others idle); caller syncs afterwards
-template <typename T>
-B2P_HD void warp_chol_solve(const T* L, int n, int ld, T* x, const Ctx& c) {
-#ifdef __CUDA_ARCH__
-  if (c.tid < 32) {
-    const int lane = c.tid;
-    for (int k = 0; k < n; k++) {
-      const T xk = x[k] / L[k * ld + k];
-      __syncwarp();
-      if (lane == 0) x[k] = xk;
-      for (int i = k + 1 + lane; i < n; i += 32) x[i] -= L[i * ld + k] * xk;
-      __syncwarp();
-    }
-    for (int k = n - 1; k >= 0; k--) {
-      const T xk = x[k] / L[k * ld + k];
-      __syncwarp();
-      if (lane == 0) x[k] = xk;
-      for (int i = lane; i < k; i += 32) x[i] -= L[k * ld + i] * xk;
-      __syncwarp();
-    }
+// dense single-block structure (tree-only systems: M and M - h*dF/dv)
+B2P_HD void sp_build_dense(SpStruct& st, int n, const Ctx& c) {
+  if (c.tid == 0) {
+    st.nblk = 1; st.later[0] = 0;
+    for (int k = 0; k < n; k++) st.rows[0][k] = (unsigned char)k;
+    st.blk[0].start = 0; st.blk[0].len = (unsigned char)n; st.blk[0].nrows = (unsigned char)n; st.blk[0].nprev = 0;
   }
-#else
-  (void)c;
-  for (int k = 0; k < n; k++) { const T xk = x[k] / L[k * ld + k]; x[k] = xk; for (int i = k + 1; i < n; i++) x[i] -= L[i * ld + k] * xk; }
-  for (int k = n - 1; k >= 0; k--) { const T xk = x[k] / L[k * ld + k]; x[k] = xk; for (int i = 0; i < k; i++) x[i] -= L[k * ld + i] * xk; }
-#endif
+  bsync(c);
+}
+B2P_HD bool sp_coupled(const SpStruct& st, int bi, int bj) { return bi == bj || ((st.later[bj] >> bi) & 1u); }   // bi >= bj
+
+// a block that is coupled to nothing (a prop resting on the table) is factored / solved by ONE lane in registers
+B2P_HD bool sp_local(const SpStruct& st, int b) { return st.blk[b].len == 6 && st.blk[b].nrows == 6 && st.blk[b].nprev == 0; }
+template <typename T>
+B2P_HD void chol6_local(T* A, int s0) {
+  T a[21];
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = 0; j <= i; j++) a[(i * (i + 1)) / 2 + j] = A[tri_idx(s0 + i, s0 + j)];
+#pragma unroll
+  for (int k = 0; k < 6; k++) {
+    T d = a[(k * (k + 1)) / 2 + k];
+    d = d > Num<T>::minval() ? sqrt(d) : sqrt(Num<T>::minval());
+    const T id = 1 / d;
+    a[(k * (k + 1)) / 2 + k] = d;
+#pragma unroll
+    for (int i = k + 1; i < 6; i++) a[(i * (i + 1)) / 2 + k] *= id;
+#pragma unroll
+    for (int i = k + 1; i < 6; i++)
+#pragma unroll
+      for (int j = k + 1; j <= i; j++) a[(i * (i + 1)) / 2 + j] -= a[(i * (i + 1)) / 2 + k] * a[(j * (j + 1)) / 2 + k];
+  }
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = 0; j <= i; j++) A[tri_idx(s0 + i, s0 + j)] = a[(i * (i + 1)) / 2 + j];
+}
+template <typename T>
+B2P_HD void solve6_local(const T* L, int s0, T* x) {   // x = 6 consecutive reals
+  T l[21], y[6];
+#pragma unroll
+  for (int i = 0; i < 6; i++)
+#pragma unroll
+    for (int j = 0; j <= i; j++) l[(i * (i + 1)) / 2 + j] = L[tri_idx(s0 + i, s0 + j)];
+#pragma unroll
+  for (int i = 0; i < 6; i++) { T v = x[i];
+#pragma unroll
+    for (int j = 0; j < i; j++) v -= l[(i * (i + 1)) / 2 + j] * y[j];
+    y[i] = v / l[(i * (i + 1)) / 2 + i]; }
+#pragma unroll
+  for (int i = 5; i >= 0; i--) { T v = y[i];
+#pragma unroll
+    for (int j = i + 1; j < 6; j++) v -= l[(j * (j + 1)) / 2 + i] * y[j];
+    y[i] = v / l[(i * (i + 1)) / 2 + i]; }
+#pragma unroll
+  for (int i = 0; i < 6; i++) x[i] = y[i];
 }
 
+// in-place A = L L' on the packed lower triangle, restricted to the structure.  tri[e] = (a << 8) | c enumerates
+// the pairs a >= c of a triangular index e (host-built table in DevModel).
+template <typename T>
+B2P_HDN void sp_cholesky(T* A, const SpStruct& st, const unsigned short* tri, const Ctx& c) {
+  for (int b = c.tid; b < st.nblk; b += c.nt) if (sp_local(st, b)) chol6_local(A, st.blk[b].start);
+  for (int b = 0; b < st.nblk; b++) {
+    if (sp_local(st, b)) continue;
+    const int start = st.blk[b].start, len = st.blk[b].len, nrows = st.blk[b].nrows;
+    for (int kk = 0; kk < len; kk++) {
+      const int k = start + kk, R = nrows - kk - 1, kb = tri_idx(k, 0);
+      const unsigned char* lst = st.rows[b] + kk + 1;
+      T d = A[kb + k];
+      d = d > Num<T>::minval() ? sqrt(d) : sqrt(Num<T>::minval());
+      const T id = 1 / d;
+      bsync(c);                                     // every lane has read the pivot
+      if (c.tid == 0) A[kb + k] = d;
+      for (int a = c.tid; a < R; a += c.nt) { const int i = lst[a]; A[tri_idx(i, k)] *= id; }
+      bsync(c);
+      const int cnt = (R * (R + 1)) >> 1;
+      for (int e = c.tid; e < cnt; e += c.nt) {
+        const unsigned t = tri[e]; const int i = lst[t >> 8], j = lst[t & 255u];
+        A[tri_idx(i, j)] -= A[tri_idx(i, k)] * A[tri_idx(j, k)];
+      }
+      bsync(c);
+    }
+  }
+}
+// x <- (L L')^-1 x ; x is indexed by dof through sp_dof(u, np6, ntd)
+template <typename T>
+B2P_HDN void sp_solve(const T* L, const SpStruct& st, T* x, int np6, int ntd, const Ctx& c) {
+  for (int b = c.tid; b < st.nblk; b += c.nt) if (sp_local(st, b)) solve6_local(L, st.blk[b].start, x + sp_dof(st.blk[b].start, np6, ntd));
+  for (int b = 0; b < st.nblk; b++) {
+    if (sp_local(st, b)) continue;
+    const int start = st.blk[b].start, len = st.blk[b].len, nrows = st.blk[b].nrows;
+    for (int kk = 0; kk < len; kk++) {
+      const int k = start + kk, R = nrows - kk - 1, dk = sp_dof(k, np6, ntd);
+      const unsigned char* lst = st.rows[b] + kk + 1;
+      const T xk = x[dk] / L[tri_idx(k, k)];
+      bsync(c);
+      if (c.tid == 0) x[dk] = xk;
+      for (int a = c.tid; a < R; a += c.nt) { const int i = lst[a]; x[sp_dof(i, np6, ntd)] -= L[tri_idx(i, k)] * xk; }
+      bsync(c);
+    }
+  }
+  for (int b = st.nblk - 1; b >= 0; b--) {
+    if (sp_local(st, b)) continue;
+    const int start = st.blk[b].start, len = st.blk[b].len, np = st.blk[b].nprev;
+    for (int kk = len - 1; kk >= 0; kk--) {
+      const int k = start + kk, dk = sp_dof(k, np6, ntd), kb = tri_idx(k, 0);
+      const T xk = x[dk] / L[kb + k];
+      bsync(c);
+      if (c.tid == 0) x[dk] = xk;
+      for (int a = c.tid; a < np + kk; a += c.nt) { const int j = a < np ? st.prev[b][a] : start + (a - np); x[sp_dof(j, np6, ntd)] -= L[kb + j] * xk; }
+      bsync(c);
+    }
+  }
+}
 
 }  // namespace b2p

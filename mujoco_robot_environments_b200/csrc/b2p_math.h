@@ -57,6 +57,38 @@ B2P_HD int block_scan(const Ctx& c, int v, int& total, int* /*unused*/ = nullptr
   (void)c; total = v; return 0;
 #endif
 }
+// minimum of an int over the warp
+B2P_HD int block_min(const Ctx& c, int v) {
+#ifdef __CUDA_ARCH__
+  (void)c;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) { const int y = __shfl_xor_sync(0xffffffffu, v, o); v = y < v ? y : v; }
+#else
+  (void)c;
+#endif
+  return v;
+}
+// bitwise OR of an unsigned over the warp
+B2P_HD unsigned block_or(const Ctx& c, unsigned v) {
+#ifdef __CUDA_ARCH__
+  (void)c;
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v |= __shfl_xor_sync(0xffffffffu, v, o);
+#else
+  (void)c;
+#endif
+  return v;
+}
+// rank of this lane among the lanes whose flag is set (lane order); total = number of set flags
+B2P_HD int block_rank(const Ctx& c, bool flag, int& total) {
+#ifdef __CUDA_ARCH__
+  const unsigned b = __ballot_sync(0xffffffffu, flag);
+  total = __popc(b);
+  return __popc(b & ((1u << c.tid) - 1u));
+#else
+  (void)c; total = flag ? 1 : 0; return 0;
+#endif
+}
 // OR of a per-lane predicate over the warp
 B2P_HD bool warp_any(const Ctx& c, bool p) {
 #ifdef __CUDA_ARCH__

@@ -30,8 +30,19 @@ constexpr int MAXEQ = 4;
 constexpr int MAXU = 8;
 constexpr int MAXLEVEL = 12;
 constexpr int PROP_BODY0 = MAXTB;
-constexpr int JW = MAXTD - 1 + 6; // 21: compressed Jacobian row width (15 tree slots + 6 prop slots)
-constexpr int SEGB = MAXTD - 1;   // 15: first slot of segment B
+constexpr int JPOOL = 2304;      // reals of packed constraint Jacobian per env
+constexpr int SP_MAXBLK = 1 + MAXP;                  // solver blocks: props, then the tree
+constexpr int HPACK = (MAXNV * (MAXNV + 1)) / 2;     // packed lower triangle of the Newton Hessian
+constexpr int MPACK = (MAXTD * (MAXTD + 1)) / 2;     // packed lower triangle of the tree mass matrix
+constexpr int TRI_N = ((MAXNV - 1) * MAXNV) / 2;     // pairs a >= c with a < MAXNV - 1 ... enumerated by DevModel::tri
+
+// block-sparsity structure of a symmetric matrix in solver order (see b2p_linalg.h)
+struct SpBlock { unsigned char start, len, nrows, nprev; };
+struct SpStruct {
+  int nblk; SpBlock blk[SP_MAXBLK]; unsigned char later[8];
+  unsigned char rows[SP_MAXBLK][MAXNV];      // own rows, then rows of later coupled blocks (ascending)
+  unsigned char prev[SP_MAXBLK][6 * MAXP];   // columns of earlier coupled blocks (ascending)
+};
 
 template <typename T>
 struct PairParam {               // per candidate geom pair, mixed contact parameters (App. B item 10)
@@ -57,6 +68,7 @@ struct alignas(16) DevModel {
   // geoms
   int geom_type[MAXG], geom_body[MAXG], geom_vertadr[MAXG], geom_vertnum[MAXG], geom_prop[MAXG];
   T geom_size[MAXG][3], geom_pos[MAXG][3], geom_quat[MAXG][4], geom_rbound[MAXG], geom_invweight0[MAXG][2];
+  T geom_aabb_c[MAXG][3];        // centre of the geom-frame bounding box (half extents = geom_size for boxes AND meshes)
   // sites: 0 attachment_site, 1 pinch
   T site_pos[2][3], site_quat[2][4];
   // equality
@@ -67,6 +79,9 @@ struct alignas(16) DevModel {
   T act_trncoef[MAXU][2], act_gain[MAXU], act_bias[MAXU][3], act_ctrlrange[MAXU][2], act_forcerange[MAXU][2];
   // OSC configuration (config/robots/arm/controller_config/osc.yaml)
   T osc_gains[6], osc_null[7], osc_pos_thresh, osc_ori_thresh;
+  // linear-algebra tables: tri[e] = (a << 8) | c for the e-th pair a >= c ; dense structure of the tree block
+  unsigned short tri[TRI_N + 3]; SpStruct sp_tree;
+  T impl_hD[MPACK];             // packed lower triangle of -h * d(qfrc_passive + qfrc_actuator)/d(qvel) (integrator matrix = M + impl_hD)
 };
 
 // ------------------------------------------------------------------------------------------ host builder
@@ -149,6 +164,8 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     m.geom_vertadr[g] = gm[g] >= 0 ? vadr[gm[g]] : 0; m.geom_vertnum[g] = gm[g] >= 0 ? vnum[gm[g]] : 0;
     cp(m.geom_size[g], b.D(B2PM_F_GEOM_SIZE) + 3 * g, 3); cp(m.geom_pos[g], b.D(B2PM_F_GEOM_POS) + 3 * g, 3); cp(m.geom_quat[g], b.D(B2PM_F_GEOM_QUAT) + 4 * g, 4);
     m.geom_rbound[g] = b.D(B2PM_F_GEOM_RBOUND)[g]; cp(m.geom_invweight0[g], b.D(B2PM_F_GEOM_INVWEIGHT0) + 2 * g, 2);
+    cp(m.geom_aabb_c[g], b.D(B2PM_F_GEOM_AABB) + 6 * g, 3);
+    if (gt[g] == B2P_GEOM_MESH) for (int k = 0; k < 3; k++) if (std::fabs(b.D(B2PM_F_GEOM_AABB)[6 * g + 3 + k] - m.geom_size[g][k]) > 1e-9) return "mesh geom_size must equal its bounding-box half extents";
   }
   const int sid[2] = {b.C(B2PM_C_SITE_ATTACHMENT), b.C(B2PM_C_SITE_PINCH)};
   for (int s = 0; s < 2; s++) {
@@ -171,6 +188,21 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   }
   const double g6[6] = {350, 20, 500, 100, 200, 30}, q0[7] = {0, -0.785, 0, -2.356, 0, 1.571, 0.785};
   cp(m.osc_gains, g6, 6); cp(m.osc_null, q0, 7); m.osc_pos_thresh = 5e-3; m.osc_ori_thresh = 68e-3;
+  { int e = 0; for (int a = 0; a < MAXNV - 1; a++) for (int cc = 0; cc <= a; cc++) m.tri[e++] = (unsigned short)((a << 8) | cc); }
+  m.sp_tree.nblk = 1; m.sp_tree.blk[0].start = 0; m.sp_tree.blk[0].len = (unsigned char)ntd; m.sp_tree.blk[0].nrows = (unsigned char)ntd; m.sp_tree.blk[0].nprev = 0;
+  for (int k = 0; k < ntd; k++) m.sp_tree.rows[0][k] = (unsigned char)k;
+  {   // integrator matrix correction (App. B item 15): Euler = h*damping on the diagonal; implicitfast adds the affine actuator's
+      // velocity term -h * bias_vel * coef_i * coef_j wherever (i, j) lies inside M's (ancestor) sparsity pattern
+    const double h = m.timestep;
+    for (int i = 0; i < ntd; i++) for (int j = 0; j <= i; j++) {
+      double v = 0;
+      if (i == j) v += h * m.dof_damping[i];
+      if (m.integrator == B2P_INT_IMPLICITFAST && (i == j || (m.anc_mask[i + 1] & (1u << j))))
+        for (int a = 0; a < m.nu; a++) if (m.act_bias[a][2] != 0) for (int x = 0; x < m.act_trnnum[a]; x++) for (int y = 0; y < m.act_trnnum[a]; y++)
+          if (m.act_trndof[a][x] == i && m.act_trndof[a][y] == j) v -= h * m.act_trncoef[a][x] * m.act_trncoef[a][y] * m.act_bias[a][2];
+      m.impl_hD[(i * (i + 1)) / 2 + j] = v;
+    }
+  }
   // global tables
   ht.mesh_vert.assign(b.D(B2PM_F_MESH_VERT), b.D(B2PM_F_MESH_VERT) + b.n(B2PM_F_MESH_VERT));
   ht.mesh_nbradr.assign(b.I(B2PM_F_MESH_NBRADR), b.I(B2PM_F_MESH_NBRADR) + b.n(B2PM_F_MESH_NBRADR));
@@ -219,11 +251,11 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
   CR(jnt_pos); CR(jnt_axis); CR(jnt_stiffness); CR(jnt_range); CR(jnt_margin); CR(jnt_solref); CR(jnt_solimp); CR(qpos0); CR(qpos_spring);
   CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass);
   CI(geom_type); CI(geom_body); CI(geom_vertadr); CI(geom_vertnum); CI(geom_prop);
-  CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(site_pos); CR(site_quat);
+  CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(geom_aabb_c); CR(site_pos); CR(site_quat);
   CI(eq_type); CI(eq_obj1); CI(eq_obj2); CR(eq_data); CR(eq_solref); CR(eq_solimp);
   CI(act_trnnum); CI(act_trndof); CI(act_ctrllimited); CI(act_forcelimited);
   CR(act_trncoef); CR(act_gain); CR(act_bias); CR(act_ctrlrange); CR(act_forcerange);
-  CR(osc_gains); CR(osc_null); CR(osc_pos_thresh); CR(osc_ori_thresh);
+  CR(osc_gains); CR(osc_null); CR(osc_pos_thresh); CR(osc_ori_thresh); CI(tri); CI(sp_tree); CR(impl_hD);
 #undef CI
 #undef CR
 }

@@ -1,5 +1,5 @@
 #pragma once
-#include "b2p_scratch.h"
+#include "b2p_linalg.h"
 
 namespace b2p {
 
@@ -47,39 +47,62 @@ B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0,
   }
 }
 template <typename T>
-B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s, int r) {
-  T v = 0; const int a = s.row_a[r], b = s.row_b[r];
-  if (a >= 0) { const int st = block_start(m, a), n = a == 0 ? m.ntd : 6; for (int k = 0; k < n; k++) v += s.J[r][k] * s.qvel[st + k]; }
-  if (b >= 0) { const int st = block_start(m, b); for (int k = 0; k < 6; k++) v += s.J[r][SEGB + k] * s.qvel[st + k]; }
-  return v;
-}
-template <typename T>
 B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
-  T v = 0; const int a = s.row_a[r], b = s.row_b[r];
-  if (a >= 0) { const int st = block_start(m, a), n = a == 0 ? m.ntd : 6; for (int k = 0; k < n; k++) v += s.J[r][k] * x[st + k]; }
-  if (b >= 0) { const int st = block_start(m, b); for (int k = 0; k < 6; k++) v += s.J[r][SEGB + k] * x[st + k]; }
+  const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a);
+  const T* j = s.Jp + s.joff[r];
+  T v = 0;
+  for (int k = 0; k < wa; k++) v += j[k] * x[sa + k];
+  if (b >= 0) { const int sb = block_start(m, b); for (int k = 0; k < 6; k++) v += j[wa + k] * x[sb + k]; }
   return v;
 }
+template <typename T> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s, int r) { return row_dot(m, s, r, s.qvel); }
 
-// mj_makeConstraint + mj_referenceConstraint: equality -> limits -> contacts, rows complete incl. aref
+// mj_makeConstraint + mj_referenceConstraint: equality -> limits -> contacts, rows complete incl. aref.
+// One lane builds one item (an equality, a joint limit side, or a contact = 3 rows); row numbers and packed-Jacobian
+// offsets come from warp prefix sums, so the row order is deterministic and identical to MuJoCo's.  The same pass
+// records, per dof block, which items touch it (brow lists) and which blocks share a row (cpl_pairs) -- the sparsity
+// the Newton solver exploits.
 template <typename T>
-B2P_HD void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
-  const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon;
-  int base = 0;
+B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
+  const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
+  int base = 0, jbase = 0, first_drop = MAXEFC + 1; unsigned pairs = 0;
+  int nb[SP_MAXBLK];
+  for (int b = 0; b < SP_MAXBLK; b++) nb[b] = 0;
   for (int i0 = 0; i0 < nitem; i0 += c.nt) {
-    const int it = i0 + c.tid; int nr = 0, kind = -1, id = 0; T dist = 0;
+    const int it = i0 + c.tid; int nr = 0, kind = -1, id = 0, ba = 0, bb = -1, seg1 = 0, seg2 = 0; T dist = 0;
     if (it < nitem) {
       if (it < m.neq) { kind = ROW_EQ; id = it; nr = m.eq_type[it] == B2P_EQ_CONNECT ? 3 : 1; }
       else if (it < m.neq + nlim) {
         const int j = (it - m.neq) >> 1, side = ((it - m.neq) & 1) ? 1 : -1;
         if (m.jnt_limited[j]) { dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]); if (dist < m.jnt_margin[j]) { kind = ROW_LIMIT; id = j * 2 + (side > 0); nr = 1; } }
-      } else { id = it - m.neq - nlim; if (s.c_dist[id] < s.c_incl[id]) { kind = ROW_CONTACT; nr = 3; } }
+      } else {
+        id = it - m.neq - nlim;
+        if (s.c_dist[id] < s.c_incl[id]) {
+          kind = ROW_CONTACT; nr = 3;
+          // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
+          const int p = s.c_pair[id], b1 = m.geom_body[g.pair_g1[p]], b2 = m.geom_body[g.pair_g2[p]];
+          const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
+          ba = (t1 || t2) ? 0 : -1;
+          if (b1 >= PROP_BODY0) { if (ba < 0) ba = 1 + b1 - PROP_BODY0; else { bb = 1 + b1 - PROP_BODY0; seg1 = block_width(m, ba); } }
+          if (b2 >= PROP_BODY0) { if (ba < 0) ba = 1 + b2 - PROP_BODY0; else { bb = 1 + b2 - PROP_BODY0; seg2 = block_width(m, ba); } }
+          if (ba < 0) { kind = -1; nr = 0; }     // static-static pairs never reach here (filtered at compile time)
+        }
+      }
     }
-    int tot; const int ofs = block_scan(c, nr, tot);
-    int r0 = base + ofs;
-    if (nr > 0 && r0 + nr > MAXEFC) { nr = 0; if (kind == ROW_CONTACT) s.c_row[id] = -1; s.flags |= FLAG_EFCFULL; }
+    const int w = nr > 0 ? block_width(m, ba) + (bb >= 0 ? 6 : 0) : 0;
+    int tot, jtot; const int ofs = block_scan(c, nr, tot), jofs = block_scan(c, nr * w, jtot);
+    const int r0 = base + ofs, j0 = jbase + jofs;
+    if (nr > 0 && (r0 + nr > MAXEFC || j0 + nr * w > JPOOL)) {   // dropped items always form a suffix (offsets include dropped ones)
+      if (r0 < first_drop) first_drop = r0;
+      if (kind == ROW_CONTACT) s.c_row[id] = -1;
+      s.flags |= FLAG_EFCFULL; nr = 0;
+    }
     if (nr > 0) {
-      for (int q = 0; q < nr; q++) { for (int k = 0; k < JW; k++) s.J[r0 + q][k] = 0; s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_b[r0 + q] = -1; s.row_a[r0 + q] = 0; }
+      for (int q = 0; q < nr; q++) {
+        s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb; s.joff[r0 + q] = (short)(j0 + q * w);
+      }
+      T* J0 = s.Jp + j0;
+      for (int k = 0; k < nr * w; k++) J0[k] = 0;
       if (kind == ROW_EQ && nr == 3) {
         const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];
         mulmv(g1, s.xmat[b1], m.eq_data[id]); mulmv(g2, s.xmat[b2], m.eq_data[id] + 3);
@@ -87,52 +110,57 @@ B2P_HD void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, 
         const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
         for (int q = 0; q < 3; q++) {
           T ax[3] = {T(q == 0), T(q == 1), T(q == 2)};
-          add_jac(m, s, s.J[r0 + q], 0, b1, g1, ax, T(1)); add_jac(m, s, s.J[r0 + q], 0, b2, g2, ax, T(-1));
+          add_jac(m, s, J0 + q * w, 0, b1, g1, ax, T(1)); add_jac(m, s, J0 + q * w, 0, b2, g2, ax, T(-1));
           T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
           s.D[r0 + q] = 1 / R; s.aref[r0 + q] = -B * row_vel(m, s, r0 + q) - K * imp * res[q];
         }
       } else if (kind == ROW_EQ) {
         const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
         const T x = s.qpos[j2] - m.qpos0[j2], pos = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
-        s.J[r0][j1] = 1; s.J[r0][j2] = -cf[1];
+        J0[j1] = 1; J0[j2] = -cf[1];
         T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], pos, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
         s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * pos;
       } else if (kind == ROW_LIMIT) {
         const int j = id >> 1, side = (id & 1) ? 1 : -1;
-        s.J[r0][j] = T(-side);
+        J0[j] = T(-side);
         T K, B, imp, R; row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
         s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * (dist - m.jnt_margin[j]);
       } else {
         const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
         const PairParam<T>& pp = g.pair_param[p];
-        // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
-        int ba = -1, bb = -1, seg1 = 0, seg2 = 0;
-        const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
-        if (t1 || t2) ba = 0;
-        if (b1 >= PROP_BODY0) { if (ba < 0) { ba = 1 + b1 - PROP_BODY0; seg1 = 0; } else { bb = 1 + b1 - PROP_BODY0; seg1 = SEGB; } }
-        if (b2 >= PROP_BODY0) { if (ba < 0) { ba = 1 + b2 - PROP_BODY0; seg2 = 0; } else { bb = 1 + b2 - PROP_BODY0; seg2 = SEGB; } }
-        T iw1[2], iw2[2];
-        for (int k = 0; k < 2; k++) { iw1[k] = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][k] : m.geom_invweight0[g1][k]; iw2[k] = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][k] : m.geom_invweight0[g2][k]; }
-        const T tran = iw1[0] + iw2[0];
+        const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
         T K, B, imp, R0;
-        row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], tran, false, K, B, imp, R0);
+        row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
         const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
-        s.c_mu[id] = s.c_fric[id][0] * sqrt(R1 / R0); s.c_row[id] = (short)r0;
+        s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0); s.c_row[id] = (short)r0;
         for (int q = 0; q < 3; q++) {
-          s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
           const T* ax = s.c_frame[id] + 3 * q;
-          add_jac(m, s, s.J[r0 + q], seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, s.J[r0 + q], seg1, b1, s.c_pos[id], ax, T(-1));
+          add_jac(m, s, J0 + q * w, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0 + q * w, seg1, b1, s.c_pos[id], ax, T(-1));
           const T vel = row_vel(m, s, r0 + q);
           if (q == 0) { s.D[r0] = 1 / R0; s.aref[r0] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
           else { s.D[r0 + q] = 1 / R1; s.aref[r0 + q] = -B * vel; }
         }
       }
+      if (bb >= 0) {   // solver blocks: prop p -> p, tree -> nprop
+        const int sa = ba == 0 ? m.nprop : ba - 1, sb = bb - 1, hi = sa > sb ? sa : sb, lo = sa > sb ? sb : sa;
+        pairs |= 1u << (hi * SP_MAXBLK + lo);
+      }
     }
-    base += tot;
+    for (int b = 0; b < nblk; b++) {   // per-block item lists, in row order
+      int nt; const bool f = nr > 0 && (ba == b || bb == b); const int rk = block_rank(c, f, nt);
+      if (f) { if (b == 0) s.brow0[nb[0] + rk] = (unsigned char)r0; else s.browp[b - 1][nb[b] + rk] = (unsigned char)r0; }
+      nb[b] += nt;
+    }
+    base += tot; jbase += jtot;
   }
-  if (c.tid == 0) s.nefc = base < MAXEFC ? base : MAXEFC;
+  first_drop = block_min(c, first_drop);
+  pairs = block_or(c, pairs);
+  if (c.tid == 0) {
+    s.nefc = base < first_drop ? base : first_drop; s.jused = jbase; s.cpl_pairs = pairs;
+    for (int b = 0; b < SP_MAXBLK; b++) s.nbrow[b] = nb[b];
+  }
   bsync(c);
+  sp_build(s.sp, m.nprop, m.ntd, pairs, c);
 }
-
 
 }  // namespace b2p

@@ -18,27 +18,31 @@ struct alignas(16) Scratch {
   T qpos[MAXNQ], qvel[MAXNV], qacc_ws[MAXNV], time, rec_pad[REC_SIZE - (MAXNQ + 2 * MAXNV + 1)], ctrl[MAXU];
   // per-env prop parameters
   T psize[MAXP][3], pinertia[MAXP][3], pinvw[MAXP][2]; int pactive[MAXP];
-  // tree
-  T xpos[MAXTB][3], xquat[MAXTB][4], xmat[MAXTB][9], xanchor[MAXTD][3], xaxis[MAXTD][3];
-  T cinert[MAXTB][10], crb[MAXTB][10], cdof[MAXTD][6], cdof_dot[MAXTD][6], cvel[MAXTB][6], cacc[MAXTB][6], cfrc[MAXTB][6];
+  // tree (spatial quantities about the fixed reference point m.ref)
+  T xpos[MAXTB][3], xquat[MAXTB][4], xmat[MAXTB][9];
+  T crb[MAXTB][10], cdof[MAXTD][6], cvel[MAXTB][6], cacc[MAXTB][6], cfrc[MAXTB][6];
   T ppos[MAXP][3], pmat[MAXP][9];
   T gpos[MAXG][3], gmat[MAXG][9], grbound[MAXG], site_xpos[2][3], site_xmat[2][9];
-  // dynamics
-  T Marm[MAXTD * MAXTD], Larm[MAXTD * MAXTD], Mdiag[MAXNV];
+  // dynamics: tree mass matrix dense (OSC, M*x) + packed Cholesky factor; props diagonal
+  T Marm[MAXTD * MAXTD], Larm[MPACK], Mdiag[MAXNV];
   T qfrc_bias[MAXNV], qfrc_passive[MAXNV], qfrc_act[MAXNV], qfrc_smooth[MAXNV], qacc_smooth[MAXNV], qacc[MAXNV], qfrc_con[MAXNV];
   T act_force[MAXU];
   // contacts
-  int ncand, ncon, nefc, flags, niter;
+  int ncand, ncon, nefc, flags, niter, jused, nmpr; unsigned cpl_pairs;
   short cand[MAXCAND];
-  T c_dist[MAXCON], c_pos[MAXCON][3], c_frame[MAXCON][9], c_mu[MAXCON], c_fric[MAXCON][2], c_incl[MAXCON];
+  T c_dist[MAXCON], c_pos[MAXCON][3], c_frame[MAXCON][9], c_mu[MAXCON], c_fric[MAXCON], c_incl[MAXCON];
   short c_pair[MAXCON], c_row[MAXCON];
-  // constraint rows (compressed Jacobian: slots 0..14 segment A, 15..20 segment B)
-  T J[MAXEFC][JW], D[MAXEFC], aref[MAXEFC], Jaref[MAXEFC], Jv[MAXEFC], force[MAXEFC];
+  // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
+  // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
+  T Jp[JPOOL], D[MAXEFC], aref[MAXEFC], Jaref[MAXEFC], Jv[MAXEFC], force[MAXEFC];
   signed char row_a[MAXEFC], row_b[MAXEFC], row_type[MAXEFC], row_state[MAXEFC];
-  short row_id[MAXEFC];
+  short row_id[MAXEFC], joff[MAXEFC];
   T cW[MAXCON][6];               // per-contact 3x3 symmetric Hessian weight (xx,yy,zz,xy,xz,yz) in row space
-  // solver
-  T H[MAXNV * MAXNV], grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV];
+  // per-block row lists (block 0 = tree, 1+p = prop p): first row of every item (eq/limit row, or contact triple)
+  unsigned char brow0[MAXEFC], browp[MAXP][MAXCON]; int nbrow[SP_MAXBLK];
+  // solver: packed lower-triangular Hessian in solver order (props first, tree last) + its sparsity structure
+  SpStruct sp;
+  T H[HPACK], grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV];
   // settle / frozen-arm support
   T hold_q[MAXTD], hold_v[MAXTD];
 };
@@ -46,13 +50,15 @@ struct alignas(16) Scratch {
 // block id of a dof: 0 = tree, 1+p = prop p
 template <typename T> B2P_HD int dof_block(const DevModel<T>& m, int d) { return d < m.ntd ? 0 : 1 + (d - m.ntd) / 6; }
 template <typename T> B2P_HD int block_start(const DevModel<T>& m, int blk) { return blk == 0 ? 0 : m.ntd + 6 * (blk - 1); }
-// slot of dof d inside row r, or -1
-template <typename T> B2P_HD int row_slot(const DevModel<T>& m, const Scratch<T>& s, int r, int d) {
-  int blk = dof_block(m, d), a = s.row_a[r], b = s.row_b[r];
-  if (a == blk) return d - block_start(m, blk);
-  if (b == blk) return SEGB + d - block_start(m, blk);
-  return -1;
+template <typename T> B2P_HD int block_width(const DevModel<T>& m, int blk) { return blk == 0 ? m.ntd : 6; }
+// pointer to the slots of block `blk` inside row r, or nullptr when the row does not touch the block
+template <typename T> B2P_HD const T* row_seg(const DevModel<T>& m, const Scratch<T>& s, int r, int blk) {
+  const int a = s.row_a[r];
+  if (a == blk) return s.Jp + s.joff[r];
+  if (s.row_b[r] == blk) return s.Jp + s.joff[r] + block_width(m, a);
+  return nullptr;
 }
+template <typename T> B2P_HD const unsigned char* block_rows(const Scratch<T>& s, int blk) { return blk == 0 ? s.brow0 : s.browp[blk - 1]; }
 
 // HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
 // launch parameters shared by kernel and host emulation

@@ -14,7 +14,7 @@ B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, c
 }
 // per-item (rows of eq/limit, whole contacts) force/state/cost from s.Jaref; returns this thread's cost part
 template <typename T>
-B2P_HD T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess) {
+B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess) {
   T cost = 0;
   for (int r = c.tid; r < s.nefc; r += c.nt) {
     const int tp = s.row_type[r];
@@ -26,7 +26,7 @@ B2P_HD T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bo
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
-    const T mu = s.c_mu[k], f1 = s.c_fric[k][0], f2 = s.c_fric[k][1];
+    const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     const T j0 = s.Jaref[r], j1 = s.Jaref[r + 1], j2 = s.Jaref[r + 2];
     const T N = j0 * mu, U1 = j1 * f1, U2 = j2 * f2, Tt = sqrt(U1 * U1 + U2 * U2);
     T* W = s.cW[k];
@@ -52,50 +52,63 @@ B2P_HD T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bo
   }
   return cost;
 }
-// qfrc_con = J' force
+// qfrc_con = J' force: one lane per dof, walking only the items of the dof's block
 template <typename T>
-B2P_HD void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) {
+    const int blk = dof_block(m, d), o = d - block_start(m, blk), n = s.nbrow[blk];
+    const unsigned char* lst = block_rows(s, blk);
     T a = 0;
-    for (int r = 0; r < s.nefc; r++) { const T f = s.force[r]; if (f == 0) continue; const int sl = row_slot(m, s, r, d); if (sl >= 0) a += s.J[r][sl] * f; }
+    for (int q = 0; q < n; q++) {
+      const int r = lst[q], tp = s.row_type[r], nr = (tp == ROW_CONTACT || (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT)) ? 3 : 1;
+      const T* seg = row_seg(m, s, r, blk);
+      const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
+      for (int k = 0; k < nr; k++) { const T f = s.force[r + k]; if (f != 0) a += seg[k * w + o] * f; }
+    }
     s.qfrc_con[d] = a;
   }
 }
-// H = M + J' W J (lower triangle, dense nv x nv with leading dimension MAXNV)
+// H = M + J' W J on the packed lower triangle in solver order (props first, tree last), only inside the block
+// structure s.sp: one lane per matrix element, walking the item list of the element's row block.
 template <typename T>
-B2P_HD void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
-  const int nv = m.nv, cnt = nv * (nv + 1) / 2;
-  for (int e = c.tid; e < cnt; e += c.nt) {
-    int i = (int)((sqrt(T(8) * e + 1) - 1) * T(0.5));
-    while ((i + 1) * (i + 2) / 2 <= e) i++;
-    while (i * (i + 1) / 2 > e) i--;
-    const int j = e - i * (i + 1) / 2;
-    const int bi = dof_block(m, i), bj = dof_block(m, j), oi = i - block_start(m, bi), oj = j - block_start(m, bj);
-    T h = 0;
-    if (bi == 0 && bj == 0) h = s.Marm[i * MAXTD + j]; else if (i == j) h = s.Mdiag[i];
-    for (int r = 0; r < s.nefc; r++) {
-      const int a = s.row_a[r], b = s.row_b[r];
-      const int si = a == bi ? oi : (b == bi ? SEGB + oi : -1);
-      if (si < 0) { if (s.row_type[r] == ROW_CONTACT) r += 2; continue; }
-      const int sj = a == bj ? oj : (b == bj ? SEGB + oj : -1);
-      if (sj < 0) { if (s.row_type[r] == ROW_CONTACT) r += 2; continue; }
-      if (s.row_type[r] != ROW_CONTACT) { if (s.row_state[r] == ST_QUADRATIC) h += s.D[r] * s.J[r][si] * s.J[r][sj]; }
-      else {
-        const int st = s.row_state[r];
-        if (st != ST_SATISFIED) {
-          const T* W = s.cW[s.row_id[r]];
-          const T a0 = s.J[r][si], a1 = s.J[r + 1][si], a2 = s.J[r + 2][si], b0 = s.J[r][sj], b1 = s.J[r + 1][sj], b2 = s.J[r + 2][sj];
-          h += W[0] * a0 * b0 + W[1] * a1 * b1 + W[2] * a2 * b2 + W[3] * (a0 * b1 + a1 * b0) + W[4] * (a0 * b2 + a2 * b0) + W[5] * (a1 * b2 + a2 * b1);
+B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  const int np = m.nprop, np6 = 6 * np, ntd = m.ntd;
+  for (int sbi = 0; sbi <= np; sbi++) for (int sbj = 0; sbj <= sbi; sbj++) {
+    if (!sp_coupled(s.sp, sbi, sbj)) continue;
+    const int bi = sbi == np ? 0 : sbi + 1, bj = sbj == np ? 0 : sbj + 1;      // dof blocks (0 = tree, 1+p = prop p)
+    const int ni = block_width(m, bi), nj = block_width(m, bj), ui0 = sbi == np ? np6 : 6 * sbi, uj0 = sbj == np ? np6 : 6 * sbj;
+    const int cnt = sbi == sbj ? (ni * (ni + 1)) >> 1 : ni * nj, n = s.nbrow[bi];
+    const unsigned char* lst = block_rows(s, bi);
+    for (int e = c.tid; e < cnt; e += c.nt) {
+      int oi, oj;
+      if (sbi == sbj) { const unsigned t = m.tri[e]; oi = t >> 8; oj = t & 255u; } else { oi = e / nj; oj = e - oi * nj; }
+      T h = 0;
+      if (sbi == sbj) h = bi == 0 ? s.Marm[oi * MAXTD + oj] : (oi == oj ? s.Mdiag[ntd + 6 * (bi - 1) + oi] : T(0));
+      for (int q = 0; q < n; q++) {
+        const int r = lst[q], tp = s.row_type[r];
+        const T* sj = bi == bj ? nullptr : row_seg(m, s, r, bj);
+        if (bi != bj && !sj) continue;
+        const T* si = row_seg(m, s, r, bi);
+        if (bi == bj) sj = si;
+        const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
+        if (tp == ROW_CONTACT) {
+          if (s.row_state[r] != ST_SATISFIED) {
+            const T* W = s.cW[s.row_id[r]];
+            const T a0 = si[oi], a1 = si[w + oi], a2 = si[2 * w + oi], b0 = sj[oj], b1 = sj[w + oj], b2 = sj[2 * w + oj];
+            h += W[0] * a0 * b0 + W[1] * a1 * b1 + W[2] * a2 * b2 + W[3] * (a0 * b1 + a1 * b0) + W[4] * (a0 * b2 + a2 * b0) + W[5] * (a1 * b2 + a2 * b1);
+          }
+        } else {
+          const int nr = (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1;
+          for (int k = 0; k < nr; k++) if (s.row_state[r + k] == ST_QUADRATIC) h += s.D[r + k] * si[k * w + oi] * sj[k * w + oj];
         }
-        r += 2;
       }
+      s.H[tri_idx(ui0 + oi, uj0 + oj)] = h;
     }
-    s.H[i * MAXNV + j] = h;
   }
 }
 template <typename T> struct LsPt { T alpha, cost, d1, d2; };
 template <typename T>
-B2P_HD LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, const T* qg) {
+B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, const T* qg) {
   T q0 = 0, q1 = 0, q2 = 0, ec = 0, e1 = 0, e2 = 0;
   for (int r = c.tid; r < s.nefc; r += c.nt) {
     const int tp = s.row_type[r];
@@ -106,7 +119,7 @@ B2P_HD LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, c
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
-    const T mu = s.c_mu[k], f1 = s.c_fric[k][0], f2 = s.c_fric[k][1];
+    const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     T t0 = 0, t1 = 0, t2 = 0;
     for (int q = 0; q < 3; q++) { const T D = s.D[r + q], j0 = s.Jaref[r + q], jv = s.Jv[r + q]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }
     const T U0 = s.Jaref[r] * mu, V0 = s.Jv[r] * mu, u1 = s.Jaref[r + 1] * f1, u2 = s.Jaref[r + 2] * f2, v1 = s.Jv[r + 1] * f1, v2 = s.Jv[r + 2] * f2;
@@ -132,7 +145,7 @@ B2P_HD LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, c
 }
 // Jaref = J*x - aref, Ma = M*x, returns total cost (all threads)
 template <typename T>
-B2P_HD T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x) {
+B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x) {
   for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] = row_dot(m, s, r, x) - s.aref[r];
   mul_M(m, s, s.Ma, x, c);
   bsync(c);
@@ -141,13 +154,12 @@ B2P_HD T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x) 
   block_sum(c, v);
   return v[0];
 }
-// cost, gradient, Hessian factor, Newton direction at s.qacc (s.Jaref / s.Ma consistent with it)
+// cost and gradient at s.qacc (s.Jaref / s.Ma consistent with it); also the per-contact cone Hessian weights
 template <typename T>
-B2P_HD T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2) {
+B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2) {
   T v[2] = {constraint_update(m, s, c, true), 0};
   bsync(c);
   mul_JT_force(m, s, c);
-  assemble_H(m, s, c);
   bsync(c);
   for (int d = c.tid; d < m.nv; d += c.nt) {
     const T gd = s.Ma[d] - s.qfrc_smooth[d] - s.qfrc_con[d];
@@ -155,14 +167,21 @@ B2P_HD T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gra
     v[0] += T(0.5) * (s.Ma[d] - s.qfrc_smooth[d]) * (s.qacc[d] - s.qacc_smooth[d]);
   }
   block_sum(c, v);
-  block_cholesky(s.H, m.nv, MAXNV, c);
-  warp_chol_solve(s.H, m.nv, MAXNV, s.Mgrad, c);
-  bsync(c);
   gradnorm2 = v[1];
   return v[0];
 }
+// Newton direction: search = -H^-1 grad with H = M + J' W J factored on its block structure
 template <typename T>
-B2P_HD T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale) {
+B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  assemble_H(m, s, c);
+  bsync(c);
+  sp_cholesky(s.H, s.sp, m.tri, c);
+  sp_solve(s.H, s.sp, s.Mgrad, 6 * m.nprop, m.ntd, c);
+  for (int d = c.tid; d < m.nv; d += c.nt) s.search[d] = -s.Mgrad[d];
+  bsync(c);
+}
+template <typename T>
+B2P_HDN T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale) {
   T v[4] = {0, 0, 0, 0};
   mul_M(m, s, s.Mv, s.search, c);
   for (int r = c.tid; r < s.nefc; r += c.nt) s.Jv[r] = row_dot(m, s, r, s.search);
@@ -200,7 +219,7 @@ B2P_HD T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale)
   return best.alpha;
 }
 template <typename T>
-B2P_HD void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   const int nv = m.nv;
   if (s.nefc == 0) {
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] = s.qacc_smooth[d]; s.qfrc_con[d] = 0; }
@@ -214,10 +233,11 @@ B2P_HD void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c)
   bsync(c);
   cost_at(m, s, c, s.qacc);
   T gn2, cost = solver_update(m, s, c, gn2);
-  for (int d = c.tid; d < nv; d += c.nt) s.search[d] = -s.Mgrad[d];
-  bsync(c);
   int it = 0;
+  // MuJoCo factors the Hessian before testing for termination; the factor at the converged point is never used, so the
+  // test comes first here (identical iterates, one factorisation less per step)
   for (; it < m.iterations; it++) {
+    newton_direction(m, s, c);
     const T alpha = line_search(m, s, c, scale);
     if (alpha == 0) break;
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] += alpha * s.search[d]; s.Ma[d] += alpha * s.Mv[d]; }
@@ -227,8 +247,6 @@ B2P_HD void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c)
     cost = solver_update(m, s, c, gn2);
     const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
     if (improvement < m.tolerance || gradient < m.tolerance) { it++; break; }
-    for (int d = c.tid; d < nv; d += c.nt) s.search[d] = -s.Mgrad[d];
-    bsync(c);
   }
   if (c.tid == 0) { s.niter = it; if (it >= m.iterations) s.flags |= FLAG_SOLVER_MAXITER; }
   bsync(c);

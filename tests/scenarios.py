@@ -90,3 +90,33 @@ def oracle_state(o):
     r[REC_QPOS:REC_QPOS + NQ] = o.qpos[:NQ]; r[REC_QVEL:REC_QVEL + NV] = o.qvel[:NV]
     r[REC_QACC:REC_QACC + NV] = o.qacc_warmstart[:NV]; r[REC_TIME] = o.time[0]
     return r
+
+
+def coupled_states(kind="grasp", seed=0):
+    """Scenes that exercise the coupled solver blocks (test infrastructure; uses the oracle as scene generator).
+    grasp: gripper pre-closed around prop 0 hovering between the pads (tree <-> prop rows, box-box pad contacts);
+    stack: prop 1 resting on prop 0 (prop <-> prop rows); grasp_stack: both (fill-in between the tree and prop 1)."""
+    from orc import Oracle
+    st, size, active = make_states(1, seed=seed, jitter=0.0)
+    active[0, :] = (1, 1, 1, 0)
+    o = Oracle(default_blob())
+    park = st.copy()
+    for p in range(NP):
+        park[0, 15 + 7 * p:15 + 7 * p + 3] = (5.0 + p, 5.0, 0.2)
+    oracle_load(o, park[0], size[0], np.zeros(NP, np.uint8)); o.set_option("full_contacts", 0)
+    o.step1(); bias = o.qfrc_bias[:7].copy()
+    pads = [18, 24]     # right_pad1, left_pad1 geoms (names.json)
+    for _ in range(1500):
+        o.ctrl[:7] = o.qfrc_bias[:7]; o.ctrl[7] = 255.0
+        o.step()
+        if abs(o.geom_xpos[pads[1]][0] - o.geom_xpos[pads[0]][0]) < 2 * 0.004 + 2 * size[0, 0, 0] + 0.004:
+            break
+    st[0, :15] = o.qpos[:15]; st[0, REC_QVEL:REC_QVEL + 15] = o.qvel[:15]
+    mid = 0.5 * (o.geom_xpos[pads[0]] + o.geom_xpos[pads[1]])
+    if kind in ("grasp", "grasp_stack"):
+        st[0, 15:18] = mid; st[0, 18:22] = (1, 0, 0, 0)
+    if kind == "stack":
+        st[0, 22:25] = st[0, 15:18] + (0, 0, 2 * size[0, 0, 2] - 1e-4); st[0, 25:29] = st[0, 18:22]
+    if kind == "grasp_stack":
+        st[0, 22:25] = mid + (0, 0, size[0, 0, 2] + size[0, 1, 2] - 1e-4); st[0, 25:29] = (1, 0, 0, 0)
+    return st, size, active

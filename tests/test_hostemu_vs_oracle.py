@@ -86,3 +86,24 @@ def test_settle(blob):
             break
     assert 300 < k < 2000 and k == r["steps_done"][0]
     assert np.abs(got[0, :sc.NQ] - o.qpos[:sc.NQ]).max() < 1e-9
+
+
+@pytest.mark.parametrize("kind", ["grasp", "stack", "grasp_stack"])
+@pytest.mark.parametrize("dtype,tol", [(np.float64, 1e-7), (np.float32, 5e-3)])
+def test_coupled_blocks(blob, kind, dtype, tol):
+    """Gripper squeezing a prop / stacked props: constraint rows couple the tree and prop blocks of the Newton Hessian
+    (block-sparse Cholesky with fill-in), checked step by step against the oracle's dense solve."""
+    st, size, active = sc.coupled_states(kind)
+    e = HostEmu(blob, dtype); o = Oracle(blob)
+    sc.oracle_load(o, st[0], size[0], active[0]); o.set_option("full_contacts", 0)
+    o.step1(); ctrl = np.zeros((1, sc.NU)); ctrl[0, :7] = o.qfrc_bias[:7]; ctrl[0, 7] = 255.0
+    got = st.astype(dtype); steps = 40
+    r = e.run(MODE_PHYSICS, got, n_steps=steps, ctrl=ctrl, prop_size=size, prop_active=active)
+    assert r["status"][0] == 0
+    o.ctrl[:] = ctrl[0]; ncoupled = 0
+    for _ in range(steps):
+        o.step()
+        ncoupled = max(ncoupled, o.dim("nefc"))
+    assert ncoupled > 7 + 12                      # more than equality + one resting prop: pads / stacked faces touch
+    assert np.abs(got[0, :sc.NQ] - o.qpos[:sc.NQ]).max() < tol
+    assert np.abs(got[0, sc.REC_QVEL:sc.REC_QVEL + sc.NV] - o.qvel[:sc.NV]).max() < 200 * tol

@@ -15,7 +15,7 @@ import subprocess
 import sys
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-CORE = os.path.join(ROOT, "mujoco_robot_environments_b200", "csrc", "b2p_core.h")
+CSRC = os.path.join(ROOT, "mujoco_robot_environments_b200", "csrc")
 RAW_KEYS = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "launch__registers_per_thread", "launch__grid_size",
             "launch__block_size", "launch__occupancy_limit_shared_mem", "launch__occupancy_limit_registers",
             "sm__warps_active.avg.pct_of_peak_sustained_active", "smsp__issue_active.avg.pct_of_peak_sustained_active",
@@ -33,13 +33,19 @@ def ncu_csv(rep, *args):
 
 
 def functions():
-    funcs = []
-    for i, l in enumerate(open(CORE).read().split("\n"), 1):
-        if "B2P_HD" in l and (l.startswith("B2P_HD") or l.startswith("template")):
-            m = re.search(r"(\w+)\(", l.split("B2P_HD", 1)[1])
-            if m:
-                funcs.append((i, m.group(1)))
-    return funcs
+    """{file: [(first line, function name), ...]} for every header of csrc/."""
+    out = {}
+    for f in os.listdir(CSRC):
+        if not f.endswith((".h", ".cuh")):
+            continue
+        funcs = []
+        for i, l in enumerate(open(os.path.join(CSRC, f)).read().split("\n"), 1):
+            if "B2P_HD" in l and (l.startswith("B2P_HD") or l.startswith("template")):
+                m = re.search(r"(\w+)\(", l.split("B2P_HD", 1)[1])
+                if m:
+                    funcs.append((i, m.group(1)))
+        out[f] = funcs
+    return out
 
 
 def main():
@@ -55,9 +61,9 @@ def main():
     src = ncu_csv(rep, "--page", "source", "--print-source", "cuda,sass")
     funcs = functions()
 
-    def fn(line):
-        name = "?"
-        for i, n in funcs:
+    def fn(f, line):
+        name = f
+        for i, n in funcs.get(f, []):
             if i <= line:
                 name = n
             else:
@@ -74,7 +80,7 @@ def main():
     ti, ts = sum(v[0] for v in agg.values()) or 1, sum(v[1] for v in agg.values()) or 1
     fa, fs = collections.Counter(), collections.Counter()
     for (f, l), (ni, ns, _) in agg.items():
-        k = fn(l) if f == "b2p_core.h" else f
+        k = fn(f, l)
         fa[k] += ni
         fs[k] += ns
     lines += ["", "warp instructions executed: %d   stall samples: %d" % (ti, ts), "", "by function (share of instructions / share of samples):"]
