@@ -33,26 +33,29 @@ B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   bsync(c);
 }
 template <typename T>
-B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
-  forward_sweep(m, s, c);
-  backward_sweep(m, s, c);
-  dynamics_terms(m, s, c);
-  collide(m, g, s, c, full_contacts);
-  make_rows(m, g, s, c);
+B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
+  csync(c);
+  if (active) { forward_sweep(m, s, c); backward_sweep(m, s, c); dynamics_terms(m, s, c); }
+  csync(c);
+  if (active) collide(m, g, s, c, full_contacts);
+  csync(c);
+  if (active) make_rows(m, g, s, c);
 }
 template <typename T>
-B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree) {
-  actuation_and_smooth(m, s, c);
-  solve_constraints(m, s, c);
-  {   // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
+B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
+  csync(c);
+  if (active) {
+    actuation_and_smooth(m, s, c);
+    solve_constraints(m, s, c);
+    // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
     unsigned bad = 0;
     for (int d = c.tid; d < m.nv; d += c.nt) { if (!(fabs(s.qacc[d]) < T(1e10))) bad |= FLAG_BADQACC; if (!(fabs(s.qvel[d]) < T(1e10))) bad |= FLAG_BADQVEL; }
     for (int d = c.tid; d < m.nq; d += c.nt) if (!(fabs(s.qpos[d]) < T(1e10))) bad |= FLAG_BADQPOS;
     bad = block_or(c, bad);
     if (c.tid == 0 && bad) s.flags |= (int)bad;
   }
-  if (do_integrate) integrate(m, s, c, freeze_tree);
-  else bsync(c);
+  csync(c);
+  if (active) { if (do_integrate) integrate(m, s, c, freeze_tree); else bsync(c); }
 }
 
 template <typename T>
@@ -77,62 +80,71 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
   for (int i = c.tid; i < MAXEFC; i += c.nt) o[L::EFC_FORCE + i] = i < s.nefc ? s.force[i] : T(0);
 }
 
-// One scene, whole launch: load the state record, run the requested mode, store the record.
+// One scene, whole launch: load the state record, run the requested mode, store the record.  `active` = this warp holds
+// a scene; an idle warp of a lockstep CTA still walks the same stage barriers.
 template <typename T>
-B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded) {
+B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded, bool active = true) {
   const int nv = m.nv;
-  T* rec = a.state + (size_t)env * a.state_stride;
-  if (!state_preloaded) {   // the CUDA kernel stages the record with one TMA bulk copy instead
-    T* head = s.qpos;
-    for (int i = c.tid; i < REC_SIZE; i += c.nt) head[i] = rec[i];
-  }
-  for (int i = c.tid; i < MAXP * 3; i += c.nt) s.psize[i / 3][i % 3] = a.prop_size ? a.prop_size[(size_t)env * MAXP * 3 + i] : m.geom_size[0][0];
-  for (int i = c.tid; i < MAXP; i += c.nt) s.pactive[i] = i < m.nprop ? (a.prop_active ? a.prop_active[(size_t)env * MAXP + i] : 1) : 0;
-  for (int i = c.tid; i < MAXU; i += c.nt) s.ctrl[i] = (a.ctrl && i < m.nu) ? a.ctrl[(size_t)env * m.nu + i] : T(0);
-  if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; }
-  bsync(c);
-  if (!a.prop_size) {   // default: sizes from the model's prop geoms
-    for (int g0 = c.tid; g0 < m.ngeom; g0 += c.nt) if (m.geom_prop[g0] >= 0) for (int k = 0; k < 3; k++) s.psize[m.geom_prop[g0]][k] = m.geom_size[g0][k];
+  T* rec = a.state + (size_t)(active ? env : 0) * a.state_stride;
+  if (active) {
+    if (!state_preloaded) {   // the CUDA kernel stages the record with one TMA bulk copy instead
+      T* head = s.qpos;
+      for (int i = c.tid; i < REC_SIZE; i += c.nt) head[i] = rec[i];
+    }
+    for (int i = c.tid; i < MAXP * 3; i += c.nt) s.psize[i / 3][i % 3] = a.prop_size ? a.prop_size[(size_t)env * MAXP * 3 + i] : m.geom_size[0][0];
+    for (int i = c.tid; i < MAXP; i += c.nt) s.pactive[i] = i < m.nprop ? (a.prop_active ? a.prop_active[(size_t)env * MAXP + i] : 1) : 0;
+    for (int i = c.tid; i < MAXU; i += c.nt) s.ctrl[i] = (a.ctrl && i < m.nu) ? a.ctrl[(size_t)env * m.nu + i] : T(0);
+    if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; }
     bsync(c);
+    if (!a.prop_size) {   // default: sizes from the model's prop geoms
+      for (int g0 = c.tid; g0 < m.ngeom; g0 += c.nt) if (m.geom_prop[g0] >= 0) for (int k = 0; k < 3; k++) s.psize[m.geom_prop[g0]][k] = m.geom_size[g0][k];
+      bsync(c);
+    }
+    prop_params(m, s, c);
   }
-  prop_params(m, s, c);
   const bool full = a.full_contacts != 0;
   if (a.mode == MODE_FORWARD) {
-    step1(m, g, s, c, full);
-    step2(m, s, c, false, false);
+    step1(m, g, s, c, full, active);
+    step2(m, s, c, false, false, active);
   } else if (a.mode == MODE_PHYSICS) {
-    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full); step2(m, s, c, true, false); }
-    step1(m, g, s, c, full);   // leave derived quantities consistent with the final state (dm_control legacy step order)
+    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2(m, s, c, true, false, active); }
+    step1(m, g, s, c, full, active);   // leave derived quantities consistent with the final state (dm_control legacy step order)
   } else if (a.mode == MODE_OSC) {
     // RobotArm.run_controller (robot_arm.py:61-94): per tick OSC torque + gripper command, control_steps x physics.step()
     T tg[13];
-    for (int i = 0; i < 13; i++) tg[i] = a.target[(size_t)env * 13 + i];
-    const bool grip = a.grip ? a.grip[env] != 0 : false;
+    for (int i = 0; i < 13; i++) tg[i] = active ? a.target[(size_t)env * 13 + i] : T(0);
+    const bool grip = (active && a.grip) ? a.grip[env] != 0 : false;
     bool conv = false;
-    step1(m, g, s, c, full);
+    step1(m, g, s, c, full, active);
     for (int t = 0; t < a.n_steps; t++) {
-      if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }   // min_max.py:14-19
-      bsync(c);
-      for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false); step1(m, g, s, c, full); }
-      if (osc_converged(m, s, tg)) conv = true;
+      csync(c);
+      if (active) {
+        if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }   // min_max.py:14-19
+        bsync(c);
+      }
+      for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); step1(m, g, s, c, full, active); }
+      if (active && osc_converged(m, s, tg)) conv = true;
     }
-    if (c.tid == 0 && a.converged) a.converged[env] = conv ? 1 : 0;
+    if (active && c.tid == 0 && a.converged) a.converged[env] = conv ? 1 : 0;
   } else if (a.mode == MODE_SETTLE) {
     // PropPlacer settle loop (prop_initializer.py:245-257): arm + gripper held static, per-env early exit
-    for (int d = c.tid; d < m.ntd; d += c.nt) { s.hold_q[d] = s.qpos[d]; s.hold_v[d] = s.qvel[d]; }
-    bsync(c);
-    int done = 0;
+    if (active) { for (int d = c.tid; d < m.ntd; d += c.nt) { s.hold_q[d] = s.qpos[d]; s.hold_v[d] = s.qvel[d]; } bsync(c); }
+    int done = 0; bool fin = !active;
     for (int k = 0; k < a.n_steps; k++) {
-      step1(m, g, s, c, full); step2(m, s, c, true, true);
-      done = k + 1;
-      T mx[2] = {0, 0};   // max |qvel|, |qacc| over ACTIVE prop dofs: computed redundantly by every thread (nv is tiny)
-      for (int d = m.ntd; d < nv; d++) if (s.pactive[(d - m.ntd) / 6]) { const T v = fabs(s.qvel[d]), ac = fabs(s.qacc[d]); if (v > mx[0]) mx[0] = v; if (ac > mx[1]) mx[1] = ac; }
-      bsync(c);
-      if (mx[0] < a.settle_qvel_tol && mx[1] < a.settle_qacc_tol && done > a.settle_min_steps) break;
+      if (csync_and(c, fin)) break;
+      step1(m, g, s, c, full, !fin); step2(m, s, c, true, true, !fin);
+      if (!fin) {
+        done = k + 1;
+        T mx[2] = {0, 0};   // max |qvel|, |qacc| over ACTIVE prop dofs: computed redundantly by every lane (nv is tiny)
+        for (int d = m.ntd; d < nv; d++) if (s.pactive[(d - m.ntd) / 6]) { const T v = fabs(s.qvel[d]), ac = fabs(s.qacc[d]); if (v > mx[0]) mx[0] = v; if (ac > mx[1]) mx[1] = ac; }
+        bsync(c);
+        if (mx[0] < a.settle_qvel_tol && mx[1] < a.settle_qacc_tol && done > a.settle_min_steps) fin = true;
+      }
     }
-    step1(m, g, s, c, full);
-    if (c.tid == 0 && a.steps_done) a.steps_done[env] = done;
+    step1(m, g, s, c, full, active);
+    if (active && c.tid == 0 && a.steps_done) a.steps_done[env] = done;
   }
+  if (!active) return;
   bsync(c);
   if (!state_preloaded) { const T* head = s.qpos; for (int i = c.tid; i < REC_SIZE; i += c.nt) rec[i] = head[i]; }
   if (c.tid == 0 && a.status) a.status[env] |= s.flags;

@@ -60,7 +60,7 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
   static_assert(offsetof(Scratch<T>, qpos) == 0 && sizeof(Scratch<T>) % 16 == 0, "state record must head a 16-byte aligned Scratch");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const Ctx c = {lane, 32};
+  const Ctx c = {lane, 32, a.lockstep != 0};
   if (threadIdx.x == 0) {
     for (int i = 0; i <= KernelCfg<T>::kWarps; i++) mbar_init(&sm.bar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -71,19 +71,23 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   Scratch<T>& s = sm.scratch[warp];
   unsigned long long* bar = &sm.bar[1 + warp];
   unsigned phase = 0;
-  for (;;) {
+  for (;;) {   // one round = one scene per warp; in lockstep mode the CTA's warps walk the round's stages together
     int env = 0;
-    if (lane == 0) env = atomicAdd(next_env, 1);
+    if (lane == 0) { do { env = atomicAdd(next_env, 1); } while (env < a.n_env && a.env_mask && !a.env_mask[env]); }
     env = __shfl_sync(0xffffffffu, env, 0);
-    if (env >= a.n_env) break;
-    if (a.env_mask && !a.env_mask[env]) continue;
-    T* rec = a.state + (size_t)env * a.state_stride;
-    if (lane == 0) { fence_async_smem(); mbar_expect_tx(bar, kRecBytes); tma_load_1d(s.qpos, rec, kRecBytes, bar); }
-    mbar_wait(bar, phase); phase ^= 1;
-    run_env(sm.model, g, s, a, env, c, true);
-    __syncwarp();
-    if (lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }
-    __syncwarp();
+    const bool active = env < a.n_env;
+    if (c.lock ? !__syncthreads_or(active) : !active) break;
+    T* rec = a.state + (size_t)(active ? env : 0) * a.state_stride;
+    if (active) {
+      if (lane == 0) { fence_async_smem(); mbar_expect_tx(bar, kRecBytes); tma_load_1d(s.qpos, rec, kRecBytes, bar); }
+      mbar_wait(bar, phase); phase ^= 1;
+    }
+    run_env(sm.model, g, s, a, env, c, true, active);
+    if (active) {
+      __syncwarp();
+      if (lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }
+      __syncwarp();
+    }
   }
 }
 

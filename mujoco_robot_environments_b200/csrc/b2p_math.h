@@ -16,7 +16,7 @@ enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3 };
 
-struct Ctx { int tid, nt; };
+struct Ctx { int tid, nt; bool lock; };   // lock: the CTA's warps advance stage by stage together (shared instruction stream)
 
 template <typename T> struct Num;
 template <> struct Num<double> { static B2P_HD double eps() { return 2.220446049250313e-16; } static B2P_HD double minval() { return 1e-15; } static B2P_HD double big() { return 1e300; } };
@@ -28,6 +28,23 @@ template <> struct Num<float> { static B2P_HD float eps() { return 1.1920929e-7f
 B2P_HD void bsync(const Ctx&) {
 #ifdef __CUDA_ARCH__
   __syncwarp();
+#endif
+}
+// CTA-wide stage barrier, only in lockstep mode: the warps of a CTA (one scene each) enter every pipeline stage
+// together so that they share instruction-cache lines -- the per-step code is ~10x the SM's 32 KB L1.5 I-cache.
+// Every warp of the CTA must reach every csync(), whether or not it holds a scene.
+B2P_HD void csync(const Ctx& c) {
+#ifdef __CUDA_ARCH__
+  if (c.lock) __syncthreads();
+#else
+  (void)c;
+#endif
+}
+B2P_HD bool csync_and(const Ctx& c, bool p) {
+#ifdef __CUDA_ARCH__
+  return c.lock ? (__syncthreads_and(p) != 0) : p;
+#else
+  (void)c; return p;
 #endif
 }
 // deterministic warp-wide sum of K values (xor butterfly: every lane ends with the same bits)
