@@ -116,6 +116,11 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     const bool grip = (active && a.grip) ? a.grip[env] != 0 : false;
     bool conv = false;
     step1(m, g, s, c, full, active);
+    if (a.n_steps == 0 && active) {   // OSC.compute_control_output() / is_converged() for the current state, no stepping (derived-output CTRL)
+      if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }
+      bsync(c);
+      conv = osc_converged(m, s, tg);
+    }
     for (int t = 0; t < a.n_steps; t++) {
       csync(c);
       if (active) {

@@ -1,0 +1,277 @@
+"""BatchedRearrangementEnv: the reference's ``RearrangementEnv`` reset/step API with a leading scene dimension.
+
+Reference behaviour mirrored (mujoco_robot_environments/tasks/rearrangement.py):
+  * constructor  :54-210   scene = arena + table + FER/Robotiq2F85 + N props (N, sizes sampled per scene, props.py:277-291,604-617)
+  * ``reset()``  :297-337  physics.reset, arm -> home, PropPlacer (environment/prop_initializer.py:164-283), RobotArm, eef_home_pose
+  * ``step()``   :339-356  alternates scripted ``pick`` (:358-401) and ``place`` (:403-440): 5 x (set_target, run_controller)
+The env batch is heterogeneous: every scene is padded to ``model.nprop`` props; props a scene does not
+have are parked away from the table with collisions and dynamics disabled.
+
+Camera observations of the reference come from ``mujoco.Renderer`` (OpenGL): unavailable on this box.  The observation
+returned here is the state a policy / data generator can be computed from (poses), see ``_compute_observation``.
+"""
+from __future__ import annotations
+
+import collections
+import enum
+import math
+from typing import Any, Dict, Iterable, Optional
+
+import numpy as np
+import torch
+
+from . import config as cfglib
+from .controllers import BatchedMinMax, BatchedOSC
+from .physics import BatchedPhysics
+from .robot_arm import BatchedRobotArm
+
+TABLE_GEOM = "table/table"
+DOWN_QUAT = (0.0, 0.0, 1.0, 0.0)        # mju_mat2Quat(R.from_euler('xyz', [0, 180, 0])), rearrangement.py:391-393
+PARK_XY = (5.0, 5.0)
+
+
+class StepType(enum.IntEnum):           # dm_env.StepType
+    FIRST = 0
+    MID = 1
+    LAST = 2
+
+
+TimeStep = collections.namedtuple("TimeStep", ["step_type", "reward", "discount", "observation"])   # dm_env.TimeStep
+
+
+class BatchedRearrangementEnv:
+    def __init__(self, viewer=None, cfg: Optional[Dict[str, Any]] = None, num_envs: int = 1, device=None,
+                 dtype: torch.dtype = torch.float32, overrides: Optional[Iterable[str]] = None, seed: Optional[int] = None,
+                 sampler: str = "auto", strict: Optional[bool] = None):
+        if viewer:
+            raise RuntimeError("passive viewer: unavailable on this box (no graphics stack)")
+        self._cfg = cfg if cfg is not None else cfglib.compose(overrides)
+        self.num_envs = int(num_envs)
+        self._physics = BatchedPhysics(self.num_envs, dtype=dtype, device=device)
+        p = self._physics
+        if abs(p.model.opt.timestep - float(self._cfg["physics_dt"])) > 1e-12:
+            raise ValueError("physics_dt=%g differs from the compiled model's timestep %g: recompile the scene blob (tools/compile_scene.py)"
+                             % (self._cfg["physics_dt"], p.model.opt.timestep))
+        self.strict = (self.num_envs == 1) if strict is None else bool(strict)
+        self.device, self.dtype = p.device, p.dtype
+        self.max_props = p.model.nprop
+        pc = self._cfg["arena"]["props"]
+        tseed = int(self._cfg["task"]["initializers"]["seed"]) if seed is None else int(seed)
+        # scene construction randomness (props.py:604-607 num_objects, :277-284 cube size): unseeded in the reference
+        crng = np.random.default_rng(tseed + 7919)
+        lo, hi = int(pc["min_objects"]), int(pc["max_objects"])
+        n = np.full(self.num_envs, lo) if lo == hi else crng.integers(lo, hi, self.num_envs)      # np.random.randint(lo, hi): hi exclusive
+        if n.max() > self.max_props:
+            raise ValueError("prop set needs %d props, the compiled model has %d" % (n.max(), self.max_props))
+        half = crng.uniform(pc["min_object_size"], pc["max_object_size"], (self.num_envs, self.max_props, 1)).repeat(3, axis=2)
+        self.n_props = torch.tensor(n, device=self.device)
+        self.has_prop = torch.arange(self.max_props, device=self.device)[None, :] < self.n_props[:, None]
+        self.prop_half_size = torch.tensor(half, device=self.device, dtype=self.dtype)
+        p.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8))
+        # controllers (hydra partial `controller(physics, arm)` in the reference, robot_arm.py:37,46)
+        cc = self._cfg["robots"]["arm"]["controller_config"]["controller_params"]
+        ee = self._cfg["robots"]["end_effector"]["controller_config"]
+        self._osc = BatchedOSC(p, None, cc)
+        self._minmax = BatchedMinMax(ee["max_val"], ee["min_val"], self.num_envs, self.device)
+        self._robot: Optional[BatchedRobotArm] = None
+        # PropPlacer randomness: np.random.RandomState(seed) per scene (rearrangement.py:207); scene e uses seed + e so that
+        # scene 0 reproduces the reference's draw order exactly
+        self._sampler = sampler if sampler != "auto" else ("per_env" if self.num_envs <= 4096 else "vectorised")
+        self._rs = [np.random.RandomState(seed=tseed + e) for e in range(self.num_envs)] if self._sampler == "per_env" else None
+        self._vrng = np.random.default_rng(tseed)
+        self._table_gid = p.geom_id(TABLE_GEOM)
+        self._prop_gid = torch.tensor(p.model.prop_geomid, device=self.device)
+        self.mode = None
+        self.failed = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
+        self.eef_home_pose = None
+
+    # ------------------------------------------------------------------ accessors
+    @property
+    def physics(self) -> BatchedPhysics:
+        return self._physics
+
+    @property
+    def robot(self) -> BatchedRobotArm:
+        return self._robot
+
+    def close(self):
+        self._physics.close()
+
+    # ------------------------------------------------------------------ placement (PropPlacer.__call__)
+    def _sample_poses(self, envs: np.ndarray):
+        """position ~ U(min_pose, max_pose) then yaw = pi * U(0, 1) about z (rearrangement.py:189-197): 3 + 1 draws per try."""
+        w = self._cfg["task"]["initializers"]["workspace"]
+        lo, hi = np.asarray(w["min_pose"], float), np.asarray(w["max_pose"], float)
+        if self._sampler == "per_env":
+            pos = np.stack([self._rs[e].uniform(lo, hi) for e in envs]) if len(envs) else np.zeros((0, 3))
+            ang = np.array([np.pi * self._rs[e].uniform(0, 1) for e in envs])
+        else:
+            pos = self._vrng.uniform(lo, hi, (len(envs), 3)); ang = np.pi * self._vrng.uniform(0, 1, len(envs))
+        quat = np.stack([np.cos(ang / 2), np.zeros_like(ang), np.zeros_like(ang), np.sin(ang / 2)], 1) if len(envs) else np.zeros((0, 4))
+        return pos, quat
+
+    def _collides(self, k: int) -> torch.Tensor:
+        """_has_collisions_with_prop (prop_initializer.py:121-140): any listed contact (dist <= 0.6, i.e. inside the 0.15
+        detection margin) that involves prop k's geom and not the table -> bool [n_env]."""
+        p = self._physics
+        c = p.data.contact
+        valid = torch.arange(p.maxcon, device=self.device)[None, :] < p.data.ncon[:, None]
+        gk = int(self._prop_gid[k])
+        touches = (c["geom1"] == gk) | (c["geom2"] == gk)
+        table = (c["geom1"] == self._table_gid) | (c["geom2"] == self._table_gid)
+        return (valid & touches & ~table & (c["dist"] <= 0.6)).any(dim=1)
+
+    def _place_props(self, mask: torch.Tensor):
+        p = self._physics
+        pcfg = self._cfg["prop_placer"]
+        active = p.prop_active
+        # contacts disabled for all props not placed yet (prop_initializer.py:183-185)
+        active[mask] = 0
+        qadr = p.model.prop_qposadr
+        for k in range(self.max_props):
+            todo = mask & self.has_prop[:, k]
+            if not bool(todo.any()):
+                continue
+            active[todo, k] = 1
+            for _ in range(int(pcfg["max_attempts_per_prop"])):
+                envs = torch.nonzero(todo).flatten()
+                pos, quat = self._sample_poses(envs.cpu().numpy())
+                pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
+                p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
+                p.forward(full_contacts=True)
+                todo = todo & self._collides(k)
+                if not bool(todo.any()):
+                    break
+            else:
+                raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
+
+    def _park_missing_props(self, mask: torch.Tensor):
+        p = self._physics
+        for k in range(self.max_props):
+            m = mask & ~self.has_prop[:, k]
+            if bool(m.any()):
+                a = p.model.prop_qposadr[k]
+                p.qpos[m, a:a + 7] = torch.tensor([PARK_XY[0] + k, PARK_XY[1], 0.2, 1, 0, 0, 0], device=self.device, dtype=self.dtype)
+
+    def _place_and_settle(self, mask: torch.Tensor):
+        """place_and_settle (prop_initializer.py:233-278): place, settle with the arm held static, re-place scenes that did
+        not come to rest, at most max_settle_physics_attempts times."""
+        p = self._physics
+        pcfg = self._cfg["prop_placer"]
+        h = p.model.opt.timestep
+        max_steps = int(round(pcfg["max_settle_physics_time"] / h)); min_steps = int(round(pcfg["min_settle_physics_time"] / h))
+        todo = mask.clone()
+        for _ in range(int(pcfg["max_settle_physics_attempts"])):
+            self._place_props(todo)
+            t0 = p.time.clone()
+            # a freshly placed prop has no velocity (set_pose writes qpos; mj_forward leaves qvel)
+            p.qvel[todo, 15:] = 0
+            done = p.settle(max_steps, min_steps, pcfg["max_qvel_tol"], pcfg["max_qacc_tol"], mask=todo)
+            unsettled = todo & (done >= max_steps)
+            if not bool(unsettled.any()):
+                return True
+            p.time[unsettled] = t0[unsettled]                      # prop_initializer.py:258
+            todo = unsettled
+        self.settle_failed = todo
+        return False
+
+    # ------------------------------------------------------------------ dm_env API
+    def reset(self, mask: Optional[torch.Tensor] = None) -> TimeStep:
+        p = self._physics
+        m = torch.ones(self.num_envs, dtype=torch.bool, device=self.device) if mask is None else mask.to(self.device, torch.bool)
+        p.reset(m)                                                                            # rearrangement.py:302
+        home = torch.tensor(self._cfg["robots"]["arm"]["configuration"]["home"], device=self.device, dtype=self.dtype)
+        p.qpos[m, 0:7] = home                                                                 # :306
+        self._park_missing_props(m)
+        self._place_and_settle(m)                                                             # :309
+        if self._robot is None:
+            self._robot = BatchedRobotArm(p, self._osc, self._minmax, self._cfg["control_dt"])   # :319-324
+        self._minmax.set_status(torch.zeros(self.num_envs, dtype=torch.uint8, device=self.device), m)
+        p.forward(full_contacts=False)
+        home_pose = self._robot.eef_pose.clone(); home_pose[:, 0] -= 0.1                       # :327-328
+        if self.eef_home_pose is None or mask is None:
+            self.eef_home_pose = home_pose
+        else:
+            self.eef_home_pose[m] = home_pose[m]
+        self.failed[m] = False
+        p.status(clear=True)
+        self.mode = "pick"                                                                    # :331
+        return TimeStep(StepType.FIRST, 0.0, 0.0, self._compute_observation())
+
+    def step(self, action_dict) -> TimeStep:
+        observation = self._compute_observation()                                             # :343 (observation BEFORE acting)
+        if self.mode == "pick":
+            self.pick(action_dict["pose"]); self.mode = "place"
+        else:
+            self.place(action_dict["pose"]); self.mode = "pick"
+        return TimeStep(StepType.MID, 0.0, 0.0, observation)
+
+    def _phase(self, duration: float, what: str):
+        ok = self._robot.run_controller(duration)
+        bad = ~ok
+        self.failed |= bad
+        if self.strict and bool(bad.any()):
+            raise RuntimeError("Failed to " + what)                                           # rearrangement.py:372,377,...
+
+    def _pose_tensor(self, pose) -> torch.Tensor:
+        t = pose if isinstance(pose, torch.Tensor) else torch.as_tensor(np.asarray(pose))
+        if t.dim() == 1:
+            t = t.unsqueeze(0).expand(self.num_envs, 7)
+        if isinstance(pose, (torch.Tensor, np.ndarray)):
+            pose[..., 2] = 0.575                                                              # the reference mutates the caller's array (:362)
+        t = t.to(self.device, self.dtype).clone(); t[:, 2] = 0.575
+        return t
+
+    def _pick_or_place(self, pose, grip_status: str, names):
+        osc, zeros = self._osc, torch.zeros(3, device=self.device, dtype=self.dtype)
+        pose = self._pose_tensor(pose)
+        pre = pose.clone(); pre[:, 2] = 0.9
+        if grip_status == "max":
+            osc.set_target(position=pre[:, :3], velocity=zeros, quat=pre[:, 3:], angular_velocity=zeros)    # :365-370
+        else:
+            osc.set_target(position=pre[:, :3], quat=pre[:, 3:])                                            # :411-414
+        self._phase(2.0, names[0])
+        osc.set_target(position=pose[:, :3]); self._phase(2.0, names[1])
+        self._minmax.status = grip_status; self._phase(1.0, names[2])
+        osc.set_target(position=pre[:, :3]); self._phase(2.0, names[3])
+        osc.set_target(position=self.eef_home_pose, quat=torch.tensor(DOWN_QUAT, device=self.device, dtype=self.dtype))
+        self._phase(2.0, names[4])
+
+    def pick(self, pose):
+        """rearrangement.py:358-401."""
+        self._pick_or_place(pose, "max", ("move arm to pre pick position", "move arm to pick position", "close gripper",
+                                          "move arm to pre grasp position", "move arm to home position"))
+
+    def place(self, pose):
+        """rearrangement.py:403-440."""
+        self._pick_or_place(pose, "min", ("move arm to pre place position", "move arm to place position", "open gripper",
+                                          "move arm to pre place position", "move arm to home position"))
+
+    # ------------------------------------------------------------------ specs / observation
+    def _compute_observation(self) -> Dict[str, torch.Tensor]:
+        """State observation (camera images: unavailable on this box).  Views / small gathers of device tensors."""
+        p = self._physics
+        qa = p.model.prop_qposadr
+        prop = torch.stack([p.qpos[:, a:a + 7] for a in qa], 1)
+        return {"qpos": p.qpos, "qvel": p.qvel, "time": p.time, "eef_pos": p.data.site_xpos[:, 1], "prop_pos": prop[..., :3],
+                "prop_quat": prop[..., 3:], "has_prop": self.has_prop}
+
+    def observation_spec(self):
+        p = self._physics
+        return {"qpos": (self.num_envs, p.model.nq), "qvel": (self.num_envs, p.model.nv), "time": (self.num_envs,), "eef_pos": (self.num_envs, 3),
+                "prop_pos": (self.num_envs, self.max_props, 3), "prop_quat": (self.num_envs, self.max_props, 4), "has_prop": (self.num_envs, self.max_props)}
+
+    def action_spec(self):
+        """rearrangement.py:448-458: pose f64[7] (+ pixel_coords i64[2], gripper_rot f64[1] consumed by the data generator)."""
+        return {"pose": (self.num_envs, 7), "pixel_coords": (self.num_envs, 2), "gripper_rot": (self.num_envs, 1)}
+
+    @property
+    def props_info(self):
+        """rearrangement.py:277-295 (poses only; labels are render-side): per scene/prop position + orientation."""
+        o = self._compute_observation()
+        return {"position": o["prop_pos"], "orientation": o["prop_quat"], "has_prop": self.has_prop, "half_size": self.prop_half_size}
+
+
+def RearrangementEnv(viewer=None, cfg=None, **kw) -> BatchedRearrangementEnv:
+    """Single-scene façade with the reference's constructor signature ``RearrangementEnv(viewer=None, cfg=DEFAULT_CONFIG)``."""
+    return BatchedRearrangementEnv(viewer=viewer, cfg=cfg, num_envs=1, **kw)
