@@ -1,0 +1,169 @@
+"""GPU tests of the host-side mirror of the reference API (controllers, RobotArm, RearrangementEnv) and of the committed
+golden vectors, all through the C-ABI.  Oracle = checker only."""
+import os
+
+import numpy as np
+import pytest
+
+import scenarios as sc
+from orc import Oracle
+
+pytestmark = pytest.mark.gpu
+torch = pytest.importorskip("torch")
+GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+
+
+def _phys(n, dtype):
+    from mujoco_robot_environments_b200.physics import BatchedPhysics
+    return BatchedPhysics(n, dtype=dtype)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-7), (torch.float32, 2e-3)])
+def test_osc_golden_compute_control_output(dtype, tol):
+    """BatchedOSC.compute_control_output()/is_converged() == reference osc.py arithmetic (numpy golden)."""
+    from mujoco_robot_environments_b200.controllers import BatchedOSC
+    g = dict(np.load(os.path.join(GOLD, "osc_golden.npz")))
+    n = len(g["qpos"])
+    st = np.repeat(g["scene_state"][None], n, 0)
+    st[:, :7] = g["qpos"]; st[:, sc.REC_QVEL:sc.REC_QVEL + 7] = g["qvel"]
+    p = _phys(n, dtype)
+    p.state.copy_(torch.tensor(st, dtype=dtype))
+    p.set_env_params(torch.tensor(np.repeat(g["scene_size"][None], n, 0)), torch.tensor(np.repeat(g["scene_active"][None], n, 0)))
+    osc = BatchedOSC(p)
+    tg = torch.tensor(g["target"])
+    osc.set_target(position=tg[:, 0:3], velocity=tg[:, 3:6], quat=tg[:, 6:10], angular_velocity=tg[:, 10:13])
+    launches = p.launches
+    tau = osc.compute_control_output().cpu().numpy().astype(np.float64); conv = osc.is_converged().cpu().numpy()
+    assert p.launches == launches + 1
+    assert np.abs(p.state.cpu().numpy()[:, :15] - st[:, :15]).max() < 1e-6      # zero-tick launch: no stepping
+    for i in range(n):
+        if dtype == torch.float32 and not g["branch"][i]:
+            continue
+        assert np.abs(tau[i] - g["tau"][i]).max() / max(1.0, np.abs(g["tau"][i]).max()) < tol, i
+        if dtype == torch.float64:
+            assert bool(conv[i]) == bool(g["converged"][i])
+    # diagnostics agree with the golden inputs
+    pe = osc.current_position_error().cpu().numpy()
+    assert np.abs(pe - np.linalg.norm(g["target"][:, :3] - g["xpos"], axis=1)).max() < (1e-9 if dtype == torch.float64 else 1e-5)
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-9), (torch.float32, 2e-3)])
+def test_step_golden(dtype, tol):
+    g = dict(np.load(os.path.join(GOLD, "step_golden.npz")))
+    S, K = g["qpos"].shape[:2]
+    p = _phys(S, dtype)
+    p.set_env_params(torch.tensor(g["prop_size"]), torch.tensor(g["prop_active"]))
+    p.state.copy_(torch.tensor(g["state0"], dtype=dtype)); p.set_control(torch.tensor(g["ctrl"]))
+    for k in range(K):          # one launch per step, compared at EVERY step
+        p.step(1); torch.cuda.synchronize()
+        assert np.abs(p.qpos.cpu().numpy() - g["qpos"][:, k]).max() < tol, k
+        if dtype == torch.float64 and k + 1 < K:
+            # derived outputs describe the state AFTER the step (dm_control legacy order): the solver-active contact set the next step will use
+            assert (p.data.nefc.cpu().numpy() == g["nefc"][:, k + 1]).all(), k
+    assert int(p.status().cpu().max()) == 0
+    p.state.copy_(torch.tensor(g["state0"], dtype=dtype))
+    conv = p.run_controller(torch.tensor(g["target"]), torch.tensor(g["grip"]), 20).cpu().numpy()
+    assert np.abs(p.qpos.cpu().numpy() - g["osc_qpos"]).max() < tol
+    if dtype == torch.float64:
+        assert (conv == g["osc_converged"]).all()
+
+
+def test_robot_arm_run_controller_matches_oracle():
+    """BatchedRobotArm.run_controller(duration) == RobotArm.run_controller semantics (ticks = duration / control_dt, latched bit)."""
+    from mujoco_robot_environments_b200.robot_arm import BatchedRobotArm
+    n = 4
+    st, size, active = sc.make_states(n, seed=31)
+    p = _phys(n, torch.float64)
+    p.state.copy_(torch.tensor(st)); p.set_env_params(torch.tensor(size), torch.tensor(active))
+    arm = BatchedRobotArm(p)
+    assert arm.control_steps == 5 and arm.ticks_for(2.0) == 400 and arm.ticks_for(1.0) == 200
+    tg, grip = sc.random_targets(n, seed=32)
+    arm.arm_controller.set_target(position=torch.tensor(tg[:, :3]), velocity=torch.zeros(3), quat=torch.tensor(tg[0, 6:10]), angular_velocity=torch.zeros(3))
+    arm.end_effector_controller.set_status(torch.tensor(grip))
+    ok = arm.run_controller(0.25).cpu().numpy()
+    o = Oracle(sc.default_blob())
+    for e in range(n):
+        sc.oracle_load(o, st[e], size[e], active[e]); o.set_option("full_contacts", 0)
+        c = o.run_controller(tg[e], int(grip[e]), 50)
+        assert np.abs(p.qpos[e].cpu().numpy() - o.qpos[:sc.NQ]).max() < 1e-8
+        assert bool(ok[e]) == c
+    assert np.abs(arm.eef_pose[0].cpu().numpy() - o.site_xpos[4]).max() < 1 and arm.eef_pose.shape == (n, 3)
+
+
+def test_osc_gain_mutation_reaches_kernel():
+    """The tuner mutates controller_gains in place (rearrangement_controller_tuning.py:164-168): the next launch must use them."""
+    from mujoco_robot_environments_b200.robot_arm import BatchedRobotArm
+    st, size, active = sc.make_states(1, seed=33)
+    tg, grip = sc.random_targets(1, seed=34)
+    p = _phys(1, torch.float64)
+    p.state.copy_(torch.tensor(st)); p.set_env_params(torch.tensor(size), torch.tensor(active))
+    arm = BatchedRobotArm(p)
+    arm.arm_controller.set_target(position=torch.tensor(tg[:, :3]), velocity=torch.zeros(3), quat=torch.tensor(tg[:, 6:10]), angular_velocity=torch.zeros(3))
+    arm.arm_controller.controller_gains["position"]["kp"] = 123.0
+    arm.arm_controller.controller_gains["nullspace"]["kd"] = 11.0
+    arm.run_controller(0.1)
+    o = Oracle(sc.default_blob())
+    sc.oracle_load(o, st[0], size[0], active[0]); o.set_option("full_contacts", 0)
+    o.osc_config([123.0, 20, 500, 100, 200, 11.0], sc.ARM_HOME)
+    o.run_controller(tg[0], 0, 20)
+    assert np.abs(p.qpos[0].cpu().numpy() - o.qpos[:sc.NQ]).max() < 1e-8
+
+
+def test_env_reset_places_props_like_the_reference_sampler():
+    """reset(): scene 0's prop poses come from np.random.RandomState(seed=1) in the reference's draw order
+    (3 uniforms for the position, 1 for the yaw, per attempt), props end up at rest on the table, arm at home."""
+    from mujoco_robot_environments_b200.env import BatchedRearrangementEnv, StepType
+    env = BatchedRearrangementEnv(num_envs=8, dtype=torch.float64, overrides=["arena/props=colour_splitter"])
+    ts = env.reset()
+    assert ts.step_type == StepType.FIRST and env.mode == "pick"
+    p = env.physics
+    obs = ts.observation
+    has = env.has_prop.cpu().numpy(); pos = obs["prop_pos"].cpu().numpy()
+    assert ((env.n_props >= 2) & (env.n_props <= 4)).all()
+    assert np.abs(p.qpos[:, :7].cpu().numpy() - sc.ARM_HOME).max() < 1e-12                       # arm held static while settling
+    hs = env.prop_half_size.cpu().numpy()[..., 2]
+    assert np.abs(pos[..., 2][has] - (0.4 + hs[has])).max() < 2e-3                                # resting on the table top (z = 0.4)
+    assert (pos[..., 0][has] > 0.34).all() and (pos[..., 0][has] < 0.56).all() and (np.abs(pos[..., 1][has]) < 0.41).all()
+    assert (pos[..., 0][~has] > 4).all()                                                          # missing props parked
+    # x/y/yaw of scene 0's first prop = first accepted draws of RandomState(1) (first prop can only collide with the arm: never here)
+    rs = np.random.RandomState(1)
+    first = rs.uniform([0.35, -0.4, 0.43], [0.55, 0.4, 0.435]); yaw = np.pi * rs.uniform(0, 1)
+    assert np.abs(pos[0, 0, :2] - first[:2]).max() < 2e-3
+    q = obs["prop_quat"][0, 0].cpu().numpy()
+    assert abs(abs(2 * np.arctan2(q[3], q[0])) - yaw) < 2e-2
+    # placed props keep clear of each other (no contact inside the 0.15 detection margin besides the table)
+    p.forward(full_contacts=True); torch.cuda.synchronize()
+    c = p.data.contact; ncon = p.data.ncon
+    valid = torch.arange(p.maxcon, device=p.device)[None] < ncon[:, None]
+    table = p.geom_id("table/table")
+    other = valid & (c["geom1"] != table) & (c["geom2"] != table) & (c["geom1"] >= 26)
+    assert not bool(other.any())
+    assert float(env.eef_home_pose[0, 0]) == pytest.approx(float(env.robot.eef_pose[0, 0]) - 0.1, abs=1e-9)
+
+
+def test_env_pick_and_place_moves_a_prop():
+    """step({'pose'}) alternates the scripted pick / place phases (rearrangement.py:339-440) for every scene at once."""
+    from mujoco_robot_environments_b200.env import BatchedRearrangementEnv
+    env = BatchedRearrangementEnv(num_envs=4, dtype=torch.float32, strict=False)
+    ts = env.reset()
+    pos0 = ts.observation["prop_pos"][:, 0].clone(); quat0 = ts.observation["prop_quat"][:, 0]
+    yaw = 2 * torch.atan2(quat0[:, 3], quat0[:, 0])
+    # grasp orientation: gripper pointing down, rotated about z with the cube (prop_pick, rearrangement.py:579-595)
+    half = 0.5 * yaw
+    down = torch.tensor([0.0, 0.0, 1.0, 0.0], device=pos0.device)
+    qz = torch.stack([torch.cos(half), torch.zeros_like(half), torch.zeros_like(half), torch.sin(half)], 1)
+    from mujoco_robot_environments_b200.controllers import _mulquat
+    grasp = _mulquat(qz.to(torch.float32), down[None].expand(4, 4))
+    pick = torch.cat([pos0, grasp], 1)
+    t0 = float(env.physics.time[0])
+    env.step({"pose": pick})
+    assert env.mode == "place" and abs(float(env.physics.time[0]) - t0 - 9.0) < 1e-2        # 2+2+1+2+2 s of physics
+    lifted = env.physics.qpos[:, 15 + 2]
+    assert int((lifted > 0.5).sum()) >= 3                                                  # cube travels with the gripper
+    place = pick.clone(); place[:, 0] = 0.45; place[:, 1] = torch.tensor([-0.3, -0.1, 0.1, 0.3], device=pos0.device)
+    env.step({"pose": place})
+    assert env.mode == "pick"
+    final = env.physics.qpos[:, 15:18]
+    ok = ((final[:, :2] - place[:, :2]).norm(dim=1) < 0.03) & (final[:, 2] < 0.45)
+    assert int(ok.sum()) >= 3
+    assert int((env.physics.status() & 7).max()) == 0                                      # no NaN / blow-up flags
