@@ -20,8 +20,8 @@ namespace b2p {
 
 
 
-template <typename T> struct KernelCfg { static constexpr int kWarps = 6; static constexpr int kMinBlocks = 1; };
-template <> struct KernelCfg<double> { static constexpr int kWarps = 3; static constexpr int kMinBlocks = 1; };
+template <typename T> struct KernelCfg { static constexpr int kWarps = 9; static constexpr int kMinBlocks = 1; };
+template <> struct KernelCfg<double> { static constexpr int kWarps = 4; static constexpr int kMinBlocks = 1; };
 
 // ------------------------------------------------------------------------------------------ TMA / mbarrier helpers
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }

@@ -114,8 +114,7 @@ B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       for (int k = 0; k < 6; k++) v += s.cdof[j][k] * buf[k];
       if (i == j) v += m.dof_armature[i];
     }
-    s.Marm[i * MAXTD + j] = v; s.Marm[j * MAXTD + i] = v;
-    s.Larm[tri_idx(i, j)] = v;
+    s.Mt[tri_idx(i, j)] = v; s.Larm[tri_idx(i, j)] = v;
   }
   for (int d = c.tid; d < m.nv; d += c.nt) {
     if (d < n) {
@@ -173,7 +172,7 @@ B2P_HDN void integrate(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool f
   const int n = m.ntd; const T h = m.timestep;
   // M - h * d(qfrc_passive + qfrc_actuator)/d(qvel): the velocity-derivative part is a model constant (joint damping
   // on the diagonal; for implicitfast the affine actuator's -bias_vel * moment' moment inside M's sparsity), built on the host
-  for (int e = c.tid; e < (n * (n + 1)) / 2; e += c.nt) { const unsigned t = m.tri[e]; s.H[e] = s.Marm[(t >> 8) * MAXTD + (t & 255u)] + m.impl_hD[e]; }
+  for (int e = c.tid; e < (n * (n + 1)) / 2; e += c.nt) { const unsigned t = m.tri[e]; s.H[e] = s.Mt[e] + m.impl_hD[e]; }
   for (int d = c.tid; d < m.nv; d += c.nt) {
     bool active = d < n || s.pactive[(d - n) / 6];
     const T f = active ? s.qfrc_smooth[d] + s.qfrc_con[d] : T(0);

@@ -105,6 +105,59 @@ B2P_HD void solve6_local(const T* L, int s0, T* x) {   // x = 6 consecutive real
   for (int i = 0; i < 6; i++) x[i] = y[i];
 }
 
+// ---------------------------------------------------------------------------------------- dense tail block in registers
+// The tree block (arm + gripper, <= 16 dofs) is always the LAST solver block and is dense.  On the device it is factored
+// with lane i owning row i in registers and the pivot column broadcast by shuffles: no shared-memory round trips and no
+// barriers (136 SHFL + 120 FMA, fully unrolled) instead of 15 x (3 barriers + table-driven element loops).  The
+// triangular solves keep x one element per lane and read L from shared memory (row/column reads of the packed triangle
+// are bank-conflict free for 16 rows).  The host build of these templates (tests/_hostemu) keeps the generic path.
+B2P_HD bool sp_dense_tail(const SpStruct& st, int b) { return b == st.nblk - 1 && st.blk[b].nrows == st.blk[b].len && st.blk[b].len > 6 && st.blk[b].len <= 16; }
+#ifdef __CUDA_ARCH__
+template <typename T>
+__device__ __forceinline__ void chol16_warp(T* A, int s0, int n, int lane) {
+  T a[16];
+  const int i = lane;
+#pragma unroll
+  for (int j = 0; j < 16; j++) a[j] = (i < n && j <= i) ? A[tri_idx(s0 + i, s0 + j)] : ((j == i && i < 16) ? T(1) : T(0));
+  T dg = 1;
+#pragma unroll
+  for (int k = 0; k < 16; k++) {
+    const T akk = __shfl_sync(0xffffffffu, a[k], k);
+    const T d = akk > Num<T>::minval() ? sqrt(akk) : sqrt(Num<T>::minval());
+    const T id = 1 / d;
+    if (i == k) { a[k] = d; dg = d; } else if (i > k) a[k] *= id;
+#pragma unroll
+    for (int j = k + 1; j < 16; j++) { const T ljk = __shfl_sync(0xffffffffu, a[k], j); if (i >= j) a[j] -= a[k] * ljk; }
+  }
+  (void)dg;
+#pragma unroll
+  for (int j = 0; j < 16; j++) if (i < n && j <= i) A[tri_idx(s0 + i, s0 + j)] = a[j];
+}
+// x_tail <- (L L')^-1 x_tail for the dense tail block; also applies the backward updates to the np coupled earlier columns
+template <typename T>
+__device__ __forceinline__ void solve16_warp(const T* L, const SpStruct& st, int b, T* x, int np6, int ntd, int lane) {
+  const int s0 = st.blk[b].start, n = st.blk[b].len, np = st.blk[b].nprev;
+  const bool mine = lane < n;
+  T xv = mine ? x[sp_dof(s0 + lane, np6, ntd)] : T(0);
+  const T rd = mine ? 1 / L[tri_idx(s0 + lane, s0 + lane)] : T(1);
+  const int rowbase = tri_idx(s0 + (mine ? lane : 0), s0);
+  for (int k = 0; k < n; k++) {
+    const T xk = __shfl_sync(0xffffffffu, xv * rd, k);
+    if (lane == k) xv = xk; else if (mine && lane > k) xv -= L[rowbase + k] * xk;
+  }
+  T acc = 0;                                   // backward: lane a < np accumulates sum_k L[k][prev a] * x_k
+  const int pcol = lane < np ? st.prev[b][lane] : 0;
+  for (int k = n - 1; k >= 0; k--) {
+    const T xk = __shfl_sync(0xffffffffu, xv * rd, k);
+    const int kb = tri_idx(s0 + k, 0);
+    if (lane == k) xv = xk; else if (lane < k) xv -= L[kb + s0 + lane] * xk;
+    if (lane < np) acc += L[kb + pcol] * xk;
+  }
+  if (mine) x[sp_dof(s0 + lane, np6, ntd)] = xv;
+  if (lane < np) x[sp_dof(pcol, np6, ntd)] -= acc;
+}
+#endif
+
 // in-place A = L L' on the packed lower triangle, restricted to the structure.  tri[e] = (a << 8) | c enumerates
 // the pairs a >= c of a triangular index e (host-built table in DevModel).
 template <typename T>
@@ -112,6 +165,9 @@ B2P_HDN void sp_cholesky(T* A, const SpStruct& st, const unsigned short* tri, co
   for (int b = c.tid; b < st.nblk; b += c.nt) if (sp_local(st, b)) chol6_local(A, st.blk[b].start);
   for (int b = 0; b < st.nblk; b++) {
     if (sp_local(st, b)) continue;
+#ifdef __CUDA_ARCH__
+    if (sp_dense_tail(st, b)) { bsync(c); chol16_warp(A, st.blk[b].start, st.blk[b].len, c.tid); bsync(c); continue; }
+#endif
     const int start = st.blk[b].start, len = st.blk[b].len, nrows = st.blk[b].nrows;
     for (int kk = 0; kk < len; kk++) {
       const int k = start + kk, R = nrows - kk - 1, kb = tri_idx(k, 0);
@@ -138,6 +194,9 @@ B2P_HDN void sp_solve(const T* L, const SpStruct& st, T* x, int np6, int ntd, co
   for (int b = c.tid; b < st.nblk; b += c.nt) if (sp_local(st, b)) solve6_local(L, st.blk[b].start, x + sp_dof(st.blk[b].start, np6, ntd));
   for (int b = 0; b < st.nblk; b++) {
     if (sp_local(st, b)) continue;
+#ifdef __CUDA_ARCH__
+    if (sp_dense_tail(st, b)) { bsync(c); solve16_warp(L, st, b, x, np6, ntd, c.tid); bsync(c); continue; }   // forward + backward of the tail in one go
+#endif
     const int start = st.blk[b].start, len = st.blk[b].len, nrows = st.blk[b].nrows;
     for (int kk = 0; kk < len; kk++) {
       const int k = start + kk, R = nrows - kk - 1, dk = sp_dof(k, np6, ntd);
@@ -151,6 +210,9 @@ B2P_HDN void sp_solve(const T* L, const SpStruct& st, T* x, int np6, int ntd, co
   }
   for (int b = st.nblk - 1; b >= 0; b--) {
     if (sp_local(st, b)) continue;
+#ifdef __CUDA_ARCH__
+    if (sp_dense_tail(st, b)) continue;
+#endif
     const int start = st.blk[b].start, len = st.blk[b].len, np = st.blk[b].nprev;
     for (int kk = len - 1; kk >= 0; kk--) {
       const int k = start + kk, dk = sp_dof(k, np6, ntd), kb = tri_idx(k, 0);

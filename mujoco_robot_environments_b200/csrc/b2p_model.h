@@ -24,7 +24,7 @@ constexpr int MAXNV = MAXTD + 6 * MAXP;   // 40
 constexpr int MAXNQ = MAXTD + 7 * MAXP;   // 44
 constexpr int MAXG = 32;         // collidable geoms
 constexpr int MAXCON = 48;       // contacts kept per env
-constexpr int MAXEFC = 160;      // constraint rows per env
+constexpr int MAXEFC = 128;      // constraint rows per env
 constexpr int MAXCAND = 160;     // narrow-phase candidates per env
 constexpr int MAXEQ = 4;
 constexpr int MAXU = 8;

@@ -42,7 +42,7 @@ B2P_HDN void osc_torque(const DevModel<T>& m, const Scratch<T>& s, const T* tg, 
       for (int k = 0; k < 3; k++) { J[k * 7 + d] = on ? s.cdof[d][3 + k] + cr[k] : T(0); J[(3 + k) * 7 + d] = on ? s.cdof[d][k] : T(0); }
     }
   }
-  for (int i = 0; i < 7; i++) for (int j = 0; j < 7; j++) Ma[i * 7 + j] = s.Marm[i * MAXTD + j];
+  for (int i = 0; i < 7; i++) for (int j = 0; j < 7; j++) Ma[i * 7 + j] = s.Mt[i >= j ? tri_idx(i, j) : tri_idx(j, i)];
   small_chol<T, 7>(Ma); small_inv_from_chol<T, 7>(Ma, Minv);                        // osc.py:106
   for (int i = 0; i < 7; i++) for (int r = 0; r < 6; r++) { T v = 0; for (int k = 0; k < 7; k++) v += Minv[i * 7 + k] * J[r * 7 + k]; MiJt[i * 6 + r] = v; }
   for (int r = 0; r < 6; r++) for (int q = 0; q < 6; q++) { T v = 0; for (int k = 0; k < 7; k++) v += J[r * 7 + k] * MiJt[k * 6 + q]; Lxi[r * 6 + q] = v; L[r * 6 + q] = v; }

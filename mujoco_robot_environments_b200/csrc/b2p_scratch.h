@@ -12,6 +12,10 @@ struct Globals {                 // read-only global-memory tables
   const short* pair_g1; const short* pair_g2; const PairParam<T>* pair_param;
 };
 
+// Shared memory per scene is what bounds the number of resident warps (= scenes in flight) per SM, and the kernel is latency
+// bound, so Scratch is kept small: buffers whose lifetimes never overlap share storage.  "pos" members are produced by step1
+// (kinematics, collision, row construction) and are dead once make_rows / the derived-output write have run; "dyn" members
+// live only inside step2 (solver, integrator).  Everything outside the two unions persists across both.
 template <typename T>
 struct alignas(16) Scratch {
   // persisted state (one HBM record per env: qpos | qvel | qacc_warmstart | time)
@@ -19,33 +23,45 @@ struct alignas(16) Scratch {
   // per-env prop parameters
   T psize[MAXP][3], pinertia[MAXP][3], pinvw[MAXP][2]; int pactive[MAXP];
   // tree (spatial quantities about the fixed reference point m.ref)
-  T xpos[MAXTB][3], xquat[MAXTB][4], xmat[MAXTB][9];
-  T crb[MAXTB][10], cdof[MAXTD][6], cvel[MAXTB][6], cacc[MAXTB][6], cfrc[MAXTB][6];
+  T xpos[MAXTB][3], xmat[MAXTB][9], cdof[MAXTD][6];
   T ppos[MAXP][3], pmat[MAXP][9];
-  T gpos[MAXG][3], gmat[MAXG][9], grbound[MAXG], site_xpos[2][3], site_xmat[2][9];
-  // dynamics: tree mass matrix dense (OSC, M*x) + packed Cholesky factor; props diagonal
-  T Marm[MAXTD * MAXTD], Larm[MPACK], Mdiag[MAXNV];
+  T site_xpos[2][3], site_xmat[2][9];
+  // dynamics: tree mass matrix (packed lower triangle; OSC, M*x) + its packed Cholesky factor; props diagonal
+  T Mt[MPACK], Larm[MPACK], Mdiag[MAXNV];
   T qfrc_bias[MAXNV], qfrc_passive[MAXNV], qfrc_act[MAXNV], qfrc_smooth[MAXNV], qacc_smooth[MAXNV], qacc[MAXNV], qfrc_con[MAXNV];
   T act_force[MAXU];
   // contacts
   int ncand, ncon, nefc, flags, niter, jused, nmpr; unsigned cpl_pairs;
-  short cand[MAXCAND];
-  T c_dist[MAXCON], c_pos[MAXCON][3], c_frame[MAXCON][9], c_mu[MAXCON], c_fric[MAXCON], c_incl[MAXCON];
+  T c_dist[MAXCON], c_mu[MAXCON], c_fric[MAXCON], c_incl[MAXCON];
   short c_pair[MAXCON], c_row[MAXCON];
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
   // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
-  T Jp[JPOOL], D[MAXEFC], aref[MAXEFC], Jaref[MAXEFC], Jv[MAXEFC], force[MAXEFC];
+  T Jp[JPOOL], D[MAXEFC], aref[MAXEFC], force[MAXEFC];
   signed char row_a[MAXEFC], row_b[MAXEFC], row_type[MAXEFC], row_state[MAXEFC];
   short row_id[MAXEFC], joff[MAXEFC];
-  T cW[MAXCON][6];               // per-contact 3x3 symmetric Hessian weight (xx,yy,zz,xy,xz,yz) in row space
   // per-block row lists (block 0 = tree, 1+p = prop p): first row of every item (eq/limit row, or contact triple)
   unsigned char brow0[MAXEFC], browp[MAXP][MAXCON]; int nbrow[SP_MAXBLK];
-  // solver: packed lower-triangular Hessian in solver order (props first, tree last) + its sparsity structure
-  SpStruct sp;
-  T H[HPACK], grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV];
+  SpStruct sp;                   // block structure of the Newton Hessian in solver order (props first, tree last)
   // settle / frozen-arm support
   T hold_q[MAXTD], hold_v[MAXTD];
+  union {                        // ---- storage shared between step1-only ("pos") and step2-only ("dyn") buffers, part 1
+    T H[HPACK];                  // dyn: packed lower-triangular Newton Hessian / integrator matrix
+    struct {                     // pos: composite inertias + rne sweeps, contact points, broad-phase lists
+      T crb[MAXTB][10], cvel[MAXTB][6], cacc[MAXTB][6], cfrc[MAXTB][6], c_pos[MAXCON][3], xquat[MAXTB][4], grbound[MAXG];
+      short cand[MAXCAND];
+    };
+  };
+  union {                        // ---- part 2
+    struct {                     // dyn: solver vectors, per-row residuals, per-contact cone Hessian (xx,yy,zz,xy,xz,yz)
+      T grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV], Jaref[MAXEFC], Jv[MAXEFC], cW[MAXCON][6];
+    };
+    struct {                     // pos: geom poses, contact frames
+      T gpos[MAXG][3], gmat[MAXG][9], c_frame[MAXCON][9];
+    };
+  };
 };
+static_assert(sizeof(((Scratch<float>*)0)->H) >= (MAXTB * 28 + MAXCON * 3 + MAXTB * 4 + MAXG) * sizeof(float) + MAXCAND * sizeof(short), "pos side must fit under H");
+
 
 // block id of a dof: 0 = tree, 1+p = prop p
 template <typename T> B2P_HD int dof_block(const DevModel<T>& m, int d) { return d < m.ntd ? 0 : 1 + (d - m.ntd) / 6; }

@@ -8,7 +8,7 @@ namespace b2p {
 template <typename T>
 B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) {
-    if (d < m.ntd) { T a = 0; for (int j = 0; j < m.ntd; j++) a += s.Marm[d * MAXTD + j] * v[j]; r[d] = a; }
+    if (d < m.ntd) { T a = 0; for (int j = 0; j < m.ntd; j++) a += s.Mt[j <= d ? tri_idx(d, j) : tri_idx(j, d)] * v[j]; r[d] = a; }
     else r[d] = s.Mdiag[d] * v[d];
   }
 }
@@ -83,7 +83,7 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       int oi, oj;
       if (sbi == sbj) { const unsigned t = m.tri[e]; oi = t >> 8; oj = t & 255u; } else { oi = e / nj; oj = e - oi * nj; }
       T h = 0;
-      if (sbi == sbj) h = bi == 0 ? s.Marm[oi * MAXTD + oj] : (oi == oj ? s.Mdiag[ntd + 6 * (bi - 1) + oi] : T(0));
+      if (sbi == sbj) h = bi == 0 ? s.Mt[tri_idx(oi, oj)] : (oi == oj ? s.Mdiag[ntd + 6 * (bi - 1) + oi] : T(0));
       for (int q = 0; q < n; q++) {
         const int r = lst[q], tp = s.row_type[r];
         const T* sj = bi == bj ? nullptr : row_seg(m, s, r, bj);
