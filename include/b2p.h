@@ -74,6 +74,11 @@ int b2p_forward(b2p_handle h, int full_contacts, void* stream);
 int b2p_get(b2p_handle h, int field, void* dst /* [n_env][count] */, void* stream);
 int b2p_status(b2p_handle h, int32_t* flags /* device [n_env] */, int clear, void* stream);
 
+/* developer aid: per-stage cycle counters summed over scenes, [B2P_PROF_N] entries; all zero unless the library was built
+ * with -DB2P_PROF (the product build has no counters in the kernel).  Synchronises the device. */
+enum { B2P_PROF_N = 19 };
+int b2p_prof_read(b2p_handle h, unsigned long long* out, int reset);
+
 /* micro-benchmark: register-resident FMA chain, returns TFLOP/s of the handle-independent device (dtype 0/1) */
 int b2p_fma_peak(int dtype, int device, double* tflops);
 const char* b2p_last_error(void);

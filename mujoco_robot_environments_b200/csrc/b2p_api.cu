@@ -184,6 +184,12 @@ int b2p_status(b2p_handle h, int32_t* flags, int clear, void* stream) {
   if (clear) CK(cudaMemsetAsync(h->d_status, 0, (size_t)h->n_env * 4, (cudaStream_t)stream));
   return B2P_OK;
 }
+int b2p_prof_read(b2p_handle h, unsigned long long* out, int reset) {
+  if (!h || !out) return fail(B2P_ERR_ARG, "b2p_prof_read: null");
+  CK(cudaSetDevice(h->device)); CK(cudaDeviceSynchronize());
+  CK(h->dtype == B2P_F64 ? prof_read_f64(out, reset) : prof_read_f32(out, reset));
+  return B2P_OK;
+}
 int b2p_fma_peak(int dtype, int device, double* tflops) {
   if (!tflops) return B2P_ERR_ARG;
   CK(cudaSetDevice(device));

@@ -296,6 +296,7 @@ B2P_HD bool obb_separated(const T* p1, const T* m1, const T* c1, const T* h1, co
 // broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
 template <typename T>
 B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
+  PROF_T0
   if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
   for (int q = c.tid; q < m.ngeom; q += c.nt) {
     const int p = m.geom_prop[q];
@@ -329,6 +330,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
   }
   if (c.tid == 0) { s.ncand = base < MAXCAND ? base : MAXCAND; if (base > MAXCAND) s.flags |= FLAG_CANDFULL; }
   bsync(c);
+  PROF_ADD(PF_BROAD)
   const int ncand = s.ncand;
   const T tol = m.ccd_tolerance > 16 * Num<T>::eps() ? m.ccd_tolerance : 16 * Num<T>::eps();
   int cbase = 0;
@@ -371,6 +373,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
   }
   if (c.tid == 0) { s.ncon = cbase < MAXCON ? cbase : MAXCON; if (cbase > MAXCON) s.flags |= FLAG_CONTACTFULL; }
   bsync(c);
+  PROF_ADD(PF_NARROW)
 }
 
 

@@ -34,19 +34,30 @@ B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
 }
 template <typename T>
 B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
+  PROF_T0
   csync(c);
-  if (active) { forward_sweep(m, s, c); backward_sweep(m, s, c); dynamics_terms(m, s, c); }
+  PROF_ADD(PF_BARRIER)
+  if (active) { forward_sweep(m, s, c); PROF_ADD(PF_FK) backward_sweep(m, s, c); dynamics_terms(m, s, c); PROF_ADD(PF_DYN) }
   csync(c);
+  PROF_ADD(PF_BARRIER)
   if (active) collide(m, g, s, c, full_contacts);
+  PROF_ADD(PF_COLLIDE)
   csync(c);
+  PROF_ADD(PF_BARRIER)
   if (active) make_rows(m, g, s, c);
+  PROF_ADD(PF_ROWS)
 }
 template <typename T>
 B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
+  PROF_T0
   csync(c);
+  PROF_ADD(PF_BARRIER)
   if (active) {
+    PROF_COUNT(PF_NSTEP, 1)
     actuation_and_smooth(m, s, c);
+    PROF_ADD(PF_SMOOTH)
     solve_constraints(m, s, c);
+    PROF_RESET
     // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
     unsigned bad = 0;
     for (int d = c.tid; d < m.nv; d += c.nt) { if (!(fabs(s.qacc[d]) < T(1e10))) bad |= FLAG_BADQACC; if (!(fabs(s.qvel[d]) < T(1e10))) bad |= FLAG_BADQVEL; }
@@ -54,8 +65,11 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
     bad = block_or(c, bad);
     if (c.tid == 0 && bad) s.flags |= (int)bad;
   }
+  PROF_ADD(PF_MISC)
   csync(c);
+  PROF_ADD(PF_BARRIER)
   if (active) { if (do_integrate) integrate(m, s, c, freeze_tree); else bsync(c); }
+  PROF_ADD(PF_INTEGRATE)
 }
 
 // Derived-output record.  The "pos" part (site / geom poses, contacts, mass matrix, bias) reads step1 buffers that share
@@ -133,11 +147,14 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       conv = osc_converged(m, s, tg);
     }
     for (int t = 0; t < a.n_steps; t++) {
+      PROF_T0
       csync(c);
+      PROF_ADD(PF_BARRIER)
       if (active) {
         if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }   // min_max.py:14-19
         bsync(c);
       }
+      PROF_ADD(PF_OSC)
       for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); step1(m, g, s, c, full, active); }
       if (active && osc_converged(m, s, tg)) conv = true;
     }

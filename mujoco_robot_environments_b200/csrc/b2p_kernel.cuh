@@ -91,6 +91,19 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   }
 }
 
+// stage cycle counters of this translation unit (all zero unless built with -DB2P_PROF)
+static cudaError_t step_prof_read(unsigned long long* out, int reset) {
+#ifdef B2P_PROF
+  cudaError_t e = cudaMemcpyFromSymbol(out, g_prof, sizeof(unsigned long long) * PF_N);
+  if (e != cudaSuccess) return e;
+  if (reset) { unsigned long long z[PF_N] = {0}; e = cudaMemcpyToSymbol(g_prof, z, sizeof z); }
+  return e;
+#else
+  (void)reset; for (int i = 0; i < PF_N; i++) out[i] = 0;
+  return cudaSuccess;
+#endif
+}
+
 template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<T>) + 128; }
 
 // occupancy query + attribute setup (once per handle)

@@ -5,4 +5,5 @@ cudaError_t configure_f32(int device, int n_env, LaunchGeom* out) { return step_
 cudaError_t launch_f32(const LaunchGeom& lg, const void* d_model, const Globals<float>& g, const StepArgs<float>& a, int* next_env, cudaStream_t st) {
   return step_launch<float>(lg, d_model, g, a, next_env, st);
 }
+cudaError_t prof_read_f32(unsigned long long* out, int reset) { return step_prof_read(out, reset); }
 }  // namespace b2p

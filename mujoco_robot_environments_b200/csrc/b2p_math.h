@@ -16,7 +16,24 @@ enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3 };
 
-struct Ctx { int tid, nt; bool lock; };   // lock: the CTA's warps advance stage by stage together (shared instruction stream)
+struct Ctx { int tid, nt; bool lock; };
+
+// Optional per-stage cycle counters (build with -DB2P_PROF; read back through b2p_prof_read).  Off in the product build.
+enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_N };
+#if defined(B2P_PROF) && defined(__CUDACC__)
+static __device__ unsigned long long g_prof[PF_N];
+#endif
+#if defined(B2P_PROF) && defined(__CUDA_ARCH__)
+#define PROF_T0 long long pf_t0_ = clock64();
+#define PROF_ADD(i) { const long long pf_t1_ = clock64(); if (c.tid == 0) atomicAdd(&g_prof[i], (unsigned long long)(pf_t1_ - pf_t0_)); pf_t0_ = clock64(); }
+#define PROF_COUNT(i, n) { if (c.tid == 0) atomicAdd(&g_prof[i], (unsigned long long)(n)); }
+#define PROF_RESET pf_t0_ = clock64();
+#else
+#define PROF_T0
+#define PROF_ADD(i)
+#define PROF_COUNT(i, n)
+#define PROF_RESET
+#endif   // lock: the CTA's warps advance stage by stage together (shared instruction stream)
 
 template <typename T> struct Num;
 template <> struct Num<double> { static B2P_HD double eps() { return 2.220446049250313e-16; } static B2P_HD double minval() { return 1e-15; } static B2P_HD double big() { return 1e300; } };

@@ -173,12 +173,16 @@ B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gr
 // Newton direction: search = -H^-1 grad with H = M + J' W J factored on its block structure
 template <typename T>
 B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  PROF_T0
   assemble_H(m, s, c);
   bsync(c);
+  PROF_ADD(PF_ASSEMBLE)
   sp_cholesky(s.H, s.sp, m.tri, c);
+  PROF_ADD(PF_CHOL)
   sp_solve(s.H, s.sp, s.Mgrad, 6 * m.nprop, m.ntd, c);
   for (int d = c.tid; d < m.nv; d += c.nt) s.search[d] = -s.Mgrad[d];
   bsync(c);
+  PROF_ADD(PF_SOLVE)
 }
 template <typename T>
 B2P_HDN T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale) {
@@ -228,26 +232,32 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     return;
   }
   const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
+  PROF_T0
   const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
   for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
   bsync(c);
   cost_at(m, s, c, s.qacc);
   T gn2, cost = solver_update(m, s, c, gn2);
+  PROF_ADD(PF_SOLVE_INIT)
   int it = 0;
   // MuJoCo factors the Hessian before testing for termination; the factor at the converged point is never used, so the
   // test comes first here (identical iterates, one factorisation less per step)
   for (; it < m.iterations; it++) {
     newton_direction(m, s, c);
+    PROF_RESET
     const T alpha = line_search(m, s, c, scale);
+    PROF_ADD(PF_LS)
     if (alpha == 0) break;
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] += alpha * s.search[d]; s.Ma[d] += alpha * s.Mv[d]; }
     for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] += alpha * s.Jv[r];
     bsync(c);
     const T old = cost;
     cost = solver_update(m, s, c, gn2);
+    PROF_ADD(PF_UPDATE)
     const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
     if (improvement < m.tolerance || gradient < m.tolerance) { it++; break; }
   }
+  PROF_COUNT(PF_NITER, it)
   if (c.tid == 0) { s.niter = it; if (it >= m.iterations) s.flags |= FLAG_SOLVER_MAXITER; }
   bsync(c);
 }

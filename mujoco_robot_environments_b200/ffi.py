@@ -14,6 +14,8 @@ CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libb2p.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
 UNITS = ("b2p_api.cu", "b2p_kernel_f32.cu", "b2p_kernel_f64.cu")
+# per-unit flags: the fp32 throughput kernel uses the fast division / sqrt / sincos sequences (<= 2 ulp; its parity tolerance is 1e-4)
+UNIT_FLAGS = {"b2p_kernel_f32.cu": ["-use_fast_math"]}
 
 # enums of include/b2p.h
 F64, F32 = 0, 1
@@ -23,7 +25,7 @@ O = dict(SITE_XPOS=0, SITE_XMAT=1, QACC=2, QFRC_BIAS=3, CTRL=4, NCON=5, NEFC=6, 
          GEOM_XMAT=11, QACC_SMOOTH=12, EFC_FORCE=13)
 SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params",
            "b2p_osc_config", "b2p_set_full_contacts", "b2p_step_physics", "b2p_step_osc", "b2p_settle", "b2p_forward", "b2p_get",
-           "b2p_status", "b2p_fma_peak", "b2p_last_error"]
+           "b2p_status", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error"]
 
 
 def sources():
@@ -31,7 +33,7 @@ def sources():
            [os.path.join(_HERE, "..", "include", f) for f in ("b2p.h", "b2p_model_layout.h")]
 
 
-def build(force: bool = False, verbose: bool = False) -> str:
+def build(force: bool = False, verbose: bool = False, extra=()) -> str:
     """Compile libb2p.so in-tree for sm_100a (nvcc cross-compiles without a GPU).  The translation units are
     compiled in parallel (the fp32 and fp64 kernel instantiations dominate) and linked into one shared library."""
     if not force and os.path.exists(LIB_PATH) and os.path.getmtime(LIB_PATH) >= max(os.path.getmtime(s) for s in sources()):
@@ -42,7 +44,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     for u in UNITS:
         obj = os.path.join(bdir, u.replace(".cu", ".o"))
         objs.append(obj)
-        cmd = ["nvcc"] + NVCC_FLAGS + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, u)]
+        cmd = ["nvcc"] + NVCC_FLAGS + UNIT_FLAGS.get(u, []) + list(extra) + (["-Xptxas", "-v"] if verbose else []) + ["-c", "-o", obj, os.path.join(CSRC, u)]
         procs.append((cmd, subprocess.Popen(cmd)))
     for cmd, p in procs:
         if p.wait() != 0:
@@ -78,6 +80,7 @@ def lib() -> C.CDLL:
     L.b2p_forward.argtypes = [vp, i32, vp]
     L.b2p_get.argtypes = [vp, i32, vp, vp]
     L.b2p_status.argtypes = [vp, vp, i32, vp]
+    L.b2p_prof_read.argtypes = [vp, C.POINTER(C.c_ulonglong), i32]
     L.b2p_fma_peak.argtypes = [i32, i32, C.POINTER(C.c_double)]
     L.b2p_last_error.restype = C.c_char_p
     for s in SYMBOLS:
