@@ -113,23 +113,23 @@ B2P_HD void solve6_local(const T* L, int s0, T* x) {   // x = 6 consecutive real
 // are bank-conflict free for 16 rows).  The host build of these templates (tests/_hostemu) keeps the generic path.
 B2P_HD bool sp_dense_tail(const SpStruct& st, int b) { return b == st.nblk - 1 && st.blk[b].nrows == st.blk[b].len && st.blk[b].len > 6 && st.blk[b].len <= 16; }
 #ifdef __CUDA_ARCH__
+// Branch-free on purpose: entries above the diagonal (j > i) hold don't-care values that are never read, so every lane
+// executes the same FMA stream and the row stays in registers (predicated updates made ptxas demote it to local memory).
 template <typename T>
 __device__ __forceinline__ void chol16_warp(T* A, int s0, int n, int lane) {
   T a[16];
   const int i = lane;
 #pragma unroll
-  for (int j = 0; j < 16; j++) a[j] = (i < n && j <= i) ? A[tri_idx(s0 + i, s0 + j)] : ((j == i && i < 16) ? T(1) : T(0));
-  T dg = 1;
+  for (int j = 0; j < 16; j++) { const bool in = i < n && j <= i; const T v = A[in ? tri_idx(s0 + i, s0 + j) : 0]; a[j] = in ? v : (j == i ? T(1) : T(0)); }
 #pragma unroll
   for (int k = 0; k < 16; k++) {
     const T akk = __shfl_sync(0xffffffffu, a[k], k);
-    const T d = akk > Num<T>::minval() ? sqrt(akk) : sqrt(Num<T>::minval());
+    const T d = sqrt(akk > Num<T>::minval() ? akk : Num<T>::minval());
     const T id = 1 / d;
-    if (i == k) { a[k] = d; dg = d; } else if (i > k) a[k] *= id;
+    a[k] = i == k ? d : a[k] * id;
 #pragma unroll
-    for (int j = k + 1; j < 16; j++) { const T ljk = __shfl_sync(0xffffffffu, a[k], j); if (i >= j) a[j] -= a[k] * ljk; }
+    for (int j = k + 1; j < 16; j++) a[j] -= a[k] * __shfl_sync(0xffffffffu, a[k], j);
   }
-  (void)dg;
 #pragma unroll
   for (int j = 0; j < 16; j++) if (i < n && j <= i) A[tri_idx(s0 + i, s0 + j)] = a[j];
 }
@@ -138,20 +138,24 @@ template <typename T>
 __device__ __forceinline__ void solve16_warp(const T* L, const SpStruct& st, int b, T* x, int np6, int ntd, int lane) {
   const int s0 = st.blk[b].start, n = st.blk[b].len, np = st.blk[b].nprev;
   const bool mine = lane < n;
-  T xv = mine ? x[sp_dof(s0 + lane, np6, ntd)] : T(0);
-  const T rd = mine ? 1 / L[tri_idx(s0 + lane, s0 + lane)] : T(1);
-  const int rowbase = tri_idx(s0 + (mine ? lane : 0), s0);
-  for (int k = 0; k < n; k++) {
+  const int me = mine ? lane : 0;
+  T xv = mine ? x[sp_dof(s0 + me, np6, ntd)] : T(0);
+  const T rd = 1 / L[tri_idx(s0 + me, s0 + me)];
+  const int rowbase = tri_idx(s0 + me, s0);
+  for (int k = 0; k < n; k++) {                // forward: L y = b
+    const T l = (mine && lane > k) ? L[rowbase + k] : T(0);
     const T xk = __shfl_sync(0xffffffffu, xv * rd, k);
-    if (lane == k) xv = xk; else if (mine && lane > k) xv -= L[rowbase + k] * xk;
+    xv = lane == k ? xk : xv - l * xk;
   }
-  T acc = 0;                                   // backward: lane a < np accumulates sum_k L[k][prev a] * x_k
+  T acc = 0;                                   // backward: L' x = y; lane a < np accumulates sum_k L[k][prev a] * x_k
   const int pcol = lane < np ? st.prev[b][lane] : 0;
   for (int k = n - 1; k >= 0; k--) {
-    const T xk = __shfl_sync(0xffffffffu, xv * rd, k);
     const int kb = tri_idx(s0 + k, 0);
-    if (lane == k) xv = xk; else if (lane < k) xv -= L[kb + s0 + lane] * xk;
-    if (lane < np) acc += L[kb + pcol] * xk;
+    const T l = lane < k ? L[kb + s0 + lane] : T(0);
+    const T lp = lane < np ? L[kb + pcol] : T(0);
+    const T xk = __shfl_sync(0xffffffffu, xv * rd, k);
+    xv = lane == k ? xk : xv - l * xk;
+    acc += lp * xk;
   }
   if (mine) x[sp_dof(s0 + lane, np6, ntd)] = xv;
   if (lane < np) x[sp_dof(pcol, np6, ntd)] -= acc;
