@@ -295,8 +295,9 @@ B2P_HD bool obb_separated(const T* p1, const T* m1, const T* c1, const T* h1, co
 
 // broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
 template <typename T>
-B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts) {
+B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
   PROF_T0
+  if (active) {
   if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
   for (int q = c.tid; q < m.ngeom; q += c.nt) {
     const int p = m.geom_prop[q];
@@ -330,7 +331,10 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
   }
   if (c.tid == 0) { s.ncand = base < MAXCAND ? base : MAXCAND; if (base > MAXCAND) s.flags |= FLAG_CANDFULL; }
   bsync(c);
+  }
   PROF_ADD(PF_BROAD)
+  csync(c, LK_NARROW);
+  if (!active) return;
   const int ncand = s.ncand;
   const T tol = m.ccd_tolerance > 16 * Num<T>::eps() ? m.ccd_tolerance : 16 * Num<T>::eps();
   int cbase = 0;

@@ -35,14 +35,14 @@ B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
 template <typename T>
 B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
   PROF_T0
-  csync(c);
+  csync(c, LK_FK);
   PROF_ADD(PF_BARRIER)
   if (active) { forward_sweep(m, s, c); PROF_ADD(PF_FK) backward_sweep(m, s, c); dynamics_terms(m, s, c); PROF_ADD(PF_DYN) }
-  csync(c);
+  csync(c, LK_COLLIDE);
   PROF_ADD(PF_BARRIER)
-  if (active) collide(m, g, s, c, full_contacts);
+  collide(m, g, s, c, full_contacts, active);
   PROF_ADD(PF_COLLIDE)
-  csync(c);
+  csync(c, LK_ROWS);
   PROF_ADD(PF_BARRIER)
   if (active) make_rows(m, g, s, c);
   PROF_ADD(PF_ROWS)
@@ -50,14 +50,17 @@ B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, con
 template <typename T>
 B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
   PROF_T0
-  csync(c);
+  csync(c, LK_STEP2);
   PROF_ADD(PF_BARRIER)
   if (active) {
     PROF_COUNT(PF_NSTEP, 1)
     actuation_and_smooth(m, s, c);
-    PROF_ADD(PF_SMOOTH)
-    solve_constraints(m, s, c);
-    PROF_RESET
+  }
+  PROF_ADD(PF_SMOOTH)
+  csync(c, LK_SOLVE);
+  solve_constraints(m, s, c, active);
+  PROF_RESET
+  if (active) {
     // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
     unsigned bad = 0;
     for (int d = c.tid; d < m.nv; d += c.nt) { if (!(fabs(s.qacc[d]) < T(1e10))) bad |= FLAG_BADQACC; if (!(fabs(s.qvel[d]) < T(1e10))) bad |= FLAG_BADQVEL; }
@@ -66,7 +69,7 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
     if (c.tid == 0 && bad) s.flags |= (int)bad;
   }
   PROF_ADD(PF_MISC)
-  csync(c);
+  csync(c, LK_INTEGRATE);
   PROF_ADD(PF_BARRIER)
   if (active) { if (do_integrate) integrate(m, s, c, freeze_tree); else bsync(c); }
   PROF_ADD(PF_INTEGRATE)
@@ -142,17 +145,15 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     bool conv = false;
     step1(m, g, s, c, full, active);
     if (a.n_steps == 0 && active) {   // OSC.compute_control_output() / is_converged() for the current state, no stepping (derived-output CTRL)
-      if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }
-      bsync(c);
+      osc_torque(m, s, tg, grip, c);
       conv = osc_converged(m, s, tg);
     }
     for (int t = 0; t < a.n_steps; t++) {
       PROF_T0
-      csync(c);
+      csync(c, LK_TICK);
       PROF_ADD(PF_BARRIER)
       if (active) {
-        if (c.tid == 0) { T tau[7]; osc_torque(m, s, tg, tau); for (int i = 0; i < 7; i++) s.ctrl[i] = tau[i]; s.ctrl[7] = grip ? T(255) : T(0); }   // min_max.py:14-19
-        bsync(c);
+        osc_torque(m, s, tg, grip, c);
       }
       PROF_ADD(PF_OSC)
       for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); step1(m, g, s, c, full, active); }

@@ -60,7 +60,7 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
   static_assert(offsetof(Scratch<T>, qpos) == 0 && sizeof(Scratch<T>) % 16 == 0, "state record must head a 16-byte aligned Scratch");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const Ctx c = {lane, 32, a.lockstep != 0};
+  const Ctx c = {lane, 32, a.lockstep};
   if (threadIdx.x == 0) {
     for (int i = 0; i <= KernelCfg<T>::kWarps; i++) mbar_init(&sm.bar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
@@ -82,7 +82,9 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
       if (lane == 0) { fence_async_smem(); mbar_expect_tx(bar, kRecBytes); tma_load_1d(s.qpos, rec, kRecBytes, bar); }
       mbar_wait(bar, phase); phase ^= 1;
     }
+    PROF_T0
     run_env(sm.model, g, s, a, env, c, true, active);
+    if (active) PROF_ADD(PF_TOTAL)
     if (active) {
       __syncwarp();
       if (lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }

@@ -16,10 +16,10 @@ enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3 };
 
-struct Ctx { int tid, nt; bool lock; };
+struct Ctx { int tid, nt; int lock; };   // lock: bit mask of the CTA-wide stage barriers in use (LK_*), 0 = warps run free
 
 // Optional per-stage cycle counters (build with -DB2P_PROF; read back through b2p_prof_read).  Off in the product build.
-enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_N };
+enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_TOTAL, PF_N };
 #if defined(B2P_PROF) && defined(__CUDACC__)
 static __device__ unsigned long long g_prof[PF_N];
 #endif
@@ -50,11 +50,20 @@ B2P_HD void bsync(const Ctx&) {
 // CTA-wide stage barrier, only in lockstep mode: the warps of a CTA (one scene each) enter every pipeline stage
 // together so that they share instruction-cache lines -- the per-step code is ~10x the SM's 32 KB L1.5 I-cache.
 // Every warp of the CTA must reach every csync(), whether or not it holds a scene.
-B2P_HD void csync(const Ctx& c) {
+enum { LK_FK = 1, LK_COLLIDE = 2, LK_ROWS = 4, LK_STEP2 = 8, LK_INTEGRATE = 16, LK_TICK = 32, LK_NEWTON = 64, LK_NARROW = 128, LK_SOLVE = 256, LK_ALL = 511, LK_DEFAULT = 63 + 128 + 256 };
+B2P_HD void csync(const Ctx& c, int site) {
 #ifdef __CUDA_ARCH__
-  if (c.lock) __syncthreads();
+  if (c.lock & site) __syncthreads();
 #else
-  (void)c;
+  (void)c; (void)site;
+#endif
+}
+// CTA-wide OR of a per-warp predicate at barrier `site`; the warp's own predicate when that barrier is not in use
+B2P_HD bool csync_or(const Ctx& c, int site, bool p) {
+#ifdef __CUDA_ARCH__
+  return (c.lock & site) ? (__syncthreads_or(p) != 0) : p;
+#else
+  (void)c; (void)site; return p;
 #endif
 }
 B2P_HD bool csync_and(const Ctx& c, bool p) {

@@ -223,31 +223,37 @@ B2P_HDN T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale
   return best.alpha;
 }
 template <typename T>
-B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool active) {
   const int nv = m.nv;
-  if (s.nefc == 0) {
+  const bool has = active && s.nefc > 0;
+  if (active && !has) {
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] = s.qacc_smooth[d]; s.qfrc_con[d] = 0; }
     if (c.tid == 0) s.niter = 0;
     bsync(c);
-    return;
   }
   const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
+  T gn2 = 0, cost = 0;
   PROF_T0
-  const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
-  for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
-  bsync(c);
-  cost_at(m, s, c, s.qacc);
-  T gn2, cost = solver_update(m, s, c, gn2);
+  if (has) {
+    const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
+    for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
+    bsync(c);
+    cost_at(m, s, c, s.qacc);
+    cost = solver_update(m, s, c, gn2);
+  }
   PROF_ADD(PF_SOLVE_INIT)
   int it = 0;
   // MuJoCo factors the Hessian before testing for termination; the factor at the converged point is never used, so the
-  // test comes first here (identical iterates, one factorisation less per step)
-  for (; it < m.iterations; it++) {
+  // test comes first here (identical iterates, one factorisation less per step).  In lockstep mode the CTA's warps start
+  // every Newton iteration together (a scene that has converged idles through the iterations its neighbours still need).
+  bool run = has && it < m.iterations;
+  while (csync_or(c, LK_NEWTON, run)) {
+    if (!run) continue;
     newton_direction(m, s, c);
     PROF_RESET
     const T alpha = line_search(m, s, c, scale);
     PROF_ADD(PF_LS)
-    if (alpha == 0) break;
+    if (alpha == 0) { run = false; continue; }
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] += alpha * s.search[d]; s.Ma[d] += alpha * s.Mv[d]; }
     for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] += alpha * s.Jv[r];
     bsync(c);
@@ -255,11 +261,14 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     cost = solver_update(m, s, c, gn2);
     PROF_ADD(PF_UPDATE)
     const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
-    if (improvement < m.tolerance || gradient < m.tolerance) { it++; break; }
+    it++;
+    if (improvement < m.tolerance || gradient < m.tolerance || it >= m.iterations) run = false;
   }
-  PROF_COUNT(PF_NITER, it)
-  if (c.tid == 0) { s.niter = it; if (it >= m.iterations) s.flags |= FLAG_SOLVER_MAXITER; }
-  bsync(c);
+  if (has) {
+    PROF_COUNT(PF_NITER, it)
+    if (c.tid == 0) { s.niter = it; if (it >= m.iterations) s.flags |= FLAG_SOLVER_MAXITER; }
+    bsync(c);
+  }
 }
 
 
