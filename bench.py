@@ -30,6 +30,16 @@ WORKLOADS = {
     "c2": dict(envs=4096, dtype="f64", osc=False, desc="default rearrangement scene physics-only, 4096 envs, fp64 (BASELINE configs[1])"),
 }
 CONTROL_STEPS = 5
+# per-scene status bits (csrc/b2p_math.h): the first three are mj_checkPos/Vel/Acc; the rest are capacity / iteration-cap notes
+FLAG_NAMES = ["badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter"]
+
+
+def measured_traffic(workload):
+    """dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of the step kernel from the committed ncu --set full capture."""
+    try:
+        return float(json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))[workload]["dram_bytes_per_launch"])
+    except Exception:
+        return None
 
 
 # ------------------------------------------------------------------------------------------ CPU baseline (oracle port)
@@ -192,8 +202,10 @@ def run_ours(args, wl):
     e1.record(); barrier()
     e2e_ms = torch.tensor([e0.elapsed_time(e1)], dtype=torch.float64, device=dev)
     sampler.stop_flag = True; sampler.join(timeout=2)
-    status_bad = int((p.status() != 0).sum().item())
-    stats = torch.tensor([float(p.converged.sum().item()), float(n), float(status_bad)], dtype=torch.float64, device=dev)
+    st_bits = p.status()
+    status_bad = int((st_bits != 0).sum().item())
+    flag_counts = [float(((st_bits & (1 << b)) != 0).sum().item()) for b in range(len(FLAG_NAMES))]
+    stats = torch.tensor([float(p.converged.sum().item()), float(n), float(status_bad)] + flag_counts, dtype=torch.float64, device=dev)
     if world > 1:
         dist.all_reduce(total_ms, op=dist.ReduceOp.MAX); dist.all_reduce(e2e_ms, op=dist.ReduceOp.MAX)
         dist.all_reduce(stats, op=dist.ReduceOp.SUM)     # episode statistics: the only collective on this path
@@ -219,10 +231,11 @@ def run_ours(args, wl):
                 "dtype": wl["dtype"], "data": "synthetic",
                 "config": {"workload": args.workload + ": " + wl["desc"], "envs_per_gpu": n, "control_ticks_per_launch": ticks, "physics_steps_per_launch": steps_per_launch,
                            "l2": "flushed between timed iterations (192 MiB fill, untimed)", "launch": p.launch_info(), "wall_s_incl_flush": wall,
-                           "episode_stats": {"converged_envs": stats[0].item(), "envs": stats[1].item(), "bad_state_envs": stats[2].item()}},
+                           "episode_stats": {"converged_envs": stats[0].item(), "envs": stats[1].item(), "flagged_envs": stats[2].item(),
+                                             "flags": {k: stats[3 + i].item() for i, k in enumerate(FLAG_NAMES)}}},
                 "clocks": sampler.summary(), "gpu_launches": int(launches) * world,
                 "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(n * (128 * w + 1))},
-                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload),
                              "peak_source": which, "algorithmic_bytes_per_env_step": alg_b,
                              "note": "path is latency / FP-issue bound, not HBM bound (SURVEY 7.3 H7); FP pipe figures below",
                              "fma_peak_tflops_measured": fma.value}}
