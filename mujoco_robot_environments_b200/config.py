@@ -26,13 +26,30 @@ UNSUPPORTED_PROP_GROUPS = ("apple", "itl_agent_demo", "itl_rearrangement")   # s
 # config/task/*.yaml
 TASK_GROUPS: Dict[str, Dict[str, Any]] = {
     "rearrangement": dict(initializers=dict(seed=1, workspace=dict(min_pose=[0.35, -0.4, 0.43], max_pose=[0.55, 0.4, 0.435]))),   # rearrangement.yaml:2-7
-    "rearrangement_w_targets": dict(initializers=dict(seed=1, workspace=dict(min_pose=[0.35, -0.4, 0.43], max_pose=[0.55, 0.4, 0.435]))),
+    # rearrangement_w_targets.yaml:2-56 (zones are visual-only boxes on the table, rearrangement.py:104-116)
+    "rearrangement_w_targets": dict(
+        initializers=dict(seed=1, workspace=dict(min_pose=[0.35, -0.4, 0.43], max_pose=[0.55, 0.4, 0.435])),
+        target_locations={
+            "top_left": dict(name="top_left", location=[0.55, 0.4, 0.4], size=[0.075, 0.15, 0.01], rgba=[1.0, 0.0, 0.0, 0.1]),
+            "bottom_left": dict(name="bottom_left", location=[0.35, 0.4, 0.4], size=[0.075, 0.15, 0.01], rgba=[0.0, 1.0, 0.0, 0.1]),
+            "top_right": dict(name="top_right", location=[0.55, -0.4, 0.4], size=[0.075, 0.15, 0.01], rgba=[0.0, 0.0, 1.0, 0.1]),
+            "bottom_right": dict(name="bottom_right", location=[0.35, -0.4, 0.4], size=[0.075, 0.15, 0.01], rgba=[1.0, 1.0, 0.0, 0.1]),
+            "top_middle": dict(name="top_middle", location=[0.55, 0.0, 0.4], size=[0.075, 0.15, 0.01], rgba=[1.0, 0.0, 1.0, 0.1]),
+            "bottom_middle": dict(name="bottom_middle", location=[0.35, 0.0, 0.4], size=[0.075, 0.15, 0.01], rgba=[0.0, 1.0, 1.0, 0.1]),
+        },
+        colour_target_map=dict(red="top_left", green="bottom_left", blue="top_right", yellow="bottom_right", magenta="top_middle", cyan="bottom_middle")),
 }
+
+# config/arena/cameras/transporter_data_collection.yaml:1-6 (the `rearrangement_table` arena's camera list)
+CAMERAS = [dict(name="overhead_camera", pos=[0.7, 0.0, 1.3], quat=[0.707, 0.0, 0.0, -0.707], height=480, width=640, fovy=61)]
+# config/dataset/default.yaml
+DATASET = dict(num_episodes=1000, max_steps=10, max_episodes_per_file=10)
 
 DEFAULT_CONFIG: Dict[str, Any] = {
     # config/rearrangement.yaml:2-6
     "physics_dt": 0.001, "control_dt": 0.005, "gravity": [0.0, 0.0, -9.8], "nconmax": 1000, "njmax": 2000,
-    "arena": {"props": copy.deepcopy(PROP_GROUPS["colour_splitter"])},
+    "arena": {"props": copy.deepcopy(PROP_GROUPS["colour_splitter"]), "cameras": copy.deepcopy(CAMERAS)},
+    "dataset": copy.deepcopy(DATASET),
     "task": copy.deepcopy(TASK_GROUPS["rearrangement"]),
     "robots": {
         "arm": {
@@ -58,6 +75,7 @@ def compose(overrides: Optional[Iterable[str]] = None) -> Dict[str, Any]:
     cfg = copy.deepcopy(DEFAULT_CONFIG)
     for ov in overrides or ():
         key, _, val = ov.partition("=")
+        add = key.strip().startswith("+")              # hydra "+key=value": append a new key (e.g. "+name=colour_splitter")
         key = key.strip().lstrip("+")
         if key in _GROUPS:
             top, sub, table = _GROUPS[key]
@@ -76,7 +94,7 @@ def compose(overrides: Optional[Iterable[str]] = None) -> Dict[str, Any]:
             if p not in node or not isinstance(node[p], dict):
                 raise KeyError("override %r: no config node %r" % (ov, p))
             node = node[p]
-        if parts[-1] not in node:
+        if parts[-1] not in node and not add:
             raise KeyError("override %r: unknown key (prefix with a config group or use an existing dotted path)" % ov)
         node[parts[-1]] = yaml.safe_load(val)
     # ${physics_dt} / ${control_dt} interpolation of osc.yaml:3-4

@@ -22,6 +22,7 @@ import torch
 
 from . import config as cfglib
 from .controllers import BatchedMinMax, BatchedOSC
+from .expert import Camera, SortColoursExpert, sample_prop_colours
 from .physics import BatchedPhysics
 from .robot_arm import BatchedRobotArm
 
@@ -68,6 +69,13 @@ class BatchedRearrangementEnv:
         self.has_prop = torch.arange(self.max_props, device=self.device)[None, :] < self.n_props[:, None]
         self.prop_half_size = torch.tensor(half, device=self.device, dtype=self.dtype)
         p.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8))
+        # colour label + rgba per prop (props.py:604-617, :286-291); "grey" of single_block has no COLOURS entry in the reference either
+        cidx, rgba = sample_prop_colours(self.num_envs, self.max_props, [c for c in pc["colours"] if c != "grey"], crng)
+        self.prop_colour = torch.tensor(cidx, device=self.device)
+        self.prop_rgba = torch.tensor(rgba, device=self.device)
+        self.camera = Camera(next(c for c in self._cfg["arena"]["cameras"] if c["name"] == "overhead_camera"))
+        self.overhead_camera_height, self.overhead_camera_width = self.camera.height, self.camera.width
+        self._expert: Optional[SortColoursExpert] = None
         # controllers (hydra partial `controller(physics, arm)` in the reference, robot_arm.py:37,46)
         cc = self._cfg["robots"]["arm"]["controller_config"]["controller_params"]
         ee = self._cfg["robots"]["end_effector"]["controller_config"]
@@ -198,12 +206,14 @@ class BatchedRearrangementEnv:
         self.mode = "pick"                                                                    # :331
         return TimeStep(StepType.FIRST, 0.0, 0.0, self._compute_observation())
 
-    def step(self, action_dict) -> TimeStep:
+    def step(self, action_dict, active: Optional[torch.Tensor] = None) -> TimeStep:
+        """``active`` (bool [n_env], batched variant only): scenes outside it hold the arm at its home pose for the duration of
+        the phase table (their episode is over; a batch steps all scenes for the same simulated time)."""
         observation = self._compute_observation()                                             # :343 (observation BEFORE acting)
         if self.mode == "pick":
-            self.pick(action_dict["pose"]); self.mode = "place"
+            self.pick(action_dict["pose"], active); self.mode = "place"
         else:
-            self.place(action_dict["pose"]); self.mode = "pick"
+            self.place(action_dict["pose"], active); self.mode = "pick"
         return TimeStep(StepType.MID, 0.0, 0.0, observation)
 
     def _phase(self, duration: float, what: str):
@@ -222,30 +232,66 @@ class BatchedRearrangementEnv:
         t = t.to(self.device, self.dtype).clone(); t[:, 2] = 0.575
         return t
 
-    def _pick_or_place(self, pose, grip_status: str, names):
+    def _pick_or_place(self, pose, grip_status: str, names, active: Optional[torch.Tensor] = None):
         osc, zeros = self._osc, torch.zeros(3, device=self.device, dtype=self.dtype)
         pose = self._pose_tensor(pose)
         pre = pose.clone(); pre[:, 2] = 0.9
+        if active is not None:                      # idle scenes: every phase targets the home pose, gripper unchanged
+            idle = ~active.to(self.device, torch.bool)
+            home = torch.cat([self.eef_home_pose, torch.tensor(DOWN_QUAT, device=self.device, dtype=self.dtype).expand(self.num_envs, 4)], 1)
+            pose[idle] = home[idle]; pre[idle] = home[idle]
         if grip_status == "max":
             osc.set_target(position=pre[:, :3], velocity=zeros, quat=pre[:, 3:], angular_velocity=zeros)    # :365-370
         else:
             osc.set_target(position=pre[:, :3], quat=pre[:, 3:])                                            # :411-414
         self._phase(2.0, names[0])
         osc.set_target(position=pose[:, :3]); self._phase(2.0, names[1])
-        self._minmax.status = grip_status; self._phase(1.0, names[2])
+        if active is None:
+            self._minmax.status = grip_status
+        else:
+            self._minmax.set_status(torch.full((self.num_envs,), 1 if grip_status == "max" else 0, dtype=torch.uint8, device=self.device), ~idle)
+        self._phase(1.0, names[2])
         osc.set_target(position=pre[:, :3]); self._phase(2.0, names[3])
         osc.set_target(position=self.eef_home_pose, quat=torch.tensor(DOWN_QUAT, device=self.device, dtype=self.dtype))
         self._phase(2.0, names[4])
 
-    def pick(self, pose):
+    def pick(self, pose, active: Optional[torch.Tensor] = None):
         """rearrangement.py:358-401."""
         self._pick_or_place(pose, "max", ("move arm to pre pick position", "move arm to pick position", "close gripper",
-                                          "move arm to pre grasp position", "move arm to home position"))
+                                          "move arm to pre grasp position", "move arm to home position"), active)
 
-    def place(self, pose):
+    def place(self, pose, active: Optional[torch.Tensor] = None):
         """rearrangement.py:403-440."""
         self._pick_or_place(pose, "min", ("move arm to pre place position", "move arm to place position", "open gripper",
-                                          "move arm to pre place position", "move arm to home position"))
+                                          "move arm to pre place position", "move arm to home position"), active)
+
+    # ------------------------------------------------------------------ scripted expert + camera (SURVEY 8f-1)
+    @property
+    def expert(self) -> SortColoursExpert:
+        if self._expert is None:
+            self._expert = SortColoursExpert(self)
+        return self._expert
+
+    def sort_colours(self):
+        """rearrangement.py:700-751 per scene -> (in_progress [n], pick_pose [n, 7], place_pose [n, 7])."""
+        in_progress, pick, place, _ = self.expert.sort_colours()
+        return in_progress, pick, place
+
+    def prop_pick(self, prop_id):
+        return self.expert.prop_pick(torch.as_tensor(prop_id, device=self.device).expand(self.num_envs).to(torch.int64))
+
+    def prop_place(self, prop_id, min_pose=None, max_pose=None):
+        w = self._cfg["task"]["initializers"]["workspace"]
+        lo = torch.as_tensor(w["min_pose"] if min_pose is None else min_pose, device=self.device, dtype=self.dtype)
+        hi = torch.as_tensor(w["max_pose"] if max_pose is None else max_pose, device=self.device, dtype=self.dtype)
+        ex = lambda t: t.expand(self.num_envs, 3) if t.dim() == 1 else t
+        return self.expert.prop_place(torch.as_tensor(prop_id, device=self.device).expand(self.num_envs).to(torch.int64), ex(lo), ex(hi))
+
+    def world_2_pixel(self, camera_name, coords):
+        return self.camera.world_2_pixel(coords)
+
+    def get_camera_metadata(self):
+        return self.camera.metadata()
 
     # ------------------------------------------------------------------ specs / observation
     def _compute_observation(self) -> Dict[str, torch.Tensor]:
@@ -269,7 +315,8 @@ class BatchedRearrangementEnv:
     def props_info(self):
         """rearrangement.py:277-295 (poses only; labels are render-side): per scene/prop position + orientation."""
         o = self._compute_observation()
-        return {"position": o["prop_pos"], "orientation": o["prop_quat"], "has_prop": self.has_prop, "half_size": self.prop_half_size}
+        return {"position": o["prop_pos"], "orientation": o["prop_quat"], "has_prop": self.has_prop, "half_size": self.prop_half_size,
+                "rgba": self.prop_rgba, "colour": self.prop_colour}
 
 
 def RearrangementEnv(viewer=None, cfg=None, **kw) -> BatchedRearrangementEnv:
