@@ -28,6 +28,8 @@ sys.path.insert(0, os.path.join(ROOT, "tests"))
 WORKLOADS = {
     "c3": dict(envs=16384, dtype="f32", osc=True, desc="colour_splitter props + OSC in the loop, 16384 envs/GPU, fp32 (BASELINE configs[2])"),
     "c2": dict(envs=4096, dtype="f64", osc=False, desc="default rearrangement scene physics-only, 4096 envs, fp64 (BASELINE configs[1])"),
+    # side workload: overhead-camera observations of configs[3]; metric frames/s, HBM-write bound
+    "render": dict(envs=2048, dtype="f32", osc=False, desc="overhead camera rgb+depth+segmentation 480x640 of 2048 scenes/GPU, arm in view in 1 of 4 scenes"),
 }
 CONTROL_STEPS = 5
 # per-scene status bits (csrc/b2p_math.h): the first three are mj_checkPos/Vel/Acc; the rest are capacity / iteration-cap notes
@@ -120,6 +122,98 @@ def run_reference(args, wl):
             "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
+
+
+def _render_cpu_worker(args):
+    seed, seconds = args
+    import numpy as np
+    import rnd
+    import scenarios as sc
+    from orc import Oracle
+    st, size, active = sc.make_states(1, seed=seed)
+    o = Oracle(sc.default_blob()); sc.oracle_load(o, st[0], size[0], active[0]); o.forward()
+    blob = rnd.render_blob()
+    frames, t0 = 0, time.perf_counter()
+    while time.perf_counter() - t0 < seconds:
+        rnd.render(blob, o.geom_xpos, o.geom_xmat, None, size[0], active[0]); frames += 1
+    return frames, time.perf_counter() - t0
+
+
+def run_render(args, wl):
+    """frames/s of b2p_render (rgb u8 + depth f32 + seg i32 per frame = 11 B/pixel written).  One "step" = one frame of every scene."""
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    import scenarios as sc
+    from mujoco_robot_environments_b200.physics import BatchedPhysics
+    from mujoco_robot_environments_b200.render import BatchedRenderer
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local); dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    n = args.envs or wl["envs"]
+    st, size, active = sc.make_states(n, seed=1234 + rank)
+    st[::4, :7] = np.asarray([0.0, 0.35, 0.0, -1.9, 0.0, 2.25, 0.785]) + 0.2 * (np.random.default_rng(7).random((len(st[::4]), 7)) - 0.5)
+    p = BatchedPhysics(n, dtype=torch.float32, device=dev)
+    p.state.copy_(torch.tensor(st, dtype=torch.float32)); p.set_env_params(torch.tensor(size), torch.tensor(active)); p.forward(full_contacts=False)
+    r = BatchedRenderer(dev)
+    rgba = torch.tensor(np.random.default_rng(1).uniform(0, 1, (n, 4, 4)).astype(np.float32), device=dev)
+    out = r.alloc(n)
+    H, W = r.height, r.width
+    bytes_per_frame = H * W * 11
+    h_rgb = torch.empty(min(n, 64), H, W, 3, dtype=torch.uint8).pin_memory()
+    for _ in range(args.warmup):
+        r.render(p, rgba, out=out)
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local); sampler.start()
+    l0 = r.query("LAUNCHES")
+    ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
+    if world > 1:
+        dist.barrier()
+    torch.cuda.synchronize()
+    for i in range(args.steps):             # outputs (n x 3.4 MB >> 126 MB L2) are larger than L2: no flush needed
+        ev[i][0].record(); r.render(p, rgba, out=out); ev[i][1].record()
+    torch.cuda.synchronize()
+    ms = sum(a.elapsed_time(b) for a, b in ev)
+    launches = r.query("LAUNCHES") - l0
+    # end to end: poses come from a physics launch on host-provided state; a batch of frames is read back to pinned host memory
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    h_state = torch.tensor(st, dtype=torch.float32).pin_memory()
+    e0.record()
+    for i in range(max(2, args.steps)):
+        p.state.copy_(h_state, non_blocking=True); p.forward(full_contacts=False); r.render(p, rgba, out=out); h_rgb.copy_(out["rgb"][:h_rgb.shape[0]], non_blocking=True)
+    e1.record(); torch.cuda.synchronize()
+    e2e_ms = e0.elapsed_time(e1) / max(2, args.steps)
+    sampler.stop_flag = True; sampler.join(timeout=2)
+    t = torch.tensor([ms, e2e_ms], dtype=torch.float64, device=dev)
+    if world > 1:
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+    if rank == 0:
+        value = n * world * args.steps / (t[0].item() * 1e-3)
+        try:
+            peak, which = float(json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+        except Exception:
+            peak, which = 6650.0, "fallback (B200_PROFILING.md)"
+        achieved = bytes_per_frame * n / (t[0].item() * 1e-3 / args.steps) / 1e9
+        copied, cast = r.query("TILES_COPIED"), r.query("TILES_CAST")
+        line = {"metric": "overhead-camera frames/sec (rgb+depth+seg)", "value": value, "unit": "frames/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+                "ms_per_step": t[0].item() / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+                "config": {"workload": "render: " + wl["desc"], "envs_per_gpu": n, "l2": "outputs (%.1f GB per step) exceed L2" % (bytes_per_frame * n / 1e9),
+                           "tiles_copied_frac": copied / max(1, copied + cast)},
+                "clocks": sampler.summary(), "gpu_launches": int(launches) * world,
+                "e2e": {"value": n * world / (t[1].item() * 1e-3), "unit": "frames/s", "h2d_bytes_per_step": int(h_state.numel() * 4), "d2h_bytes_per_step": int(h_rgb.numel())},
+                "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic("render"),
+                             "peak_source": which, "algorithmic_bytes_per_frame": bytes_per_frame}}
+        if world == 1 and not args.no_cpu:
+            subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+            cores = os.cpu_count() or 1
+            with mp.get_context("spawn").Pool(cores) as pool:
+                res = pool.map(_render_cpu_worker, [(i, args.cpu_seconds) for i in range(cores)])
+            line["cpu_baseline"] = {"value": sum(f / s for f, s in res), "unit": "frames/s", "cores": cores, "kind": "port",
+                                    "sample": "%d processes x %.0f s of full 480x640 frames (plain-C brute-force restatement; GL renderer unavailable on this box)" % (cores, args.cpu_seconds)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.destroy_process_group()
 
 
 def run_ours(args, wl):
@@ -265,6 +359,8 @@ def main():
     wl = WORKLOADS[args.workload]
     if args.impl == "reference":
         run_reference(args, wl)
+    elif args.workload == "render":
+        run_render(args, wl)
     else:
         run_ours(args, wl)
 

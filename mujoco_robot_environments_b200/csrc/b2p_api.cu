@@ -13,6 +13,7 @@ using namespace b2p;
 
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
+namespace b2p { int api_fail(int code, const char* msg) { return fail(code, msg); } }   // shared with b2p_render.cu
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return fail(B2P_ERR_CUDA, std::string(#x) + ": " + cudaGetErrorString(e_)); } while (0)
 
 // register-resident FMA chain for the FP pipe roofline denominator

@@ -7,8 +7,9 @@ Reference behaviour mirrored (mujoco_robot_environments/tasks/rearrangement.py):
 The env batch is heterogeneous: every scene is padded to ``model.nprop`` props; props a scene does not
 have are parked away from the table with collisions and dynamics disabled.
 
-Camera observations of the reference come from ``mujoco.Renderer`` (OpenGL): unavailable on this box.  The observation
-returned here is the state a policy / data generator can be computed from (poses), see ``_compute_observation``.
+Camera observations of the reference come from ``mujoco.Renderer`` (OpenGL): unavailable on this box.  ``render()`` ray-casts
+the overhead camera on the GPU instead (csrc/b2p_render.cu); ``_compute_observation`` returns the state observation (poses)
+that the scripted expert consumes, so that stepping never pays for frames nobody reads.
 """
 from __future__ import annotations
 
@@ -76,6 +77,7 @@ class BatchedRearrangementEnv:
         self.camera = Camera(next(c for c in self._cfg["arena"]["cameras"] if c["name"] == "overhead_camera"))
         self.overhead_camera_height, self.overhead_camera_width = self.camera.height, self.camera.width
         self._expert: Optional[SortColoursExpert] = None
+        self._renderer = None
         # controllers (hydra partial `controller(physics, arm)` in the reference, robot_arm.py:37,46)
         cc = self._cfg["robots"]["arm"]["controller_config"]["controller_params"]
         ee = self._cfg["robots"]["end_effector"]["controller_config"]
@@ -286,6 +288,25 @@ class BatchedRearrangementEnv:
         hi = torch.as_tensor(w["max_pose"] if max_pose is None else max_pose, device=self.device, dtype=self.dtype)
         ex = lambda t: t.expand(self.num_envs, 3) if t.dim() == 1 else t
         return self.expert.prop_place(torch.as_tensor(prop_id, device=self.device).expand(self.num_envs).to(torch.int64), ex(lo), ex(hi))
+
+    def render(self, lo: int = 0, hi: Optional[int] = None, seg: bool = False) -> Dict[str, torch.Tensor]:
+        """``_compute_observation`` of the reference (rearrangement.py:460-478) for scenes [lo, hi): overhead rgb u8 [n, H, W, 3]
+        and depth f32 [n, H, W] in metres (+ ``segmentation`` geom ids with ``seg``), ray-cast on the GPU."""
+        if self._renderer is None:
+            from .render import BatchedRenderer
+            self._renderer = BatchedRenderer(self.device)
+        o = self._renderer.render(self._physics, self.prop_rgba, lo=lo, hi=hi, seg=seg)
+        obs = {"overhead_camera/rgb": o["rgb"], "overhead_camera/depth": o["depth"]}
+        if seg:
+            obs["segmentation"] = o["seg"]
+        return obs
+
+    def pixel_2_world(self, camera_name, coords):
+        """rearrangement.py:507-535: pixel [n, 2] -> world [n, 3] through the rendered depth at that pixel."""
+        c = torch.as_tensor(coords, device=self.device)
+        d = self.render()["overhead_camera/depth"]
+        r = torch.round(c).to(torch.int64)
+        return self.camera.pixel_2_world(c, d[torch.arange(self.num_envs, device=self.device), r[:, 1], r[:, 0]])
 
     def world_2_pixel(self, camera_name, coords):
         return self.camera.world_2_pixel(coords)

@@ -13,9 +13,10 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
 LIB_PATH = os.path.join(CSRC, "libb2p.so")
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
-UNITS = ("b2p_api.cu", "b2p_kernel_f32.cu", "b2p_kernel_f64.cu")
+UNITS = ("b2p_api.cu", "b2p_kernel_f32.cu", "b2p_kernel_f64.cu", "b2p_render.cu")
 # per-unit flags: the fp32 throughput kernel uses the fast division / sqrt / sincos sequences (<= 2 ulp; its parity tolerance is 1e-4)
-UNIT_FLAGS = {"b2p_kernel_f32.cu": ["-use_fast_math"]}
+# the ray-caster is built without FMA contraction: every pixel is bit-identical to the plain-C restatement (oracle/b2p_render_oracle.c)
+UNIT_FLAGS = {"b2p_kernel_f32.cu": ["-use_fast_math"], "b2p_render.cu": ["-fmad=false"]}
 
 # enums of include/b2p.h
 F64, F32 = 0, 1
@@ -25,12 +26,14 @@ O = dict(SITE_XPOS=0, SITE_XMAT=1, QACC=2, QFRC_BIAS=3, CTRL=4, NCON=5, NEFC=6, 
          GEOM_XMAT=11, QACC_SMOOTH=12, EFC_FORCE=13)
 SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params",
            "b2p_osc_config", "b2p_set_full_contacts", "b2p_step_physics", "b2p_step_osc", "b2p_settle", "b2p_forward", "b2p_get",
-           "b2p_status", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error"]
+           "b2p_status", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error",
+           "b2p_render_create", "b2p_render_destroy", "b2p_render_query", "b2p_render"]          # include/b2p_render.h
+RQ = dict(WIDTH=0, HEIGHT=1, NGEOM=2, LAUNCHES=3, TILES_COPIED=4, TILES_CAST=5)
 
 
 def sources():
     return [os.path.join(CSRC, f) for f in sorted(os.listdir(CSRC)) if f.endswith((".cu", ".h"))] + \
-           [os.path.join(_HERE, "..", "include", f) for f in ("b2p.h", "b2p_model_layout.h")]
+           [os.path.join(_HERE, "..", "include", f) for f in ("b2p.h", "b2p_model_layout.h", "b2p_render.h")]
 
 
 def build(force: bool = False, verbose: bool = False, extra=()) -> str:
@@ -83,6 +86,10 @@ def lib() -> C.CDLL:
     L.b2p_prof_read.argtypes = [vp, C.POINTER(C.c_ulonglong), i32]
     L.b2p_fma_peak.argtypes = [i32, i32, C.POINTER(C.c_double)]
     L.b2p_last_error.restype = C.c_char_p
+    L.b2p_render_create.argtypes = [C.c_char_p, C.c_size_t, i32, C.POINTER(vp)]
+    L.b2p_render_destroy.argtypes = [vp]
+    L.b2p_render_query.argtypes = [vp, i32]
+    L.b2p_render.argtypes = [vp, i32, vp, vp, i32, i32, vp, vp, vp, vp, vp, vp, vp]
     for s in SYMBOLS:
         getattr(L, s)  # raises AttributeError if the library does not export what include/b2p.h declares
     _lib = L

@@ -9,12 +9,14 @@ import pytest
 from mujoco_robot_environments_b200 import ffi
 
 ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
-HEADER = os.path.join(ROOT, "include", "b2p.h")
+HEADERS = [os.path.join(ROOT, "include", "b2p.h"), os.path.join(ROOT, "include", "b2p_render.h")]
 
 
 def _header_text():
-    with open(HEADER) as f:
-        txt = f.read()
+    txt = ""
+    for h in HEADERS:
+        with open(h) as f:
+            txt += f.read()
     return re.sub(r"/\*.*?\*/", "", txt, flags=re.S)
 
 
@@ -62,6 +64,9 @@ def test_enum_mirrors_match_header():
     for k, v in ffi.O.items():
         assert o["B2P_O_" + k] == v, k
     assert o["B2P_O_NFIELD"] == len(ffi.O)
+    r = _enum_block("B2P_RQ_WIDTH")
+    for k, v in ffi.RQ.items():
+        assert r["B2P_RQ_" + k] == v, k
 
 
 def test_error_paths_without_a_gpu(lib):
@@ -76,6 +81,12 @@ def test_error_paths_without_a_gpu(lib):
     assert lib.b2p_out_offset(ffi.O["SITE_XPOS"], C.byref(off), C.byref(cnt)) == 0 and cnt.value == 6
     assert lib.b2p_step_physics(None, None, 1, None) == -1
     assert lib.b2p_destroy(None) == 0
+    r = C.c_void_p()
+    assert lib.b2p_render_create(None, 0, 0, C.byref(r)) == -1 and b"b2p_render_create" in lib.b2p_last_error()
+    junk = bytes(4096)
+    assert lib.b2p_render_create(junk, len(junk), 0, C.byref(r)) == -2          # not a B2PR blob: rejected before any CUDA call
+    assert lib.b2p_render(None, 1, None, None, 0, 1, None, None, None, None, None, None, None) == -1
+    assert lib.b2p_render_destroy(None) == 0
 
 
 def test_bad_blob_is_rejected_before_touching_the_device(lib):

@@ -26,3 +26,9 @@ for tag, fuse in (("rearrangement_n4", True), ("rearrangement_n4_unfused", False
     open(os.path.join(out, tag + ".b2pm"), "wb").write(blob)
     json.dump(names, open(os.path.join(out, tag + ".names.json"), "w"), indent=0)
     print(tag, len(blob), "bytes")
+    if fuse:    # render model of the same scene (overhead camera + target zones): assets/<tag>.b2pr
+        from mujoco_robot_environments_b200 import config as cfglib
+        from mujoco_robot_environments_b200.compile import render
+        rb = render.build_render_blob(blob, names["geom"], cfglib.CAMERAS[0], cfglib.TASK_GROUPS["rearrangement_w_targets"]["target_locations"])
+        open(os.path.join(out, tag + ".b2pr"), "wb").write(rb)
+        print(tag + ".b2pr", len(rb), "bytes")
