@@ -36,14 +36,33 @@ SCENE_LIGHT = dict(pos=(0.7, 0.0, 1.6), diffuse=0.7)            # arena.xml:16 (
 ZFAR = 100.0
 
 
-def hull_planes(verts: np.ndarray) -> np.ndarray:
-    """Unique supporting planes (n, d) with n.x <= d inside, coplanar facets merged."""
+MAX_HULL_PLANES = 128   # hulls with more facets than this are rendered as the discrete oriented polytope below
+
+
+def _kdop_directions(n: int) -> np.ndarray:
+    """The 6 axis directions (so the polytope stays inside the hull's AABB, which the kernel uses as a pre-test) plus a
+    Fibonacci lattice on the sphere."""
+    m = n - 6
+    i = np.arange(m) + 0.5
+    z = 1 - 2 * i / m
+    phi = np.pi * (1 + 5 ** 0.5) * i
+    fib = np.stack([np.sqrt(1 - z * z) * np.cos(phi), np.sqrt(1 - z * z) * np.sin(phi), z], 1)
+    return np.concatenate([np.eye(3), -np.eye(3), fib], 0)
+
+
+def hull_planes(verts: np.ndarray, max_planes: int = MAX_HULL_PLANES) -> np.ndarray:
+    """Supporting planes (n, d) with n.x <= d inside.  Exact facets (coplanar triangles merged) when there are at most
+    ``max_planes`` of them; otherwise the tightest polytope with ``max_planes`` fixed face directions around the hull (outer
+    approximation; for the gripper's 600-800 vertex hulls the deviation is < 0.3 mm, a fraction of a pixel from the camera)."""
     from scipy.spatial import ConvexHull
     eq = ConvexHull(verts).equations          # n.x + off <= 0 inside
     key = np.round(eq / 1e-7).astype(np.int64)
     _, idx = np.unique(key, axis=0, return_index=True)
     eq = eq[np.sort(idx)]
-    return np.concatenate([eq[:, :3], -eq[:, 3:4]], 1)
+    if max_planes is None or len(eq) <= max_planes:
+        return np.concatenate([eq[:, :3], -eq[:, 3:4]], 1)
+    dirs = _kdop_directions(max_planes)
+    return np.concatenate([dirs, (verts @ dirs.T).max(0)[:, None]], 1)
 
 
 def build_render_blob(model_blob: bytes, geom_names: Sequence[str], camera: dict, zones: Optional[dict] = None) -> bytes:

@@ -5,8 +5,8 @@
 //   * The camera, ground, table, arm base and target zones never move, so their image (rgb + depth + segmentation, 3.4 MB)
 //     is ray-cast ONCE at handle creation and stays resident in the 126 MB L2.
 //   * Per frame, a tiny bounds kernel projects the bounding sphere of every moving geom (arm links, gripper, props) of
-//     every scene to a pixel rectangle.  The persistent frame kernel (148 x k CTAs, work items = (scene, 64x16 tile) pulled
-//     from an atomic queue) then either COPIES the background tile with 16-byte vector loads / stores -- ~85 % of the tiles
+//     every scene to a pixel rectangle.  The persistent frame kernel (148 x k CTAs, work items = (scene, 32x8 tile) pulled
+//     by one warp each from an atomic queue) then either COPIES the background tile with 16-byte vector loads / stores -- ~85 % of the tiles
 //     of a typical frame: pure HBM write streaming -- or ray-casts the tile against the static geoms plus the moving geoms
 //     whose rectangle overlaps it.
 //   * The render model (<= 32 geoms, 6 zones, camera, lights: 5 kB) is staged once per CTA in shared memory; hull planes
@@ -30,7 +30,7 @@ namespace b2p { int api_fail(int code, const char* msg); }
 
 namespace {
 
-constexpr int TW = 64, TH = 16, NT = 256, RMAXG = 32, RMAXZ = 8, PXT = TW * TH / NT;
+constexpr int TW = 32, TH = 8, NT = 256, NW = NT / 32, RMAXG = 32, RMAXZ = 8;
 constexpr int GEOM_PLANE = 0, GEOM_BOX = 6, GEOM_MESH = 7;
 constexpr unsigned MAGIC = 0x52503242u;
 
@@ -47,7 +47,7 @@ struct FrameArgs {
   const uint8_t* bg_rgb; const float* bg_depth; const int* bg_seg;
   uint8_t* rgb; float* depth; int* seg;
   const float4* planes;
-  int* queue; unsigned long long* tile_stats;
+  unsigned long long* queue; unsigned long long* tile_stats;
 };
 
 __device__ __forceinline__ float ld_real(const void* p, size_t i, int dtype) { return dtype == 0 ? (float)((const double*)p)[i] : ((const float*)p)[i]; }
@@ -120,7 +120,8 @@ __device__ __forceinline__ bool ray_box(const float* o, const float* d, const fl
   float tn = -1e30f, tf = 1e30f; int ax = 0; float sg = 0.0f;
   for (int k = 0; k < 3; k++) {
     if (dl[k] != 0.0f) {
-      float t1 = (-half[k] - ol[k]) / dl[k], t2 = (half[k] - ol[k]) / dl[k];
+      const float inv = 1.0f / dl[k];
+      float t1 = (-half[k] - ol[k]) * inv, t2 = (half[k] - ol[k]) * inv;
       const float s = dl[k] > 0.0f ? -1.0f : 1.0f;
       if (t1 > t2) { const float q = t1; t1 = t2; t2 = q; }
       if (t1 > tn) { tn = t1; ax = k; sg = s; }
@@ -144,7 +145,8 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
     for (int k = 0; k < 3; k++) {
       const float c = ol[k] - cen[k];
       if (dl[k] != 0.0f) {
-        float t1 = (-half[k] - c) / dl[k], t2 = (half[k] - c) / dl[k];
+        const float inv = 1.0f / dl[k];
+        float t1 = (-half[k] - c) * inv, t2 = (half[k] - c) * inv;
         if (t1 > t2) { const float q = t1; t1 = t2; t2 = q; }
         if (t1 > tn) tn = t1;
         if (t2 < tf) tf = t2;
@@ -158,9 +160,10 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
     const float den = P.x * dl[0] + P.y * dl[1] + P.z * dl[2];
     const float dist = P.w - (P.x * ol[0] + P.y * ol[1] + P.z * ol[2]);
     if (den == 0.0f) { if (dist < 0.0f) return false; continue; }
-    const float tt = dist / den;
-    if (den < 0.0f) { if (tt > tn) { tn = tt; best = i; } }
-    else if (tt < tf) tf = tt;
+    // entering plane (den < 0): dist / den > tn  <=>  dist < tn * den; leaving plane: dist / den < tf  <=>  dist < tf * den.
+    // The division runs only when a bound actually moves (a handful of times per ray).
+    if (den < 0.0f) { if (dist < tn * den) { tn = dist / den; best = i; } }
+    else if (dist < tf * den) tf = dist / den;
     if (tn > tf) return false;
   }
   if (best < 0 || tn <= 0.0f) return false;
@@ -246,81 +249,76 @@ __device__ void cast_pixel(const RModel& M, const TileGeoms& tg, unsigned dyn_ma
 }
 
 // ---------------------------------------------------------------------------------------- persistent frame kernel
+// One WARP per work item (scene, 32x8 tile); warps never synchronise with each other after the model is staged.
+struct WarpScratch { TileGeoms tg; __align__(16) unsigned char rgb[TH][TW * 3]; };
+
 __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restrict__ gm, FrameArgs a) {
   __shared__ RModel M;
-  __shared__ TileGeoms tg;
-  __shared__ __align__(16) unsigned char s_rgb[TH][TW * 3];
-  __shared__ int s_item; __shared__ unsigned s_mask;
-  __shared__ unsigned long long s_stats[2];
-  const int tid = threadIdx.x;
+  __shared__ WarpScratch ws[NW];
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   for (int i = tid; i < (int)(sizeof(RModel) / 4); i += NT) ((int*)&M)[i] = ((const int*)gm)[i];
-  if (tid < 2) s_stats[tid] = 0;
   __syncthreads();
+  WarpScratch& S = ws[warp];
   const int tiles_x = M.W / TW, ntile = tiles_x * (M.H / TH);
   const long long total = (long long)a.n_env * ntile;
+  unsigned n_copy = 0, n_cast = 0;
   for (;;) {
-    if (tid == 0) s_item = atomicAdd(a.queue, 1);
-    __syncthreads();
-    const long long item = s_item;
+    long long item = 0;
+    if (lane == 0) item = atomicAdd(a.queue, 1ULL);
+    item = __shfl_sync(0xffffffffu, item, 0);
     if (item >= total) break;
     const int env = (int)(item / ntile), tile = (int)(item % ntile), tx0 = (tile % tiles_x) * TW, ty0 = (tile / tiles_x) * TH;
-    if (tid < 32) {
-      bool hit = false;
-      if (!a.background) { const short4 r = a.rects[(size_t)env * RMAXG + tid]; hit = r.x <= r.z && r.x <= tx0 + TW - 1 && r.z >= tx0 && r.y <= ty0 + TH - 1 && r.w >= ty0; }
-      const unsigned m = __ballot_sync(0xffffffffu, hit);
-      if (tid == 0) s_mask = m;
-    }
-    __syncthreads();
-    const unsigned mask = s_mask;
+    bool hit = false;
+    if (!a.background) { const short4 r = a.rects[(size_t)env * RMAXG + lane]; hit = r.x <= r.z && r.x <= tx0 + TW - 1 && r.z >= tx0 && r.y <= ty0 + TH - 1 && r.w >= ty0; }
+    const unsigned mask = __ballot_sync(0xffffffffu, hit);
     const size_t img = (size_t)env * M.H * M.W;
     if (mask == 0 && !a.background) {
       // background tile: 16-byte vector copies L2 -> HBM
-      if (a.rgb && tid < TH * (TW * 3 / 16)) {
-        const int row = tid / (TW * 3 / 16), c = tid % (TW * 3 / 16);
+      if (a.rgb) for (int i = lane; i < TH * (TW * 3 / 16); i += 32) {
+        const int row = i / (TW * 3 / 16), c = i % (TW * 3 / 16);
         const size_t off = ((size_t)(ty0 + row) * M.W + tx0) * 3 + (size_t)c * 16;
         *reinterpret_cast<uint4*>(a.rgb + img * 3 + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_rgb + off));
       }
-      {
-        const int row = tid / (TW / 4), c = tid % (TW / 4);
+      for (int i = lane; i < TH * (TW / 4); i += 32) {
+        const int row = i / (TW / 4), c = i % (TW / 4);
         const size_t off = (size_t)(ty0 + row) * M.W + tx0 + (size_t)c * 4;
         if (a.depth) *reinterpret_cast<uint4*>(a.depth + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_depth + off));
         if (a.seg) *reinterpret_cast<uint4*>(a.seg + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_seg + off));
       }
-      if (tid == 0) s_stats[0]++;
+      n_copy++;
     } else {
-      if (tid < 32 && ((mask >> tid) & 1u)) {
-        const int g = tid; const size_t pb = (size_t)env * a.pose_stride;
-        for (int k = 0; k < 3; k++) tg.pos[g][k] = ld_real(a.xpos, pb + 3 * g + k, a.dtype);
-        for (int k = 0; k < 9; k++) tg.mat[g][k] = ld_real(a.xmat, pb + 9 * g + k, a.dtype);
+      __syncwarp();
+      if ((mask >> lane) & 1u) {
+        const int g = lane; const size_t pb = (size_t)env * a.pose_stride;
+        for (int k = 0; k < 3; k++) S.tg.pos[g][k] = ld_real(a.xpos, pb + 3 * g + k, a.dtype);
+        for (int k = 0; k < 9; k++) S.tg.mat[g][k] = ld_real(a.xmat, pb + 9 * g + k, a.dtype);
         const int p = M.geom[g].prop;
         if (p >= 0) {
           const size_t q = (size_t)env * M.nprop + p;
           for (int k = 0; k < 3; k++) {
-            tg.size[g][k] = a.prop_size ? ld_real(a.prop_size, q * 3 + k, a.dtype) : M.geom[g].size[k];
-            tg.rgb[g][k] = a.prop_rgba ? a.prop_rgba[q * 4 + k] : M.geom[g].rgba[k];
+            S.tg.size[g][k] = a.prop_size ? ld_real(a.prop_size, q * 3 + k, a.dtype) : M.geom[g].size[k];
+            S.tg.rgb[g][k] = a.prop_rgba ? a.prop_rgba[q * 4 + k] : M.geom[g].rgba[k];
           }
         }
       }
-      __syncthreads();
-      for (int k = 0; k < PXT; k++) {
-        const int lx = tid % TW, ly = tid / TW + (NT / TW) * k;
+      __syncwarp();
+      for (int ly = 0; ly < TH; ly++) {
         float dep; int sg;
-        cast_pixel(M, tg, mask, a.planes, tx0 + lx, ty0 + ly, &s_rgb[ly][lx * 3], &dep, &sg);
-        const size_t off = (size_t)(ty0 + ly) * M.W + tx0 + lx;
+        cast_pixel(M, S.tg, mask, a.planes, tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
+        const size_t off = (size_t)(ty0 + ly) * M.W + tx0 + lane;
         if (a.depth) a.depth[img + off] = dep;
         if (a.seg) a.seg[img + off] = sg;
       }
-      __syncthreads();
-      if (a.rgb && tid < TH * (TW * 3 / 16)) {
-        const int row = tid / (TW * 3 / 16), c = tid % (TW * 3 / 16);
+      __syncwarp();
+      if (a.rgb) for (int i = lane; i < TH * (TW * 3 / 16); i += 32) {
+        const int row = i / (TW * 3 / 16), c = i % (TW * 3 / 16);
         const size_t off = ((size_t)(ty0 + row) * M.W + tx0) * 3 + (size_t)c * 16;
-        *reinterpret_cast<uint4*>(a.rgb + img * 3 + off) = *reinterpret_cast<const uint4*>(&s_rgb[row][c * 16]);
+        *reinterpret_cast<uint4*>(a.rgb + img * 3 + off) = *reinterpret_cast<const uint4*>(&S.rgb[row][c * 16]);
       }
-      if (tid == 0) s_stats[1]++;
+      n_cast++;
     }
-    __syncthreads();
   }
-  if (tid < 2 && a.tile_stats && s_stats[tid]) atomicAdd(a.tile_stats + tid, s_stats[tid]);
+  if (lane == 0 && a.tile_stats) { if (n_copy) atomicAdd(a.tile_stats, (unsigned long long)n_copy); if (n_cast) atomicAdd(a.tile_stats + 1, (unsigned long long)n_cast); }
 }
 
 }  // namespace
@@ -328,16 +326,16 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
 struct b2p_render_s {
   int device, sms; long long launches;
   RModel hm; RModel* d_model; float4* d_planes; short4* d_rects; int rect_cap;
-  uint8_t* bg_rgb; float* bg_depth; int* bg_seg; int* d_queue; unsigned long long* d_stats;
+  uint8_t* bg_rgb; float* bg_depth; int* bg_seg; unsigned long long* d_queue; unsigned long long* d_stats;
 };
 
 static int launch_frame(b2p_render_s* h, FrameArgs& a, cudaStream_t st) {
   a.planes = h->d_planes; a.queue = h->d_queue; a.tile_stats = h->d_stats;
   a.bg_rgb = h->bg_rgb; a.bg_depth = h->bg_depth; a.bg_seg = h->bg_seg;
-  RCK(cudaMemsetAsync(h->d_queue, 0, sizeof(int), st));
+  RCK(cudaMemsetAsync(h->d_queue, 0, sizeof(unsigned long long), st));
   const long long total = (long long)a.n_env * (h->hm.W / TW) * (h->hm.H / TH);
-  long long grid = (long long)h->sms * 4;
-  if (grid > total) grid = total;
+  long long grid = (long long)h->sms * 3;
+  if (grid > (total + NW - 1) / NW) grid = (total + NW - 1) / NW;
   render_frame_kernel<<<(int)grid, NT, 0, st>>>(h->d_model, a);
   RCK(cudaGetLastError());
   h->launches++;
@@ -352,7 +350,7 @@ int b2p_render_create(const void* blob, size_t nbytes, int device, b2p_render_ha
   if ((unsigned)hd[0] != MAGIC || hd[1] != 1) return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: not a B2PR v1 blob");
   const int ng = hd[2], np = hd[3], nz = hd[4], W = hd[5], H = hd[6];
   if (ng < 1 || ng > RMAXG || nz < 0 || nz > RMAXZ || np < 0) return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: geom / zone count outside the render model class");
-  if (W % TW || H % TH || W <= 0 || H <= 0 || W > 32000 || H > 32000) return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: image size must be a multiple of the 64x16 tile");
+  if (W % TW || H % TH || W <= 0 || H <= 0 || W > 32000 || H > 32000) return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: image size must be a multiple of the 32x8 tile");
   const size_t need = 64 + 128 + (size_t)ng * 128 + (size_t)nz * 48 + (size_t)np * 16;
   if (nbytes < need) return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: truncated blob");
   b2p_render_s* h = new b2p_render_s();
@@ -371,7 +369,7 @@ int b2p_render_create(const void* blob, size_t nbytes, int device, b2p_render_ha
   RCK(cudaMalloc(&h->d_planes, (size_t)(np + 1) * 16)); RCK(cudaMemcpy(h->d_planes, p, (size_t)np * 16, cudaMemcpyHostToDevice));
   const size_t px = (size_t)W * H;
   RCK(cudaMalloc(&h->bg_rgb, px * 3)); RCK(cudaMalloc(&h->bg_depth, px * 4)); RCK(cudaMalloc(&h->bg_seg, px * 4));
-  RCK(cudaMalloc(&h->d_queue, sizeof(int))); RCK(cudaMalloc(&h->d_stats, 16)); RCK(cudaMemset(h->d_stats, 0, 16));
+  RCK(cudaMalloc(&h->d_queue, sizeof(unsigned long long))); RCK(cudaMalloc(&h->d_stats, 16)); RCK(cudaMemset(h->d_stats, 0, 16));
   // static layer: ground, table, arm base, zones -- ray-cast once, then L2-resident
   FrameArgs a; memset(&a, 0, sizeof a);
   a.n_env = 1; a.background = 1; a.rgb = h->bg_rgb; a.depth = h->bg_depth; a.seg = h->bg_seg;

@@ -34,7 +34,8 @@ static int hit_box(const float* o, const float* d, const float* pos, const float
   to_local(o, d, pos, mat, ol, dl);
   for (int k = 0; k < 3; k++) {
     if (dl[k] != 0.0f) {
-      float t1 = (-half[k] - ol[k]) / dl[k], t2 = (half[k] - ol[k]) / dl[k];
+      float inv = 1.0f / dl[k];
+      float t1 = (-half[k] - ol[k]) * inv, t2 = (half[k] - ol[k]) * inv;
       float s = dl[k] > 0.0f ? -1.0f : 1.0f;
       if (t1 > t2) { float q = t1; t1 = t2; t2 = q; }
       if (t1 > tn) { tn = t1; ax = k; sg = s; }
@@ -56,9 +57,9 @@ static int hit_hull(const float* o, const float* d, const float* pos, const floa
     float den = P[0] * dl[0] + P[1] * dl[1] + P[2] * dl[2];
     float dist = P[3] - (P[0] * ol[0] + P[1] * ol[1] + P[2] * ol[2]);
     if (den == 0.0f) { if (dist < 0.0f) return 0; continue; }
-    float tt = dist / den;
-    if (den < 0.0f) { if (tt > tn) { tn = tt; best = i; } }
-    else if (tt < tf) tf = tt;
+    /* entering plane: dist / den > tn  <=>  dist < tn * den (den < 0); leaving plane: dist / den < tf  <=>  dist < tf * den */
+    if (den < 0.0f) { if (dist < tn * den) { tn = dist / den; best = i; } }
+    else if (dist < tf * den) tf = dist / den;
     if (tn > tf) return 0;
   }
   if (best < 0 || tn <= 0.0f) return 0;

@@ -58,7 +58,7 @@ def test_render_batch_properties():
     for k in ("rgb", "depth", "seg"):
         assert torch.equal(out[k][:150], out[k][150:]), k
     copied, cast = r.query("TILES_COPIED"), r.query("TILES_CAST")
-    assert copied + cast == n * 300 and copied > 0.6 * n * 300, (copied, cast)
+    assert copied + cast == n * 1200 and copied > 0.6 * n * 1200, (copied, cast)
     # a home-pose scene: every pixel is table / zone / prop (no arm, no empty pixel), depth within [table - prop height, table]
     seg, d = out["seg"][1], out["depth"][1]
     assert int(((seg >= 2) & (seg <= 25)).sum()) == 0 and int((seg < 0).sum()) == 0

@@ -41,11 +41,18 @@ def test_hull_planes_support_their_vertices():
     v = np.asarray(A["mesh_vert"]).reshape(-1, 3)
     for mid in range(counts["nmesh"]):
         a, n = int(A["mesh_vertadr"][mid]), int(A["mesh_vertnum"][mid])
-        pl = R.hull_planes(v[a:a + n])
-        s = v[a:a + n] @ pl[:, :3].T - pl[:, 3]
+        exact = R.hull_planes(v[a:a + n], max_planes=None)
+        s = v[a:a + n] @ exact[:, :3].T - exact[:, 3]
         assert s.max() < 1e-9                                   # every vertex inside every half space
         assert ((np.abs(s) < 1e-7).sum(0) >= 3).all()           # every plane is a facet
-        assert np.abs(np.linalg.norm(pl[:, :3], axis=1) - 1).max() < 1e-9
+        pl = R.hull_planes(v[a:a + n])
+        assert len(pl) <= R.MAX_HULL_PLANES and np.abs(np.linalg.norm(pl[:, :3], axis=1) - 1).max() < 1e-9
+        s = v[a:a + n] @ pl[:, :3].T - pl[:, 3]
+        assert s.max() < 1e-9 and (np.abs(s).min(0) < 1e-9).all()      # outer approximation, every plane touches the hull
+        if len(exact) > R.MAX_HULL_PLANES:
+            # how far the polytope sticks out of the exact hull: its vertices are bounded by the support gap in the exact facet directions
+            lo, hi = v[a:a + n].min(0), v[a:a + n].max(0)
+            assert np.allclose((v[a:a + n] @ pl[:6, :3].T).max(0), np.concatenate([hi, -lo]))     # the 6 axis planes = the AABB
 
 
 def test_oracle_known_answers():
