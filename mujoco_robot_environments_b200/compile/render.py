@@ -36,7 +36,9 @@ SCENE_LIGHT = dict(pos=(0.7, 0.0, 1.6), diffuse=0.7)            # arena.xml:16 (
 ZFAR = 100.0
 
 
-MAX_HULL_PLANES = 128   # hulls with more facets than this are rendered as the discrete oriented polytope below
+MAX_HULL_PLANES = 128   # hulls with more facets than this are rendered as the discrete oriented polytope below ...
+SMALL_HULL_PLANES = 64  # ... and small parts (bounding radius <= SMALL_HULL_RADIUS: the gripper linkage) with fewer directions:
+SMALL_HULL_RADIUS = 0.045  # either way the polytope sticks out of the exact hull by less than ~1 mm (under half a pixel)
 
 
 def _kdop_directions(n: int) -> np.ndarray:
@@ -50,7 +52,13 @@ def _kdop_directions(n: int) -> np.ndarray:
     return np.concatenate([np.eye(3), -np.eye(3), fib], 0)
 
 
-def hull_planes(verts: np.ndarray, max_planes: int = MAX_HULL_PLANES) -> np.ndarray:
+def _spread(n: int) -> np.ndarray:
+    """Fixed permutation that visits 0..n-1 in a low-discrepancy order, so that the first few planes of a hull already face
+    every direction and a ray that misses the hull is rejected after a handful of planes."""
+    return np.argsort((np.arange(n) * 0.6180339887498949) % 1.0, kind="stable")
+
+
+def hull_planes(verts: np.ndarray, max_planes="auto") -> np.ndarray:
     """Supporting planes (n, d) with n.x <= d inside.  Exact facets (coplanar triangles merged) when there are at most
     ``max_planes`` of them; otherwise the tightest polytope with ``max_planes`` fixed face directions around the hull (outer
     approximation; for the gripper's 600-800 vertex hulls the deviation is < 0.3 mm, a fraction of a pixel from the camera)."""
@@ -59,10 +67,15 @@ def hull_planes(verts: np.ndarray, max_planes: int = MAX_HULL_PLANES) -> np.ndar
     key = np.round(eq / 1e-7).astype(np.int64)
     _, idx = np.unique(key, axis=0, return_index=True)
     eq = eq[np.sort(idx)]
+    if max_planes == "auto":
+        c = (verts.min(0) + verts.max(0)) / 2
+        max_planes = SMALL_HULL_PLANES if np.linalg.norm(verts - c, axis=1).max() <= SMALL_HULL_RADIUS else MAX_HULL_PLANES
     if max_planes is None or len(eq) <= max_planes:
-        return np.concatenate([eq[:, :3], -eq[:, 3:4]], 1)
-    dirs = _kdop_directions(max_planes)
-    return np.concatenate([dirs, (verts @ dirs.T).max(0)[:, None]], 1)
+        pl = np.concatenate([eq[:, :3], -eq[:, 3:4]], 1)
+    else:
+        dirs = _kdop_directions(max_planes)
+        pl = np.concatenate([dirs, (verts @ dirs.T).max(0)[:, None]], 1)
+    return pl[_spread(len(pl))]
 
 
 def build_render_blob(model_blob: bytes, geom_names: Sequence[str], camera: dict, zones: Optional[dict] = None) -> bytes:

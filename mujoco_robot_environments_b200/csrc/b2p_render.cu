@@ -4,7 +4,7 @@
 // (tasks/rearrangement.py:182-186, :460-478, :273-275).  B200-first design:
 //   * The camera, ground, table, arm base and target zones never move, so their image (rgb + depth + segmentation, 3.4 MB)
 //     is ray-cast ONCE at handle creation and stays resident in the 126 MB L2.
-//   * Per frame, a tiny bounds kernel projects the bounding sphere of every moving geom (arm links, gripper, props) of
+//   * Per frame, a tiny bounds kernel projects the oriented bounding box of every moving geom (arm links, gripper, props) of
 //     every scene to a pixel rectangle.  The persistent frame kernel (148 x k CTAs, work items = (scene, 32x8 tile) pulled
 //     by one warp each from an atomic queue) then either COPIES the background tile with 16-byte vector loads / stores -- ~85 % of the tiles
 //     of a typical frame: pure HBM write streaming -- or ray-casts the tile against the static geoms plus the moving geoms
@@ -53,8 +53,8 @@ struct FrameArgs {
 __device__ __forceinline__ float ld_real(const void* p, size_t i, int dtype) { return dtype == 0 ? (float)((const double*)p)[i] : ((const float*)p)[i]; }
 
 // ---------------------------------------------------------------------------------------- moving-geom pixel rectangles
-// one thread per (scene, geom): conservative screen rectangle of the geom's bounding sphere (empty for static geoms,
-// inactive props and spheres entirely behind / beside the view)
+// one thread per (scene, geom): conservative pixel rectangle of the geom's oriented bounding box (empty for static geoms,
+// inactive props and boxes entirely behind / beside the view)
 __global__ void render_bounds_kernel(const RModel* __restrict__ gm, FrameArgs a, short4* __restrict__ rects) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= a.n_env * RMAXG) return;
@@ -63,15 +63,10 @@ __global__ void render_bounds_kernel(const RModel* __restrict__ gm, FrameArgs a,
   if (g < gm->ngeom) {
     const RGeom& G = gm->geom[g];
     bool on = !G.is_static;
-    float rb = sqrtf(G.size[0] * G.size[0] + G.size[1] * G.size[1] + G.size[2] * G.size[2]);   // sphere around the (padded) AABB
-    float cen[3] = {G.cen[0], G.cen[1], G.cen[2]};
+    float hs[3] = {G.size[0], G.size[1], G.size[2]};       // box half sizes / padded hull AABB half sizes, centred at G.cen
     if (on && G.prop >= 0) {
       if (a.prop_active && !a.prop_active[(size_t)env * gm->nprop + G.prop]) on = false;
-      if (a.prop_size) {
-        float s0 = ld_real(a.prop_size, ((size_t)env * gm->nprop + G.prop) * 3 + 0, a.dtype), s1 = ld_real(a.prop_size, ((size_t)env * gm->nprop + G.prop) * 3 + 1, a.dtype),
-              s2 = ld_real(a.prop_size, ((size_t)env * gm->nprop + G.prop) * 3 + 2, a.dtype);
-        rb = sqrtf(s0 * s0 + s1 * s1 + s2 * s2);
-      }
+      if (a.prop_size) for (int k = 0; k < 3; k++) hs[k] = ld_real(a.prop_size, ((size_t)env * gm->nprop + G.prop) * 3 + k, a.dtype);
     }
     if (on) {
       const size_t pb = (size_t)env * a.pose_stride;
@@ -79,29 +74,21 @@ __global__ void render_bounds_kernel(const RModel* __restrict__ gm, FrameArgs a,
       for (int k = 0; k < 3; k++) p[k] = ld_real(a.xpos, pb + 3 * g + k, a.dtype);
       for (int k = 0; k < 9; k++) m[k] = ld_real(a.xmat, pb + 9 * g + k, a.dtype);
       const RCam& C = gm->cam;
-      float w[3];
-      for (int k = 0; k < 3; k++) w[k] = p[k] + m[3 * k] * cen[0] + m[3 * k + 1] * cen[1] + m[3 * k + 2] * cen[2] - C.pos[k];
-      // camera frame: x right, y up, z back (columns of cam.mat)
-      const float x = C.mat[0] * w[0] + C.mat[3] * w[1] + C.mat[6] * w[2], y = C.mat[1] * w[0] + C.mat[4] * w[1] + C.mat[7] * w[2],
-                  dz = -(C.mat[2] * w[0] + C.mat[5] * w[1] + C.mat[8] * w[2]);
-      rb = rb * 1.02f + 1e-3f;
-      // exact angular extent of the sphere per image axis (its silhouette in the x-z / y-z plane is a circle), +-2 px slack;
-      // an axis whose extent crosses the camera plane is unbounded on that side, one entirely behind it is invisible
-      float lo[2], hi[2]; bool vis = true;
-      const float ax[2] = {x, -y};                         // u grows with +x, v grows with -y
-      for (int k = 0; k < 2; k++) {
-        const float d2 = ax[k] * ax[k] + dz * dz;
-        lo[k] = -1e9f; hi[k] = 1e9f;
-        if (d2 > rb * rb) {
-          const float th = atan2f(ax[k], dz), al = asinf(fminf(1.0f, rb / sqrtf(d2)));
-          const float a0 = th - al, a1 = th + al, lim = 1.55f;
-          if (a0 > lim || a1 < -lim) vis = false;
-          if (a0 > -lim) lo[k] = (k == 0 ? C.cx : C.cy) + C.f * tanf(fminf(a0, lim)) - 2.0f;
-          if (a1 < lim) hi[k] = (k == 0 ? C.cx : C.cy) + C.f * tanf(fmaxf(a1, -lim)) + 2.0f;
-        }
+      // the 8 corners of the oriented box in the camera frame (x right, y up, z back): their pixel bounding box, +-2 px slack
+      float u0 = 1e9f, u1 = -1e9f, v0 = 1e9f, v1 = -1e9f; int behind = 0;
+      for (int c8 = 0; c8 < 8; c8++) {
+        const float l0 = G.cen[0] + ((c8 & 1) ? hs[0] : -hs[0]) * 1.01f, l1 = G.cen[1] + ((c8 & 2) ? hs[1] : -hs[1]) * 1.01f, l2 = G.cen[2] + ((c8 & 4) ? hs[2] : -hs[2]) * 1.01f;
+        float w[3];
+        for (int k = 0; k < 3; k++) w[k] = p[k] + m[3 * k] * l0 + m[3 * k + 1] * l1 + m[3 * k + 2] * l2 - C.pos[k];
+        const float x = C.mat[0] * w[0] + C.mat[3] * w[1] + C.mat[6] * w[2], y = C.mat[1] * w[0] + C.mat[4] * w[1] + C.mat[7] * w[2],
+                    dz = -(C.mat[2] * w[0] + C.mat[5] * w[1] + C.mat[8] * w[2]);
+        if (dz < 0.02f) { behind++; continue; }
+        const float u = C.cx + C.f * x / dz, v = C.cy - C.f * y / dz;
+        u0 = fminf(u0, u); u1 = fmaxf(u1, u); v0 = fminf(v0, v); v1 = fmaxf(v1, v);
       }
-      if (vis) {
-        const float u0 = fmaxf(lo[0], 0.0f), v0 = fmaxf(lo[1], 0.0f), u1 = fminf(hi[0], (float)(gm->W - 1)), v1 = fminf(hi[1], (float)(gm->H - 1));
+      if (behind > 0 && behind < 8) { u0 = v0 = -1e9f; u1 = v1 = 1e9f; }       // straddles the camera plane: do not cull
+      if (behind < 8) {
+        u0 = fmaxf(u0 - 2.0f, 0.0f); v0 = fmaxf(v0 - 2.0f, 0.0f); u1 = fminf(u1 + 2.0f, (float)(gm->W - 1)); v1 = fminf(v1 + 2.0f, (float)(gm->H - 1));
         if (u0 <= u1 && v0 <= v1) r = make_short4((short)u0, (short)v0, (short)u1, (short)v1);
       }
     }
