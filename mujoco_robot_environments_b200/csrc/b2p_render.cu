@@ -141,19 +141,21 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
     }
     if (tn > tf || tf <= 0.0f) return false;
   }
-  float tn = -1e30f, tf = 1e30f; int best = -1;
+  // Entry / exit parameters are kept as fractions num / den (entry: den < 0, exit: den > 0) and compared by cross
+  // multiplication, so the loop has no division and no data-dependent branch besides its exit; one division at the end.
+  float tn_n = 1e30f, tn_d = -1.0f, tf_n = 1e30f, tf_d = 1.0f; int best = -1;
   for (int i = 0; i < np; i++) {
     const float4 P = __ldg(planes + i);
     const float den = P.x * dl[0] + P.y * dl[1] + P.z * dl[2];
     const float dist = P.w - (P.x * ol[0] + P.y * ol[1] + P.z * ol[2]);
     if (den == 0.0f) { if (dist < 0.0f) return false; continue; }
-    // entering plane (den < 0): dist / den > tn  <=>  dist < tn * den; leaving plane: dist / den < tf  <=>  dist < tf * den.
-    // The division runs only when a bound actually moves (a handful of times per ray).
-    if (den < 0.0f) { if (dist < tn * den) { tn = dist / den; best = i; } }
-    else if (dist < tf * den) tf = dist / den;
-    if (tn > tf) return false;
+    if (den < 0.0f) { if (dist * tn_d > tn_n * den) { tn_n = dist; tn_d = den; best = i; } }      // dist / den > tn
+    else if (dist * tf_d < tf_n * den) { tf_n = dist; tf_d = den; }                              // dist / den < tf
+    if (tn_n * tf_d < tf_n * tn_d) return false;                                                 // tn > tf
   }
-  if (best < 0 || tn <= 0.0f) return false;
+  if (best < 0) return false;
+  const float tn = tn_n / tn_d;
+  if (tn <= 0.0f) return false;
   const float4 P = __ldg(planes + best);
   *t_out = tn;
   for (int k = 0; k < 3; k++) n_out[k] = mat[3 * k] * P.x + mat[3 * k + 1] * P.y + mat[3 * k + 2] * P.z;

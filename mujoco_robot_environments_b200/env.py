@@ -131,29 +131,47 @@ class BatchedRearrangementEnv:
         table = (c["geom1"] == self._table_gid) | (c["geom2"] == self._table_gid)
         return (valid & touches & ~table & (c["dist"] <= 0.6)).any(dim=1)
 
+    PLACEMENT_RESTARTS = 8
+
     def _place_props(self, mask: torch.Tensor):
+        """PropPlacer.__call__ (prop_initializer.py:164-231).  A scene whose next prop finds no free pose within
+        ``max_attempts_per_prop`` raises for a strict (single-scene) env exactly like the reference; in a batch that scene alone
+        starts its placement over (its earlier props happened to block the workspace), and is flagged ``failed`` if that keeps
+        happening."""
         p = self._physics
         pcfg = self._cfg["prop_placer"]
         active = p.prop_active
-        # contacts disabled for all props not placed yet (prop_initializer.py:183-185)
-        active[mask] = 0
         qadr = p.model.prop_qposadr
-        for k in range(self.max_props):
-            todo = mask & self.has_prop[:, k]
-            if not bool(todo.any()):
-                continue
-            active[todo, k] = 1
-            for _ in range(int(pcfg["max_attempts_per_prop"])):
-                envs = torch.nonzero(todo).flatten()
-                pos, quat = self._sample_poses(envs.cpu().numpy())
-                pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
-                p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
-                p.forward(full_contacts=True)
-                todo = todo & self._collides(k)
+        for restart in range(self.PLACEMENT_RESTARTS):
+            # contacts disabled for all props not placed yet (prop_initializer.py:183-185)
+            active[mask] = 0
+            self._park_missing_props(mask)
+            stuck = torch.zeros_like(mask)
+            for k in range(self.max_props):
+                todo = mask & self.has_prop[:, k] & ~stuck
                 if not bool(todo.any()):
-                    break
-            else:
-                raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
+                    continue
+                active[todo, k] = 1
+                for _ in range(int(pcfg["max_attempts_per_prop"])):
+                    envs = torch.nonzero(todo).flatten()
+                    pos, quat = self._sample_poses(envs.cpu().numpy())
+                    pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
+                    p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
+                    p.forward(full_contacts=True)
+                    todo = todo & self._collides(k)
+                    if not bool(todo.any()):
+                        break
+                else:
+                    if self.strict:
+                        raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
+                    stuck |= todo
+            if not bool(stuck.any()):
+                return
+            # park every prop of the stuck scenes and start their placement over
+            for k in range(self.max_props):
+                p.qpos[stuck, qadr[k]:qadr[k] + 7] = torch.tensor([PARK_XY[0] + k, PARK_XY[1], 0.2, 1, 0, 0, 0], device=self.device, dtype=self.dtype)
+            mask = stuck
+        self.failed |= mask
 
     def _park_missing_props(self, mask: torch.Tensor):
         p = self._physics
@@ -192,6 +210,7 @@ class BatchedRearrangementEnv:
         p.reset(m)                                                                            # rearrangement.py:302
         home = torch.tensor(self._cfg["robots"]["arm"]["configuration"]["home"], device=self.device, dtype=self.dtype)
         p.qpos[m, 0:7] = home                                                                 # :306
+        self.failed[m] = False
         self._park_missing_props(m)
         self._place_and_settle(m)                                                             # :309
         if self._robot is None:
@@ -203,7 +222,6 @@ class BatchedRearrangementEnv:
             self.eef_home_pose = home_pose
         else:
             self.eef_home_pose[m] = home_pose[m]
-        self.failed[m] = False
         p.status(clear=True)
         self.mode = "pick"                                                                    # :331
         return TimeStep(StepType.FIRST, 0.0, 0.0, self._compute_observation())

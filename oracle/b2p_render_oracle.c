@@ -49,7 +49,8 @@ static int hit_box(const float* o, const float* d, const float* pos, const float
 }
 
 static int hit_hull(const float* o, const float* d, const float* pos, const float* mat, const float* planes, int np, float* t_out, float* n) {
-  float ol[3], dl[3], tn = -1e30f, tf = 1e30f;
+  /* entry / exit parameters as fractions num / den (entry den < 0, exit den > 0), compared by cross multiplication */
+  float ol[3], dl[3], tn_n = 1e30f, tn_d = -1.0f, tf_n = 1e30f, tf_d = 1.0f;
   int best = -1;
   to_local(o, d, pos, mat, ol, dl);
   for (int i = 0; i < np; i++) {
@@ -57,12 +58,13 @@ static int hit_hull(const float* o, const float* d, const float* pos, const floa
     float den = P[0] * dl[0] + P[1] * dl[1] + P[2] * dl[2];
     float dist = P[3] - (P[0] * ol[0] + P[1] * ol[1] + P[2] * ol[2]);
     if (den == 0.0f) { if (dist < 0.0f) return 0; continue; }
-    /* entering plane: dist / den > tn  <=>  dist < tn * den (den < 0); leaving plane: dist / den < tf  <=>  dist < tf * den */
-    if (den < 0.0f) { if (dist < tn * den) { tn = dist / den; best = i; } }
-    else if (dist < tf * den) tf = dist / den;
-    if (tn > tf) return 0;
+    if (den < 0.0f) { if (dist * tn_d > tn_n * den) { tn_n = dist; tn_d = den; best = i; } }
+    else if (dist * tf_d < tf_n * den) { tf_n = dist; tf_d = den; }
+    if (tn_n * tf_d < tf_n * tn_d) return 0;
   }
-  if (best < 0 || tn <= 0.0f) return 0;
+  if (best < 0) return 0;
+  float tn = tn_n / tn_d;
+  if (tn <= 0.0f) return 0;
   *t_out = tn;
   for (int k = 0; k < 3; k++) n[k] = mat[3 * k] * planes[4 * best] + mat[3 * k + 1] * planes[4 * best + 1] + mat[3 * k + 2] * planes[4 * best + 2];
   return 1;
