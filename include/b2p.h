@@ -61,6 +61,10 @@ int b2p_bind_state(b2p_handle h, void* state);
 int b2p_bind_out(b2p_handle h, void* out);
 /* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active);
+/* optional per-scene OSC gains [n_env][6] reals (position kp, kd, orientation kp, kd, nullspace kp, kd): one candidate of the
+ * controller tuner per scene (automated_controller_tuning/rearrangement_controller_tuning.py:145-168 mutates
+ * `controller_gains` between roll-outs); NULL = every scene uses b2p_osc_config's gains.  The pointer is borrowed. */
+int b2p_set_env_gains(b2p_handle h, const void* gains);
 int b2p_osc_config(b2p_handle h, const double gains6[6], const double nullspace7[7], double pos_thresh, double ori_thresh);
 /* 0 = only solver-active contacts while stepping (default), 1 = list every contact inside geom margin */
 int b2p_set_full_contacts(b2p_handle h, int full);

@@ -110,6 +110,11 @@ class BatchedOSC(MujocoController):
     def target13(self) -> torch.Tensor:
         return self._target13
 
+    def set_gains_per_scene(self, gains: Optional[torch.Tensor]):
+        """Batched-only: one gain vector per scene, [n_env, 6] = (position kp, kd, orientation kp, kd, nullspace kp, kd) -- a
+        population of tuner candidates evaluated in one launch.  None returns to ``controller_gains`` for every scene."""
+        self.physics.set_env_gains(gains)
+
     # ------------------------------------------------------------------ kernel hand-off
     def push_config(self):
         """Send gains / null-space posture / thresholds to the handle when they changed (the tuner mutates

@@ -36,6 +36,7 @@ struct b2p_handle_s {
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env;
+  const void* env_gains;
 };
 
 template <typename T>
@@ -70,7 +71,7 @@ template <typename T>
 static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
-  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE;
+  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.gains = (const T*)h->env_gains;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param};
   if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, h->d_next_env, st));
   else CK(launch_f32(h->lg, h->d_model, g, a, h->d_next_env, st));
@@ -141,6 +142,7 @@ int b2p_bind_state(b2p_handle h, void* state) {
 }
 int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out = out ? out : h->own_out; return B2P_OK; }
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
+int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
 int b2p_set_full_contacts(b2p_handle h, int full) { if (!h) return B2P_ERR_ARG; h->full_contacts = full; return B2P_OK; }
 int b2p_osc_config(b2p_handle h, const double g[6], const double q0[7], double pt, double ot) {
   if (!h || !g || !q0) return fail(B2P_ERR_ARG, "b2p_osc_config: null");

@@ -142,10 +142,12 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     T tg[13];
     for (int i = 0; i < 13; i++) tg[i] = active ? a.target[(size_t)env * 13 + i] : T(0);
     const bool grip = (active && a.grip) ? a.grip[env] != 0 : false;
+    T gn[6];   // controller_gains: the handle's (osc.yaml) or this scene's row (the tuner evaluates one candidate per scene)
+    for (int i = 0; i < 6; i++) gn[i] = (active && a.gains) ? a.gains[(size_t)env * 6 + i] : m.osc_gains[i];
     bool conv = false;
     step1(m, g, s, c, full, active);
     if (a.n_steps == 0 && active) {   // OSC.compute_control_output() / is_converged() for the current state, no stepping (derived-output CTRL)
-      osc_torque(m, s, tg, grip, c);
+      osc_torque(m, s, tg, grip, c, gn);
       conv = osc_converged(m, s, tg);
     }
     for (int t = 0; t < a.n_steps; t++) {
@@ -153,7 +155,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       csync(c, LK_TICK);
       PROF_ADD(PF_BARRIER)
       if (active) {
-        osc_torque(m, s, tg, grip, c);
+        osc_torque(m, s, tg, grip, c, gn);
       }
       PROF_ADD(PF_OSC)
       for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); step1(m, g, s, c, full, active); }

@@ -43,7 +43,7 @@ B2P_HD void small_inv_col(const T* L, T* Ainv, int col) {
 // union that is dead between step1 and step2) and their entries / columns are spread over the lanes; the two tiny Cholesky
 // factorisations and the PD terms run on lane 0.
 template <typename T>
-B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T>& s, const T* tg, bool grip, const Ctx& c) {
+B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T>& s, const T* tg, bool grip, const Ctx& c, const T* gn) {
   T* w = s.H;
   T *J = w, *Ma = w + 42, *Minv = w + 91, *MiJt = w + 140, *Lxi = w + 182, *L = w + 218, *Lx = w + 254, *Nb = w + 290;
   T *dx = w + 332, *pd = w + 338, *Lpd = w + 344, *ne = w + 350, *A = w + 360, *V = w + 396;
@@ -87,7 +87,6 @@ B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T>& s, const T* tg, bool g
     T smax = 0; for (int i = 0; i < 6; i++) if (fabs(A[i * 6 + i]) > smax) smax = fabs(A[i * 6 + i]);
     for (int r = 0; r < 6; r++) for (int q = 0; q < 6; q++) { T v = 0; for (int k = 0; k < 6; k++) { const T ev = A[k * 6 + k]; if (fabs(ev) > T(1e-2) * smax) v += V[r * 6 + k] * V[q * 6 + k] / ev; } Lx[r * 6 + q] = v; }
   }
-  const T* gn = m.osc_gains;
   for (int r = c.tid; r < 6; r += c.nt) { T v = 0; for (int i = 0; i < 7; i++) v += J[r * 7 + i] * s.qvel[i]; dx[r] = v; }
   for (int i = c.tid; i < 7; i += c.nt) ne[i] = gn[4] * (m.osc_null[i] - s.qpos[i]) + gn[5] * (0 - s.qvel[i]);
   bsync(c);

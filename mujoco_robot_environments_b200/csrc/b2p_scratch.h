@@ -94,6 +94,7 @@ struct StepArgs {
   T settle_qvel_tol, settle_qacc_tol; int settle_min_steps;
   T* out;                    // MODE_FORWARD / any: optional derived-output record per env (see OutLayout)
   int out_stride;
+  const T* gains;            // MODE_OSC: optional [n_env][6] per-scene OSC gains (pos kp kd, ori kp kd, null kp kd); NULL = the model's
 };
 // derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |
 //   contacts[MAXCON] x (dist, pos3, normal3, geom1, geom2, excluded) | Marm[MAXTD*MAXTD] | gpos[MAXG][3] | gmat[MAXG][9]

@@ -160,6 +160,17 @@ class BatchedPhysics:
         q = (C.c_double * 7)(*[float(x) for x in nullspace7])
         ffi.check(self._L.b2p_osc_config(self._h, g, q, float(pos_thresh), float(ori_thresh)), "b2p_osc_config")
 
+    def set_env_gains(self, gains: Optional[torch.Tensor]):
+        """Per-scene OSC gains [n_env, 6] (position kp, kd, orientation kp, kd, nullspace kp, kd), or None for the handle's."""
+        if gains is None:
+            self._env_gains = None
+            ffi.check(self._L.b2p_set_env_gains(self._h, None))
+            return
+        g = gains.to(device=self.device, dtype=self.dtype).contiguous()
+        assert g.shape == (self.n_env, 6)
+        self._env_gains = g                      # borrowed by the handle: keep it alive
+        ffi.check(self._L.b2p_set_env_gains(self._h, g.data_ptr()))
+
     def set_full_contacts(self, full: bool):
         ffi.check(self._L.b2p_set_full_contacts(self._h, int(full)))
 

@@ -167,3 +167,39 @@ def test_env_pick_and_place_moves_a_prop():
     ok = ((final[:, :2] - place[:, :2]).norm(dim=1) < 0.03) & (final[:, 2] < 0.45)
     assert int(ok.sum()) >= 3
     assert int((env.physics.status() & 7).max()) == 0                                      # no NaN / blow-up flags
+
+
+def test_per_scene_gains_on_gpu():
+    """b2p_set_env_gains: scene i runs with gain row i (oracle configured per scene); None restores the handle's gains."""
+    n, ticks = 4, 20
+    st, size, active = sc.make_states(n, seed=41)
+    tg, grip = sc.random_targets(n, seed=42)
+    gains = np.array([[350, 20, 500, 100, 200, 30], [120, 35, 300, 60, 80, 12], [600, 50, 200, 20, 10, 5], [50, 5, 50, 5, 20, 3]], np.float64)
+    p = _phys(n, torch.float64)
+    p.state.copy_(torch.tensor(st)); p.set_env_params(torch.tensor(size), torch.tensor(active))
+    p.set_env_gains(torch.tensor(gains))
+    p.run_controller(torch.tensor(tg), torch.tensor(grip), ticks)
+    torch.cuda.synchronize()
+    o = Oracle(sc.default_blob())
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0)
+        o.osc_config(gains[i], sc.ARM_HOME)
+        o.run_controller(tg[i], int(grip[i]), ticks)
+        assert np.abs(p.qpos[i].cpu().numpy() - o.qpos[:sc.NQ]).max() < 1e-8, i
+    p.set_env_gains(None)
+    p.state.copy_(torch.tensor(st)); p.run_controller(torch.tensor(tg), torch.tensor(grip), ticks); torch.cuda.synchronize()
+    sc.oracle_load(o, st[3], size[3], active[3]); o.set_option("full_contacts", 0)
+    o.osc_config([350, 20, 500, 100, 200, 30], sc.ARM_HOME)
+    o.run_controller(tg[3], int(grip[3]), ticks)
+    assert np.abs(p.qpos[3].cpu().numpy() - o.qpos[:sc.NQ]).max() < 1e-8
+
+
+def test_batched_tuner_improves_p2p_fitness():
+    """CMA-ES over the six OSC gains with one candidate x target per scene (rearrangement_controller_tuning.py:43-70,145-198)."""
+    from mujoco_robot_environments_b200.tuning import BatchedTuner
+    t = BatchedTuner(popsize=8, targets_per_candidate=16, dtype=torch.float32, seed=0)
+    hist = t.run(generations=3, duration=1.0)
+    assert len(hist) == 3 and all(np.isfinite(h["best_fitness"]) for h in hist)
+    assert hist[-1]["best_fitness"] <= hist[0]["best_fitness"] + 1e-9
+    assert t.best_params.shape == (6,) and (t.best_params >= 0).all()
+    assert t.physics.launches >= 3

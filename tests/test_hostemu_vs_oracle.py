@@ -107,3 +107,20 @@ def test_coupled_blocks(blob, kind, dtype, tol):
     assert ncoupled > 7 + 12                      # more than equality + one resting prop: pads / stacked faces touch
     assert np.abs(got[0, :sc.NQ] - o.qpos[:sc.NQ]).max() < tol
     assert np.abs(got[0, sc.REC_QVEL:sc.REC_QVEL + sc.NV] - o.qvel[:sc.NV]).max() < 200 * tol
+
+
+def test_per_scene_gains(blob):
+    """One tuner candidate per scene (b2p_set_env_gains): every scene follows the oracle configured with ITS gain row."""
+    n, ticks = 3, 30
+    st, size, active = sc.make_states(n, seed=8)
+    tg, grip = sc.random_targets(n, seed=9)
+    gains = np.array([[350, 20, 500, 100, 200, 30], [120, 35, 300, 60, 80, 12], [600, 50, 200, 20, 10, 5]], np.float64)
+    e = HostEmu(blob, np.float64); o = Oracle(blob)
+    got = st.copy()
+    e.run(MODE_OSC, got, n_steps=ticks, target=tg, grip=grip, prop_size=size, prop_active=active, gains=gains)
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0)
+        o.osc_config(gains[i], sc.ARM_HOME)
+        o.run_controller(tg[i], int(grip[i]), ticks)
+        assert np.abs(got[i, :sc.NQ] - o.qpos[:sc.NQ]).max() < 1e-8, i
+    assert np.abs(got[0, :7] - got[1, :7]).max() > 1e-4        # and the rows really differ
