@@ -38,7 +38,7 @@ struct RGeom { int type, padr, pnum, prop, is_static, pad_i[3]; float rgba[4], s
 struct RZone { float pos[3], half[3], rgba[4], pad[2]; };
 struct RCam { float pos[3], mat[9], f, cx, cy, zfar, hl_amb, hl_diff, lpos[3], ldiff, rgb2[3], check, pad[6]; };
 static_assert(sizeof(RGeom) == 128 && sizeof(RZone) == 48 && sizeof(RCam) == 128, "B2PR record sizes");
-struct RModel { int ngeom, nplane, nzone, W, H, nprop, pad[2]; RCam cam; RGeom geom[RMAXG]; RZone zone[RMAXZ]; };
+struct RModel { int ngeom, nplane, nzone, W, H, nprop, n_static, pad; RCam cam; RGeom geom[RMAXG]; RZone zone[RMAXZ]; int static_ids[RMAXG]; };
 
 struct FrameArgs {
   int n_env, pose_stride, dtype, background;
@@ -122,7 +122,7 @@ __device__ __forceinline__ bool ray_box(const float* o, const float* d, const fl
 }
 
 __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const float* pos, const float* mat, const float* cen, const float* half,
-                                         const float4* __restrict__ planes, int np, float* t_out, float* n_out) {
+                                         const float4* __restrict__ planes, int np, float t_max, float* t_out, float* n_out) {
   float ol[3], dl[3];
   const float w0 = o[0] - pos[0], w1 = o[1] - pos[1], w2 = o[2] - pos[2];
   for (int k = 0; k < 3; k++) { ol[k] = mat[k] * w0 + mat[3 + k] * w1 + mat[6 + k] * w2; dl[k] = mat[k] * d[0] + mat[3 + k] * d[1] + mat[6 + k] * d[2]; }
@@ -140,6 +140,7 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
       } else if (fabsf(c) > half[k]) return false;
     }
     if (tn > tf || tf <= 0.0f) return false;
+    if (tn > t_max) return false;      // the hull lies inside the box: it cannot beat (or tie) a hit nearer than the box's entry
   }
   // Entry / exit parameters are kept as fractions num / den (entry: den < 0, exit: den > 0) and compared by cross
   // multiplication, so the loop has no division and no data-dependent branch besides its exit; one division at the end.
@@ -187,29 +188,32 @@ __device__ __forceinline__ float shade_factor(const RCam& C, const float* p, con
 }
 __device__ __forceinline__ float clamp01(float x) { return fminf(1.0f, fmaxf(0.0f, x)); }
 
-struct TileGeoms { float pos[RMAXG][3], mat[RMAXG][9], size[RMAXG][3], rgb[RMAXG][3]; };
+struct TileGeoms { float pos[RMAXG][3], mat[RMAXG][9], size[RMAXG][3], rgb[RMAXG][3]; unsigned char order[RMAXG]; int n_order; };
 
 // one pixel: nearest opaque geom among the static geoms and the listed moving geoms, then the nearest translucent zone in front
-__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, unsigned dyn_mask, const float4* __restrict__ planes, int u, int v,
+__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const float4* __restrict__ planes, int u, int v,
                            unsigned char* rgb_out, float* depth_out, int* seg_out) {
   const RCam& C = M.cam;
   const float dc0 = ((float)u - C.cx) / C.f, dc1 = (C.cy - (float)v) / C.f;             // camera-frame direction (x, y, -1): t is the axial depth
   float d[3], o[3] = {C.pos[0], C.pos[1], C.pos[2]};
   for (int k = 0; k < 3; k++) d[k] = C.mat[3 * k] * dc0 + C.mat[3 * k + 1] * dc1 - C.mat[3 * k + 2];
   float best_t = C.zfar; int best_id = -1; float bn[3] = {0, 0, 0}, brgb[3] = {0, 0, 0};
-  for (int g = 0; g < M.ngeom; g++) {
+  // Moving geoms first, nearest first (tg.order), then the static ones: a hull whose bounding box starts behind the current hit
+  // is skipped without touching its planes.  The winner is order independent: smallest t, then smallest geom id.
+  const int n_items = tg.n_order + M.n_static;
+  for (int it = 0; it < n_items; it++) {
+    const int g = it < tg.n_order ? tg.order[it] : M.static_ids[it - tg.n_order];
     const RGeom& G = M.geom[g];
     const bool dyn = !G.is_static;
-    if (dyn && !((dyn_mask >> g) & 1u)) continue;
     const float* pos = dyn ? tg.pos[g] : G.spos;
     const float* mat = dyn ? tg.mat[g] : G.smat;
     float t, n[3], rgb[3];
     bool hit;
     if (G.type == GEOM_BOX) { hit = ray_box(o, d, pos, mat, (dyn && G.prop >= 0) ? tg.size[g] : G.size, &t, n); }
-    else if (G.type == GEOM_MESH) { hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, &t, n); }
+    else if (G.type == GEOM_MESH) { hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, best_t, &t, n); }
     else if (G.type == GEOM_PLANE) { hit = ray_ground(o, d, pos, mat, G.size, C.check, G.rgba, C.rgb2, &t, n, rgb); }
     else hit = false;
-    if (hit && t < best_t) {
+    if (hit && (t < best_t || (t == best_t && g < best_id))) {
       best_t = t; best_id = g; bn[0] = n[0]; bn[1] = n[1]; bn[2] = n[2];
       if (G.type != GEOM_PLANE) { const float* c = (dyn && G.prop >= 0) ? tg.rgb[g] : G.rgba; rgb[0] = c[0]; rgb[1] = c[1]; rgb[2] = c[2]; }
       brgb[0] = rgb[0]; brgb[1] = rgb[1]; brgb[2] = rgb[2];
@@ -290,10 +294,19 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
           }
         }
       }
+      {   // nearest-first order of the listed geoms (depth of the geom origin along the view axis; ties by id)
+        const bool on = (mask >> lane) & 1u;
+        float key = 3.0e38f;
+        if (on) key = -(M.cam.mat[2] * (S.tg.pos[lane][0] - M.cam.pos[0]) + M.cam.mat[5] * (S.tg.pos[lane][1] - M.cam.pos[1]) + M.cam.mat[8] * (S.tg.pos[lane][2] - M.cam.pos[2]));
+        int rank = 0;
+        for (int j = 0; j < 32; j++) { const float kj = __shfl_sync(0xffffffffu, key, j); if (((mask >> j) & 1u) && (kj < key || (kj == key && j < lane))) rank++; }
+        if (on) S.tg.order[rank] = (unsigned char)lane;
+        if (lane == 0) S.tg.n_order = __popc(mask);
+      }
       __syncwarp();
       for (int ly = 0; ly < TH; ly++) {
         float dep; int sg;
-        cast_pixel(M, S.tg, mask, a.planes, tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
+        cast_pixel(M, S.tg, a.planes, tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
         const size_t off = (size_t)(ty0 + ly) * M.W + tx0 + lane;
         if (a.depth) a.depth[img + off] = dep;
         if (a.seg) a.seg[img + off] = sg;
@@ -351,6 +364,8 @@ int b2p_render_create(const void* blob, size_t nbytes, int device, b2p_render_ha
   memcpy(&M.cam, p, 128); p += 128;
   memcpy(M.geom, p, (size_t)ng * 128); p += (size_t)ng * 128;
   memcpy(M.zone, p, (size_t)nz * 48); p += (size_t)nz * 48;
+  M.n_static = 0;
+  for (int g = 0; g < ng; g++) if (M.geom[g].is_static) M.static_ids[M.n_static++] = g;
   for (int g = 0; g < ng; g++) if (M.geom[g].type == GEOM_MESH && (M.geom[g].padr < 0 || M.geom[g].padr + M.geom[g].pnum > np)) { delete h; return b2p::api_fail(B2P_ERR_MODEL, "b2p_render_create: plane range"); }
   RCK(cudaSetDevice(device));
   RCK(cudaDeviceGetAttribute(&h->sms, cudaDevAttrMultiProcessorCount, device));
