@@ -33,14 +33,14 @@ def pack_action(pose: torch.Tensor, pixel: torch.Tensor) -> torch.Tensor:
     return torch.cat([pose.to(torch.float64), pixel.to(torch.float64), torch.zeros(pose.shape[0], 1, dtype=torch.float64, device=pose.device)], 1)
 
 
-def rollout_episode(env, max_steps: int, render: bool = False) -> Dict[str, torch.Tensor]:
+def rollout_episode(env, max_steps: int, render: bool = False, resample_props: bool = False) -> Dict[str, torch.Tensor]:
     """One episode per scene.  -> dict of device tensors with leading dim n_env:
     ``actions`` [n, T, 2, 10] (pick, place), ``valid`` [n, T] (the scene acted in round t), ``prop_pos0`` / ``prop_quat0`` (state
     observation at reset), ``success`` [n] (every prop inside its colour zone at the end), ``failed`` [n], ``rounds`` [n];
     with ``render`` also ``rgb`` u8 [n, T, 2, H, W, 3] / ``depth`` f32 [n, T, 2, H, W] (the observation ``step`` returns: the
     frame BEFORE acting, rearrangement.py:343)."""
     n, dev = env.num_envs, env.device
-    ts = env.reset()
+    ts = env.reset(resample_props=resample_props)
     obs0 = ts.observation
     actions = torch.zeros(n, max_steps, 2, ACTION_WIDTH, dtype=torch.float64, device=dev)
     valid = torch.zeros(n, max_steps, dtype=torch.bool, device=dev)
@@ -86,8 +86,9 @@ def generate(num_envs: int = 1024, episodes_per_env: int = 1, cfg: Optional[dict
                                   seed=base_seed + 100003 * rank, strict=False)
     demos, t0 = [], time.perf_counter()
     launches0 = env.physics.launches
-    for _ in range(episodes_per_env):
-        demos.append(rollout_episode(env, T, render))
+    for ep in range(episodes_per_env):
+        # the reference builds a fresh env (new props) every 10 episodes (transporter_network_data_generation.py:99-101,118)
+        demos.append(rollout_episode(env, T, render, resample_props=ep > 0 and ep % 10 == 0))
     torch.cuda.synchronize(env.device)
     wall = time.perf_counter() - t0
     local = {k: torch.cat([d[k] for d in demos], 0) for k in demos[0] if all(k in d for d in demos)}

@@ -59,21 +59,14 @@ class BatchedRearrangementEnv:
         self.max_props = p.model.nprop
         pc = self._cfg["arena"]["props"]
         tseed = int(self._cfg["task"]["initializers"]["seed"]) if seed is None else int(seed)
-        # scene construction randomness (props.py:604-607 num_objects, :277-284 cube size): unseeded in the reference
-        crng = np.random.default_rng(tseed + 7919)
-        lo, hi = int(pc["min_objects"]), int(pc["max_objects"])
-        n = np.full(self.num_envs, lo) if lo == hi else crng.integers(lo, hi, self.num_envs)      # np.random.randint(lo, hi): hi exclusive
-        if n.max() > self.max_props:
-            raise ValueError("prop set needs %d props, the compiled model has %d" % (n.max(), self.max_props))
-        half = crng.uniform(pc["min_object_size"], pc["max_object_size"], (self.num_envs, self.max_props, 1)).repeat(3, axis=2)
-        self.n_props = torch.tensor(n, device=self.device)
-        self.has_prop = torch.arange(self.max_props, device=self.device)[None, :] < self.n_props[:, None]
-        self.prop_half_size = torch.tensor(half, device=self.device, dtype=self.dtype)
-        p.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8))
-        # colour label + rgba per prop (props.py:604-617, :286-291); "grey" of single_block has no COLOURS entry in the reference either
-        cidx, rgba = sample_prop_colours(self.num_envs, self.max_props, [c for c in pc["colours"] if c != "grey"], crng)
-        self.prop_colour = torch.tensor(cidx, device=self.device)
-        self.prop_rgba = torch.tensor(rgba, device=self.device)
+        # scene construction randomness (props.py:604-607 num_objects, :277-284 cube size, :286-291 colour): unseeded in the reference
+        self._crng = np.random.default_rng(tseed + 7919)
+        self.n_props = torch.zeros(self.num_envs, dtype=torch.int64, device=self.device)
+        self.has_prop = torch.zeros(self.num_envs, self.max_props, dtype=torch.bool, device=self.device)
+        self.prop_half_size = torch.zeros(self.num_envs, self.max_props, 3, device=self.device, dtype=self.dtype)
+        self.prop_colour = torch.zeros(self.num_envs, self.max_props, dtype=torch.int64, device=self.device)
+        self.prop_rgba = torch.zeros(self.num_envs, self.max_props, 4, dtype=torch.float32, device=self.device)
+        self.resample_scenes()
         self.camera = Camera(next(c for c in self._cfg["arena"]["cameras"] if c["name"] == "overhead_camera"))
         self.overhead_camera_height, self.overhead_camera_width = self.camera.height, self.camera.width
         self._expert: Optional[SortColoursExpert] = None
@@ -86,7 +79,9 @@ class BatchedRearrangementEnv:
         self._robot: Optional[BatchedRobotArm] = None
         # PropPlacer randomness: np.random.RandomState(seed) per scene (rearrangement.py:207); scene e uses seed + e so that
         # scene 0 reproduces the reference's draw order exactly
-        self._sampler = sampler if sampler != "auto" else ("per_env" if self.num_envs <= 4096 else "vectorised")
+        # "device": proposals drawn with the device generator, no host round trip inside the rejection loops
+        self._sampler = sampler if sampler != "auto" else ("per_env" if self.num_envs <= 4096 else "device")
+        self._dgen = torch.Generator(device=self.device); self._dgen.manual_seed(tseed)
         self._rs = [np.random.RandomState(seed=tseed + e) for e in range(self.num_envs)] if self._sampler == "per_env" else None
         self._vrng = np.random.default_rng(tseed)
         self._table_gid = p.geom_id(TABLE_GEOM)
@@ -94,6 +89,30 @@ class BatchedRearrangementEnv:
         self.mode = None
         self.failed = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
         self.eef_home_pose = None
+
+    def resample_scenes(self, mask: Optional[torch.Tensor] = None):
+        """Draw prop count, cube size and colour / rgba for the scenes in ``mask`` (all by default): what constructing a NEW
+        ``RearrangementEnv`` does in the reference (``add_objects``, props.py:583-639; the data generator builds a fresh env every
+        10 episodes, transporter_network_data_generation.py:99-101).  Takes effect at the next ``reset`` of those scenes."""
+        pc = self._cfg["arena"]["props"]
+        idx = np.arange(self.num_envs) if mask is None else torch.nonzero(mask.to(self.device)).flatten().cpu().numpy()
+        k = len(idx)
+        if k == 0:
+            return
+        lo, hi = int(pc["min_objects"]), int(pc["max_objects"])
+        n = np.full(k, lo) if lo == hi else self._crng.integers(lo, hi, k)                    # np.random.randint(lo, hi): hi exclusive
+        if n.max() > self.max_props:
+            raise ValueError("prop set needs %d props, the compiled model has %d" % (n.max(), self.max_props))
+        half = self._crng.uniform(pc["min_object_size"], pc["max_object_size"], (k, self.max_props, 1)).repeat(3, axis=2)
+        # "grey" of single_block has no COLOURS entry in the reference either
+        cidx, rgba = sample_prop_colours(k, self.max_props, [c for c in pc["colours"] if c != "grey"], self._crng)
+        di = torch.as_tensor(idx, device=self.device)
+        self.n_props[di] = torch.tensor(n, device=self.device)
+        self.has_prop[di] = torch.arange(self.max_props, device=self.device)[None, :] < self.n_props[di][:, None]
+        self.prop_half_size[di] = torch.tensor(half, device=self.device, dtype=self.dtype)
+        self.prop_colour[di] = torch.tensor(cidx, device=self.device)
+        self.prop_rgba[di] = torch.tensor(rgba, device=self.device)
+        self._physics.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8))
 
     # ------------------------------------------------------------------ accessors
     @property
@@ -152,14 +171,24 @@ class BatchedRearrangementEnv:
                 if not bool(todo.any()):
                     continue
                 active[todo, k] = 1
-                for _ in range(int(pcfg["max_attempts_per_prop"])):
-                    envs = torch.nonzero(todo).flatten()
-                    pos, quat = self._sample_poses(envs.cpu().numpy())
-                    pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
-                    p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
+                for attempt in range(int(pcfg["max_attempts_per_prop"])):
+                    if self._sampler == "device":
+                        # every scene draws; only the scenes still searching take the proposal (no nonzero / host sync per try)
+                        w = self._cfg["task"]["initializers"]["workspace"]
+                        lo = torch.tensor(w["min_pose"], device=self.device, dtype=self.dtype); hi = torch.tensor(w["max_pose"], device=self.device, dtype=self.dtype)
+                        u = torch.rand(self.num_envs, 4, device=self.device, dtype=self.dtype, generator=self._dgen)
+                        ang = math.pi * u[:, 3]
+                        pose = torch.cat([lo + (hi - lo) * u[:, :3], torch.cos(ang / 2)[:, None], torch.zeros(self.num_envs, 2, device=self.device, dtype=self.dtype),
+                                          torch.sin(ang / 2)[:, None]], 1)
+                        p.qpos[:, qadr[k]:qadr[k] + 7] = torch.where(todo[:, None], pose, p.qpos[:, qadr[k]:qadr[k] + 7])
+                    else:
+                        envs = torch.nonzero(todo).flatten()
+                        pos, quat = self._sample_poses(envs.cpu().numpy())
+                        pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
+                        p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
                     p.forward(full_contacts=True)
                     todo = todo & self._collides(k)
-                    if not bool(todo.any()):
+                    if (self._sampler != "device" or attempt % 4 == 3) and not bool(todo.any()):
                         break
                 else:
                     if self.strict:
@@ -204,9 +233,13 @@ class BatchedRearrangementEnv:
         return False
 
     # ------------------------------------------------------------------ dm_env API
-    def reset(self, mask: Optional[torch.Tensor] = None) -> TimeStep:
+    def reset(self, mask: Optional[torch.Tensor] = None, resample_props: bool = False) -> TimeStep:
+        """``mask`` resets a subset of scenes; ``resample_props`` re-draws their prop count / size / colour first (a new env in
+        the reference)."""
         p = self._physics
         m = torch.ones(self.num_envs, dtype=torch.bool, device=self.device) if mask is None else mask.to(self.device, torch.bool)
+        if resample_props:
+            self.resample_scenes(m)
         p.reset(m)                                                                            # rearrangement.py:302
         home = torch.tensor(self._cfg["robots"]["arm"]["configuration"]["home"], device=self.device, dtype=self.dtype)
         p.qpos[m, 0:7] = home                                                                 # :306

@@ -203,3 +203,27 @@ def test_batched_tuner_improves_p2p_fitness():
     assert hist[-1]["best_fitness"] <= hist[0]["best_fitness"] + 1e-9
     assert t.best_params.shape == (6,) and (t.best_params >= 0).all()
     assert t.physics.launches >= 3
+
+
+def test_device_sampler_reset_and_scene_resampling():
+    """proposals drawn on the device (no host round trip per rejection round); every placed prop respects the
+    reference's rule (no listed contact with another prop), and ``reset(resample_props=True)`` re-draws count / size / colour."""
+    from mujoco_robot_environments_b200.env import BatchedRearrangementEnv
+    env = BatchedRearrangementEnv(num_envs=128, sampler="device", strict=False, dtype=torch.float32)
+    env.reset()
+    assert not bool(env.failed.any())
+    p = env.physics
+    qa = p.model.prop_qposadr
+    pos = torch.stack([p.qpos[:, a:a + 3] for a in qa], 1)
+    lo, hi = torch.tensor([0.35, -0.4], device=env.device), torch.tensor([0.55, 0.4], device=env.device)
+    inside = ((pos[..., :2] >= lo - 0.02) & (pos[..., :2] <= hi + 0.02)).all(-1)
+    assert bool(inside[env.has_prop].all())
+    assert bool((pos[..., 2][env.has_prop] - 0.4 - env.prop_half_size[..., 2][env.has_prop]).abs().max() < 2e-3)      # resting on the table
+    d = (pos[:, :, None, :2] - pos[:, None, :, :2]).norm(dim=-1)
+    pair = env.has_prop[:, :, None] & env.has_prop[:, None, :] & ~torch.eye(4, dtype=torch.bool, device=env.device)[None]
+    assert float(d[pair].min()) > 0.15            # outside each other's 0.15 contact margin (prop_initializer.py:121-140)
+    n0, c0 = env.n_props.clone(), env.prop_colour.clone()
+    env.reset(resample_props=True)
+    assert not torch.equal(n0, env.n_props) and not torch.equal(c0, env.prop_colour)
+    assert bool((env.n_props >= 2).all() & (env.n_props <= 4).all())
+    assert torch.equal(p.prop_active.bool(), env.has_prop)
