@@ -147,8 +147,9 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
   float tn_n = 1e30f, tn_d = -1.0f, tf_n = 1e30f, tf_d = 1.0f; int best = -1;
   for (int i = 0; i < np; i++) {
     const float4 P = __ldg(planes + i);
-    const float den = P.x * dl[0] + P.y * dl[1] + P.z * dl[2];
-    const float dist = P.w - (P.x * ol[0] + P.y * ol[1] + P.z * ol[2]);
+    // explicit fused multiply-adds (the oracle calls C99 fmaf at the same places; everything else in this file is unfused)
+    const float den = __fmaf_rn(P.z, dl[2], __fmaf_rn(P.y, dl[1], P.x * dl[0]));
+    const float dist = P.w - __fmaf_rn(P.z, ol[2], __fmaf_rn(P.y, ol[1], P.x * ol[0]));
     if (den == 0.0f) { if (dist < 0.0f) return false; continue; }
     if (den < 0.0f) { if (dist * tn_d > tn_n * den) { tn_n = dist; tn_d = den; best = i; } }      // dist / den > tn
     else if (dist * tf_d < tf_n * den) { tf_n = dist; tf_d = den; }                              // dist / den < tf

@@ -55,8 +55,9 @@ static int hit_hull(const float* o, const float* d, const float* pos, const floa
   to_local(o, d, pos, mat, ol, dl);
   for (int i = 0; i < np; i++) {
     const float* P = planes + 4 * i;
-    float den = P[0] * dl[0] + P[1] * dl[1] + P[2] * dl[2];
-    float dist = P[3] - (P[0] * ol[0] + P[1] * ol[1] + P[2] * ol[2]);
+    /* the two plane dot products are fused multiply-adds (correctly rounded fmaf), as in the kernel */
+    float den = fmaf(P[2], dl[2], fmaf(P[1], dl[1], P[0] * dl[0]));
+    float dist = P[3] - fmaf(P[2], ol[2], fmaf(P[1], ol[1], P[0] * ol[0]));
     if (den == 0.0f) { if (dist < 0.0f) return 0; continue; }
     if (den < 0.0f) { if (dist * tn_d > tn_n * den) { tn_n = dist; tn_d = den; best = i; } }
     else if (dist * tf_d < tf_n * den) { tf_n = dist; tf_d = den; }
