@@ -5,10 +5,17 @@ namespace b2p {
 
 // ------------------------------------------------------------------------------------------ collision
 template <typename T>
-struct CObj { const T* pos; const T* mat; const T* size; const T* vert; int type, vadr, vnum, cur; T margin; };
+struct CObj { const T* pos; const T* mat; const T* size; const T* vert; int type, vadr, vnum, cur; T margin; const int* start; };
 
 // support point in world direction dir (|dir| = 1), inflated by margin/2.  Meshes: hill climbing over the
-// hull graph with warm start inside one query (what MuJoCo does for meshes with a graph).
+// hull graph with warm start inside one query (what MuJoCo does for meshes with a graph).  The FIRST call of a query starts
+// from the hull's extreme vertex along the nearest of 26 tabulated directions (Globals::geom_start) instead of vertex 0:
+// the climb is a chain of dependent global loads, and this cuts it from ~sqrt(nvert) steps to one or two.  On a convex
+// hull the climb ends at the same maximum wherever it starts.
+// slot of a (unit) direction in the 3x3x3 start table: each component quantised to {-1, 0, +1} at +-0.4
+template <typename T> B2P_HD int start_slot(const T* d) {
+  return ((d[0] > T(0.4)) - (d[0] < T(-0.4)) + 1) * 9 + ((d[1] > T(0.4)) - (d[1] < T(-0.4)) + 1) * 3 + ((d[2] > T(0.4)) - (d[2] < T(-0.4)) + 1);
+}
 template <typename T>
 B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
   T ld[3], lp[3];
@@ -16,7 +23,9 @@ B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
   if (o.type == B2P_GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? o.size[k] : -o.size[k];
   } else {
-    int v = o.cur; T best = dot3(g.mesh_vert + 3 * v, ld);
+    int v = o.cur;
+    if (v < 0) v = o.start[start_slot(ld)];
+    T best = dot3(g.mesh_vert + 3 * v, ld);
     for (int guard = 0; guard < 4096; guard++) {
       int nb = v; const int a = g.nbradr[v], n = g.nbrnum[v];
       for (int q = 0; q < n; q++) { const int u = g.nbr[a + q]; const T d = dot3(g.mesh_vert + 3 * u, ld); if (d > best) { best = d; nb = u; } }
@@ -353,8 +362,8 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
         bool convex = true;
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw); convex = n < 0; if (n < 0) n = 0; }
         if (convex) {
-          CObj<T> a = {s.gpos[g1], s.gmat[g1], sz1, nullptr, t1, m.geom_vertadr[g1], m.geom_vertnum[g1], m.geom_vertadr[g1], md};
-          CObj<T> b = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], m.geom_vertadr[g2], md};
+          CObj<T> a = {s.gpos[g1], s.gmat[g1], sz1, nullptr, t1, m.geom_vertadr[g1], m.geom_vertnum[g1], -1, md, g.geom_start + 27 * g1};
+          CObj<T> b = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, md, g.geom_start + 27 * g2};
           T depth, dir[3], pos[3];
           if (mpr_penetration(a, b, g, m.ccd_iterations, tol, depth, dir, pos) && depth >= 0) {
             raw.dist[0] = md - depth; cp3(raw.normal, dir); cp3(raw.pos[0], pos); n = 1;

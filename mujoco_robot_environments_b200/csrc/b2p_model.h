@@ -86,7 +86,7 @@ struct alignas(16) DevModel {
 
 // ------------------------------------------------------------------------------------------ host builder
 struct HostTables {              // global-memory tables, always fp64 on host; converted on upload
-  std::vector<double> mesh_vert; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr;
+  std::vector<double> mesh_vert; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr, geom_start;
   std::vector<int> pair_g1, pair_g2; std::vector<double> pair_param;  // 12 doubles per pair
 };
 
@@ -213,6 +213,20 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     const int nmesh = b.C(B2PM_C_NMESH);
     for (int me = 0; me < nmesh; me++) for (int v = vadr[me]; v < vadr[me] + vnum[me]; v++)
       for (int q = ht.mesh_nbradr[v]; q < ht.mesh_nbradr[v] + ht.mesh_nbrnum[v]; q++) ht.mesh_nbr[q] += vadr[me];
+  }
+  // hill-climb start table: for every mesh geom and each of the 26 quantised directions the hull's extreme vertex (global index)
+  ht.geom_start.assign((size_t)MAXG * 27, 0);
+  for (int g = 0; g < m.ngeom; g++) {
+    if (m.geom_vertnum[g] <= 0) continue;
+    for (int q = 0; q < 27; q++) {
+      const double d[3] = {double(q / 9 - 1), double((q / 3) % 3 - 1), double(q % 3 - 1)};
+      int best = m.geom_vertadr[g]; double bd = -1e300;
+      for (int v = m.geom_vertadr[g]; v < m.geom_vertadr[g] + m.geom_vertnum[g]; v++) {
+        const double x = ht.mesh_vert[3 * v] * d[0] + ht.mesh_vert[3 * v + 1] * d[1] + ht.mesh_vert[3 * v + 2] * d[2];
+        if (x > bd) { bd = x; best = v; }
+      }
+      ht.geom_start[(size_t)g * 27 + q] = best;
+    }
   }
   const int *p1 = b.I(B2PM_F_PAIR_GEOM1), *p2 = b.I(B2PM_F_PAIR_GEOM2), *prio = b.I(B2PM_F_GEOM_PRIORITY);
   const double *fr = b.D(B2PM_F_GEOM_FRICTION), *sr = b.D(B2PM_F_GEOM_SOLREF), *si = b.D(B2PM_F_GEOM_SOLIMP), *sm = b.D(B2PM_F_GEOM_SOLMIX);

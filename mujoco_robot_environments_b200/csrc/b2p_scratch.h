@@ -10,6 +10,7 @@ template <typename T>
 struct Globals {                 // read-only global-memory tables
   const T* mesh_vert; const int* nbradr; const int* nbrnum; const int* nbr;
   const short* pair_g1; const short* pair_g2; const PairParam<T>* pair_param;
+  const int* geom_start;         // [ngeom][27] hill-climb start vertex per quantised direction (mesh geoms)
 };
 
 // Shared memory per scene is what bounds the number of resident warps (= scenes in flight) per SM, and the kernel is latency

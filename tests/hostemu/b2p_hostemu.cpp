@@ -31,7 +31,7 @@ static Emu<T>* make(const void* blob, size_t n) {
     for (int k = 0; k < 5; k++) p.solimp[k] = (T)q[5 + k];
     p.margin = (T)q[10]; p.gap = (T)q[11]; e->pp.push_back(p);
   }
-  e->g.mesh_vert = e->mesh_vert.data(); e->g.nbradr = e->ht.mesh_nbradr.data(); e->g.nbrnum = e->ht.mesh_nbrnum.data(); e->g.nbr = e->ht.mesh_nbr.data();
+  e->g.mesh_vert = e->mesh_vert.data(); e->g.nbradr = e->ht.mesh_nbradr.data(); e->g.nbrnum = e->ht.mesh_nbrnum.data(); e->g.nbr = e->ht.mesh_nbr.data(); e->g.geom_start = e->ht.geom_start.data();
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
   e->s = new Scratch<T>();
   return e;
