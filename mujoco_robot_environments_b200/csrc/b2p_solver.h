@@ -14,14 +14,18 @@ B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, c
 }
 // per-item (rows of eq/limit, whole contacts) force/state/cost from s.Jaref; returns this thread's cost part
 template <typename T>
-B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess) {
-  T cost = 0;
+B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess, unsigned* dirty = nullptr) {
+  // dirty: this thread saw a row change state, or a contact in the cone's middle zone (whose Hessian block moves with the point):
+  // when no thread did, the Newton Hessian of the previous iteration -- and its factor in s.H -- is still exact
+  T cost = 0; unsigned chg = 0;
   for (int r = c.tid; r < s.nefc; r += c.nt) {
     const int tp = s.row_type[r];
     if (tp == ROW_CONTACT) continue;
     const T j = s.Jaref[r];
+    const int old = s.row_state[r];
     if (tp == ROW_EQ || j < 0) { s.force[r] = -s.D[r] * j; s.row_state[r] = ST_QUADRATIC; cost += T(0.5) * s.D[r] * j * j; }
     else { s.force[r] = 0; s.row_state[r] = ST_SATISFIED; }
+    chg |= (unsigned)(old != s.row_state[r]);
   }
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
@@ -30,6 +34,7 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, b
     const T j0 = s.Jaref[r], j1 = s.Jaref[r + 1], j2 = s.Jaref[r + 2];
     const T N = j0 * mu, U1 = j1 * f1, U2 = j2 * f2, Tt = sqrt(U1 * U1 + U2 * U2);
     T* W = s.cW[k];
+    const int old = s.row_state[r];
     if (N >= mu * Tt || (Tt <= 0 && N >= 0)) {
       for (int q = 0; q < 3; q++) { s.force[r + q] = 0; s.row_state[r + q] = ST_SATISFIED; }
       if (want_hess) for (int q = 0; q < 6; q++) W[q] = 0;
@@ -49,7 +54,9 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, b
         W[0] = h00 * mu * mu; W[1] = h11 * f1 * f1; W[2] = h22 * f2 * f2; W[3] = h01 * mu * f1; W[4] = h02 * mu * f2; W[5] = h12 * f1 * f2;
       }
     }
+    chg |= (unsigned)(old != s.row_state[r] || s.row_state[r] == ST_CONE);
   }
+  if (dirty) *dirty = chg;
   return cost;
 }
 // qfrc_con = J' force: one lane per dof, walking only the items of the dof's block
@@ -156,8 +163,10 @@ B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x)
 }
 // cost and gradient at s.qacc (s.Jaref / s.Ma consistent with it); also the per-contact cone Hessian weights
 template <typename T>
-B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2) {
-  T v[2] = {constraint_update(m, s, c, true), 0};
+B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2, bool& hess_dirty) {
+  unsigned chg = 0;
+  T v[2] = {constraint_update(m, s, c, true, &chg), 0};
+  hess_dirty = block_or(c, chg) != 0;
   bsync(c);
   mul_JT_force(m, s, c);
   bsync(c);
@@ -172,13 +181,15 @@ B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gr
 }
 // Newton direction: search = -H^-1 grad with H = M + J' W J factored on its block structure
 template <typename T>
-B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool refactor) {
   PROF_T0
-  assemble_H(m, s, c);
-  bsync(c);
-  PROF_ADD(PF_ASSEMBLE)
-  sp_cholesky(s.H, s.sp, m.tri, c);
-  PROF_ADD(PF_CHOL)
+  if (refactor) {   // otherwise s.H still holds the factor of the identical Hessian of the previous iteration
+    assemble_H(m, s, c);
+    bsync(c);
+    PROF_ADD(PF_ASSEMBLE)
+    sp_cholesky(s.H, s.sp, m.tri, c);
+    PROF_ADD(PF_CHOL)
+  }
   sp_solve(s.H, s.sp, s.Mgrad, 6 * m.nprop, m.ntd, c);
   for (int d = c.tid; d < m.nv; d += c.nt) s.search[d] = -s.Mgrad[d];
   bsync(c);
@@ -232,14 +243,15 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     bsync(c);
   }
   const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
-  T gn2 = 0, cost = 0;
+  T gn2 = 0, cost = 0; bool dirty = true;
   PROF_T0
   if (has) {
     const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
     for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
     bsync(c);
     cost_at(m, s, c, s.qacc);
-    cost = solver_update(m, s, c, gn2);
+    cost = solver_update(m, s, c, gn2, dirty);
+    dirty = true;   // nothing factored yet in this step
   }
   PROF_ADD(PF_SOLVE_INIT)
   int it = 0;
@@ -249,7 +261,7 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
   bool run = has && it < m.iterations;
   while (csync_or(c, LK_NEWTON, run)) {
     if (!run) continue;
-    newton_direction(m, s, c);
+    newton_direction(m, s, c, dirty);
     PROF_RESET
     const T alpha = line_search(m, s, c, scale);
     PROF_ADD(PF_LS)
@@ -258,7 +270,7 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] += alpha * s.Jv[r];
     bsync(c);
     const T old = cost;
-    cost = solver_update(m, s, c, gn2);
+    cost = solver_update(m, s, c, gn2, dirty);
     PROF_ADD(PF_UPDATE)
     const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
     it++;
