@@ -5,6 +5,7 @@
 #include <cstdio>
 #include <cstdlib>
 #include <string>
+#include <vector>
 
 #include "../../include/b2p.h"
 #include "b2p_launch.h"
@@ -33,7 +34,7 @@ struct b2p_handle_s {
   LaunchGeom lg;
   long long launches;
   DevModel<double> hmodel;
-  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; short *d_g1, *d_g2; void* d_pair_param;
+  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env;
   const void* env_gains;
@@ -57,6 +58,13 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   CK(cudaMalloc(&h->d_g1, g1.size() * 2 + 16)); CK(cudaMemcpy(h->d_g1, g1.data(), g1.size() * 2, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_g2, g2.size() * 2 + 16)); CK(cudaMemcpy(h->d_g2, g2.data(), g2.size() * 2, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_geom_start, ht.geom_start.size() * 4 + 16)); CK(cudaMemcpy(h->d_geom_start, ht.geom_start.data(), ht.geom_start.size() * 4, cudaMemcpyHostToDevice));
+  {
+    std::vector<NbrPt<T>> np(ht.mesh_nbr.size()); std::vector<NbrSpan> ns(ht.mesh_nbradr.size());
+    for (size_t q = 0; q < np.size(); q++) { const int u = ht.mesh_nbr[q]; np[q].x = (T)ht.mesh_vert[3 * u]; np[q].y = (T)ht.mesh_vert[3 * u + 1]; np[q].z = (T)ht.mesh_vert[3 * u + 2]; np[q].idx = u; }
+    for (size_t v = 0; v < ns.size(); v++) { ns[v].adr = ht.mesh_nbradr[v]; ns[v].num = ht.mesh_nbrnum[v]; }
+    CK(cudaMalloc(&h->d_nbr_pt, np.size() * sizeof(NbrPt<T>) + 32)); CK(cudaMemcpy(h->d_nbr_pt, np.data(), np.size() * sizeof(NbrPt<T>), cudaMemcpyHostToDevice));
+    CK(cudaMalloc(&h->d_nbr_span, ns.size() * sizeof(NbrSpan) + 16)); CK(cudaMemcpy(h->d_nbr_span, ns.data(), ns.size() * sizeof(NbrSpan), cudaMemcpyHostToDevice));
+  }
   CK(cudaMalloc(&h->d_nbradr, ht.mesh_nbradr.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbradr, ht.mesh_nbradr.data(), ht.mesh_nbradr.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_nbrnum, ht.mesh_nbrnum.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbrnum, ht.mesh_nbrnum.data(), ht.mesh_nbrnum.size() * 4, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_nbr, ht.mesh_nbr.size() * 4 + 16)); CK(cudaMemcpy(h->d_nbr, ht.mesh_nbr.data(), ht.mesh_nbr.size() * 4, cudaMemcpyHostToDevice));
@@ -73,7 +81,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.gains = (const T*)h->env_gains;
-  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start};
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span};
   if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, h->d_next_env, st));
   else CK(launch_f32(h->lg, h->d_model, g, a, h->d_next_env, st));
   h->launches++;
@@ -111,7 +119,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;

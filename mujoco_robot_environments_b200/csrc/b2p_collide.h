@@ -1,5 +1,8 @@
 #pragma once
 #include "b2p_scratch.h"
+#ifndef B2P_NBR_BATCH_F32
+#define B2P_NBR_BATCH_F32 4
+#endif
 
 namespace b2p {
 
@@ -12,13 +15,22 @@ struct CObj { const T* pos; const T* mat; const T* size; const T* vert; int type
 // from the hull's extreme vertex along the nearest of 26 tabulated directions (Globals::geom_start) instead of vertex 0:
 // the climb is a chain of dependent global loads, and this cuts it from ~sqrt(nvert) steps to one or two.  On a convex
 // hull the climb ends at the same maximum wherever it starts.
+// neighbours fetched per batch in the hill climb
+template <typename T> struct NbrBatch { static constexpr int value = B2P_NBR_BATCH_F32; };
+template <> struct NbrBatch<double> { static constexpr int value = 8; };
 // slot of a (unit) direction in the 3x3x3 start table: each component quantised to {-1, 0, +1} at +-0.4
 template <typename T> B2P_HD int start_slot(const T* d) {
   return ((d[0] > T(0.4)) - (d[0] < T(-0.4)) + 1) * 9 + ((d[1] > T(0.4)) - (d[1] < T(-0.4)) + 1) * 3 + ((d[2] > T(0.4)) - (d[2] < T(-0.4)) + 1);
 }
+#ifdef B2P_HOST_COUNTERS
+static long g_support_calls = 0, g_climb_steps = 0, g_mpr_calls = 0;
+#endif
 template <typename T>
 B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
   T ld[3], lp[3];
+#ifdef B2P_HOST_COUNTERS
+  g_support_calls++;
+#endif
   mulmtv(ld, o.mat, dir);
   if (o.type == B2P_GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? o.size[k] : -o.size[k];
@@ -26,11 +38,26 @@ B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
     int v = o.cur;
     if (v < 0) v = o.start[start_slot(ld)];
     T best = dot3(g.mesh_vert + 3 * v, ld);
+    // every climb step is two dependent global loads: the vertex's neighbour span, then up to 8 neighbours at once (coordinates
+    // inline, independent of each other) -- not a load -> index -> load chain per neighbour
     for (int guard = 0; guard < 4096; guard++) {
-      int nb = v; const int a = g.nbradr[v], n = g.nbrnum[v];
-      for (int q = 0; q < n; q++) { const int u = g.nbr[a + q]; const T d = dot3(g.mesh_vert + 3 * u, ld); if (d > best) { best = d; nb = u; } }
+      int nb = v; const NbrSpan sp = g.nbr_span[v];
+      constexpr int NB = NbrBatch<T>::value;
+      for (int q0 = 0; q0 < sp.num; q0 += NB) {
+        T dq[NB]; int uq[NB];
+#pragma unroll
+        for (int j = 0; j < NB; j++) {
+          if (q0 + j < sp.num) { const NbrPt<T> pt = g.nbr_pt[sp.adr + q0 + j]; dq[j] = pt.x * ld[0] + pt.y * ld[1] + pt.z * ld[2]; uq[j] = pt.idx; }
+          else { dq[j] = best; uq[j] = v; }
+        }
+#pragma unroll
+        for (int j = 0; j < NB; j++) if (dq[j] > best) { best = dq[j]; nb = uq[j]; }
+      }
       if (nb == v) break;
       v = nb;
+#ifdef B2P_HOST_COUNTERS
+      g_climb_steps++;
+#endif
     }
     o.cur = v; cp3(lp, g.mesh_vert + 3 * v);
   }
@@ -83,6 +110,9 @@ template <typename T> B2P_HD T point_tri_dist2(const T* a, const T* b, const T* 
 template <typename T>
 B2P_HDN bool mpr_penetration(CObj<T>& o1, CObj<T>& o2, const Globals<T>& g, int maxiter, T tol, T& depth, T* dir, T* pos) {
   Sup<T> p[4], v4; T d[3], va[3], vb[3];
+#ifdef B2P_HOST_COUNTERS
+  g_mpr_calls++;
+#endif
   for (int k = 0; k < 3; k++) { p[0].v1[k] = o1.pos[k]; p[0].v2[k] = o2.pos[k]; p[0].v[k] = p[0].v1[k] - p[0].v2[k]; }
   if (is_zero(p[0].v[0]) && is_zero(p[0].v[1]) && is_zero(p[0].v[2])) p[0].v[0] += T(1e-5);
   for (int k = 0; k < 3; k++) d[k] = -p[0].v[k];
@@ -357,19 +387,32 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
       const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1];
       const T* sz2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+#if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
+      const long long nt0_ = clock64(); int nkind_ = 0;
+#endif
       if (t1 == B2P_GEOM_PLANE) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
       else {
         bool convex = true;
+#if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
+        nkind_ = (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) ? 1 : 2;
+#endif
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw); convex = n < 0; if (n < 0) n = 0; }
         if (convex) {
           CObj<T> a = {s.gpos[g1], s.gmat[g1], sz1, nullptr, t1, m.geom_vertadr[g1], m.geom_vertnum[g1], -1, md, g.geom_start + 27 * g1};
           CObj<T> b = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, md, g.geom_start + 27 * g2};
           T depth, dir[3], pos[3];
+#ifdef B2P_SKIP_MPR
+          if (false) {
+#else
           if (mpr_penetration(a, b, g, m.ccd_iterations, tol, depth, dir, pos) && depth >= 0) {
+#endif
             raw.dist[0] = md - depth; cp3(raw.normal, dir); cp3(raw.pos[0], pos); n = 1;
           }
         }
       }
+#if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
+      { const unsigned long long dt_ = (unsigned long long)(clock64() - nt0_); atomicAdd(&g_prof[nkind_ == 1 ? PF_OSC : (nkind_ == 2 ? PF_MISC : PF_SMOOTH)], dt_); atomicAdd(&g_prof[nkind_ == 1 ? PF_INTEGRATE : (nkind_ == 2 ? PF_UPDATE : PF_LS)], 1ULL); }
+#endif
       int keep = 0;   // drop points not strictly inside the detection margin
       for (int i = 0; i < n; i++) if (raw.dist[i] < md) { if (keep != i) { raw.dist[keep] = raw.dist[i]; cp3(raw.pos[keep], raw.pos[i]); } keep++; }
       n = keep;

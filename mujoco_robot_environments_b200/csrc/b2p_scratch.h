@@ -6,11 +6,16 @@ namespace b2p {
 // ------------------------------------------------------------------------------------------ per-env scratch
 // HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
 constexpr int REC_QPOS = 0, REC_QVEL = MAXNQ, REC_QACC = MAXNQ + MAXNV, REC_TIME = MAXNQ + 2 * MAXNV, REC_SIZE = 128;
+// one hull-graph neighbour with its coordinates inline (one 16-byte load in fp32), and (first neighbour, count) per vertex
+template <typename T> struct alignas(16) NbrPt { T x, y, z; int idx; };
+struct NbrSpan { int adr, num; };
 template <typename T>
 struct Globals {                 // read-only global-memory tables
   const T* mesh_vert; const int* nbradr; const int* nbrnum; const int* nbr;
   const short* pair_g1; const short* pair_g2; const PairParam<T>* pair_param;
   const int* geom_start;         // [ngeom][27] hill-climb start vertex per quantised direction (mesh geoms)
+  const NbrPt<T>* nbr_pt;        // [nmeshnbr] neighbour vertex coordinates + index, same order as nbr
+  const NbrSpan* nbr_span;       // [nmeshvert]
 };
 
 // Shared memory per scene is what bounds the number of resident warps (= scenes in flight) per SM, and the kernel is latency

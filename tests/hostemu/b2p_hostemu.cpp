@@ -12,7 +12,7 @@ using namespace b2p;
 template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
-  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span;
   Globals<T> g; Scratch<T>* s;
 };
 
@@ -32,6 +32,10 @@ static Emu<T>* make(const void* blob, size_t n) {
     p.margin = (T)q[10]; p.gap = (T)q[11]; e->pp.push_back(p);
   }
   e->g.mesh_vert = e->mesh_vert.data(); e->g.nbradr = e->ht.mesh_nbradr.data(); e->g.nbrnum = e->ht.mesh_nbrnum.data(); e->g.nbr = e->ht.mesh_nbr.data(); e->g.geom_start = e->ht.geom_start.data();
+  e->nbr_pt.resize(e->ht.mesh_nbr.size()); e->nbr_span.resize(e->ht.mesh_nbradr.size());
+  for (size_t q = 0; q < e->nbr_pt.size(); q++) { const int u = e->ht.mesh_nbr[q]; e->nbr_pt[q].x = (T)e->ht.mesh_vert[3 * u]; e->nbr_pt[q].y = (T)e->ht.mesh_vert[3 * u + 1]; e->nbr_pt[q].z = (T)e->ht.mesh_vert[3 * u + 2]; e->nbr_pt[q].idx = u; }
+  for (size_t v = 0; v < e->nbr_span.size(); v++) { e->nbr_span[v].adr = e->ht.mesh_nbradr[v]; e->nbr_span[v].num = e->ht.mesh_nbrnum[v]; }
+  e->g.nbr_pt = e->nbr_pt.data(); e->g.nbr_span = e->nbr_span.data();
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
   e->s = new Scratch<T>();
   return e;
