@@ -44,7 +44,7 @@ TimeStep = collections.namedtuple("TimeStep", ["step_type", "reward", "discount"
 class BatchedRearrangementEnv:
     def __init__(self, viewer=None, cfg: Optional[Dict[str, Any]] = None, num_envs: int = 1, device=None,
                  dtype: torch.dtype = torch.float32, overrides: Optional[Iterable[str]] = None, seed: Optional[int] = None,
-                 sampler: str = "auto", strict: Optional[bool] = None):
+                 sampler: str = "auto", strict: Optional[bool] = None, camera_obs: Optional[bool] = None):
         if viewer:
             raise RuntimeError("passive viewer: unavailable on this box (no graphics stack)")
         self._cfg = cfg if cfg is not None else cfglib.compose(overrides)
@@ -55,6 +55,9 @@ class BatchedRearrangementEnv:
             raise ValueError("physics_dt=%g differs from the compiled model's timestep %g: recompile the scene blob (tools/compile_scene.py)"
                              % (self._cfg["physics_dt"], p.model.opt.timestep))
         self.strict = (self.num_envs == 1) if strict is None else bool(strict)
+        # the reference's observation IS the camera pair (rearrangement.py:460-478): on by default for the single-scene facade,
+        # opt-in for a batch (2.15 MB per scene and observation)
+        self.camera_obs = (self.num_envs == 1) if camera_obs is None else bool(camera_obs)
         self.device, self.dtype = p.device, p.dtype
         self.max_props = p.model.nprop
         pc = self._cfg["arena"]["props"]
@@ -367,17 +370,25 @@ class BatchedRearrangementEnv:
 
     # ------------------------------------------------------------------ specs / observation
     def _compute_observation(self) -> Dict[str, torch.Tensor]:
-        """State observation (camera images: unavailable on this box).  Views / small gathers of device tensors."""
+        """State observation (views / small gathers of device tensors) and, with ``camera_obs``, the reference's observation keys
+        ``overhead_camera/rgb`` / ``overhead_camera/depth`` (rearrangement.py:460-478) ray-cast on the GPU."""
         p = self._physics
         qa = p.model.prop_qposadr
         prop = torch.stack([p.qpos[:, a:a + 7] for a in qa], 1)
-        return {"qpos": p.qpos, "qvel": p.qvel, "time": p.time, "eef_pos": p.data.site_xpos[:, 1], "prop_pos": prop[..., :3],
-                "prop_quat": prop[..., 3:], "has_prop": self.has_prop}
+        obs = {"qpos": p.qpos, "qvel": p.qvel, "time": p.time, "eef_pos": p.data.site_xpos[:, 1], "prop_pos": prop[..., :3],
+               "prop_quat": prop[..., 3:], "has_prop": self.has_prop}
+        if self.camera_obs:
+            obs.update(self.render())
+        return obs
 
     def observation_spec(self):
         p = self._physics
-        return {"qpos": (self.num_envs, p.model.nq), "qvel": (self.num_envs, p.model.nv), "time": (self.num_envs,), "eef_pos": (self.num_envs, 3),
+        spec = {"qpos": (self.num_envs, p.model.nq), "qvel": (self.num_envs, p.model.nv), "time": (self.num_envs,), "eef_pos": (self.num_envs, 3),
                 "prop_pos": (self.num_envs, self.max_props, 3), "prop_quat": (self.num_envs, self.max_props, 4), "has_prop": (self.num_envs, self.max_props)}
+        if self.camera_obs:       # rearrangement.py:442-451
+            spec["overhead_camera/depth"] = (self.num_envs, self.overhead_camera_height, self.overhead_camera_width)
+            spec["overhead_camera/rgb"] = (self.num_envs, self.overhead_camera_height, self.overhead_camera_width, 3)
+        return spec
 
     def action_spec(self):
         """rearrangement.py:448-458: pose f64[7] (+ pixel_coords i64[2], gripper_rot f64[1] consumed by the data generator)."""
@@ -386,9 +397,28 @@ class BatchedRearrangementEnv:
     @property
     def props_info(self):
         """rearrangement.py:277-295 (poses only; labels are render-side): per scene/prop position + orientation."""
-        o = self._compute_observation()
-        return {"position": o["prop_pos"], "orientation": o["prop_quat"], "has_prop": self.has_prop, "half_size": self.prop_half_size,
+        p = self._physics
+        prop = torch.stack([p.qpos[:, a:a + 7] for a in p.model.prop_qposadr], 1)
+        return {"position": prop[..., :3], "orientation": prop[..., 3:], "has_prop": self.has_prop, "half_size": self.prop_half_size,
                 "rgba": self.prop_rgba, "colour": self.prop_colour}
+
+    def prop_bboxes(self) -> torch.Tensor:
+        """``get_bbox`` of ``props_info`` (rearrangement.py:251-283): PASCAL-VOC box (xmin, ymin, xmax, ymax) of every prop in the
+        segmentation image of the overhead camera -> int64 [n_env, max_props, 4]; (-1, -1, -1, -1) for a prop out of view."""
+        seg = self.render(seg=True)["segmentation"]
+        n, H, W = seg.shape
+        out = torch.full((n, self.max_props, 4), -1, dtype=torch.int64, device=self.device)
+        xs, ys = torch.arange(W, device=self.device), torch.arange(H, device=self.device)
+        for k in range(self.max_props):
+            m = seg == int(self._prop_gid[k])
+            cols, rows = m.any(1), m.any(2)
+            seen = cols.any(1)
+            big = torch.iinfo(torch.int64).max
+            x0 = torch.where(cols, xs, big).min(1).values; x1 = torch.where(cols, xs, -1).max(1).values
+            y0 = torch.where(rows, ys, big).min(1).values; y1 = torch.where(rows, ys, -1).max(1).values
+            box = torch.stack([x0, y0, x1, y1], 1)
+            out[:, k] = torch.where(seen[:, None], box, out[:, k])
+        return out
 
 
 def RearrangementEnv(viewer=None, cfg=None, **kw) -> BatchedRearrangementEnv:

@@ -74,7 +74,8 @@ def test_env_render_and_pixel_2_world():
     from mujoco_robot_environments_b200.env import BatchedRearrangementEnv
     from mujoco_robot_environments_b200.data_generation import COLOUR_SPLITTER_OVERRIDES
     env = BatchedRearrangementEnv(cfg=C.compose(COLOUR_SPLITTER_OVERRIDES), num_envs=8, strict=False)
-    env.reset()
+    ts = env.reset()
+    assert "overhead_camera/rgb" not in ts.observation          # batch default: state observation only
     obs = env.render(seg=True)
     assert obs["overhead_camera/rgb"].shape == (8, 480, 640, 3) and obs["overhead_camera/rgb"].dtype == torch.uint8
     assert obs["overhead_camera/depth"].shape == (8, 480, 640) and obs["overhead_camera/depth"].dtype == torch.float32
@@ -87,5 +88,23 @@ def test_env_render_and_pixel_2_world():
     c = obs["overhead_camera/rgb"][e, px[:, 1].long(), px[:, 0].long()].float()
     base = env.prop_rgba[:, 0, :3]
     assert bool((c.argmax(1) == base.argmax(1)).all() | (base.max(1).values - base.min(1).values < 0.3).all())
+    # bounding boxes from the segmentation image contain the projected prop centre and are about one prop wide
+    bb = env.prop_bboxes()
+    b0 = bb[:, 0]
+    assert bool(((b0[:, 0] <= px[:, 0]) & (px[:, 0] <= b0[:, 2]) & (b0[:, 1] <= px[:, 1]) & (px[:, 1] <= b0[:, 3])).all())
+    assert bool(((b0[:, 2] - b0[:, 0]) < 30).all() & ((b0[:, 2] - b0[:, 0]) >= 12).all())
+    assert bool((bb[~env.has_prop] == -1).all())
     w = env.pixel_2_world("overhead_camera/overhead_camera", px.to(torch.float64))
     assert float((w - top.double()).abs().max()) < 3e-3
+
+
+def test_single_scene_facade_observation_is_the_camera_pair():
+    """RearrangementEnv(viewer=None, cfg=...) keeps the reference's observation keys and specs (rearrangement.py:442-478)."""
+    from mujoco_robot_environments_b200.env import RearrangementEnv
+    env = RearrangementEnv(dtype=torch.float64)
+    ts = env.reset()
+    o = ts.observation
+    assert o["overhead_camera/rgb"].shape == (1, 480, 640, 3) and o["overhead_camera/depth"].shape == (1, 480, 640)
+    spec = env.observation_spec()
+    assert spec["overhead_camera/rgb"] == (1, 480, 640, 3) and spec["overhead_camera/depth"] == (1, 480, 640)
+    assert float(o["overhead_camera/depth"].max()) <= 0.9 + 1e-6
