@@ -93,6 +93,7 @@ static int run_mode(b2p_handle h, int mode, int n_steps, int control_steps, int 
                     const uint8_t* mask, uint8_t* conv, int32_t* steps_done, double vt, double at, int min_steps, void* stream) {
   StepArgs<T> a; std::memset(&a, 0, sizeof a);
   { const char* ls = getenv("B2P_LOCKSTEP"); a.lockstep = ls ? atoi(ls) : LK_DEFAULT; }
+  { const char* lg = getenv("B2P_LOCKGROUP"); a.lock_group = lg ? atoi(lg) : 0; }
   a.mode = mode; a.n_steps = n_steps; a.control_steps = control_steps; a.full_contacts = full;
   a.ctrl = (const T*)(ctrl ? ctrl : h->d_zero_ctrl); a.target = (const T*)target; a.grip = grip; a.env_mask = mask; a.converged = conv; a.steps_done = steps_done;
   a.settle_qvel_tol = (T)vt; a.settle_qacc_tol = (T)at; a.settle_min_steps = min_steps;

@@ -60,7 +60,12 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
   static_assert(offsetof(Scratch<T>, qpos) == 0 && sizeof(Scratch<T>) % 16 == 0, "state record must head a 16-byte aligned Scratch");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const Ctx c = {lane, 32, a.lockstep};
+  // lockstep groups: the CTA's warps walk the stage barriers in groups of a.lock_group warps (named barriers 1..), so that a
+  // warp waits for the slowest solve of its group only; the whole CTA meets once per scene at the queue
+  const int lg = (a.lock_group > 0 && a.lock_group < KernelCfg<T>::kWarps) ? a.lock_group : 0;
+  int grp_n = 0, grp_id = 0;
+  if (lg) { grp_id = warp / lg; const int w0 = grp_id * lg, w1 = (w0 + lg < KernelCfg<T>::kWarps) ? w0 + lg : KernelCfg<T>::kWarps; grp_n = 32 * (w1 - w0); grp_id += 1; }
+  const Ctx c = {lane, 32, a.lockstep, grp_id, grp_n};
   if (threadIdx.x == 0) {
     for (int i = 0; i <= KernelCfg<T>::kWarps; i++) mbar_init(&sm.bar[i], 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");

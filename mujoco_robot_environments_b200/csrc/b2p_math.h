@@ -16,7 +16,7 @@ enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3 };
 
-struct Ctx { int tid, nt; int lock; };   // lock: bit mask of the CTA-wide stage barriers in use (LK_*), 0 = warps run free
+struct Ctx { int tid, nt; int lock; int bar_id, bar_n; };   // bar_n > 0: the lockstep group is bar_n threads on named barrier bar_id (a sub-group of the CTA's warps)   // lock: bit mask of the CTA-wide stage barriers in use (LK_*), 0 = warps run free
 
 // Optional per-stage cycle counters (build with -DB2P_PROF; read back through b2p_prof_read).  Off in the product build.
 enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_TOTAL, PF_N };
@@ -53,7 +53,7 @@ B2P_HD void bsync(const Ctx&) {
 enum { LK_FK = 1, LK_COLLIDE = 2, LK_ROWS = 4, LK_STEP2 = 8, LK_INTEGRATE = 16, LK_TICK = 32, LK_NEWTON = 64, LK_NARROW = 128, LK_SOLVE = 256, LK_ALL = 511, LK_DEFAULT = 63 + 128 + 256 };
 B2P_HD void csync(const Ctx& c, int site) {
 #ifdef __CUDA_ARCH__
-  if (c.lock & site) __syncthreads();
+  if (c.lock & site) { if (c.bar_n) asm volatile("bar.sync %0, %1;" ::"r"(c.bar_id), "r"(c.bar_n) : "memory"); else __syncthreads(); }
 #else
   (void)c; (void)site;
 #endif
@@ -61,14 +61,22 @@ B2P_HD void csync(const Ctx& c, int site) {
 // CTA-wide OR of a per-warp predicate at barrier `site`; the warp's own predicate when that barrier is not in use
 B2P_HD bool csync_or(const Ctx& c, int site, bool p) {
 #ifdef __CUDA_ARCH__
-  return (c.lock & site) ? (__syncthreads_or(p) != 0) : p;
+  if (!(c.lock & site)) return p;
+  if (!c.bar_n) return __syncthreads_or(p) != 0;
+  unsigned r;
+  asm volatile("{ .reg .pred p, q; setp.ne.u32 q, %3, 0; bar.red.or.pred p, %1, %2, q; selp.u32 %0, 1, 0, p; }" : "=r"(r) : "r"(c.bar_id), "r"(c.bar_n), "r"((unsigned)p) : "memory");
+  return r != 0;
 #else
   (void)c; (void)site; return p;
 #endif
 }
 B2P_HD bool csync_and(const Ctx& c, bool p) {
 #ifdef __CUDA_ARCH__
-  return c.lock ? (__syncthreads_and(p) != 0) : p;
+  if (!c.lock) return p;
+  if (!c.bar_n) return __syncthreads_and(p) != 0;
+  unsigned r;
+  asm volatile("{ .reg .pred p, q; setp.ne.u32 q, %3, 0; bar.red.and.pred p, %1, %2, q; selp.u32 %0, 1, 0, p; }" : "=r"(r) : "r"(c.bar_id), "r"(c.bar_n), "r"((unsigned)p) : "memory");
+  return r != 0;
 #else
   (void)c; return p;
 #endif
