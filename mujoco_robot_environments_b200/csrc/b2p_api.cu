@@ -139,7 +139,7 @@ int b2p_query(b2p_handle h, int what) {
 int b2p_out_offset(int field, int* offset, int* count) {
   typedef OutLayout L;
   static const int off[B2P_O_NFIELD] = {L::SITE_XPOS, L::SITE_XMAT, L::QACC, L::QFRC_BIAS, L::CTRL, L::NCON, L::NEFC, L::NITER, L::CONTACT, L::MARM, L::GPOS, L::GMAT, L::QACC_SMOOTH, L::EFC_FORCE};
-  static const int cnt[B2P_O_NFIELD] = {6, 18, MAXNV, MAXNV, MAXU, 1, 1, 1, MAXCON * L::CONTACT_W, MAXTD * MAXTD, MAXG * 3, MAXG * 9, MAXNV, MAXEFC};
+  static const int cnt[B2P_O_NFIELD] = {6, 18, MAXNV, MAXNV, MAXU, 1, 1, 1, MAXCON * L::CONTACT_W, MAXTD * MAXTD, MAXG * 3, MAXG * 9, MAXNV, MAXEFC_OUT};
   if (field < 0 || field >= B2P_O_NFIELD) return fail(B2P_ERR_ARG, "b2p_out_offset: unknown field");
   if (offset) *offset = off[field];
   if (count) *count = cnt[field];

@@ -103,7 +103,7 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
     for (int i = c.tid; i < MAXNV; i += c.nt) { o[L::QACC + i] = i < m.nv ? s.qacc[i] : T(0); o[L::QACC_SMOOTH + i] = i < m.nv ? s.qacc_smooth[i] : T(0); }
     for (int i = c.tid; i < MAXU; i += c.nt) o[L::CTRL + i] = s.ctrl[i];
     if (c.tid == 0) o[L::NITER] = T(s.niter);
-    for (int i = c.tid; i < MAXEFC; i += c.nt) o[L::EFC_FORCE + i] = i < s.nefc ? s.force[i] : T(0);
+    for (int i = c.tid; i < MAXEFC_OUT; i += c.nt) o[L::EFC_FORCE + i] = i < s.nefc ? s.force[i] : T(0);
   }
 }
 

@@ -20,7 +20,10 @@ namespace b2p {
 
 
 
-template <typename T> struct KernelCfg { static constexpr int kWarps = 9; static constexpr int kMinBlocks = 1; };
+#ifndef B2P_WARPS_F32
+#define B2P_WARPS_F32 9
+#endif
+template <typename T> struct KernelCfg { static constexpr int kWarps = B2P_WARPS_F32; static constexpr int kMinBlocks = 1; };
 template <> struct KernelCfg<double> { static constexpr int kWarps = 4; static constexpr int kMinBlocks = 1; };
 
 // ------------------------------------------------------------------------------------------ TMA / mbarrier helpers

@@ -24,13 +24,23 @@ constexpr int MAXNV = MAXTD + 6 * MAXP;   // 40
 constexpr int MAXNQ = MAXTD + 7 * MAXP;   // 44
 constexpr int MAXG = 32;         // collidable geoms
 constexpr int MAXCON = 48;       // contacts kept per env
-constexpr int MAXEFC = 128;      // constraint rows per env
 constexpr int MAXCAND = 160;     // narrow-phase candidates per env
 constexpr int MAXEQ = 4;
 constexpr int MAXU = 8;
 constexpr int MAXLEVEL = 12;
 constexpr int PROP_BODY0 = MAXTB;
-constexpr int JPOOL = 2304;      // reals of packed constraint Jacobian per env
+// Constraint pools per scene, per dtype: rows (equality + limits + 3 per contact) and reals of packed Jacobian.  Shared memory per
+// scene bounds the warps per SM: fp32 runs 9 scenes per SM with these sizes; fp64 runs 4 and has room for pools that hold
+// MAXCON contacts x 3 rows + every equality / limit row, so the parity mode never drops a contact for lack of rows.
+#ifndef B2P_EFC_F32
+#define B2P_EFC_F32 128
+#endif
+#ifndef B2P_JPOOL_F32
+#define B2P_JPOOL_F32 2304
+#endif
+template <typename T> struct Pool { static constexpr int EFC = B2P_EFC_F32, JP = B2P_JPOOL_F32; };
+template <> struct Pool<double> { static constexpr int EFC = 160, JP = 2944; };
+constexpr int MAXEFC_OUT = 160;  // efc_force slots in the derived-output record (both dtypes)
 constexpr int SP_MAXBLK = 1 + MAXP;                  // solver blocks: props, then the tree
 constexpr int HPACK = (MAXNV * (MAXNV + 1)) / 2;     // packed lower triangle of the Newton Hessian
 constexpr int MPACK = (MAXTD * (MAXTD + 1)) / 2;     // packed lower triangle of the tree mass matrix

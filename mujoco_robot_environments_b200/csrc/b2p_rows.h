@@ -65,7 +65,7 @@ template <typename T> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s
 template <typename T>
 B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
   const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
-  int base = 0, jbase = 0, first_drop = MAXEFC + 1; unsigned pairs = 0;
+  int base = 0, jbase = 0, first_drop = Pool<T>::EFC + 1; unsigned pairs = 0;
   int nb[SP_MAXBLK];
   for (int b = 0; b < SP_MAXBLK; b++) nb[b] = 0;
   for (int i0 = 0; i0 < nitem; i0 += c.nt) {
@@ -92,7 +92,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
     const int w = nr > 0 ? block_width(m, ba) + (bb >= 0 ? 6 : 0) : 0;
     int tot, jtot; const int ofs = block_scan(c, nr, tot), jofs = block_scan(c, nr * w, jtot);
     const int r0 = base + ofs, j0 = jbase + jofs;
-    if (nr > 0 && (r0 + nr > MAXEFC || j0 + nr * w > JPOOL)) {   // dropped items always form a suffix (offsets include dropped ones)
+    if (nr > 0 && (r0 + nr > Pool<T>::EFC || j0 + nr * w > Pool<T>::JP)) {   // dropped items always form a suffix (offsets include dropped ones)
       if (r0 < first_drop) first_drop = r0;
       if (kind == ROW_CONTACT) s.c_row[id] = -1;
       s.flags |= FLAG_EFCFULL; nr = 0;

@@ -42,11 +42,11 @@ struct alignas(16) Scratch {
   short c_pair[MAXCON], c_row[MAXCON];
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
   // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
-  T Jp[JPOOL], D[MAXEFC], aref[MAXEFC], force[MAXEFC];
-  signed char row_a[MAXEFC], row_b[MAXEFC], row_type[MAXEFC], row_state[MAXEFC];
-  short row_id[MAXEFC], joff[MAXEFC];
+  T Jp[Pool<T>::JP], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
+  signed char row_a[Pool<T>::EFC], row_b[Pool<T>::EFC], row_type[Pool<T>::EFC], row_state[Pool<T>::EFC];
+  short row_id[Pool<T>::EFC], joff[Pool<T>::EFC];
   // per-block row lists (block 0 = tree, 1+p = prop p): first row of every item (eq/limit row, or contact triple)
-  unsigned char brow0[MAXEFC], browp[MAXP][MAXCON]; int nbrow[SP_MAXBLK];
+  unsigned char brow0[Pool<T>::EFC], browp[MAXP][MAXCON]; int nbrow[SP_MAXBLK];
   SpStruct sp;                   // block structure of the Newton Hessian in solver order (props first, tree last)
   // settle / frozen-arm support
   T hold_q[MAXTD], hold_v[MAXTD];
@@ -59,7 +59,7 @@ struct alignas(16) Scratch {
   };
   union {                        // ---- part 2
     struct {                     // dyn: solver vectors, per-row residuals, per-contact cone Hessian (xx,yy,zz,xy,xz,yz)
-      T grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV], Jaref[MAXEFC], Jv[MAXEFC], cW[MAXCON][6];
+      T grad[MAXNV], Mgrad[MAXNV], search[MAXNV], Ma[MAXNV], Mv[MAXNV], tmpv[MAXNV], Jaref[Pool<T>::EFC], Jv[Pool<T>::EFC], cW[MAXCON][6];
     };
     struct {                     // pos: geom poses, contact frames
       T gpos[MAXG][3], gmat[MAXG][9], c_frame[MAXCON][9];
@@ -107,7 +107,7 @@ struct StepArgs {
 struct OutLayout {
   static constexpr int SITE_XPOS = 0, SITE_XMAT = 6, QACC = 24, QFRC_BIAS = QACC + MAXNV, CTRL = QFRC_BIAS + MAXNV, NCON = CTRL + MAXU, NEFC = NCON + 1,
                        NITER = NEFC + 1, CONTACT = NITER + 1, CONTACT_W = 10, MARM = CONTACT + MAXCON * CONTACT_W, GPOS = MARM + MAXTD * MAXTD,
-                       GMAT = GPOS + MAXG * 3, QACC_SMOOTH = GMAT + MAXG * 9, EFC_FORCE = QACC_SMOOTH + MAXNV, SIZE = EFC_FORCE + MAXEFC;
+                       GMAT = GPOS + MAXG * 3, QACC_SMOOTH = GMAT + MAXG * 9, EFC_FORCE = QACC_SMOOTH + MAXNV, SIZE = EFC_FORCE + MAXEFC_OUT;
 };
 
 }  // namespace b2p

@@ -65,7 +65,7 @@ def rollout_episode(env, max_steps: int, render: bool = False, resample_props: b
     in_progress = env.has_prop & ~env.expert.within_target()
     out = {"actions": actions, "valid": valid, "prop_pos0": obs0["prop_pos"].clone(), "prop_quat0": obs0["prop_quat"].clone(),
            "prop_colour": env.prop_colour, "has_prop": env.has_prop, "success": ~in_progress.any(1) & alive, "failed": env.failed.clone(),
-           "rounds": valid.sum(1)}
+           "rounds": valid.sum(1), "status": env.physics.status().clone()}     # status: OR of the kernel's per-scene flags over the episode
     if render and frames["rgb"]:
         T = len(frames["rgb"]) // 2
         out["rgb"] = torch.stack(frames["rgb"], 1).view(n, T, 2, *frames["rgb"][0].shape[1:])
@@ -93,14 +93,16 @@ def generate(num_envs: int = 1024, episodes_per_env: int = 1, cfg: Optional[dict
     wall = time.perf_counter() - t0
     local = {k: torch.cat([d[k] for d in demos], 0) for k in demos[0] if all(k in d for d in demos)}
     stats = torch.tensor([float(local["success"].numel()), float(local["success"].sum()), float(local["rounds"].sum()), float(local["failed"].sum()),
-                          float(env.physics.time.sum().item() / env.physics.model.opt.timestep), float(env.physics.launches - launches0)],
+                          float(env.physics.time.sum().item() / env.physics.model.opt.timestep), float(env.physics.launches - launches0)]
+                         + [float(((local["status"] & (1 << b)) != 0).sum()) for b in range(len(env.physics.STATUS_FLAGS))],
                          dtype=torch.float64, device=env.device)
     wall_t = distlib.max_over_ranks(torch.tensor([wall], dtype=torch.float64, device=env.device))
     distlib.reduce_stats(stats)
     gathered = {k: distlib.gather_demos(v.to(torch.uint8) if v.dtype == torch.bool else v) for k, v in local.items()}
     s = stats.tolist()
     stat = {"episodes": s[0], "successes": s[1], "pick_place_rounds": s[2], "failed": s[3], "physics_env_steps_last_episode": s[4], "kernel_launches": s[5],
-            "wall_s": wall_t.item(), "world_size": world, "envs_per_gpu": num_envs}
+            "wall_s": wall_t.item(), "world_size": world, "envs_per_gpu": num_envs,
+            "flagged_episodes": {k: s[6 + i] for i, k in enumerate(env.physics.STATUS_FLAGS)}}
     env.close()
     return (gathered if rank == 0 else None), stat
 

@@ -180,6 +180,9 @@ class BatchedPhysics:
         if prop_active is not None:
             self.prop_active.copy_(prop_active.to(self.prop_active))
 
+    # bit k of status(): the first three are mj_checkPos / Vel / Acc, the rest capacity / iteration-cap notes (csrc/b2p_math.h)
+    STATUS_FLAGS = ("badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter")
+
     def status(self, clear: bool = False) -> torch.Tensor:
         """Per-env OR of bad-state flags (dm_control check_invalid_state equivalent)."""
         ffi.check(self._L.b2p_status(self._h, self._status.data_ptr(), int(clear), self._stream()))

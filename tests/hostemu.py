@@ -37,7 +37,7 @@ def lib():
 
 def out_slices():
     """Field -> slice of the derived-output record (csrc/b2p_core.h OutLayout)."""
-    MAXNV, MAXU, MAXCON, MAXTD, MAXG, MAXEFC = 40, 8, 48, 16, 32, 128
+    MAXNV, MAXU, MAXCON, MAXTD, MAXG, MAXEFC = 40, 8, 48, 16, 32, 160
     o, d = 0, {}
     for name, n in (("site_xpos", 6), ("site_xmat", 18), ("qacc", MAXNV), ("qfrc_bias", MAXNV), ("ctrl", MAXU), ("ncon", 1), ("nefc", 1),
                     ("niter", 1), ("contact", MAXCON * 10), ("Marm", MAXTD * MAXTD), ("gpos", MAXG * 3), ("gmat", MAXG * 9),
