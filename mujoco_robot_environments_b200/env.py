@@ -23,7 +23,7 @@ import torch
 
 from . import config as cfglib
 from .controllers import BatchedMinMax, BatchedOSC
-from .expert import Camera, SortColoursExpert, sample_prop_colours
+from .expert import Camera, SortColoursExpert, euler_xyz_matrix, mat2quat, sample_prop_colours
 from .physics import BatchedPhysics
 from .robot_arm import BatchedRobotArm
 
@@ -320,6 +320,24 @@ class BatchedRearrangementEnv:
         """rearrangement.py:403-440."""
         self._pick_or_place(pose, "min", ("move arm to pre place position", "move arm to place position", "open gripper",
                                           "move arm to pre place position", "move arm to home position"), active)
+
+    def random_pick_and_place(self):
+        """rearrangement.py:667-698, per scene: pick pose = position of the scene's first prop + grasp quat
+        mju_mat2Quat(R_xyz(0, 180, yaw) in degrees), place pose = U(workspace) + the same quat -> (pick [n, 7], place [n, 7]).
+        The reference hands the wxyz body quaternion to scipy's ``R.from_quat`` (which reads xyzw) before taking
+        yaw = atan2(R10, R00); the same reading is kept here, so a prop that is only yawed gets yaw = 0."""
+        p = self._physics
+        first = self.has_prop.to(torch.int64).argmax(1)
+        e = torch.arange(self.num_envs, device=self.device)
+        prop = torch.stack([p.qpos[:, a:a + 7] for a in p.model.prop_qposadr], 1)[e, first]
+        x, y, z, w = prop[:, 3], prop[:, 4], prop[:, 5], prop[:, 6]
+        yaw = torch.atan2(2 * (x * y + z * w), 1 - 2 * (y * y + z * z))
+        zero = torch.zeros_like(yaw)
+        quat = mat2quat(euler_xyz_matrix(zero, zero + math.pi, yaw)).to(self.dtype)
+        ws = self._cfg["task"]["initializers"]["workspace"]
+        lo, hi = (torch.tensor(ws[k], device=self.device, dtype=self.dtype) for k in ("min_pose", "max_pose"))
+        place = lo + (hi - lo) * torch.rand(self.num_envs, 3, device=self.device, dtype=self.dtype, generator=self._dgen)
+        return torch.cat([prop[:, :3].clone(), quat], 1), torch.cat([place, quat], 1)
 
     # ------------------------------------------------------------------ scripted expert + camera (SURVEY 8f-1)
     @property

@@ -87,6 +87,7 @@ class BatchedTuner:
         self.strategy = CMAES(6, self.popsize, sigma_init, mean_init, seed)
         self.gen = torch.Generator(device=p.device); self.gen.manual_seed(seed + 1)
         self.best_params = np.abs(self.strategy.best_member)
+        self._env, self._seed = None, seed
         # point-to-point motion needs no props: all parked with collisions off (the reference's single block plays no part in p2p_fitness)
         self._home = torch.zeros_like(p.state[0])
         self._home[:p.model.nq] = p.model.qpos0.to(p.device)
@@ -123,11 +124,56 @@ class BatchedTuner:
         f = torch.where(bad | ~torch.isfinite(f), torch.full_like(f, 2e6), f)
         return f.view(self.popsize, self.tpc).mean(1).double().cpu().numpy()
 
-    def run(self, generations: int = 50, duration: float = 4.0) -> List[Dict[str, float]]:
+    def circle_fitness(self, params: np.ndarray, radius: float = 0.1, speed: float = 0.1) -> np.ndarray:
+        """:73-111: fixed orientation R_xyz(0, 180, 0), the first 20 of 100 way-points of a circle of ``radius`` around
+        (0.25, 0, 0.9); ``run_controller(5.0)`` to the first, ``run_controller(1.0)`` to each; fitness = 0, or 1e6 for a candidate
+        that missed a way-point (the reference raises there).  ``speed`` is unused, as in the reference."""
+        p = self.physics
+        p.state[:] = self._home
+        self.osc.set_gains_per_scene(torch.tensor(params, device=p.device, dtype=p.dtype).repeat_interleave(self.tpc, dim=0))
+        z = torch.zeros(1, device=p.device, dtype=torch.float64)
+        quat = mat2quat(euler_xyz_matrix(z, z + math.pi, z)).to(p.dtype).expand(p.n_env, 4)
+        zeros = torch.zeros(3, device=p.device, dtype=p.dtype)
+        ang = torch.arange(20, device=p.device, dtype=torch.float64) * (2 * math.pi / 100)
+        way = torch.stack([radius * torch.cos(ang) + 0.25, radius * torch.sin(ang), torch.full_like(ang, 0.9)], 1).to(p.dtype)
+        goto = lambda w, dur: (self.osc.set_target(position=w.expand(p.n_env, 3), velocity=zeros, quat=quat, angular_velocity=zeros),
+                               self.robot.run_controller(dur))[1]
+        goto(way[0], 5.0)
+        ok = torch.ones(p.n_env, dtype=torch.bool, device=p.device)
+        for w in way:
+            ok &= goto(w, 1.0)
+        ok &= (p.status(clear=True) & 7) == 0
+        return ((~ok).double() * 1e6).view(self.popsize, self.tpc).mean(1).cpu().numpy()
+
+    def pick_place_fitness(self, params: np.ndarray) -> np.ndarray:
+        """Second tuning stage (:113-129,161-171): ``random_pick_and_place`` on a single-block scene, pick then place through the
+        env's phase tables, fitness = 1000 x distance of the block to the place target (whose z the place phase table has set to
+        0.575, as in the reference), 1e6 for a scene in which a phase did not converge.  One (candidate, place target) per scene."""
+        env = self._pick_place_env()
+        env.reset()
+        env._osc.set_gains_per_scene(torch.tensor(params, device=env.device, dtype=env.dtype).repeat_interleave(self.tpc, dim=0))
+        pick, place = env.random_pick_and_place()
+        env.pick(pick); env.place(place)
+        pos = env.props_info["position"][torch.arange(env.num_envs, device=env.device), env.has_prop.to(torch.int64).argmax(1)]
+        f = 1000.0 * (place[:, :3] - pos).norm(dim=1)
+        bad = env.failed | ((env.physics.status(clear=True) & 7) != 0) | ~torch.isfinite(f)
+        f = torch.where(bad, torch.full_like(f, 1e6), f)
+        return f.view(self.popsize, self.tpc).mean(1).double().cpu().numpy()
+
+    def _pick_place_env(self):
+        if self._env is None:
+            from .env import BatchedRearrangementEnv
+            self._env = BatchedRearrangementEnv(cfg=self.cfg, num_envs=self.popsize * self.tpc, device=self.physics.device, dtype=self.physics.dtype,
+                                                seed=self._seed, strict=False, camera_obs=False)
+        return self._env
+
+    def run(self, generations: int = 50, duration: float = 4.0, method: str = "p2p") -> List[Dict[str, float]]:
+        """One CMA-ES stage (:183-192).  The reference runs ``p2p`` and then ``pick_place`` with the same strategy state."""
+        evaluate = {"p2p": lambda x: self.p2p_fitness(x, duration), "circle": self.circle_fitness, "pick_place": self.pick_place_fitness}[method]
         hist = []
         for g in range(generations):
             x = self.strategy.ask()
-            fit = self.p2p_fitness(np.abs(x), duration)                                       # "only consider positive params" (:187)
+            fit = evaluate(np.abs(x))                                                         # "only consider positive params" (:187)
             self.strategy.tell(x, fit)
             self.best_params = np.abs(self.strategy.best_member)
             hist.append({"generation": g, "best_fitness": self.strategy.best_fitness, "mean_fitness": float(fit.mean()), "sigma": self.strategy.sigma})

@@ -205,6 +205,29 @@ def test_batched_tuner_improves_p2p_fitness():
     assert t.physics.launches >= 3
 
 
+def test_tuner_circle_and_pick_place_stages():
+    """The tuner's other two objectives (rearrangement_controller_tuning.py:73-129,161-171): circle tracking with the config's
+    gains converges (fitness 0) and fails (1e6) with gains that cannot hold the arm; the pick-and-place stage returns
+    1000 x block-to-target distance per candidate, and CMA-ES runs on it."""
+    from mujoco_robot_environments_b200.tuning import BatchedTuner
+    t = BatchedTuner(popsize=4, targets_per_candidate=8, dtype=torch.float32, seed=0)
+    g = t.cfg["robots"]["arm"]["controller_config"]["controller_params"]["gains"]
+    good = [g["position"]["kp"], g["position"]["kd"], g["orientation"]["kp"], g["orientation"]["kd"], g["nullspace"]["kp"], g["nullspace"]["kd"]]
+    params = np.array([good, good, [1e-3] * 6, good], dtype=np.float64)
+    f = t.circle_fitness(params)
+    assert f.shape == (4,) and f[0] == 0.0 and f[1] == 0.0 and f[3] == 0.0 and f[2] == 1e6
+    f = t.pick_place_fitness(params)
+    assert f.shape == (4,) and np.isfinite(f).all()
+    assert f[0] < 1e3 and f[2] > f[0]             # the block ends within a metre-scale of the target; dead gains are worse
+    env = t._pick_place_env()
+    assert env.num_envs == 32 and int(env.n_props.max()) == 1
+    pick, place = env.random_pick_and_place()
+    assert pick.shape == (32, 7) and place.shape == (32, 7)
+    assert bool((pick[:, 3:] - place[:, 3:]).abs().max() == 0)
+    hist = t.run(generations=2, method="pick_place")
+    assert len(hist) == 2 and np.isfinite(hist[-1]["best_fitness"])
+
+
 def test_device_sampler_reset_and_scene_resampling():
     """proposals drawn on the device (no host round trip per rejection round); every placed prop respects the
     reference's rule (no listed contact with another prop), and ``reset(resample_props=True)`` re-draws count / size / colour."""
