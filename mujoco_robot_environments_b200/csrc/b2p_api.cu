@@ -28,6 +28,30 @@ __global__ void fma_peak_kernel(T* out, int iters) {
   out[blockIdx.x * blockDim.x + threadIdx.x] = a0 + a1 + a2 + a3 + a4 + a5 + a6 + a7;
 }
 
+// ------------------------------------------------------------------------------------------ scene queue order
+// The CTA's warps walk the stages of a step in lockstep, so a round costs what its slowest scene costs, and the launch ends
+// when the last round does.  Scenes are therefore handed out heaviest first, neighbours in the queue having done similar work
+// in the previous launch (work proxy written by the kernel): a counting sort over 256 buckets, one block.  The order within a
+// bucket is arbitrary; results do not depend on which warp steps a scene.
+__global__ void __launch_bounds__(1024) b2p_order_kernel(const int* __restrict__ work, int n, int* __restrict__ order) {
+  __shared__ int hist[256]; __shared__ float total;
+  for (int i = threadIdx.x; i < 256; i += blockDim.x) hist[i] = 0;
+  if (threadIdx.x == 0) total = 0.f;
+  __syncthreads();
+  float part = 0.f;
+  for (int e = threadIdx.x; e < n; e += blockDim.x) part += (float)max(work[e], 0);
+  for (int o = 16; o; o >>= 1) part += __shfl_xor_sync(0xffffffffu, part, o);
+  if ((threadIdx.x & 31) == 0) atomicAdd(&total, part);
+  __syncthreads();
+  const float scale = 96.f * (float)n / fmaxf(total, 1.f);      // bucket width = mean work / 96; everything above 2.6 x the mean shares the top bucket
+  auto bucket = [&](int e) { return min(255, (int)((float)max(work[e], 0) * scale)); };
+  for (int e = threadIdx.x; e < n; e += blockDim.x) atomicAdd(&hist[bucket(e)], 1);
+  __syncthreads();
+  if (threadIdx.x == 0) { int acc = 0; for (int b = 255; b >= 0; b--) { const int k = hist[b]; hist[b] = acc; acc += k; } }
+  __syncthreads();
+  for (int e = threadIdx.x; e < n; e += blockDim.x) order[atomicAdd(&hist[bucket(e)], 1)] = e;
+}
+
 // ------------------------------------------------------------------------------------------ handle
 struct b2p_handle_s {
   int dtype, device, n_env, full_contacts, nq, nv, nu, nprop, ngeom;
@@ -38,6 +62,7 @@ struct b2p_handle_s {
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env;
   const void* env_gains;
+  int *d_work, *d_order; int work_steps, sort_queue;   // work_steps: physics steps behind d_work (0 = none yet)
 };
 
 template <typename T>
@@ -73,6 +98,9 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   h->out = h->own_out;
   CK(cudaMalloc(&h->d_next_env, sizeof(int)));
   CK(sizeof(T) == 8 ? configure_f64(h->device, h->n_env, &h->lg) : configure_f32(h->device, h->n_env, &h->lg));
+  CK(cudaMalloc(&h->d_work, (size_t)h->n_env * 4)); CK(cudaMemset(h->d_work, 0, (size_t)h->n_env * 4));
+  CK(cudaMalloc(&h->d_order, (size_t)h->n_env * 4));
+  { const char* sq = getenv("B2P_SORT_QUEUE"); h->sort_queue = sq ? atoi(sq) : (h->n_env > h->lg.grid * h->lg.warps_per_cta); }   // pays off once there is more than one round
   return B2P_OK;
 }
 
@@ -82,6 +110,13 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.gains = (const T*)h->env_gains;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span};
+  a.work = h->d_work; a.order = nullptr;
+  if (h->sort_queue && h->work_steps > 0) {
+    b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
+    CK(cudaGetLastError());
+    a.order = h->d_order;
+  }
+  if ((a.mode == MODE_PHYSICS || a.mode == MODE_OSC) && a.n_steps > 0) h->work_steps = a.mode == MODE_OSC ? a.n_steps * a.control_steps : a.n_steps;
   if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, h->d_next_env, st));
   else CK(launch_f32(h->lg, h->d_model, g, a, h->d_next_env, st));
   h->launches++;
@@ -120,7 +155,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;

@@ -130,12 +130,13 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     prop_params(m, s, c);
   }
   const bool full = a.full_contacts != 0;
+  int work = 0;   // scheduling hint for the next launch (see StepArgs::work)
   if (a.mode == MODE_FORWARD) {
     step1(m, g, s, c, full, active);
     if (active && a.out) { bsync(c); write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, OUT_POS); bsync(c); }
     step2(m, s, c, false, false, active);
   } else if (a.mode == MODE_PHYSICS) {
-    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2(m, s, c, true, false, active); }
+    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); }
     step1(m, g, s, c, full, active);   // leave derived quantities consistent with the final state (dm_control legacy step order)
   } else if (a.mode == MODE_OSC) {
     // RobotArm.run_controller (robot_arm.py:61-94): per tick OSC torque + gripper command, control_steps x physics.step()
@@ -158,7 +159,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
         osc_torque(m, s, tg, grip, c, gn);
       }
       PROF_ADD(PF_OSC)
-      for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); step1(m, g, s, c, full, active); }
+      for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); step1(m, g, s, c, full, active); }
       if (active && osc_converged(m, s, tg)) conv = true;
     }
     if (active && c.tid == 0 && a.converged) a.converged[env] = conv ? 1 : 0;
@@ -184,6 +185,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
   bsync(c);
   if (!state_preloaded) { const T* head = s.qpos; for (int i = c.tid; i < REC_SIZE; i += c.nt) rec[i] = head[i]; }
   if (c.tid == 0 && a.status) a.status[env] |= s.flags;
+  if (c.tid == 0 && a.work && (a.mode == MODE_PHYSICS || a.mode == MODE_OSC) && a.n_steps > 0) a.work[env] = work;
   if (a.out) write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, a.mode == MODE_FORWARD ? OUT_DYN : (OUT_POS | OUT_DYN));
 }
 

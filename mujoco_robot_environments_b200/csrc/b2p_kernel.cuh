@@ -81,7 +81,9 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   unsigned phase = 0;
   for (;;) {   // one round = one scene per warp; in lockstep mode the CTA's warps walk the round's stages together
     int env = 0;
-    if (lane == 0) { do { env = atomicAdd(next_env, 1); } while (env < a.n_env && a.env_mask && !a.env_mask[env]); }
+    if (lane == 0) {
+      do { env = atomicAdd(next_env, 1); if (a.order && env < a.n_env) env = a.order[env]; } while (env < a.n_env && a.env_mask && !a.env_mask[env]);
+    }
     env = __shfl_sync(0xffffffffu, env, 0);
     const bool active = env < a.n_env;
     if (c.lock ? !__syncthreads_or(active) : !active) break;

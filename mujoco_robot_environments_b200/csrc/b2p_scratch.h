@@ -100,6 +100,8 @@ struct StepArgs {
   T settle_qvel_tol, settle_qacc_tol; int settle_min_steps;
   T* out;                    // MODE_FORWARD / any: optional derived-output record per env (see OutLayout)
   int out_stride;
+  const int* order;          // optional [n_env]: queue position -> scene (scenes ordered by the work they did in the previous launch)
+  int* work;                 // optional [n_env] out: work proxy of this launch, sum over steps of nefc * (2 + Newton iterations)
   const T* gains;            // MODE_OSC: optional [n_env][6] per-scene OSC gains (pos kp kd, ori kp kd, null kp kd); NULL = the model's
 };
 // derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |
