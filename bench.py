@@ -274,7 +274,7 @@ def run_ours(args, wl):
         one_step(i)
     barrier()
     sampler = ClockSampler(local); sampler.start()
-    launches0 = p.launches
+    launches0, order0 = p.launches, p.order_launches
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(args.steps)]
     barrier()
     wall0 = time.perf_counter()
@@ -285,6 +285,7 @@ def run_ours(args, wl):
     wall = time.perf_counter() - wall0
     kern_ms = [a.elapsed_time(b) for a, b in ev]
     launches = p.launches - launches0
+    order_launches = p.order_launches - order0
     total_ms = torch.tensor([sum(kern_ms)], dtype=torch.float64, device=dev)
     # end-to-end leg: same call with HOST buffers (pinned), h2d of the action + d2h of state/converged inside the timed region
     e2e_steps = max(2, args.steps)
@@ -327,7 +328,7 @@ def run_ours(args, wl):
                            "l2": "flushed between timed iterations (192 MiB fill, untimed)", "launch": p.launch_info(), "wall_s_incl_flush": wall,
                            "episode_stats": {"converged_envs": stats[0].item(), "envs": stats[1].item(), "flagged_envs": stats[2].item(),
                                              "flags": {k: stats[3 + i].item() for i, k in enumerate(FLAG_NAMES)}}},
-                "clocks": sampler.summary(), "gpu_launches": int(launches) * world,
+                "clocks": sampler.summary(), "gpu_launches": int(launches + order_launches) * world,
                 "e2e": {"value": e2e_value, "unit": "env-steps/s", "h2d_bytes_per_step": int(h2d), "d2h_bytes_per_step": int(n * (128 * w + 1))},
                 "roofline": {"bound": "hbm", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(args.workload),
                              "peak_source": which, "algorithmic_bytes_per_env_step": alg_b,

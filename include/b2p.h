@@ -39,7 +39,8 @@ enum { B2P_OK = 0, B2P_ERR_ARG = -1, B2P_ERR_MODEL = -2, B2P_ERR_CUDA = -3, B2P_
 enum {
   B2P_Q_NQ = 0, B2P_Q_NV, B2P_Q_NU, B2P_Q_NPROP, B2P_Q_STATE_STRIDE, B2P_Q_OUT_STRIDE, B2P_Q_MAXPROP,
   B2P_Q_REC_QPOS, B2P_Q_REC_QVEL, B2P_Q_REC_QACC_WARMSTART, B2P_Q_REC_TIME, B2P_Q_LAUNCHES, B2P_Q_SMEM_BYTES,
-  B2P_Q_BLOCKS_PER_SM, B2P_Q_THREADS, B2P_Q_GRID, B2P_Q_MAXCON, B2P_Q_NGEOM
+  B2P_Q_BLOCKS_PER_SM, B2P_Q_THREADS, B2P_Q_GRID, B2P_Q_MAXCON, B2P_Q_NGEOM,
+  B2P_Q_ORDER_LAUNCHES   /* launches of the scene-queue ordering kernel (one before each step launch once a batch exceeds one round) */
 };
 /* derived-output fields (b2p_get / offsets inside the output record via b2p_out_offset) */
 enum {

@@ -56,7 +56,7 @@ __global__ void __launch_bounds__(1024) b2p_order_kernel(const int* __restrict__
 struct b2p_handle_s {
   int dtype, device, n_env, full_contacts, nq, nv, nu, nprop, ngeom;
   LaunchGeom lg;
-  long long launches;
+  long long launches, order_launches;
   DevModel<double> hmodel;
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
@@ -114,7 +114,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
     CK(cudaGetLastError());
-    a.order = h->d_order;
+    a.order = h->d_order; h->order_launches++;
   }
   if ((a.mode == MODE_PHYSICS || a.mode == MODE_OSC) && a.n_steps > 0) h->work_steps = a.mode == MODE_OSC ? a.n_steps * a.control_steps : a.n_steps;
   if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, h->d_next_env, st));
@@ -168,6 +168,7 @@ int b2p_query(b2p_handle h, int what) {
     case B2P_Q_REC_QPOS: return REC_QPOS; case B2P_Q_REC_QVEL: return REC_QVEL; case B2P_Q_REC_QACC_WARMSTART: return REC_QACC; case B2P_Q_REC_TIME: return REC_TIME;
     case B2P_Q_LAUNCHES: return (int)h->launches; case B2P_Q_SMEM_BYTES: return h->lg.smem_bytes; case B2P_Q_BLOCKS_PER_SM: return h->lg.blocks_per_sm;
     case B2P_Q_THREADS: return h->lg.threads; case B2P_Q_GRID: return h->lg.grid; case B2P_Q_MAXCON: return MAXCON; case B2P_Q_NGEOM: return h->ngeom;
+    case B2P_Q_ORDER_LAUNCHES: return (int)h->order_launches;
   }
   return B2P_ERR_ARG;
 }

@@ -21,7 +21,7 @@ UNIT_FLAGS = {"b2p_kernel_f32.cu": ["-use_fast_math"], "b2p_render.cu": ["-fmad=
 # enums of include/b2p.h
 F64, F32 = 0, 1
 Q = dict(NQ=0, NV=1, NU=2, NPROP=3, STATE_STRIDE=4, OUT_STRIDE=5, MAXPROP=6, REC_QPOS=7, REC_QVEL=8, REC_QACC_WARMSTART=9,
-         REC_TIME=10, LAUNCHES=11, SMEM_BYTES=12, BLOCKS_PER_SM=13, THREADS=14, GRID=15, MAXCON=16, NGEOM=17)
+         REC_TIME=10, LAUNCHES=11, SMEM_BYTES=12, BLOCKS_PER_SM=13, THREADS=14, GRID=15, MAXCON=16, NGEOM=17, ORDER_LAUNCHES=18)
 O = dict(SITE_XPOS=0, SITE_XMAT=1, QACC=2, QFRC_BIAS=3, CTRL=4, NCON=5, NEFC=6, NITER=7, CONTACT=8, MARM=9, GEOM_XPOS=10,
          GEOM_XMAT=11, QACC_SMOOTH=12, EFC_FORCE=13)
 SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params",

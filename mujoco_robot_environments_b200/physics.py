@@ -192,6 +192,11 @@ class BatchedPhysics:
     def launches(self) -> int:
         return self._L.b2p_query(self._h, ffi.Q["LAUNCHES"])
 
+    @property
+    def order_launches(self) -> int:
+        """Launches of the scene-queue ordering kernel (csrc/b2p_api.cu: b2p_order_kernel)."""
+        return self._L.b2p_query(self._h, ffi.Q["ORDER_LAUNCHES"])
+
     def launch_info(self) -> dict:
         return {k.lower(): self._L.b2p_query(self._h, ffi.Q[k]) for k in ("SMEM_BYTES", "BLOCKS_PER_SM", "THREADS", "GRID")}
 
