@@ -69,6 +69,10 @@ int b2p_set_env_gains(b2p_handle h, const void* gains);
 int b2p_osc_config(b2p_handle h, const double gains6[6], const double nullspace7[7], double pos_thresh, double ori_thresh);
 /* 0 = only solver-active contacts while stepping (default), 1 = list every contact inside geom margin */
 int b2p_set_full_contacts(b2p_handle h, int full);
+/* sticky scene mask for b2p_step_physics / b2p_step_osc (device [n_env], borrowed; NULL = all): scenes with mask 0 are not
+ * stepped and none of their outputs is written -- the batched form of "this scene's episode is over"
+ * (transporter_network_data_generation.py:108-112 stops stepping an env once its demonstration is complete or has failed) */
+int b2p_set_env_mask(b2p_handle h, const uint8_t* env_mask);
 
 int b2p_step_physics(b2p_handle h, const void* ctrl /* [n_env][nu] */, int n_steps, void* stream);
 int b2p_step_osc(b2p_handle h, const void* target13 /* [n_env][13] pos vel quat angvel */, const uint8_t* grip /* [n_env] */,

@@ -61,7 +61,7 @@ struct b2p_handle_s {
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env;
-  const void* env_gains;
+  const void* env_gains; const unsigned char* env_mask;
   int *d_work, *d_order; int work_steps, sort_queue;   // work_steps: physics steps behind d_work (0 = none yet)
 };
 
@@ -189,6 +189,7 @@ int b2p_bind_state(b2p_handle h, void* state) {
 int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out = out ? out : h->own_out; return B2P_OK; }
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
 int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
+int b2p_set_env_mask(b2p_handle h, const uint8_t* mask) { if (!h) return B2P_ERR_ARG; h->env_mask = mask; return B2P_OK; }
 int b2p_set_full_contacts(b2p_handle h, int full) { if (!h) return B2P_ERR_ARG; h->full_contacts = full; return B2P_OK; }
 int b2p_osc_config(b2p_handle h, const double g[6], const double q0[7], double pt, double ot) {
   if (!h || !g || !q0) return fail(B2P_ERR_ARG, "b2p_osc_config: null");
@@ -205,11 +206,11 @@ int b2p_osc_config(b2p_handle h, const double g[6], const double q0[7], double p
 
 int b2p_step_physics(b2p_handle h, const void* ctrl, int n_steps, void* stream) {
   if (!h || n_steps < 0) return fail(B2P_ERR_ARG, "b2p_step_physics: bad argument");
-  return DISPATCH(h, MODE_PHYSICS, n_steps, 1, h->full_contacts, ctrl, nullptr, nullptr, nullptr, nullptr, nullptr, 0, 0, 0, stream);
+  return DISPATCH(h, MODE_PHYSICS, n_steps, 1, h->full_contacts, ctrl, nullptr, nullptr, h->env_mask, nullptr, nullptr, 0, 0, 0, stream);
 }
 int b2p_step_osc(b2p_handle h, const void* target13, const uint8_t* grip, int n_ticks, int control_steps, uint8_t* converged, void* stream) {
   if (!h || !target13 || n_ticks < 0 || control_steps < 1) return fail(B2P_ERR_ARG, "b2p_step_osc: bad argument");
-  return DISPATCH(h, MODE_OSC, n_ticks, control_steps, h->full_contacts, nullptr, target13, grip, nullptr, converged, nullptr, 0, 0, 0, stream);
+  return DISPATCH(h, MODE_OSC, n_ticks, control_steps, h->full_contacts, nullptr, target13, grip, h->env_mask, converged, nullptr, 0, 0, 0, stream);
 }
 int b2p_settle(b2p_handle h, const uint8_t* mask, int max_steps, int min_steps, double vt, double at, int32_t* steps_done, void* stream) {
   if (!h || max_steps < 0) return fail(B2P_ERR_ARG, "b2p_settle: bad argument");

@@ -91,6 +91,7 @@ class BatchedRearrangementEnv:
         self._prop_gid = torch.tensor(p.model.prop_geomid, device=self.device)
         self.mode = None
         self.failed = torch.zeros(self.num_envs, dtype=torch.bool, device=self.device)
+        self._active = None                                   # scenes being stepped by the current phase table (None = all)
         self.eef_home_pose = None
 
     def resample_scenes(self, mask: Optional[torch.Tensor] = None):
@@ -263,8 +264,8 @@ class BatchedRearrangementEnv:
         return TimeStep(StepType.FIRST, 0.0, 0.0, self._compute_observation())
 
     def step(self, action_dict, active: Optional[torch.Tensor] = None) -> TimeStep:
-        """``active`` (bool [n_env], batched variant only): scenes outside it hold the arm at its home pose for the duration of
-        the phase table (their episode is over; a batch steps all scenes for the same simulated time)."""
+        """``active`` (bool [n_env], batched variant only): scenes outside it are not stepped (their episode is over, as in the
+        reference's data generator, which stops calling ``step`` on an env whose demonstration is complete or has failed)."""
         observation = self._compute_observation()                                             # :343 (observation BEFORE acting)
         if self.mode == "pick":
             self.pick(action_dict["pose"], active); self.mode = "place"
@@ -274,7 +275,7 @@ class BatchedRearrangementEnv:
 
     def _phase(self, duration: float, what: str):
         ok = self._robot.run_controller(duration)
-        bad = ~ok
+        bad = ~ok if self._active is None else ~ok & self._active          # scenes outside the mask were not stepped
         self.failed |= bad
         if self.strict and bool(bad.any()):
             raise RuntimeError("Failed to " + what)                                           # rearrangement.py:372,377,...
@@ -292,8 +293,10 @@ class BatchedRearrangementEnv:
         osc, zeros = self._osc, torch.zeros(3, device=self.device, dtype=self.dtype)
         pose = self._pose_tensor(pose)
         pre = pose.clone(); pre[:, 2] = 0.9
-        if active is not None:                      # idle scenes: every phase targets the home pose, gripper unchanged
-            idle = ~active.to(self.device, torch.bool)
+        if active is not None:                      # idle scenes (episode over) are not stepped at all: b2p_set_env_mask
+            self._active = active.to(self.device, torch.bool)
+            self._physics.set_env_mask(self._active)
+            idle = ~self._active
             home = torch.cat([self.eef_home_pose, torch.tensor(DOWN_QUAT, device=self.device, dtype=self.dtype).expand(self.num_envs, 4)], 1)
             pose[idle] = home[idle]; pre[idle] = home[idle]
         if grip_status == "max":
@@ -310,6 +313,9 @@ class BatchedRearrangementEnv:
         osc.set_target(position=pre[:, :3]); self._phase(2.0, names[3])
         osc.set_target(position=self.eef_home_pose, quat=torch.tensor(DOWN_QUAT, device=self.device, dtype=self.dtype))
         self._phase(2.0, names[4])
+        if active is not None:
+            self._active = None
+            self._physics.set_env_mask(None)
 
     def pick(self, pose, active: Optional[torch.Tensor] = None):
         """rearrangement.py:358-401."""

@@ -171,6 +171,18 @@ class BatchedPhysics:
         self._env_gains = g                      # borrowed by the handle: keep it alive
         ffi.check(self._L.b2p_set_env_gains(self._h, g.data_ptr()))
 
+    def set_env_mask(self, mask: Optional[torch.Tensor]):
+        """Sticky scene mask for ``step`` / ``run_controller`` (bool / uint8 [n_env]; None = all): masked-out scenes are not
+        stepped and keep their state, time and ``converged`` bit -- their episode is over."""
+        if mask is None:
+            self._env_mask = None
+            ffi.check(self._L.b2p_set_env_mask(self._h, None))
+            return
+        m = mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        assert m.shape == (self.n_env,)
+        self._env_mask = m                       # borrowed by the handle: keep it alive
+        ffi.check(self._L.b2p_set_env_mask(self._h, m.data_ptr()))
+
     def set_full_contacts(self, full: bool):
         ffi.check(self._L.b2p_set_full_contacts(self._h, int(full)))
 
