@@ -80,6 +80,14 @@ int b2p_step_osc(b2p_handle h, const void* target13 /* [n_env][13] pos vel quat 
 int b2p_settle(b2p_handle h, const uint8_t* env_mask /* NULL = all */, int max_steps, int min_steps, double qvel_tol,
                double qacc_tol, int32_t* steps_done /* [n_env] or NULL */, void* stream);
 int b2p_forward(b2p_handle h, int full_contacts, void* stream);
+/* SortColours.prop_place (tasks/rearrangement.py:597-665) for every scene in ONE launch: up to max_attempts proposals per scene,
+ * position ~ U(box lo, box hi) (box: device [n_env][6] reals lo3 | hi3), gripper-down orientation, accepted when the prop
+ * (prop: device [n_env] prop index) has no contact closer than `dist` with any geom but `table_geom` after kinematics + the full
+ * collision pass.  Proposals are a counter-based function of (seed, scene, attempt).  out: device [n_env][4] reals = accepted
+ * xyz, attempts used (negative: nothing accepted).  The bound state is left untouched (the reference searches on a deepcopy
+ * of the physics); scenes with env_mask 0 are skipped and their out row is not written. */
+int b2p_place_search(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* env_mask /* NULL = all */, int max_attempts,
+                     double dist, int table_geom, unsigned seed, void* out, void* stream);
 int b2p_get(b2p_handle h, int field, void* dst /* [n_env][count] */, void* stream);
 int b2p_status(b2p_handle h, int32_t* flags /* device [n_env] */, int clear, void* stream);
 

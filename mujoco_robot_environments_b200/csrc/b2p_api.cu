@@ -134,6 +134,14 @@ static int run_mode(b2p_handle h, int mode, int n_steps, int control_steps, int 
   a.settle_qvel_tol = (T)vt; a.settle_qacc_tol = (T)at; a.settle_min_steps = min_steps;
   return launch<T>(h, a, (cudaStream_t)stream);
 }
+template <typename T>
+static int place_mode(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* mask, int max_attempts, double dist, int table_geom, unsigned seed, void* out, void* stream) {
+  StepArgs<T> a; std::memset(&a, 0, sizeof a);
+  { const char* ls = getenv("B2P_LOCKSTEP"); a.lockstep = ls ? atoi(ls) : LK_DEFAULT; }
+  a.mode = MODE_PLACE; a.n_steps = max_attempts; a.control_steps = 1; a.full_contacts = 1; a.env_mask = mask;
+  a.place_prop = prop; a.place_box = (const T*)box; a.place_dist = (T)dist; a.place_table = table_geom; a.place_seed = seed; a.place_out = (T*)out;
+  return launch<T>(h, a, (cudaStream_t)stream);
+}
 extern "C" {
 
 const char* b2p_last_error(void) { return g_err.c_str(); }
@@ -211,6 +219,11 @@ int b2p_step_physics(b2p_handle h, const void* ctrl, int n_steps, void* stream) 
 int b2p_step_osc(b2p_handle h, const void* target13, const uint8_t* grip, int n_ticks, int control_steps, uint8_t* converged, void* stream) {
   if (!h || !target13 || n_ticks < 0 || control_steps < 1) return fail(B2P_ERR_ARG, "b2p_step_osc: bad argument");
   return DISPATCH(h, MODE_OSC, n_ticks, control_steps, h->full_contacts, nullptr, target13, grip, h->env_mask, converged, nullptr, 0, 0, 0, stream);
+}
+int b2p_place_search(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* mask, int max_attempts, double dist, int table_geom, unsigned seed, void* out, void* stream) {
+  if (!h || !prop || !box || !out || max_attempts < 0) return fail(B2P_ERR_ARG, "b2p_place_search: bad argument");
+  return h->dtype == B2P_F64 ? place_mode<double>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream)
+                             : place_mode<float>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream);
 }
 int b2p_settle(b2p_handle h, const uint8_t* mask, int max_steps, int min_steps, double vt, double at, int32_t* steps_done, void* stream) {
   if (!h || max_steps < 0) return fail(B2P_ERR_ARG, "b2p_settle: bad argument");

@@ -109,7 +109,7 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
 
 // One scene, whole launch: load the state record, run the requested mode, store the record.  `active` = this warp holds
 // a scene; an idle warp of a lockstep CTA still walks the same stage barriers.
-template <typename T>
+template <typename T, bool kPlace = false>   // kPlace: the placement-search kernel (MODE_PLACE) is its own instantiation, so the step kernels' code is untouched by it
 B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded, bool active = true) {
   const int nv = m.nv;
   T* rec = a.state + (size_t)(active ? env : 0) * a.state_stride;
@@ -128,6 +128,50 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       bsync(c);
     }
     prop_params(m, s, c);
+  }
+  if constexpr (kPlace) {
+    // SortColours prop_place (rearrangement.py:597-665) as one launch: draw a position in the scene's box, put the prop there
+    // (gripper-down orientation), run kinematics + the full collision pass, accept when no contact of the prop with anything
+    // but the table is closer than place_dist.  The live state is not written back (the reference works on a deepcopy).
+    int gid = -1, qa = m.ntd; T lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0};
+    if (active) {
+      const int pid = a.place_prop[env]; qa = m.ntd + 7 * pid;
+      for (int g0 = 0; g0 < m.ngeom; g0++) if (m.geom_prop[g0] == pid) gid = g0;
+      for (int k = 0; k < 3; k++) { lo[k] = a.place_box[(size_t)env * 6 + k]; hi[k] = a.place_box[(size_t)env * 6 + 3 + k]; }
+    }
+    bool fin = !active, found = false; int used = 0;
+    for (int k = 0; k < a.n_steps; k++) {
+      if (csync_and(c, fin)) break;
+      if (!fin) {
+        if (c.tid == 0) {
+          T* q = s.qpos + qa;
+          for (int d = 0; d < 3; d++) q[d] = lo[d] + (hi[d] - lo[d]) * (T)uniform01(a.place_seed, (unsigned)env, (unsigned)k, (unsigned)d);
+          q[3] = 0; q[4] = 0; q[5] = 1; q[6] = 0;
+        }
+        bsync(c);
+      }
+      csync(c, LK_FK);
+      if (!fin) forward_sweep(m, s, c);
+      csync(c, LK_COLLIDE);
+      collide(m, g, s, c, true, !fin);
+      if (!fin) {
+        bsync(c);
+        unsigned hit = 0;
+        for (int i = c.tid; i < s.ncon; i += c.nt) {
+          const int p = s.c_pair[i], g1 = g.pair_g1[p], g2 = g.pair_g2[p];
+          if ((g1 == gid || g2 == gid) && g1 != a.place_table && g2 != a.place_table && s.c_dist[i] <= a.place_dist) hit = 1;
+        }
+        hit = block_or(c, hit);
+        used = k + 1;
+        if (!hit) { found = true; fin = true; }
+      }
+    }
+    if (active && c.tid == 0 && a.place_out) {
+      T* o = a.place_out + (size_t)env * 4;
+      for (int d = 0; d < 3; d++) o[d] = s.qpos[qa + d];
+      o[3] = found ? T(used) : T(-used - 1);
+    }
+    return;
   }
   const bool full = a.full_contacts != 0;
   int work = 0;   // scheduling hint for the next launch (see StepArgs::work)

@@ -53,7 +53,7 @@ struct alignas(16) SmemLayout {
   alignas(8) unsigned long long bar[1 + KernelCfg<T>::kWarps];
 };
 
-template <typename T>
+template <typename T, bool kPlace>
 __global__ void __launch_bounds__(32 * KernelCfg<T>::kWarps, KernelCfg<T>::kMinBlocks)
 b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int* __restrict__ next_env) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -93,11 +93,11 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
       mbar_wait(bar, phase); phase ^= 1;
     }
     PROF_T0
-    run_env(sm.model, g, s, a, env, c, true, active);
+    run_env<T, kPlace>(sm.model, g, s, a, env, c, true, active);
     if (active) PROF_ADD(PF_TOTAL)
     if (active) {
       __syncwarp();
-      if (lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }
+      if (!kPlace && lane == 0) { fence_async_smem(); tma_store_1d(rec, s.qpos, kRecBytes); }
       __syncwarp();
     }
   }
@@ -122,11 +122,13 @@ template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<
 template <typename T>
 static cudaError_t step_configure(int device, int n_env, LaunchGeom* out) {
   const size_t smem = step_smem_size<T>();
-  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0, sms = 0;
   const int threads = 32 * KernelCfg<T>::kWarps;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T>, threads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T, false>, threads, smem);
   if (e != cudaSuccess) return e;
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) return e;
@@ -142,7 +144,8 @@ template <typename T>
 static cudaError_t step_launch(const LaunchGeom& lg, const void* d_model, const Globals<T>& g, const StepArgs<T>& a, int* next_env, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(next_env, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
-  b2p_step_kernel<T><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  if (a.mode == MODE_PLACE) b2p_step_kernel<T, true><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  else b2p_step_kernel<T, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
   return cudaGetLastError();
 }
 

@@ -14,7 +14,10 @@ namespace b2p {
 enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
 enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
-enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3 };
+enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3, MODE_PLACE = 4 };
+// counter-based uniform in [0, 1): placement proposals are a function of (seed, scene, attempt, coordinate) only
+B2P_HD unsigned hash32(unsigned x) { x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16; return x; }
+B2P_HD double uniform01(unsigned seed, unsigned env, unsigned k, unsigned d) { return (hash32(hash32(hash32(seed ^ (0x9e3779b9U * (env + 1U))) + k) + d) >> 8) * (1.0 / 16777216.0); }
 
 struct Ctx { int tid, nt; int lock; int bar_id, bar_n; };   // bar_n > 0: the lockstep group is bar_n threads on named barrier bar_id (a sub-group of the CTA's warps)   // lock: bit mask of the CTA-wide stage barriers in use (LK_*), 0 = warps run free
 

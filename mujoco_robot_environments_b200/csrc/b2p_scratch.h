@@ -102,6 +102,9 @@ struct StepArgs {
   int out_stride;
   const int* order;          // optional [n_env]: queue position -> scene (scenes ordered by the work they did in the previous launch)
   int* work;                 // optional [n_env] out: work proxy of this launch, sum over steps of nefc * (2 + Newton iterations)
+  // MODE_PLACE (expert prop_place): per scene the prop to place and the box [lo3 | hi3] proposals are drawn from
+  const int* place_prop; const T* place_box; T place_dist; int place_table; unsigned place_seed;
+  T* place_out;              // [n_env][4]: accepted position xyz, attempts used (negative: none accepted within n_steps attempts)
   const T* gains;            // MODE_OSC: optional [n_env][6] per-scene OSC gains (pos kp kd, ori kp kd, null kp kd); NULL = the model's
 };
 // derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |

@@ -9,8 +9,8 @@ Reference behaviour mirrored (mujoco_robot_environments/tasks/rearrangement.py):
   * camera maths                :480-548  ``_get_camera_intrinsics`` / ``_get_camera_extrinsics`` / ``world_2_pixel`` / ``pixel_2_world``
 and environment/props.py:13-20 (COLOURS), :286-291 (colour noise), :604-617 (colour of prop i).
 
-Everything here is small tensor algebra on the scene batch (torch = plumbing); the collision query behind ``prop_place`` is the
-``b2p_forward(full_contacts=1)`` kernel, i.e. the same broad/narrow phase the step kernel runs.
+Everything here is small tensor algebra on the scene batch (torch = plumbing); the rejection loop behind ``prop_place`` runs on the
+device in one launch (``b2p_place_search``: kinematics + the step kernel's broad/narrow phase per proposal).
 """
 from __future__ import annotations
 
@@ -138,7 +138,6 @@ class SortColoursExpert:
 
     MAX_PLACE_ATTEMPTS = 10000         # rearrangement.py:629
     PLACE_DIST = 0.05                  # rearrangement.py:623
-    CHECK_EVERY = 8                    # attempts between "is every scene done?" host checks
 
     def __init__(self, env):
         self.env = env
@@ -151,6 +150,7 @@ class SortColoursExpert:
         seed = int(task["initializers"]["seed"]) + 1           # prop_place_random_state, rearrangement.py:208
         self._rs = np.random.RandomState(seed=seed) if env.num_envs == 1 else None
         self._gen = torch.Generator(device=env.device); self._gen.manual_seed(seed)
+        self._seed, self._place_calls = int(seed), 0
         self.place_attempts = 0
         self.place_failed = torch.zeros(env.num_envs, dtype=torch.bool, device=env.device)
 
@@ -180,39 +180,23 @@ class SortColoursExpert:
         return lo + (hi - lo) * torch.rand(lo.shape, device=lo.device, dtype=lo.dtype, generator=self._gen)
 
     def prop_place(self, prop_id: torch.Tensor, min_pose: torch.Tensor, max_pose: torch.Tensor, active: Optional[torch.Tensor] = None) -> torch.Tensor:
-        """Collision-free place pose per scene -> [n, 7]; scenes outside ``active`` get zeros.  Works on a saved copy of the
-        state record (``deepcopy(self._physics)`` in the reference): the live state and derived outputs are restored.
+        """Collision-free place pose per scene -> [n, 7]; scenes outside ``active`` get zeros.  The search runs in the kernel's
+        own scratch copy of the scene (``deepcopy(self._physics)`` in the reference): state and derived outputs are not written.
         A scene that finds no pose within MAX_PLACE_ATTEMPTS raises for a strict (single-scene) env like the reference
         (rearrangement.py:665) and is flagged in ``self.place_failed`` (and ``env.failed``) for a batch."""
         env, p = self.env, self.env.physics
         n = env.num_envs
-        todo = torch.ones(n, dtype=torch.bool, device=env.device) if active is None else active.clone()
-        out = torch.zeros(n, 7, device=env.device, dtype=env.dtype)
-        saved_state, saved_out = p.state.clone(), p.out.clone()
-        qadr = torch.tensor(p.model.prop_qposadr, device=env.device)[prop_id]
-        gid = env._prop_gid[prop_id]
+        todo = torch.ones(n, dtype=torch.bool, device=env.device) if active is None else active.to(env.device, torch.bool)
         quat = torch.tensor(DOWN_QUAT, device=env.device, dtype=env.dtype).expand(n, 4)
-        cols = qadr[:, None] + torch.arange(7, device=env.device)[None, :]
-        rows = torch.arange(n, device=env.device)[:, None]
-        slots = torch.arange(p.maxcon, device=env.device)[None, :]
-        home = p.qpos[rows, cols].clone()
-        try:
-            for attempt in range(self.MAX_PLACE_ATTEMPTS):
-                if attempt % self.CHECK_EVERY == 0 and not bool(todo.any()):
-                    break
-                pose = torch.cat([self._uniform(min_pose, max_pose), quat], 1)
-                p.qpos[rows, cols] = torch.where(todo[:, None], pose, home)     # scenes that are done keep their live pose
-                p.forward(full_contacts=True)
-                self.place_attempts += 1
-                c = p.data.contact
-                touches = (c["geom1"] == gid[:, None]) | (c["geom2"] == gid[:, None])
-                table = (c["geom1"] == env._table_gid) | (c["geom2"] == env._table_gid)
-                coll = ((slots < p.data.ncon[:, None]) & touches & ~table & (c["dist"] <= self.PLACE_DIST)).any(1)
-                ok = todo & ~coll
-                out = torch.where(ok[:, None], pose, out)
-                todo = todo & coll
-        finally:
-            p.state.copy_(saved_state); p.out.copy_(saved_out)
+        self._place_calls += 1
+        # one launch: every scene runs its own rejection loop on the device (proposal -> kinematics -> full collision pass ->
+        # the dist <= PLACE_DIST rule of :623), the bound state is never written
+        res = p.place_search(prop_id, min_pose, max_pose, env._table_gid, self.PLACE_DIST, self.MAX_PLACE_ATTEMPTS,
+                             seed=self._seed * 1000003 + self._place_calls, mask=todo)
+        found = todo & (res[:, 3] > 0)
+        self.place_attempts += int(res[:, 3].abs().max().item()) if bool(todo.any()) else 0
+        out = torch.cat([res[:, :3], quat], 1) * found[:, None]
+        todo = todo & ~found
         self.place_failed = todo
         if bool(todo.any()):
             if env.strict:

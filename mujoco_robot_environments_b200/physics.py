@@ -155,6 +155,20 @@ class BatchedPhysics:
                                      self.steps_done.data_ptr(), self._stream()), "b2p_settle")
         return self.steps_done
 
+    def place_search(self, prop_id: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor, table_geom: int, dist: float, max_attempts: int,
+                     seed: int, mask: Optional[torch.Tensor] = None) -> torch.Tensor:
+        """SortColours.prop_place for every scene in one launch (``b2p_place_search``) -> [n_env, 4] = accepted xyz, attempts used
+        (negative: nothing accepted).  State and derived outputs are untouched; rows outside ``mask`` are zero."""
+        pid = prop_id.to(device=self.device, dtype=torch.int32).contiguous()
+        box = torch.cat([lo, hi], 1).to(device=self.device, dtype=self.dtype).contiguous()
+        m = None if mask is None else mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        assert pid.shape == (self.n_env,) and box.shape == (self.n_env, 6)
+        out = torch.zeros(self.n_env, 4, device=self.device, dtype=self.dtype)
+        ffi.check(self._L.b2p_place_search(self._h, pid.data_ptr(), box.data_ptr(), None if m is None else m.data_ptr(), int(max_attempts), float(dist),
+                                           int(table_geom), int(seed) & 0xFFFFFFFF, out.data_ptr(), self._stream()), "b2p_place_search")
+        self._keep = (pid, box, m)
+        return out
+
     def osc_config(self, gains6, nullspace7, pos_thresh=5e-3, ori_thresh=68e-3):
         g = (C.c_double * 6)(*[float(x) for x in gains6])
         q = (C.c_double * 7)(*[float(x) for x in nullspace7])

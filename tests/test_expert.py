@@ -88,6 +88,22 @@ def test_sort_colours_episode_on_gpu():
     others = pos.clone(); others[e, pid] = 100.0
     d = (others[:, :, :2] - place[:, None, :2]).norm(dim=2)
     assert bool((d[ip][env.has_prop[ip]] > 0.05).all())
+    # independent check of the device-side search (b2p_place_search): put every placed prop at its pose, list the contacts with
+    # b2p_forward and apply the reference's rule (rearrangement.py:617-625) on the host side
+    p = env.physics
+    saved, saved_out = p.state.clone(), p.out.clone()
+    qadr = torch.tensor(p.model.prop_qposadr, device=env.device)[pid]
+    cols = qadr[:, None] + torch.arange(7, device=env.device)[None, :]
+    p.qpos[e[:, None], cols] = torch.where(ip[:, None], place.to(p.dtype), p.qpos[e[:, None], cols])
+    p.forward(full_contacts=True)
+    c, gid = p.data.contact, env._prop_gid[pid]
+    touches = (c["geom1"] == gid[:, None]) | (c["geom2"] == gid[:, None])
+    table = (c["geom1"] == env._table_gid) | (c["geom2"] == env._table_gid)
+    slots = torch.arange(p.maxcon, device=env.device)[None, :]
+    coll = ((slots < p.data.ncon[:, None]) & touches & ~table & (c["dist"] <= ex.PLACE_DIST)).any(1)
+    assert not bool(coll[ip].any())
+    p.state.copy_(saved); p.out.copy_(saved_out)
+    assert ex.place_attempts >= 1
     out = rollout_episode(env, 4)
     n1 = int((env.has_prop & ex.within_target()).sum())
     total = int(env.has_prop.sum())
