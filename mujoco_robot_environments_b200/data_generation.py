@@ -73,8 +73,57 @@ def rollout_episode(env, max_steps: int, render: bool = False, resample_props: b
     return out
 
 
+def rollout_recycled(env, episodes: int, max_steps: int) -> Dict[str, torch.Tensor]:
+    """At least ``episodes`` episodes on the scene batch with finished scenes recycled: after every pick/place round the scenes
+    whose demonstration is complete, has failed or has used ``max_steps`` rounds are recorded, reset (new props every 10th
+    episode of a scene, transporter_network_data_generation.py:99-101,118) and start their next episode while the others carry
+    on, so every round steps a full batch (a late round of ``rollout_episode`` steps only the stragglers, and one scene-step
+    costs the same ~0.2 ms whatever the batch).  Same record layout as ``rollout_episode`` (leading dim = episodes, in
+    completion order), state observations only."""
+    n, dev = env.num_envs, env.device
+    obs0 = env.reset().observation
+    actions = torch.zeros(n, max_steps, 2, ACTION_WIDTH, dtype=torch.float64, device=dev)
+    valid = torch.zeros(n, max_steps, dtype=torch.bool, device=dev)
+    pos0, quat0 = obs0["prop_pos"].clone(), obs0["prop_quat"].clone()
+    t = torch.zeros(n, dtype=torch.int64, device=dev)
+    played = torch.zeros(n, dtype=torch.int64, device=dev)           # episodes finished per scene
+    status = torch.zeros(n, dtype=torch.int32, device=dev)           # reset() clears the kernel's flags for the whole batch
+    e = torch.arange(n, device=dev)
+    chunks, done = [], 0
+    while done < episodes:
+        in_progress, pick, place = env.sort_colours()                # flags scenes without a collision-free place pose as failed
+        act = in_progress & ~env.failed & (t < max_steps)
+        ended = ~act
+        if bool(ended.any()):
+            status |= env.physics.status()
+            unsorted = (env.has_prop & ~env.expert.within_target()).any(1)
+            chunks.append({"actions": actions[ended].clone(), "valid": valid[ended].clone(), "prop_pos0": pos0[ended].clone(),
+                           "prop_quat0": quat0[ended].clone(), "prop_colour": env.prop_colour[ended].clone(), "has_prop": env.has_prop[ended].clone(),
+                           "success": (~unsorted & ~env.failed)[ended], "failed": env.failed[ended].clone(), "rounds": valid[ended].sum(1),
+                           "status": status[ended].clone()})
+            done += int(ended.sum())
+            played[ended] += 1
+            fresh = ended & (played % 10 == 0)                       # a "new env" in the reference: props re-drawn
+            if bool((ended & ~fresh).any()):
+                env.reset(mask=ended & ~fresh)
+            if bool(fresh.any()):
+                env.reset(mask=fresh, resample_props=True)
+            obs = env._compute_observation()
+            pos0[ended], quat0[ended] = obs["prop_pos"][ended], obs["prop_quat"][ended]
+            actions[ended] = 0; valid[ended] = False; t[ended] = 0; status[ended] = 0
+            continue
+        pick_px = env.world_2_pixel("overhead_camera/overhead_camera", pick[:, :3])
+        place_px = env.world_2_pixel("overhead_camera/overhead_camera", place[:, :3])
+        actions[e, t, 0] = pack_action(pick, pick_px); actions[e, t, 1] = pack_action(place, place_px)
+        valid[e, t] = True
+        env.step({"pose": pick.clone(), "pixel_coords": pick_px, "gripper_rot": 0.0})
+        env.step({"pose": place.clone(), "pixel_coords": place_px, "gripper_rot": 0.0})
+        t += 1
+    return {k: torch.cat([c[k] for c in chunks], 0) for k in chunks[0]}
+
+
 def generate(num_envs: int = 1024, episodes_per_env: int = 1, cfg: Optional[dict] = None, device=None, dtype=torch.float32,
-             seed: Optional[int] = None, render: bool = False, max_steps: Optional[int] = None):
+             seed: Optional[int] = None, render: bool = False, max_steps: Optional[int] = None, recycle: bool = False):
     """Run ``episodes_per_env`` episodes on ``num_envs`` scenes of THIS rank, gather to rank 0.
     -> (demos dict on rank 0 / None elsewhere, stats dict summed over ranks)."""
     from .env import BatchedRearrangementEnv
@@ -86,7 +135,11 @@ def generate(num_envs: int = 1024, episodes_per_env: int = 1, cfg: Optional[dict
                                   seed=base_seed + 100003 * rank, strict=False)
     demos, t0 = [], time.perf_counter()
     launches0 = env.physics.launches
-    for ep in range(episodes_per_env):
+    if recycle:
+        if render:
+            raise ValueError("recycle=True records state observations only")
+        demos.append(rollout_recycled(env, num_envs * episodes_per_env, T))
+    for ep in range(0 if recycle else episodes_per_env):
         # the reference builds a fresh env (new props) every 10 episodes (transporter_network_data_generation.py:99-101,118)
         demos.append(rollout_episode(env, T, render, resample_props=ep > 0 and ep % 10 == 0))
     torch.cuda.synchronize(env.device)
@@ -113,9 +166,10 @@ def main():
     ap.add_argument("--episodes", type=int, default=1, help="episodes per scene")
     ap.add_argument("--max-steps", type=int, default=None)
     ap.add_argument("--render", action="store_true")
+    ap.add_argument("--recycle", action="store_true", help="finished scenes start their next episode at once (full batch every round)")
     ap.add_argument("--out", default=None, help="rank 0 writes <out>.npz")
     a = ap.parse_args()
-    demos, stat = generate(a.envs, a.episodes, render=a.render, max_steps=a.max_steps)
+    demos, stat = generate(a.envs, a.episodes, render=a.render, max_steps=a.max_steps, recycle=a.recycle)
     if demos is not None:
         if a.out:
             os.makedirs(os.path.dirname(os.path.abspath(a.out)), exist_ok=True)

@@ -110,3 +110,23 @@ def test_sort_colours_episode_on_gpu():
     assert out["actions"].shape == (96, 4, 2, 10) and out["valid"][:, 0].any()
     assert n1 > n0 and n1 > 0.6 * total, (n0, n1, total)
     assert int((env.physics.status() & 7).ne(0).sum()) == 0          # no BADQPOS / BADQVEL / BADQACC during the grasping episode
+
+
+@pytest.mark.gpu
+def test_recycled_rollout_on_gpu():
+    """Finished scenes start their next episode while the others carry on: at least the requested number of episodes comes
+    back in the record layout of rollout_episode, rounds never exceed max_steps, and a successful episode is a sorted scene."""
+    from mujoco_robot_environments_b200.env import BatchedRearrangementEnv
+    from mujoco_robot_environments_b200.data_generation import rollout_recycled
+    env = BatchedRearrangementEnv(cfg=C.compose(COLOUR_SPLITTER_OVERRIDES), num_envs=48, strict=False)
+    out = rollout_recycled(env, 80, 3)
+    m = out["success"].shape[0]
+    assert m >= 80
+    assert out["actions"].shape == (m, 3, 2, 10) and out["valid"].shape == (m, 3) and out["prop_pos0"].shape[0] == m
+    assert int(out["rounds"].max()) <= 3 and bool((out["rounds"] == out["valid"].sum(1)).all())
+    assert bool((out["valid"][:, 1:] <= out["valid"][:, :-1]).all())                 # rounds are a prefix
+    assert not bool((out["success"] & out["failed"]).any())
+    assert int(out["success"].sum()) > 0.3 * m
+    used = out["actions"][out["valid"]]
+    assert bool((used[:, 0, 2] > 0.3).all()) and bool(torch.isfinite(used).all())   # pick heights on the table
+    assert int((out["status"] & 7).ne(0).sum()) == 0
