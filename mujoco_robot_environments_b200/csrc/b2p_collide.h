@@ -221,6 +221,7 @@ B2P_HD int plane_box(const T* ppos, const T* pmat, const T* bpos, const T* bmat,
 
 // SAT (15 axes) + reference-face clipping / edge-edge point.  Returns #contacts, or -1 when the boxes are
 // separated by 0 < s <= margin (caller then runs the margin-inflated convex query: one closest-feature contact).
+#define BB_TIE 1e-6
 template <typename T>
 B2P_HDN int box_box(const T* p1, const T* m1, const T* s1, const T* p2, const T* m2, const T* s2, T margin, RawCon<T>& out, T* clip_scratch = nullptr) {
   T R[9], aR[9], t[3], dp[3];
@@ -240,7 +241,7 @@ B2P_HDN int box_box(const T* p1, const T* m1, const T* s1, const T* p2, const T*
     T tj = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
     T s = fabs(tj) - (s2[j] + s1[0] * aR[j] + s1[1] * aR[3 + j] + s1[2] * aR[6 + j]);
     if (s > margin) return 0;
-    if (s > best) { best = s; code = 3 + j; }
+    if (s > best + T(BB_TIE)) { best = s; code = 3 + j; }   // parallel faces tie up to rounding: box 1 keeps the reference face
   }
   T best_edge = -Num<T>::big(); int ecode = -1;
   for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) {
@@ -301,8 +302,10 @@ B2P_HDN int box_box(const T* p1, const T* m1, const T* s1, const T* p2, const T*
     int nn = 0;
     for (int v = 0; v < np; v++) {
       const T *A = poly[v], *Bp = poly[(v + 1) % np];
-      const T da = (A[0] - pa[0]) * ax[0] + (A[1] - pa[1]) * ax[1] + (A[2] - pa[2]) * ax[2] - lim;
-      const T db = (Bp[0] - pa[0]) * ax[0] + (Bp[1] - pa[1]) * ax[1] + (Bp[2] - pa[2]) * ax[2] - lim;
+      T da = (A[0] - pa[0]) * ax[0] + (A[1] - pa[1]) * ax[1] + (A[2] - pa[2]) * ax[2] - lim;
+      T db = (Bp[0] - pa[0]) * ax[0] + (Bp[1] - pa[1]) * ax[1] + (Bp[2] - pa[2]) * ax[2] - lim;
+      if (fabs(da) < T(BB_TIE)) da = 0;   // a vertex within a micron of the clip plane lies ON it (aligned boxes: gripper pads, cube on cube)
+      if (fabs(db) < T(BB_TIE)) db = 0;
       if (da <= 0) { cp3(tmp[nn], A); nn++; }
       if ((da < 0 && db > 0) || (da > 0 && db < 0)) { const T sx = da / (da - db); for (int k = 0; k < 3; k++) tmp[nn][k] = A[k] + sx * (Bp[k] - A[k]); nn++; }
     }

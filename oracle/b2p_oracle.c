@@ -565,6 +565,7 @@ static int plane_box(const double* ppos, const double* pmat, const double* bpos,
 /* Box-box: separating-axis test (15 axes) + reference-face clipping (<= 8 points) or edge-edge point.
  * returns #contacts, or -1 when the boxes are separated by 0 < s <= margin (caller falls back to the
  * margin-inflated convex routine, which reports the single closest-feature contact). */
+#define BB_TIE 1e-6
 static int box_box(const double* p1, const double* m1, const double* s1, const double* p2, const double* m2, const double* s2, double margin, rawcon_t* out) {
   double R[9], aR[9], t[3], dp[3];
   for (int k = 0; k < 3; k++) dp[k] = p2[k] - p1[k];
@@ -583,7 +584,7 @@ static int box_box(const double* p1, const double* m1, const double* s1, const d
     double tj = t[0] * R[j] + t[1] * R[3 + j] + t[2] * R[6 + j];
     double s = fabs(tj) - (s2[j] + s1[0] * aR[j] + s1[1] * aR[3 + j] + s1[2] * aR[6 + j]);
     if (s > margin) return 0;
-    if (s > best) { best = s; code = 3 + j; }
+    if (s > best + BB_TIE) { best = s; code = 3 + j; }   /* parallel faces tie up to rounding: box 1 keeps the reference face */
   }
   double best_edge = -1e300; int ecode = -1;
   for (int i = 0; i < 3; i++) for (int j = 0; j < 3; j++) { /* edge i of box1 x edge j of box2, in box-1 coordinates */
@@ -643,6 +644,8 @@ static int box_box(const double* p1, const double* m1, const double* s1, const d
       const double *A = poly[v], *Bp = poly[(v + 1) % np];
       double da = (A[0] - pa[0]) * ax[0] + (A[1] - pa[1]) * ax[1] + (A[2] - pa[2]) * ax[2] - lim;
       double db = (Bp[0] - pa[0]) * ax[0] + (Bp[1] - pa[1]) * ax[1] + (Bp[2] - pa[2]) * ax[2] - lim;
+      if (fabs(da) < BB_TIE) da = 0;   /* a vertex within a micron of the clip plane lies ON it (aligned boxes: gripper pads, cube on cube) */
+      if (fabs(db) < BB_TIE) db = 0;
       if (da <= 0) { memcpy(tmp[nn++], A, 24); }
       if ((da < 0 && db > 0) || (da > 0 && db < 0)) { double s = da / (da - db); for (int k = 0; k < 3; k++) tmp[nn][k] = A[k] + s * (Bp[k] - A[k]); nn++; }
     }
