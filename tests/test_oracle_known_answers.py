@@ -310,3 +310,181 @@ def test_halton_rollout_raises_no_flags(model):
         o.step()
     assert np.isfinite(o.qpos).all() and np.isfinite(o.qvel).all() and np.isfinite(o.qacc).all()
     assert np.abs(o.qvel).max() < 50
+
+
+# ------------------------------------------------------------------------------------------ closed-form pins (SURVEY 8c fixture 2)
+def closed_form_penetration(m=0.1, n_contacts=4, g=G, solref=(0.02, 1.0), solimp=(0.9, 0.95, 0.001, 0.5, 2.0), invweight=None):
+    """Steady-state penetration r of a body of mass m resting on n contacts with MuJoCo's soft-constraint model (App. B item 9):
+    each normal row carries f = D K imp r with D = 1/R, R = (1 - imp)/imp * diagApprox, diagApprox = 1/m (the table is static),
+    K = 1/(dmax^2 timeconst^2 dampratio^2), imp = imp(r) from solimp  =>  r = m g (1 - imp) diagApprox / (n K imp^2), a fixed point."""
+    d0, d1, w, mid, pw = solimp
+    K = 1 / (d1 * d1 * solref[0] ** 2 * solref[1] ** 2)
+    diag = (1 / m) if invweight is None else invweight
+    r = 1e-4
+    for _ in range(200):
+        x = abs(r) / w
+        y = 1.0 if x >= 1 else (x if pw == 1 else (x ** pw / mid ** (pw - 1) if x <= mid else 1 - (1 - x) ** pw / (1 - mid) ** (pw - 1)))
+        imp = d0 + y * (d1 - d0)
+        r = m * g * (1 - imp) * diag / (n_contacts * K * imp * imp)
+    return r
+
+
+def test_steady_state_penetration_is_the_solref_solimp_closed_form(model):
+    """Pins K, imp(r), R = (1 - imp)/imp * diagApprox and geom_invweight0 jointly: the resting depth of the cube equals the fixed point
+    of r = m g (1 - imp(r)) / (m 4 K imp(r)^2) with the default solref (0.02, 1) / solimp (0.9, 0.95, 0.001, 0.5, 2)."""
+    blob = model[0]
+    o, st, size, active = _fresh(blob, seed=2)
+    o.set_option("full_contacts", 0)
+    for _ in range(3000):
+        o.step_frozen_arm()
+    want = closed_form_penetration()
+    assert 1.0e-4 < want < 1.2e-4
+    for p in range(int(active.sum())):
+        pen = 0.4 + size[p][2] - o.qpos[15 + 7 * p + 2]
+        assert abs(pen - want) < 1e-9 * want + 1e-12, (pen, want)
+
+
+def _incline(blob, tan_theta, mu, steps=400):
+    import blobtools as bt
+    th = np.arctan(tan_theta)
+    o = Oracle(bt.tilted(blob, th, mu))
+    st, size, active = sc.make_states(1, seed=2)
+    active[0, 1:] = 0
+    st[0, 15:18] = (0.45, 0.0, 0.4 + size[0, 0, 2] - 1e-4); st[0, 18:22] = (1, 0, 0, 0)
+    sc.oracle_load(o, st[0], size[0], active[0]); o.set_option("full_contacts", 0)
+    for _ in range(steps):
+        o.step_frozen_arm()
+    return o.qpos[15] - 0.45, o.qvel[15], th
+
+
+def test_incline_sticks_iff_tan_theta_below_mu(model):
+    """Cube on the table under gravity tilted by theta (mu = 0.5 < 1 so that it slides before it tips): it stays put for
+    tan(theta) < mu (soft friction rows: a creep of ~0.1 mm/s, no more) and slides with a = g (sin - mu cos) for tan(theta) > mu."""
+    blob = model[0]
+    t = 0.4
+    for tan_theta in (0.364, 0.45):
+        x, v, th = _incline(blob, tan_theta, 0.5)
+        assert abs(x) < 2e-4 and abs(v) < 1e-3, (tan_theta, x, v)
+    for tan_theta in (0.55, 0.7):
+        x, v, th = _incline(blob, tan_theta, 0.5)
+        a = G * (np.sin(th) - 0.5 * np.cos(th))
+        assert abs(x - 0.5 * a * t * t) < 0.05 * 0.5 * a * t * t, (tan_theta, x, 0.5 * a * t * t)
+
+
+def pendulum_setup(blob, dof=1):
+    """One-dof physical pendulum: the undamped arm with every dof but `dof` locked by a 1e8 armature.  -> (blob, q*, T) with q* the
+    stable equilibrium and T = 2 pi sqrt(I / kappa), I = qM[dof, dof] (pinned by test_mass_matrix_from_independent_jacobians),
+    kappa = d2 PE / dq2 from finite differences of sum_b m_b g z_com,b."""
+    import blobtools as bt
+    b = bt.free_arm(blob, lock_all_but=dof)
+    counts, opts, arrays = B.unpack(b)
+    mass = arrays["body_mass"]
+    o = Oracle(b)
+    st, size, active = sc.make_states(1, seed=2)
+    active[0, :] = 0; st[0, :15] = 0
+
+    def pe(q):
+        s = st[0].copy(); s[dof] = q
+        sc.oracle_load(o, s, size[0], active[0]); o.forward()
+        return float((mass * G * o.xipos[:, 2]).sum())
+    qs = np.linspace(-np.pi, np.pi, 721)
+    q0 = qs[int(np.argmin([pe(q) for q in qs]))]
+    eps, kappa = 1e-4, 0.0
+    for _ in range(30):
+        ep, em, e0 = pe(q0 + eps), pe(q0 - eps), pe(q0)
+        kappa = (ep - 2 * e0 + em) / eps ** 2
+        q0 -= (ep - em) / (2 * eps) / kappa
+    pe(q0)
+    inertia = o.qm[dof, dof]
+    return b, st[0], size[0], active[0], q0, 2 * np.pi * np.sqrt(inertia / kappa)
+
+
+def measure_period(step, get_q, q0, T, h=H):
+    """mean time between downward zero crossings of q - q0 over ~3 periods (linear interpolation inside the step)"""
+    ts, prev, t = [], get_q() - q0, 0.0
+    for _ in range(int(3.3 * T / h)):
+        step(); t += h
+        cur = get_q() - q0
+        if prev > 0 and cur <= 0:
+            ts.append(t - h + h * prev / (prev - cur))
+        prev = cur
+    return float(np.mean(np.diff(ts)))
+
+
+def test_pendulum_period(model):
+    """Small oscillation (0.02 rad) of the locked-up arm about joint2: period = 2 pi sqrt(I / kappa) (1 + a^2/16), to 1e-5."""
+    b, st, size, active, q0, T = pendulum_setup(model[0])
+    o = Oracle(b)
+    amp = 0.02
+    s = st.copy(); s[1] = q0 + amp
+    sc.oracle_load(o, s, size, active)
+    got = measure_period(o.step, lambda: o.qpos[1], q0, T)
+    assert abs(got / (T * (1 + amp * amp / 16)) - 1) < 1e-5, (got, T)
+
+
+def _free_arm_energy(blob, h, integrator, T=0.5):
+    import blobtools as bt
+    b = bt.free_arm(blob, timestep=h, integrator=integrator)
+    counts, opts, arrays = B.unpack(b)
+    mass = arrays["body_mass"]
+    o = Oracle(b)
+    st, size, active = sc.make_states(1, seed=2)
+    active[0, :] = 0
+    st[0, :7] = sc.ARM_HOME; st[0, 7:15] = 0
+    st[0, sc.REC_QVEL:sc.REC_QVEL + 7] = [0.5, -0.4, 0.3, 0.6, -0.5, 0.4, 0.3]
+    sc.oracle_load(o, st[0], size[0], active[0])
+    E = []
+    for _ in range(int(round(T / h)) + 1):
+        o.forward()
+        v = o.qvel[:15]
+        E.append(0.5 * v @ o.qm[:15, :15] @ v + float((mass * G * o.xipos[:, 2]).sum()))
+        o.step()
+    E = np.array(E)
+    return float(np.abs(E - E[0]).max()), float(0.5 * v @ o.qm[:15, :15] @ v)
+
+
+@pytest.mark.parametrize("integrator", [B.INT_IMPLICITFAST, B.INT_EULER])
+def test_energy_drift_of_the_undamped_arm_is_first_order_in_h(model, integrator):
+    """No damping, springs, limits, equalities, contacts or actuation: E = 1/2 v'Mv + sum m g z is conserved by the continuous system;
+    the semi-implicit integrator's error is O(h) -- halving h halves the worst deviation (both integrators reduce to the same scheme)."""
+    d1, ke = _free_arm_energy(model[0], 1e-3, integrator)
+    d2, _ = _free_arm_energy(model[0], 5e-4, integrator)
+    assert d1 < 0.01 * ke
+    assert 1.8 < d1 / d2 < 2.2, (d1, d2)
+
+
+@pytest.mark.parametrize("integrator", [B.INT_IMPLICITFAST, B.INT_EULER])
+def test_integrator_matrix_against_numpy(model, integrator):
+    """mj_Euler: (M + h diag(damping)) qacc+ = qfrc_smooth + qfrc_constraint; implicitfast additionally subtracts
+    h * d(qfrc_actuator)/d(qvel) = -h * bias_vel * moment' moment of the affine gripper actuator wherever (i, j) lies in M's
+    sparsity pattern (App. B item 15).  qvel' = qvel + h qacc+, recomputed with numpy from the oracle's M and forces."""
+    import blobtools as bt
+    blob, counts, opts, arrays = model
+    b = bt.surgery(blob, opts=dict(integrator=integrator))
+    o, st, size, active = _fresh(b, seed=5)
+    o.qvel[:7] = np.linspace(-0.3, 0.3, 7); o.qvel[7] = 0.4; o.qvel[11] = 0.3
+    o.ctrl[:] = [3, -2, 1, 1, 0.5, -0.5, 0.2, 100]
+    o.set_option("full_contacts", 0)
+    o.forward()
+    nv = 15
+    M = o.qm[:nv, :nv].copy(); f = (o.qfrc_smooth + o.qfrc_constraint)[:nv].copy(); v0 = o.qvel[:nv].copy()
+    A = M + H * np.diag(arrays["dof_damping"][:nv])
+    if integrator == B.INT_IMPLICITFAST:
+        for a in range(counts["nu"]):
+            bv = arrays["act_bias"][a][2]
+            if bv == 0:
+                continue
+            for x in range(arrays["act_trnnum"][a]):
+                for y in range(arrays["act_trnnum"][a]):
+                    i, j = arrays["act_trndof"][a][x], arrays["act_trndof"][a][y]
+                    if M[i, j] != 0 or i == j:
+                        A[i, j] -= H * arrays["act_trncoef"][a][x] * arrays["act_trncoef"][a][y] * bv
+    want = v0 + H * np.linalg.solve(A, f)
+    o.step2()
+    assert np.abs(o.qvel[:nv] - want).max() < 1e-9 * max(1.0, np.abs(want).max())
+    # the two integrators really differ on this state (the drivers accelerate)
+    if integrator == B.INT_EULER:
+        o2, *_ = _fresh(blob, seed=5)
+        o2.qvel[:7] = np.linspace(-0.3, 0.3, 7); o2.qvel[7] = 0.4; o2.qvel[11] = 0.3
+        o2.ctrl[:] = [3, -2, 1, 1, 0.5, -0.5, 0.2, 100]; o2.set_option("full_contacts", 0); o2.step()
+        assert np.abs(o2.qvel[:nv] - o.qvel[:nv]).max() > 1e-4
