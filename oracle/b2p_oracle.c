@@ -35,7 +35,7 @@ struct orc_t {
   const int* hdr; const double* opt; const int* table;
   int nq, nv, nu, nbody, njnt, ngeom, nsite, neq, npair, nmesh, nprop;
   double timestep, gravity[3], impratio, tolerance, ls_tolerance, ccd_tolerance, meaninertia;
-  int iterations, ls_iterations, integrator, cone, ccd_iterations, full_contacts;
+  int iterations, ls_iterations, integrator, cone, ccd_iterations, full_contacts, solver;
   /* per-scene mutable model params (props) */
   double geom_size[3 * MAXGEOM], geom_rbound[MAXGEOM], body_mass[MAXBODY], body_inertia[3 * MAXBODY];
   double body_invweight0[2 * MAXBODY], geom_invweight0[2 * MAXGEOM], dof_invweight0[MAXNV];
@@ -231,7 +231,7 @@ void orc_set_prop(orc_t* o, int p, const double half[3], int active) {
 }
 void orc_set_option(orc_t* o, int what, double v) {
   if (what == 0) o->full_contacts = (int)v; else if (what == 1) o->integrator = (int)v;
-  else if (what == 2) o->tolerance = v; else if (what == 3) o->iterations = (int)v;
+  else if (what == 2) o->tolerance = v; else if (what == 3) o->iterations = (int)v; else if (what == 4) o->solver = (int)v;
 }
 int orc_dim(orc_t* o, int w) {
   int d[10] = {o->nq, o->nv, o->nu, o->nbody, o->ngeom, o->nsite, o->ncon, o->nefc, o->nprop, o->solver_iter};
@@ -1084,9 +1084,130 @@ static double total_cost_at(orc_t* o, const double* qacc, double* jar, double* M
   for (int i = 0; i < nv; i++) cost += 0.5 * (Ma[i] - o->qfrc_smooth[i]) * (qacc[i] - o->qacc_smooth[i]);
   return cost;
 }
+
+/* ------------------------------------------------------------------ PGS solver (App. B item 14): the DUAL of the problem Newton solves.
+ * minimise  1/2 f'(A + R)f + f'b   over  f in Omega,   A = J M^-1 J',  b = J qacc_smooth - aref,
+ * Omega: equality rows free, limit rows f >= 0, elliptic contacts f_n >= 0, sum_k (f_tk / friction_k)^2 <= f_n^2 (the TRUE friction
+ * cone; the primal solver works with the R-scaled cone and contact.mu instead).  Block Gauss-Seidel in MuJoCo's order: scalar rows
+ * exactly; a contact by (1) a move along the ray through its current force, (2) the normal alone when the force sits at the apex,
+ * else the friction components with the normal held fixed, a 2-variable QCQP (mju_QCQP2).  A second, independent minimiser of the
+ * same convex problem: agreement with Newton checks R, D, contact.mu and the cone zones jointly (SURVEY 8c fixture 3). */
+static void qcqp2(const double A[4], const double b[2], const double d[2], double r, double x[2]) {
+  /* min 1/2 x'Ax + x'b  s.t. (x0/d0)^2 + (x1/d1)^2 <= r^2 ; scale y = x/d */
+  double a00 = A[0] * d[0] * d[0], a01 = A[1] * d[0] * d[1], a11 = A[3] * d[1] * d[1], b0 = b[0] * d[0], b1 = b[1] * d[1];
+  double la = 0, y0 = 0, y1 = 0;
+  for (int it = 0; it < 40; it++) {
+    double m00 = a00 + la, m11 = a11 + la, det = m00 * m11 - a01 * a01;
+    if (det < 1e-300) break;
+    y0 = -(m11 * b0 - a01 * b1) / det; y1 = -(-a01 * b0 + m00 * b1) / det;
+    double val = y0 * y0 + y1 * y1 - r * r;
+    if (val < 1e-14 * (1 + r * r)) break;                       /* inside (la = 0) or on the boundary */
+    double z0 = (m11 * y0 - a01 * y1) / det, z1 = (-a01 * y0 + m00 * y1) / det;   /* (As + la I)^-1 y */
+    double deriv = -2 * (y0 * z0 + y1 * z1);
+    if (deriv > -1e-300) break;
+    la -= val / deriv;
+    if (la < 0) la = 0;
+  }
+  x[0] = y0 * d[0]; x[1] = y1 * d[1];
+}
+static void solve_pgs(orc_t* o) {
+  int nv = o->nv, n = o->nefc;
+  double* AR = (double*)calloc((size_t)n * n + (size_t)n * nv + 3 * (size_t)n, sizeof(double));
+  double *X = AR + (size_t)n * n, *b = X + (size_t)n * nv, *f = b + n, *res = f + n;
+  for (int r = 0; r < n; r++) {                                  /* X_r = M^-1 J_r' */
+    memcpy(X + (size_t)r * nv, o->efc_J + (size_t)r * nv, 8 * nv);
+    for (int i = 0; i < nv; i++) if (!o->dof_active[i]) X[(size_t)r * nv + i] = 0;
+    solve_tree(o, o->qLD, X + (size_t)r * nv);
+    for (int i = 0; i < nv; i++) if (!o->dof_active[i]) X[(size_t)r * nv + i] = 0;
+  }
+  for (int r = 0; r < n; r++) {
+    for (int c = 0; c < n; c++) { double v = 0; const double* J = o->efc_J + (size_t)c * nv; for (int i = 0; i < nv; i++) v += J[i] * X[(size_t)r * nv + i]; AR[(size_t)r * n + c] = v; }
+    AR[(size_t)r * n + r] += o->efc_R[r];
+    double v = 0; const double* J = o->efc_J + (size_t)r * nv; for (int i = 0; i < nv; i++) v += J[i] * o->qacc_smooth[i];
+    b[r] = v - o->efc_aref[r];
+  }
+  /* warm start: forces the primal map assigns to qacc_warmstart, if their dual cost beats f = 0 */
+  {
+    double* jar = res; double* Ma = (double*)calloc(nv, sizeof(double));
+    total_cost_at(o, o->qacc_warmstart, jar, Ma); free(Ma);
+    double c = 0;
+    for (int r = 0; r < n; r++) { double v = 0; for (int k = 0; k < n; k++) v += AR[(size_t)r * n + k] * o->efc_force[k]; c += o->efc_force[r] * (0.5 * v + b[r]); }
+    for (int r = 0; r < n; r++) f[r] = c < 0 ? o->efc_force[r] : 0;
+  }
+  double scale = 1 / (o->meaninertia * (nv > 1 ? nv : 1));
+  int it = 0;
+  for (; it < o->iterations; it++) {
+    double improvement = 0;
+    for (int r = 0; r < n; r++) {
+      int dim = 1;
+      if (o->efc_type[r] == ROW_CONTACT) dim = o->con[o->efc_id[r]].dim;
+      double old[6], rs[6];
+      for (int k = 0; k < dim; k++) { double v = b[r + k]; const double* a = AR + (size_t)(r + k) * n; for (int c = 0; c < n; c++) v += a[c] * f[c]; rs[k] = v; old[k] = f[r + k]; }
+      if (dim == 1) {
+        f[r] -= rs[0] / AR[(size_t)r * n + r];
+        if (o->efc_type[r] != ROW_EQ && f[r] < 0) f[r] = 0;
+      } else {
+        contact_t* c = &o->con[o->efc_id[r]];
+        double Ab[36];
+        for (int i = 0; i < dim; i++) for (int j = 0; j < dim; j++) Ab[i * dim + j] = AR[(size_t)(r + i) * n + r + j];
+        /* (1) ray update */
+        if (f[r] > MINVAL) {
+          double v1[6], den = 0, num = 0;
+          for (int i = 0; i < dim; i++) { v1[i] = 0; for (int j = 0; j < dim; j++) v1[i] += Ab[i * dim + j] * old[j]; }
+          for (int i = 0; i < dim; i++) { den += old[i] * v1[i]; num += old[i] * rs[i]; }
+          if (den >= MINVAL) {
+            double x = -num / den;
+            if (f[r] + x * old[0] < 0) x = -1;                  /* do not leave the cone through the apex */
+            for (int i = 0; i < dim; i++) f[r + i] += x * old[i];
+          }
+        }
+        /* residual of the block with the rest fixed: bc = rs - Ab * old ; current block value v */
+        double bc[6], v[6];
+        for (int i = 0; i < dim; i++) { v[i] = f[r + i]; bc[i] = rs[i]; for (int j = 0; j < dim; j++) bc[i] -= Ab[i * dim + j] * old[j]; }
+        if (v[0] < MINVAL) {
+          /* (2) at the apex the gradient of the block cost is bc.  The apex is optimal iff -bc has no component inside the cone;
+           * otherwise minimise along the projection d of -bc onto the cone (normal-only updates stall when the contact must start
+           * sliding: d then lies on the cone boundary, not on its axis) */
+          double mu1 = c->friction[0], an = -bc[0], bt[2] = {-bc[1], -bc[2]}, nb = sqrt(bt[0] * bt[0] + bt[1] * bt[1]), d[3] = {0, 0, 0};
+          if (nb <= mu1 * an) { d[0] = an; d[1] = bt[0]; d[2] = bt[1]; }
+          else if (mu1 * nb > -an) { d[0] = (an + mu1 * nb) / (1 + mu1 * mu1); d[1] = mu1 * d[0] * bt[0] / nb; d[2] = mu1 * d[0] * bt[1] / nb; }
+          double den = 0, num = 0;
+          for (int i = 0; i < 3; i++) { num += d[i] * bc[i]; for (int j = 0; j < 3; j++) den += d[i] * Ab[i * dim + j] * d[j]; }
+          double x = den > MINVAL ? -num / den : 0;
+          if (x < 0) x = 0;
+          for (int i = 0; i < 3; i++) { v[i] = x * d[i]; f[r + i] = v[i]; }
+        }
+        if (v[0] >= MINVAL) {                                   /* (3) friction with the normal fixed (QCQP) */
+          if (dim != 3) { fprintf(stderr, "orc: PGS handles condim 1 and 3 only\n"); }
+          double A2[4] = {Ab[1 * dim + 1], Ab[1 * dim + 2], Ab[2 * dim + 1], Ab[2 * dim + 2]};
+          double b2[2] = {bc[1] + Ab[1 * dim] * v[0], bc[2] + Ab[2 * dim] * v[0]}, d2[2] = {c->friction[0], c->friction[1]}, x2[2];
+          qcqp2(A2, b2, d2, v[0], x2);
+          f[r + 1] = x2[0]; f[r + 2] = x2[1];
+        }
+      }
+      /* cost change of this block: dc = 1/2 d'Ab d + d'rs */
+      double dc = 0;
+      for (int i = 0; i < dim; i++) { double di = f[r + i] - old[i]; dc += di * rs[i]; for (int j = 0; j < dim; j++) dc += 0.5 * di * AR[(size_t)(r + i) * n + r + j] * (f[r + j] - old[j]); }
+      if (dc > 1e-10) { for (int i = 0; i < dim; i++) f[r + i] = old[i]; dc = 0; }   /* never accept an increase */
+      improvement -= dc;
+      r += dim - 1;
+    }
+    o->solver_stats[0] = improvement * scale;
+    if (improvement * scale < o->tolerance) { it++; break; }
+  }
+  o->solver_iter = it;
+  memcpy(o->efc_force, f, 8 * n);
+  memset(o->qfrc_constraint, 0, 8 * nv);
+  for (int r = 0; r < n; r++) if (f[r] != 0) { const double* J = o->efc_J + (size_t)r * nv; for (int i = 0; i < nv; i++) o->qfrc_constraint[i] += J[i] * f[r]; }
+  for (int i = 0; i < nv; i++) o->qacc[i] = o->dof_active[i] ? o->qfrc_constraint[i] : 0;
+  solve_tree(o, o->qLD, o->qacc);
+  for (int i = 0; i < nv; i++) o->qacc[i] = o->dof_active[i] ? o->qacc[i] + o->qacc_smooth[i] : o->qacc_smooth[i];
+  free(AR);
+}
 static void fwd_constraint(orc_t* o) {
   int nv = o->nv; o->solver_iter = 0;
   if (o->nefc == 0) { memcpy(o->qacc, o->qacc_smooth, 8 * nv); memset(o->qfrc_constraint, 0, 8 * nv); return; }
+  if (o->solver == 1) { solve_pgs(o); return; }
   double* buf = (double*)calloc((size_t)2 * ORC_MAXEFC + 6 * MAXNV + MAXNV * MAXNV, sizeof(double));
   solver_t s; s.o = o; s.Jaref = buf; s.Jv = buf + ORC_MAXEFC; s.Ma = s.Jv + ORC_MAXEFC; s.Mv = s.Ma + MAXNV; s.search = s.Mv + MAXNV;
   s.grad = s.search + MAXNV; s.Mgrad = s.grad + MAXNV; s.H = s.Mgrad + MAXNV + MAXNV;

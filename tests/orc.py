@@ -99,7 +99,7 @@ class Oracle:
         self.L.orc_set_prop(self.h, p, a, int(active))
 
     def set_option(self, what, v):
-        self.L.orc_set_option(self.h, dict(full_contacts=0, integrator=1, tolerance=2, iterations=3)[what], float(v))
+        self.L.orc_set_option(self.h, dict(full_contacts=0, integrator=1, tolerance=2, iterations=3, solver=4)[what], float(v))
 
     def contacts(self):
         n = self.dim("ncon")
