@@ -68,9 +68,15 @@ def _cpu_worker(args):
     return steps, time.perf_counter() - t0
 
 
+CPU_BUILD = "gcc -O3 -march=native -DNDEBUG -DORC_FAST (oracle/Makefile: libb2p_oracle_fast.so; hill-climb hull support, OBB mid phase, sparse rows, no per-step malloc)"
+
+
 def cpu_baseline(seconds: float, osc: bool, cores: int | None = None):
+    """The CPU arm: the oracle's TIMING build (same source as the strict parity build, same results), one scene per process on every host core."""
     cores = cores or os.cpu_count() or 1
-    subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
+    os.environ["ORC_FAST"] = "1"                      # inherited by the spawned workers: tests/orc.py loads libb2p_oracle_fast.so
+    # -march=native: always rebuilt on the machine that times it (the .so in the snapshot was built on another CPU)
+    subprocess.check_call(["make", "-B", "-C", os.path.join(ROOT, "oracle"), "libb2p_oracle_fast.so"], stdout=subprocess.DEVNULL)
     with mp.get_context("spawn").Pool(cores) as pool:
         res = pool.map(_cpu_worker, [(i, seconds, osc) for i in range(cores)])
     return sum(s / t for s, t in res), cores
@@ -104,6 +110,12 @@ class ClockSampler(threading.Thread):
 
 
 # ------------------------------------------------------------------------------------------ arms
+def workload_config(args, wl):
+    """the keys that NAME the workload: identical in both arms (the driver compares them)"""
+    return {"workload": args.workload + ": " + wl["desc"], "envs_per_gpu": args.envs or wl["envs"], "control_ticks_per_launch": args.ticks,
+            "physics_steps_per_launch": args.ticks * CONTROL_STEPS}
+
+
 def run_reference(args, wl):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
@@ -115,10 +127,10 @@ def run_reference(args, wl):
         if i >= args.warmup:
             vals.append(v)
     value = sum(vals) / len(vals)
-    sample = "%d processes x %.1f s each of the same scenes/targets, one env per process (oracle C port of mj_step + OSC; MuJoCo not installable)" % (cores, per_step_s)
+    sample = "%d processes x %.1f s each of the same scenes/targets, one env per process (oracle C port of mj_step + OSC, %s; MuJoCo not installable)" % (cores, per_step_s, CPU_BUILD)
     line = {"impl": "reference", "metric": "env-steps/sec (physics+OSC)" if wl["osc"] else "env-steps/sec (physics only)", "value": value, "unit": "env-steps/s",
             "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": per_step_s * 1e3, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": {"workload": args.workload + ": " + wl["desc"]},
+            "vs_baseline": None, "dtype": "f64", "data": "synthetic", "config": workload_config(args, wl),
             "cpu_baseline": {"value": value, "unit": "env-steps/s", "cores": cores, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": "env-steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     print(json.dumps(line), flush=True)
@@ -245,10 +257,9 @@ def run_ours(args, wl):
     h_gr = [torch.tensor(g).pin_memory() for _, g in tgs]
     d_tg = [t.to(dev) for t in h_tg]; d_gr = [g.to(dev) for g in h_gr]
     h_state = torch.empty_like(p.state, device="cpu").pin_memory(); h_conv = torch.empty(n, dtype=torch.uint8).pin_memory()
-    o_bias = None
     if not wl["osc"]:
-        from orc import Oracle
-        o = Oracle(sc.default_blob()); sc.oracle_load(o, st[0], size[0], active[0]); o.step1(); o_bias = o.qfrc_bias[:7].copy()
+        p.forward(full_contacts=False); torch.cuda.synchronize()
+        o_bias = p.data.qfrc_bias[0, :7].cpu().numpy().astype(np.float64)        # gravity load of the home pose: the kernel's own qfrc_bias
         ctrls = [torch.tensor(sc.halton_ctrl(min(n, 256), i, o_bias), dtype=dtype, device=dev).repeat((n + 255) // 256, 1)[:n].contiguous() for i in range(n_t)]
         h_ctrl = [c.cpu().pin_memory() for c in ctrls]
 
@@ -324,8 +335,8 @@ def run_ours(args, wl):
         line = {"metric": "env-steps/sec (physics+OSC)" if wl["osc"] else "env-steps/sec (physics only)", "value": value, "unit": "env-steps/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms.item() / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": wl["dtype"], "data": "synthetic",
-                "config": {"workload": args.workload + ": " + wl["desc"], "envs_per_gpu": n, "control_ticks_per_launch": ticks, "physics_steps_per_launch": steps_per_launch,
-                           "l2": "flushed between timed iterations (192 MiB fill, untimed)", "launch": p.launch_info(), "wall_s_incl_flush": wall,
+                "config": {**workload_config(args, wl),
+                           "l2": "flushed between timed iterations (192 MiB fill, untimed); the e2e leg runs back to back without the flush", "launch": p.launch_info(), "wall_s_incl_flush": wall,
                            "episode_stats": {"converged_envs": stats[0].item(), "envs": stats[1].item(), "flagged_envs": stats[2].item(),
                                              "flags": {k: stats[3 + i].item() for i, k in enumerate(FLAG_NAMES)}}},
                 "clocks": sampler.summary(), "gpu_launches": int(launches + order_launches) * world,
@@ -337,7 +348,7 @@ def run_ours(args, wl):
         if world == 1 and not args.no_cpu:
             v, cores = cpu_baseline(args.cpu_seconds, wl["osc"])
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
-                                    "sample": "%d processes x %.0f s, one env per process, same scene/target distribution (oracle C port; MuJoCo not installable here)" % (cores, args.cpu_seconds)}
+                                    "sample": "%d processes x %.0f s, one env per process, same scene/target distribution (oracle C port, %s; MuJoCo not installable here)" % (cores, args.cpu_seconds, CPU_BUILD)}
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()

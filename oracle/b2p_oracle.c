@@ -55,6 +55,8 @@ struct orc_t {
   contact_t con[ORC_MAXCON]; int ncon;
   int nefc, efc_type[ORC_MAXEFC], efc_id[ORC_MAXEFC], efc_state[ORC_MAXEFC];
   double* efc_J; /* nefc x nv dense */
+  int efc_nnz[ORC_MAXEFC]; unsigned char* efc_ind; /* per row: indices of the non-zero Jacobian entries (ORC_MAXEFC x MAXNV) */
+  double *jacbuf, *solbuf; /* scratch of make_constraint (4 x 3 x nv) and of the solver, allocated once */
   double efc_pos[ORC_MAXEFC], efc_margin[ORC_MAXEFC], efc_D[ORC_MAXEFC], efc_R[ORC_MAXEFC], efc_aref[ORC_MAXEFC];
   double efc_vel[ORC_MAXEFC], efc_force[ORC_MAXEFC], efc_diagApprox[ORC_MAXEFC], efc_KBIP[4 * ORC_MAXEFC];
   double solver_stats[4]; int solver_iter;
@@ -213,12 +215,15 @@ orc_t* orc_create(const void* blob, size_t nbytes) {
   for (int p = 0; p < o->nprop; p++) { memcpy(o->prop_size + 3 * p, o->geom_size + 3 * pg[p], 24); o->prop_active[p] = 1; }
   apply_prop_params(o);
   o->efc_J = (double*)calloc((size_t)ORC_MAXEFC * MAXNV, sizeof(double));
+  o->efc_ind = (unsigned char*)calloc((size_t)ORC_MAXEFC * MAXNV, 1);
+  o->jacbuf = (double*)calloc((size_t)12 * MAXNV, sizeof(double));
+  o->solbuf = (double*)calloc((size_t)2 * ORC_MAXEFC + 8 * MAXNV + MAXNV * MAXNV, sizeof(double));
   double g[6] = {350, 20, 500, 100, 200, 30}, q0[7] = {0, -0.785, 0, -2.356, 0, 1.571, 0.785};
   orc_osc_config(o, g, q0, 5e-3, 68e-3);
   orc_reset(o);
   return o;
 }
-void orc_destroy(orc_t* o) { if (o) { free(o->efc_J); free(o->blob); free(o); } }
+void orc_destroy(orc_t* o) { if (o) { free(o->efc_J); free(o->efc_ind); free(o->jacbuf); free(o->solbuf); free(o->blob); free(o); } }
 void orc_reset(orc_t* o) {
   memcpy(o->qpos, FD(o, B2PM_F_QPOS0), 8 * o->nq);
   memset(o->qvel, 0, sizeof o->qvel); memset(o->ctrl, 0, sizeof o->ctrl);
@@ -398,24 +403,39 @@ static void jac_point(orc_t* o, int body, const double* point, double* jacp, dou
 }
 
 /* ------------------------------------------------------------------ collision */
-typedef struct { const double* pos; const double* mat; int type; const double* size; const double* vert; int nvert; double margin; } cobj_t;
+typedef struct { const double* pos; const double* mat; int type; const double* size; const double* vert; int nvert; double margin;
+                 const int *nbradr, *nbrnum, *nbr; int cur; } cobj_t;   /* hull graph (mesh-local indices) + warm-start vertex: timing build only */
 
-/* support point of a box / convex mesh in world direction dir (|dir|=1), inflated by margin/2 (App. B item 12) */
-static void support(const cobj_t* c, const double* dir, double* res) {
+/* support point of a box / convex mesh in world direction dir (|dir|=1), inflated by margin/2 (App. B item 12).
+ * Strict build: exhaustive search over the hull vertices.  Timing build (-DORC_FAST, bench.py's CPU arm): hill climbing over the
+ * hull's vertex graph with a warm start inside one query, which is what MuJoCo does for meshes that carry graph data; on a convex
+ * hull both reach the same maximum. */
+static void support(cobj_t* c, const double* dir, double* res) {
   double ld[3], lp[3];
   mulmatTvec3(ld, c->mat, dir);
   if (c->type == B2P_GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? c->size[k] : -c->size[k];
   } else {
+#ifdef ORC_FAST
+    int v = c->cur; double bd = dot3(c->vert + 3 * v, ld);
+    for (;;) {
+      int nb = v;
+      for (int q = c->nbradr[v]; q < c->nbradr[v] + c->nbrnum[v]; q++) { int u = c->nbr[q]; double d = dot3(c->vert + 3 * u, ld); if (d > bd) { bd = d; nb = u; } }
+      if (nb == v) break;
+      v = nb;
+    }
+    c->cur = v; memcpy(lp, c->vert + 3 * v, 24);
+#else
     int best = 0; double bd = -1e300;
     for (int i = 0; i < c->nvert; i++) { double d = dot3(c->vert + 3 * i, ld); if (d > bd) { bd = d; best = i; } }
     memcpy(lp, c->vert + 3 * best, 24);
+#endif
   }
   mulmatvec3(res, c->mat, lp);
   for (int k = 0; k < 3; k++) res[k] += c->pos[k] + 0.5 * c->margin * dir[k];
 }
 typedef struct { double v[3], v1[3], v2[3]; } sup_t;
-static void mink_support(const cobj_t* a, const cobj_t* b, const double* dir, sup_t* s) {
+static void mink_support(cobj_t* a, cobj_t* b, const double* dir, sup_t* s) {
   double nd[3] = {-dir[0], -dir[1], -dir[2]};
   support(a, dir, s->v1); support(b, nd, s->v2);
   for (int k = 0; k < 3; k++) s->v[k] = s->v1[k] - s->v2[k];
@@ -457,7 +477,7 @@ static double point_tri_dist2(const double* a, const double* b, const double* c,
 }
 /* Minkowski Portal Refinement after libccd's ccdMPRPenetration (what mjc_Convex calls in 3.2.x).
  * returns 1 and (depth, dir [obj1->obj2], pos) if the inflated shapes intersect */
-static int mpr_penetration(const cobj_t* o1, const cobj_t* o2, int maxiter, double tol, double* depth, double* dir, double* pos) {
+static int mpr_penetration(cobj_t* o1, cobj_t* o2, int maxiter, double tol, double* depth, double* dir, double* pos) {
   sup_t p[4], v4; double d[3], va[3], vb[3];
   /* discoverPortal */
   for (int k = 0; k < 3; k++) { p[0].v1[k] = o1->pos[k]; p[0].v2[k] = o2->pos[k]; p[0].v[k] = p[0].v1[k] - p[0].v2[k]; }
@@ -705,15 +725,35 @@ static void collision(orc_t* o) {
     } else {
       double dif[3] = {x2[0] - x1[0], x2[1] - x1[1], x2[2] - x1[2]};
       if (norm3(dif) > o->geom_rbound[g1] + o->geom_rbound[g2] + md) continue;
+#ifdef ORC_FAST
+      { /* mid phase of the timing build: the geoms' oriented bounding boxes along their 6 face normals (conservative: never drops a contact) */
+        const double* ab = FD(o, B2PM_F_GEOM_AABB);
+        const double *c1 = ab + 6 * g1, *c2 = ab + 6 * g2, *h1 = gprop[g1] >= 0 ? o->geom_size + 3 * g1 : ab + 6 * g1 + 3, *h2 = gprop[g2] >= 0 ? o->geom_size + 3 * g2 : ab + 6 * g2 + 3;
+        double w1[3], w2[3], t[3], sep = 0; mulmatvec3(w1, m1, c1); mulmatvec3(w2, m2, c2);
+        for (int k = 0; k < 3; k++) t[k] = (x2[k] + w2[k]) - (x1[k] + w1[k]);
+        for (int i = 0; i < 3 && !sep; i++) {
+          double ti = t[0] * m1[i] + t[1] * m1[3 + i] + t[2] * m1[6 + i], r = h1[i];
+          for (int j = 0; j < 3; j++) r += h2[j] * fabs(m1[i] * m2[j] + m1[3 + i] * m2[3 + j] + m1[6 + i] * m2[6 + j]);
+          if (fabs(ti) > r + md + 1e-6) sep = 1;
+        }
+        for (int j = 0; j < 3 && !sep; j++) {
+          double tj = t[0] * m2[j] + t[1] * m2[3 + j] + t[2] * m2[6 + j], r = h2[j];
+          for (int i = 0; i < 3; i++) r += h1[i] * fabs(m1[i] * m2[j] + m1[3 + i] * m2[3 + j] + m1[6 + i] * m2[6 + j]);
+          if (fabs(tj) > r + md + 1e-6) sep = 1;
+        }
+        if (sep) continue;
+      }
+#endif
       int convex = 1;
       if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) {
         n = box_box(x1, m1, o->geom_size + 3 * g1, x2, m2, o->geom_size + 3 * g2, md, raw);
         convex = (n < 0); if (n < 0) n = 0;
       }
       if (convex) {
-        cobj_t a = {x1, m1, t1, o->geom_size + 3 * g1, NULL, 0, md}, b = {x2, m2, t2, o->geom_size + 3 * g2, NULL, 0, md};
-        if (t1 == B2P_GEOM_MESH) { a.vert = mvert + 3 * vadr[gmesh[g1]]; a.nvert = vnum[gmesh[g1]]; }
-        if (t2 == B2P_GEOM_MESH) { b.vert = mvert + 3 * vadr[gmesh[g2]]; b.nvert = vnum[gmesh[g2]]; }
+        cobj_t a = {x1, m1, t1, o->geom_size + 3 * g1, NULL, 0, md, NULL, NULL, NULL, 0}, b = {x2, m2, t2, o->geom_size + 3 * g2, NULL, 0, md, NULL, NULL, NULL, 0};
+        const int *nadr = FI(o, B2PM_F_MESH_NBRADR), *nnum = FI(o, B2PM_F_MESH_NBRNUM), *nbr = FI(o, B2PM_F_MESH_NBR);
+        if (t1 == B2P_GEOM_MESH) { int v0 = vadr[gmesh[g1]]; a.vert = mvert + 3 * v0; a.nvert = vnum[gmesh[g1]]; a.nbradr = nadr + v0; a.nbrnum = nnum + v0; a.nbr = nbr; }
+        if (t2 == B2P_GEOM_MESH) { int v0 = vadr[gmesh[g2]]; b.vert = mvert + 3 * v0; b.nvert = vnum[gmesh[g2]]; b.nbradr = nadr + v0; b.nbrnum = nnum + v0; b.nbr = nbr; }
         double depth, dir[3], pos[3];
         if (mpr_penetration(&a, &b, o->ccd_iterations, o->ccd_tolerance, &depth, dir, pos) && depth >= 0) {
           raw[0].dist = md - depth; memcpy(raw[0].normal, dir, 24); memcpy(raw[0].pos, pos, 24); n = 1;
@@ -768,7 +808,7 @@ static void finish_row(orc_t* o, int r, const double* solref_in, const double* s
 }
 static void make_constraint(orc_t* o) {
   int nv = o->nv;
-  double* jp1 = (double*)malloc(sizeof(double) * 3 * nv * 4); double *jp2 = jp1 + 3 * nv, *jr1 = jp2 + 3 * nv, *jr2 = jr1 + 3 * nv;
+  double* jp1 = o->jacbuf; double *jp2 = jp1 + 3 * nv, *jr1 = jp2 + 3 * nv, *jr2 = jr1 + 3 * nv;
   o->nefc = 0;
   /* equality */
   const int *et = FI(o, B2PM_F_EQ_TYPE), *e1 = FI(o, B2PM_F_EQ_OBJ1ID), *e2 = FI(o, B2PM_F_EQ_OBJ2ID);
@@ -839,15 +879,24 @@ static void make_constraint(orc_t* o) {
       c->mu = c->friction[0] * sqrt(o->efc_R[r0 + 1] / o->efc_R[r0]);
     }
   }
-  for (int r = 0; r < o->nefc; r++) o->efc_D[r] = 1 / o->efc_R[r];
-  free(jp1);
+  for (int r = 0; r < o->nefc; r++) {
+    o->efc_D[r] = 1 / o->efc_R[r];
+    const double* J = o->efc_J + (size_t)r * nv; unsigned char* ind = o->efc_ind + (size_t)r * MAXNV; int n = 0;
+    for (int i = 0; i < nv; i++) if (J[i] != 0) ind[n++] = (unsigned char)i;
+    o->efc_nnz[r] = n;
+  }
+}
+/* J_r . x over the row's non-zero entries (same summation order as the dense loop: skipped terms are exact zeros) */
+static double row_dot(const orc_t* o, int r, const double* x) {
+  const double* J = o->efc_J + (size_t)r * o->nv; const unsigned char* ind = o->efc_ind + (size_t)r * MAXNV; double v = 0;
+  for (int k = 0; k < o->efc_nnz[r]; k++) v += J[ind[k]] * x[ind[k]];
+  return v;
 }
 /* mj_referenceConstraint: aref = -B*vel - K*imp*(pos-margin) */
 static void reference_constraint(orc_t* o) {
   int nv = o->nv;
   for (int r = 0; r < o->nefc; r++) {
-    double v = 0; const double* J = o->efc_J + (size_t)r * nv;
-    for (int i = 0; i < nv; i++) v += J[i] * o->qvel[i];
+    double v = row_dot(o, r, o->qvel);
     o->efc_vel[r] = v;
     o->efc_aref[r] = -o->efc_KBIP[4 * r + 1] * v - o->efc_KBIP[4 * r] * o->efc_KBIP[4 * r + 2] * (o->efc_pos[r] - o->efc_margin[r]);
   }
@@ -966,7 +1015,8 @@ static double constraint_update(orc_t* o, const double* jar, double* H) {
           for (int a = 0; a < dim; a++) for (int b = 0; b < dim; b++) {
             double h = hl[a * dim + b]; if (h == 0) continue;
             const double *Ja = o->efc_J + (size_t)(r + a) * nv, *Jb = o->efc_J + (size_t)(r + b) * nv;
-            for (int i = 0; i < nv; i++) { if (Ja[i] == 0) continue; double t = h * Ja[i]; for (int j = 0; j < nv; j++) H[i * nv + j] += t * Jb[j]; }
+            const unsigned char *ia = o->efc_ind + (size_t)(r + a) * MAXNV, *ib = o->efc_ind + (size_t)(r + b) * MAXNV;
+            for (int x = 0; x < o->efc_nnz[r + a]; x++) { int i = ia[x]; double t = h * Ja[i]; double* Hi = H + i * nv; for (int y = 0; y < o->efc_nnz[r + b]; y++) Hi[ib[y]] += t * Jb[ib[y]]; }
           }
         }
       }
@@ -995,11 +1045,11 @@ static void solver_update(solver_t* s, const double* qacc) {
   memcpy(s->H, o->qM, 8 * nv * nv);
   double cost = constraint_update(o, s->Jaref, s->H);
   for (int r = 0; r < o->nefc; r++) if (o->efc_state[r] == ST_QUADRATIC) {
-    const double* J = o->efc_J + (size_t)r * nv; double D = o->efc_D[r];
-    for (int i = 0; i < nv; i++) { if (J[i] == 0) continue; double t = D * J[i]; for (int j = 0; j < nv; j++) s->H[i * nv + j] += t * J[j]; }
+    const double* J = o->efc_J + (size_t)r * nv; double D = o->efc_D[r]; const unsigned char* ind = o->efc_ind + (size_t)r * MAXNV; int nz = o->efc_nnz[r];
+    for (int a = 0; a < nz; a++) { int i = ind[a]; double t = D * J[i]; double* Hi = s->H + i * nv; for (int b = 0; b < nz; b++) Hi[ind[b]] += t * J[ind[b]]; }
   }
   memset(o->qfrc_constraint, 0, 8 * nv);
-  for (int r = 0; r < o->nefc; r++) if (o->efc_force[r] != 0) { const double* J = o->efc_J + (size_t)r * nv; for (int i = 0; i < nv; i++) o->qfrc_constraint[i] += J[i] * o->efc_force[r]; }
+  for (int r = 0; r < o->nefc; r++) if (o->efc_force[r] != 0) { const double* J = o->efc_J + (size_t)r * nv; const unsigned char* ind = o->efc_ind + (size_t)r * MAXNV; for (int k = 0; k < o->efc_nnz[r]; k++) o->qfrc_constraint[ind[k]] += J[ind[k]] * o->efc_force[r]; }
   double gauss = 0;
   for (int i = 0; i < nv; i++) { gauss += 0.5 * (s->Ma[i] - o->qfrc_smooth[i]) * (qacc[i] - o->qacc_smooth[i]); s->grad[i] = s->Ma[i] - o->qfrc_smooth[i] - o->qfrc_constraint[i]; }
   s->cost = cost + gauss;
@@ -1048,7 +1098,7 @@ static double line_search(solver_t* s) {
   if (snorm < MINVAL) return 0;
   double gtol = o->tolerance * o->ls_tolerance * snorm / s->scale;
   mul_M(o, s->Mv, s->search);
-  for (int r = 0; r < o->nefc; r++) { double v = 0; const double* J = o->efc_J + (size_t)r * nv; for (int i = 0; i < nv; i++) v += J[i] * s->search[i]; s->Jv[r] = v; }
+  for (int r = 0; r < o->nefc; r++) s->Jv[r] = row_dot(o, r, s->search);
   double g1 = 0, g2 = 0, g0 = 0;
   for (int i = 0; i < nv; i++) { g1 += s->search[i] * (s->Ma[i] - o->qfrc_smooth[i]); g2 += 0.5 * s->search[i] * s->Mv[i]; g0 += 0.5 * (s->Ma[i] - o->qfrc_smooth[i]) * (o->qacc[i] - o->qacc_smooth[i]); }
   s->quadGauss[0] = g0; s->quadGauss[1] = g1; s->quadGauss[2] = g2;
@@ -1078,7 +1128,7 @@ static double line_search(solver_t* s) {
 }
 static double total_cost_at(orc_t* o, const double* qacc, double* jar, double* Ma) {
   int nv = o->nv;
-  for (int r = 0; r < o->nefc; r++) { double v = 0; const double* J = o->efc_J + (size_t)r * nv; for (int i = 0; i < nv; i++) v += J[i] * qacc[i]; jar[r] = v - o->efc_aref[r]; }
+  for (int r = 0; r < o->nefc; r++) jar[r] = row_dot(o, r, qacc) - o->efc_aref[r];
   mul_M(o, Ma, qacc);
   double cost = constraint_update(o, jar, NULL);
   for (int i = 0; i < nv; i++) cost += 0.5 * (Ma[i] - o->qfrc_smooth[i]) * (qacc[i] - o->qacc_smooth[i]);
@@ -1208,7 +1258,7 @@ static void fwd_constraint(orc_t* o) {
   int nv = o->nv; o->solver_iter = 0;
   if (o->nefc == 0) { memcpy(o->qacc, o->qacc_smooth, 8 * nv); memset(o->qfrc_constraint, 0, 8 * nv); return; }
   if (o->solver == 1) { solve_pgs(o); return; }
-  double* buf = (double*)calloc((size_t)2 * ORC_MAXEFC + 6 * MAXNV + MAXNV * MAXNV, sizeof(double));
+  double* buf = o->solbuf; memset(buf, 0, sizeof(double) * ((size_t)2 * ORC_MAXEFC + 6 * MAXNV));
   solver_t s; s.o = o; s.Jaref = buf; s.Jv = buf + ORC_MAXEFC; s.Ma = s.Jv + ORC_MAXEFC; s.Mv = s.Ma + MAXNV; s.search = s.Mv + MAXNV;
   s.grad = s.search + MAXNV; s.Mgrad = s.grad + MAXNV; s.H = s.Mgrad + MAXNV + MAXNV;
   s.scale = 1 / (o->meaninertia * (nv > 1 ? nv : 1));
@@ -1233,7 +1283,6 @@ static void fwd_constraint(orc_t* o) {
     for (int i = 0; i < nv; i++) s.search[i] = -s.Mgrad[i];
   }
   o->solver_iter = it; o->solver_stats[2] = s.cost;
-  free(buf);
 }
 
 /* ------------------------------------------------------------------ pipeline */

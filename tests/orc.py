@@ -17,7 +17,8 @@ _lib = None
 def lib():
     global _lib
     if _lib is None:
-        so = os.path.join(ROOT, "oracle", "libb2p_oracle.so")
+        # ORC_FAST=1 selects the timing build (-O3 -march=native; bench.py's CPU arm); parity tests use the strict build
+        so = os.path.join(ROOT, "oracle", "libb2p_oracle_fast.so" if os.environ.get("ORC_FAST") == "1" else "libb2p_oracle.so")
         src = os.path.join(ROOT, "oracle", "b2p_oracle.c")
         if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
             subprocess.check_call(["make", "-C", os.path.join(ROOT, "oracle")], stdout=subprocess.DEVNULL)
