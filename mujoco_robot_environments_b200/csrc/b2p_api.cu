@@ -60,7 +60,7 @@ struct b2p_handle_s {
   DevModel<double> hmodel;
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
-  void* d_zero_ctrl; int* d_next_env;
+  void* d_zero_ctrl; int* d_next_env; void* d_jovf;
   const void* env_gains; const unsigned char* env_mask;
   int *d_work, *d_order; int work_steps, sort_queue;   // work_steps: physics steps behind d_work (0 = none yet)
 };
@@ -98,6 +98,7 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   h->out = h->own_out;
   CK(cudaMalloc(&h->d_next_env, sizeof(int)));
   CK(sizeof(T) == 8 ? configure_f64(h->device, h->n_env, &h->lg) : configure_f32(h->device, h->n_env, &h->lg));
+  CK(cudaMalloc(&h->d_jovf, (size_t)h->lg.grid * h->lg.warps_per_cta * Pool<T>::JP * sizeof(T)));   // Jacobian overflow: one area per resident warp
   CK(cudaMalloc(&h->d_work, (size_t)h->n_env * 4)); CK(cudaMemset(h->d_work, 0, (size_t)h->n_env * 4));
   CK(cudaMalloc(&h->d_order, (size_t)h->n_env * 4));
   { const char* sq = getenv("B2P_SORT_QUEUE"); h->sort_queue = sq ? atoi(sq) : (h->n_env > h->lg.grid * h->lg.warps_per_cta); }   // pays off once there is more than one round
@@ -109,7 +110,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.gains = (const T*)h->env_gains;
-  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span};
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf};
   a.work = h->d_work; a.order = nullptr;
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
@@ -163,7 +164,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;

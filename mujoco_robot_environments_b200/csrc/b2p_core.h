@@ -55,6 +55,7 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
   if (active) {
     PROF_COUNT(PF_NSTEP, 1)
     actuation_and_smooth(m, s, c);
+    NANCHK(1, s.qacc_smooth, m.nv)
   }
   PROF_ADD(PF_SMOOTH)
   csync(c, LK_SOLVE);

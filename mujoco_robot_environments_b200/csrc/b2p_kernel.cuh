@@ -21,10 +21,13 @@ namespace b2p {
 
 
 #ifndef B2P_WARPS_F32
-#define B2P_WARPS_F32 9
+#define B2P_WARPS_F32 12
 #endif
 template <typename T> struct KernelCfg { static constexpr int kWarps = B2P_WARPS_F32; static constexpr int kMinBlocks = 1; };
-template <> struct KernelCfg<double> { static constexpr int kWarps = 4; static constexpr int kMinBlocks = 1; };
+#ifndef B2P_WARPS_F64
+#define B2P_WARPS_F64 6
+#endif
+template <> struct KernelCfg<double> { static constexpr int kWarps = B2P_WARPS_F64; static constexpr int kMinBlocks = 1; };
 
 // ------------------------------------------------------------------------------------------ TMA / mbarrier helpers
 __device__ __forceinline__ unsigned smem_u32(const void* p) { return (unsigned)__cvta_generic_to_shared(p); }
@@ -77,6 +80,8 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   if (threadIdx.x == 0) { mbar_expect_tx(&sm.bar[0], kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar[0]); }
   mbar_wait(&sm.bar[0], 0);
   Scratch<T>& s = sm.scratch[warp];
+  if (lane == 0) s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP;
+  __syncwarp();
   unsigned long long* bar = &sm.bar[1 + warp];
   unsigned phase = 0;
   for (;;) {   // one round = one scene per warp; in lockstep mode the CTA's warps walk the round's stages together

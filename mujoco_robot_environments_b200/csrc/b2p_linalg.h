@@ -58,6 +58,12 @@ B2P_HD void sp_build_dense(SpStruct& st, int n, const Ctx& c) {
 B2P_HD bool sp_coupled(const SpStruct& st, int bi, int bj) { return bi == bj || ((st.later[bj] >> bi) & 1u); }   // bi >= bj
 
 // a block that is coupled to nothing (a prop resting on the table) is factored / solved by ONE lane in registers
+// Pivot floor of the Cholesky factorisations.  The Newton Hessian M + J'WJ carries cone blocks whose entries grow like 1/|tangential
+// residual|; in fp32 the rounding noise of such entries (1e-7 relative) can exceed the small pivots the light gripper links and
+// props contribute, and a pivot that comes out <= 0 used to be replaced by 1e-15 -- whose inverse square root (3e7) sent the Newton
+// direction to inf (2 of 17 000 fp32 data-generation episodes).  A pivot below 64 eps of its ORIGINAL diagonal entry is noise: it is
+// replaced by that bound, which keeps the factor finite and the direction a descent direction (the exact line search does the rest).
+template <typename T> B2P_HD T pivot_floor(T diag0) { const T f = 64 * Num<T>::eps() * fabs(diag0); return f > Num<T>::minval() ? f : Num<T>::minval(); }
 B2P_HD bool sp_local(const SpStruct& st, int b) { return st.blk[b].len == 6 && st.blk[b].nrows == 6 && st.blk[b].nprev == 0; }
 template <typename T>
 B2P_HD void chol6_local(T* A, int s0) {
@@ -66,10 +72,14 @@ B2P_HD void chol6_local(T* A, int s0) {
   for (int i = 0; i < 6; i++)
 #pragma unroll
     for (int j = 0; j <= i; j++) a[(i * (i + 1)) / 2 + j] = A[tri_idx(s0 + i, s0 + j)];
+  T d0[6];
+#pragma unroll
+  for (int k = 0; k < 6; k++) d0[k] = a[(k * (k + 1)) / 2 + k];
 #pragma unroll
   for (int k = 0; k < 6; k++) {
     T d = a[(k * (k + 1)) / 2 + k];
-    d = d > Num<T>::minval() ? sqrt(d) : sqrt(Num<T>::minval());
+    const T fl = pivot_floor(d0[k]);
+    d = d > fl ? sqrt(d) : sqrt(fl);
     const T id = 1 / d;
     a[(k * (k + 1)) / 2 + k] = d;
 #pragma unroll
@@ -117,14 +127,14 @@ B2P_HD bool sp_dense_tail(const SpStruct& st, int b) { return b == st.nblk - 1 &
 // executes the same FMA stream and the row stays in registers (predicated updates made ptxas demote it to local memory).
 template <typename T>
 __device__ __forceinline__ void chol16_warp(T* A, int s0, int n, int lane) {
-  T a[16];
+  T a[16], fl = Num<T>::minval();
   const int i = lane;
 #pragma unroll
-  for (int j = 0; j < 16; j++) { const bool in = i < n && j <= i; const T v = A[in ? tri_idx(s0 + i, s0 + j) : 0]; a[j] = in ? v : (j == i ? T(1) : T(0)); }
+  for (int j = 0; j < 16; j++) { const bool in = i < n && j <= i; const T v = A[in ? tri_idx(s0 + i, s0 + j) : 0]; a[j] = in ? v : (j == i ? T(1) : T(0)); if (j == i) fl = pivot_floor(a[j]); }
 #pragma unroll
   for (int k = 0; k < 16; k++) {
-    const T akk = __shfl_sync(0xffffffffu, a[k], k);
-    const T d = sqrt(akk > Num<T>::minval() ? akk : Num<T>::minval());
+    const T akk = __shfl_sync(0xffffffffu, a[k] > fl ? a[k] : fl, k);   // lane k: its pivot, floored relative to its original diagonal
+    const T d = sqrt(akk);
     const T id = 1 / d;
     a[k] = i == k ? d : a[k] * id;
 #pragma unroll
@@ -165,7 +175,7 @@ __device__ __forceinline__ void solve16_warp(const T* L, const SpStruct& st, int
 // in-place A = L L' on the packed lower triangle, restricted to the structure.  tri[e] = (a << 8) | c enumerates
 // the pairs a >= c of a triangular index e (host-built table in DevModel).
 template <typename T>
-B2P_HDN void sp_cholesky(T* A, const SpStruct& st, const unsigned short* tri, const Ctx& c) {
+B2P_HDN void sp_cholesky(T* A, const SpStruct& st, const unsigned short* tri, const Ctx& c, const T* diag0 = nullptr) {   // diag0: original diagonal by solver index (pivot floor), or none
   for (int b = c.tid; b < st.nblk; b += c.nt) if (sp_local(st, b)) chol6_local(A, st.blk[b].start);
   for (int b = 0; b < st.nblk; b++) {
     if (sp_local(st, b)) continue;
@@ -177,7 +187,8 @@ B2P_HDN void sp_cholesky(T* A, const SpStruct& st, const unsigned short* tri, co
       const int k = start + kk, R = nrows - kk - 1, kb = tri_idx(k, 0);
       const unsigned char* lst = st.rows[b] + kk + 1;
       T d = A[kb + k];
-      d = d > Num<T>::minval() ? sqrt(d) : sqrt(Num<T>::minval());
+      const T fl = diag0 ? pivot_floor(diag0[k]) : Num<T>::minval();
+      d = d > fl ? sqrt(d) : sqrt(fl);
       const T id = 1 / d;
       bsync(c);                                     // every lane has read the pivot
       if (c.tid == 0) A[kb + k] = d;

@@ -152,6 +152,13 @@ B2P_HD bool warp_any(const Ctx& c, bool p) {
 #endif
 }
 
+// Debug build only (-DB2P_NANTRACE, tools/catch_bad_state.py): the first probe that sees a non-finite value leaves its code in bits 8.. of the scene's status
+#ifdef B2P_NANTRACE
+#define NANCHK(code, ptr, n) { unsigned nb_ = 0; for (int i_ = c.tid; i_ < (n); i_ += c.nt) if (!(fabs((ptr)[i_]) < 1e30)) nb_ = 1; nb_ = block_or(c, nb_); if (nb_ && c.tid == 0 && !(s.flags >> 8)) s.flags |= (code) << 8; bsync(c); }
+#else
+#define NANCHK(code, ptr, n)
+#endif
+
 // ------------------------------------------------------------------------------------------ small math
 template <typename T> B2P_HD T dot3(const T* a, const T* b) { return a[0] * b[0] + a[1] * b[1] + a[2] * b[2]; }
 template <typename T> B2P_HD void cross3(T* r, const T* a, const T* b) {

@@ -38,8 +38,18 @@ constexpr int PROP_BODY0 = MAXTB;
 #ifndef B2P_JPOOL_F32
 #define B2P_JPOOL_F32 2304
 #endif
-template <typename T> struct Pool { static constexpr int EFC = B2P_EFC_F32, JP = B2P_JPOOL_F32; };
-template <> struct Pool<double> { static constexpr int EFC = 160, JP = 2944; };
+// JP is the capacity of a scene's packed Jacobian; only the first JPS reals live in shared memory.  A scene at rest needs ~400
+// (7 equality rows on the tree + 16 prop-table contacts x 3 rows x 6), so JPS is sized for that and the rows of heavier scenes
+// (grasps, arm contacts) spill to a per-warp overflow area in global memory (L1/L2 resident): shared memory per scene is what
+// bounds the scenes in flight per SM, and the kernel is latency bound.
+#ifndef B2P_JPS_F32
+#define B2P_JPS_F32 768
+#endif
+#ifndef B2P_JPS_F64
+#define B2P_JPS_F64 704
+#endif
+template <typename T> struct Pool { static constexpr int EFC = B2P_EFC_F32, JP = B2P_JPOOL_F32, JPS = B2P_JPS_F32; };
+template <> struct Pool<double> { static constexpr int EFC = 160, JP = 2944, JPS = B2P_JPS_F64; };
 constexpr int MAXEFC_OUT = 160;  // efc_force slots in the derived-output record (both dtypes)
 constexpr int SP_MAXBLK = 1 + MAXP;                  // solver blocks: props, then the tree
 constexpr int HPACK = (MAXNV * (MAXNV + 1)) / 2;     // packed lower triangle of the Newton Hessian

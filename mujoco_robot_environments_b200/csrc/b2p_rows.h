@@ -49,7 +49,7 @@ B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0,
 template <typename T>
 B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
   const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a);
-  const T* j = s.Jp + s.joff[r];
+  const T* j = jrow(s, r);
   T v = 0;
   for (int k = 0; k < wa; k++) v += j[k] * x[sa + k];
   if (b >= 0) { const int sb = block_start(m, b); for (int k = 0; k < 6; k++) v += j[wa + k] * x[sb + k]; }
@@ -98,10 +98,12 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       s.flags |= FLAG_EFCFULL; nr = 0;
     }
     if (nr > 0) {
+      const bool in_smem = j0 + nr * w <= Pool<T>::JPS;   // an item's rows never straddle the two pools
       for (int q = 0; q < nr; q++) {
-        s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb; s.joff[r0 + q] = (short)(j0 + q * w);
+        s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
+        s.joff[r0 + q] = (short)(in_smem ? j0 + q * w : -(j0 + q * w) - 1);
       }
-      T* J0 = s.Jp + j0;
+      T* J0 = in_smem ? s.Jp + j0 : s.jovf + j0;
       for (int k = 0; k < nr * w; k++) J0[k] = 0;
       if (kind == ROW_EQ && nr == 3) {
         const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];

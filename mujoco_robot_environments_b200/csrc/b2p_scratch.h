@@ -16,6 +16,7 @@ struct Globals {                 // read-only global-memory tables
   const int* geom_start;         // [ngeom][27] hill-climb start vertex per quantised direction (mesh geoms)
   const NbrPt<T>* nbr_pt;        // [nmeshnbr] neighbour vertex coordinates + index, same order as nbr
   const NbrSpan* nbr_span;       // [nmeshvert]
+  T* jovf;                       // [warp slots][Pool<T>::JP] Jacobian rows that do not fit a scene's shared-memory pool
 };
 
 // Shared memory per scene is what bounds the number of resident warps (= scenes in flight) per SM, and the kernel is latency
@@ -42,7 +43,8 @@ struct alignas(16) Scratch {
   short c_pair[MAXCON], c_row[MAXCON];
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
   // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
-  T Jp[Pool<T>::JP], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
+  T Jp[Pool<T>::JPS], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
+  T* jovf;                       // this warp's overflow area (global memory, Pool<T>::JP reals): joff[r] < 0 <=> row r lives at jovf[-joff[r] - 1]
   signed char row_a[Pool<T>::EFC], row_b[Pool<T>::EFC], row_type[Pool<T>::EFC], row_state[Pool<T>::EFC];
   short row_id[Pool<T>::EFC], joff[Pool<T>::EFC];
   // per-block row lists (block 0 = tree, 1+p = prop p): first row of every item (eq/limit row, or contact triple)
@@ -73,11 +75,13 @@ static_assert(sizeof(((Scratch<float>*)0)->H) >= (MAXTB * 28 + MAXCON * 3 + MAXT
 template <typename T> B2P_HD int dof_block(const DevModel<T>& m, int d) { return d < m.ntd ? 0 : 1 + (d - m.ntd) / 6; }
 template <typename T> B2P_HD int block_start(const DevModel<T>& m, int blk) { return blk == 0 ? 0 : m.ntd + 6 * (blk - 1); }
 template <typename T> B2P_HD int block_width(const DevModel<T>& m, int blk) { return blk == 0 ? m.ntd : 6; }
+// first slot of packed Jacobian row r: shared-memory pool, or the warp's global overflow area
+template <typename T> B2P_HD const T* jrow(const Scratch<T>& s, int r) { const int o = s.joff[r]; return o >= 0 ? s.Jp + o : s.jovf + (-o - 1); }
 // pointer to the slots of block `blk` inside row r, or nullptr when the row does not touch the block
 template <typename T> B2P_HD const T* row_seg(const DevModel<T>& m, const Scratch<T>& s, int r, int blk) {
   const int a = s.row_a[r];
-  if (a == blk) return s.Jp + s.joff[r];
-  if (s.row_b[r] == blk) return s.Jp + s.joff[r] + block_width(m, a);
+  if (a == blk) return jrow(s, r);
+  if (s.row_b[r] == blk) return jrow(s, r) + block_width(m, a);
   return nullptr;
 }
 template <typename T> B2P_HD const unsigned char* block_rows(const Scratch<T>& s, int blk) { return blk == 0 ? s.brow0 : s.browp[blk - 1]; }

@@ -186,8 +186,10 @@ B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c,
   if (refactor) {   // otherwise s.H still holds the factor of the identical Hessian of the previous iteration
     assemble_H(m, s, c);
     bsync(c);
+    for (int u = c.tid; u < m.nv; u += c.nt) s.tmpv[u] = s.H[tri_idx(u, u)];   // original diagonal, by solver index: the pivot floor's reference
+    bsync(c);
     PROF_ADD(PF_ASSEMBLE)
-    sp_cholesky(s.H, s.sp, m.tri, c);
+    sp_cholesky(s.H, s.sp, m.tri, c, s.tmpv);
     PROF_ADD(PF_CHOL)
   }
   sp_solve(s.H, s.sp, s.Mgrad, 6 * m.nprop, m.ntd, c);
@@ -250,7 +252,9 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
     bsync(c);
     cost_at(m, s, c, s.qacc);
+    NANCHK(2, s.Jaref, s.nefc)
     cost = solver_update(m, s, c, gn2, dirty);
+    NANCHK(3, s.grad, nv) NANCHK(4, &s.cW[0][0], 6 * s.ncon)
     dirty = true;   // nothing factored yet in this step
   }
   PROF_ADD(PF_SOLVE_INIT)
@@ -262,8 +266,10 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
   while (csync_or(c, LK_NEWTON, run)) {
     if (!run) continue;
     newton_direction(m, s, c, dirty);
+    NANCHK(5 + 16 * it, s.search, nv)
     PROF_RESET
     const T alpha = line_search(m, s, c, scale);
+    { T al_[1] = {alpha}; NANCHK(6 + 16 * it, al_, 1) }
     PROF_ADD(PF_LS)
     if (alpha == 0) { run = false; continue; }
     for (int d = c.tid; d < nv; d += c.nt) { s.qacc[d] += alpha * s.search[d]; s.Ma[d] += alpha * s.Mv[d]; }
@@ -271,6 +277,7 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
     bsync(c);
     const T old = cost;
     cost = solver_update(m, s, c, gn2, dirty);
+    NANCHK(7 + 16 * it, s.grad, nv) NANCHK(8 + 16 * it, &s.cW[0][0], 6 * s.ncon)
     PROF_ADD(PF_UPDATE)
     const T improvement = scale * (old - cost), gradient = scale * sqrt(gn2);
     it++;

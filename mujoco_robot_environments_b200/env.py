@@ -329,15 +329,16 @@ class BatchedRearrangementEnv:
 
     def random_pick_and_place(self):
         """rearrangement.py:667-698, per scene: pick pose = position of the scene's first prop + grasp quat
-        mju_mat2Quat(R_xyz(0, 180, yaw) in degrees), place pose = U(workspace) + the same quat -> (pick [n, 7], place [n, 7]).
-        The reference hands the wxyz body quaternion to scipy's ``R.from_quat`` (which reads xyzw) before taking
-        yaw = atan2(R10, R00); the same reading is kept here, so a prop that is only yawed gets yaw = 0."""
+        mju_mat2Quat(R_xyz(0, 180, yaw) in degrees) with yaw = atan2(R10, R00) of the prop's geom_xmat, signed (``props_info`` stores
+        ``R.from_matrix(geom_xmat).as_quat()``, i.e. xyzw, which ``R.from_quat`` reads back unchanged: rearrangement.py:246-247,676-679);
+        place pose = U(workspace) + the same quat -> (pick [n, 7], place [n, 7])."""
         p = self._physics
         first = self.has_prop.to(torch.int64).argmax(1)
         e = torch.arange(self.num_envs, device=self.device)
         prop = torch.stack([p.qpos[:, a:a + 7] for a in p.model.prop_qposadr], 1)[e, first]
-        x, y, z, w = prop[:, 3], prop[:, 4], prop[:, 5], prop[:, 6]
-        yaw = torch.atan2(2 * (x * y + z * w), 1 - 2 * (y * y + z * z))
+        # the prop geom sits at the body origin with the body's orientation: geom_xmat = R(qpos[3:7]), quaternion (w, x, y, z)
+        w, x, y, z = prop[:, 3], prop[:, 4], prop[:, 5], prop[:, 6]
+        yaw = torch.atan2(2 * (x * y + w * z), 1 - 2 * (y * y + z * z))
         zero = torch.zeros_like(yaw)
         quat = mat2quat(euler_xyz_matrix(zero, zero + math.pi, yaw)).to(self.dtype)
         ws = self._cfg["task"]["initializers"]["workspace"]
@@ -399,8 +400,10 @@ class BatchedRearrangementEnv:
         p = self._physics
         qa = p.model.prop_qposadr
         prop = torch.stack([p.qpos[:, a:a + 7] for a in qa], 1)
-        obs = {"qpos": p.qpos, "qvel": p.qvel, "time": p.time, "eef_pos": p.data.site_xpos[:, 1], "prop_pos": prop[..., :3],
-               "prop_quat": prop[..., 3:], "has_prop": self.has_prop}
+        # copies, not views: the TimeStep of step() is the observation BEFORE acting (rearrangement.py:343) and pick / place advance
+        # the state buffers in place
+        obs = {"qpos": p.qpos.clone(), "qvel": p.qvel.clone(), "time": p.time.clone(), "eef_pos": p.data.site_xpos[:, 1].clone(), "prop_pos": prop[..., :3],
+               "prop_quat": prop[..., 3:], "has_prop": self.has_prop.clone()}
         if self.camera_obs:
             obs.update(self.render())
         return obs

@@ -11,12 +11,14 @@ import subprocess
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(_HERE, "csrc")
-LIB_PATH = os.path.join(CSRC, "libb2p.so")
+LIB_PATH = os.environ.get("B2P_LIB") or os.path.join(CSRC, "libb2p.so")      # B2P_LIB: a debug build (tools/), never a fallback
 NVCC_FLAGS = ["-gencode", "arch=compute_100a,code=sm_100a", "-O3", "-lineinfo", "-std=c++17", "-Xcompiler", "-fPIC"]
 UNITS = ("b2p_api.cu", "b2p_kernel_f32.cu", "b2p_kernel_f64.cu", "b2p_render.cu")
-# per-unit flags: the fp32 throughput kernel uses the fast division / sqrt / sincos sequences (<= 2 ulp; its parity tolerance is 1e-4)
-# the ray-caster is built without FMA contraction: every pixel is bit-identical to the plain-C restatement (oracle/b2p_render_oracle.c)
-UNIT_FLAGS = {"b2p_kernel_f32.cu": ["-use_fast_math"], "b2p_render.cu": ["-fmad=false"]}
+# per-unit flags.  fp32 throughput kernel: approximate division / square root (<= 2 ulp) and flush-to-zero, but NOT -use_fast_math:
+# its __sinf / __cosf / __powf substitutions (absolute error 2^-21) made the Newton solve of ill-conditioned grasps wander (39
+# iterations and a wrong qacc on tests/golden/bad_state_fp32_0.json, against 2 iterations with these flags) for 3 % of throughput.
+# The ray-caster is built without FMA contraction: every pixel is bit-identical to the plain-C restatement (oracle/b2p_render_oracle.c)
+UNIT_FLAGS = {"b2p_kernel_f32.cu": ["--prec-div=false", "--prec-sqrt=false", "--ftz=true"], "b2p_render.cu": ["-fmad=false"]}
 
 # enums of include/b2p.h
 F64, F32 = 0, 1

@@ -12,7 +12,7 @@ using namespace b2p;
 template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
-  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf;
   Globals<T> g; Scratch<T>* s;
 };
 
@@ -37,7 +37,8 @@ static Emu<T>* make(const void* blob, size_t n) {
   for (size_t v = 0; v < e->nbr_span.size(); v++) { e->nbr_span[v].adr = e->ht.mesh_nbradr[v]; e->nbr_span[v].num = e->ht.mesh_nbrnum[v]; }
   e->g.nbr_pt = e->nbr_pt.data(); e->g.nbr_span = e->nbr_span.data();
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
-  e->s = new Scratch<T>();
+  e->jovf.assign(Pool<T>::JP, T(0)); e->g.jovf = e->jovf.data();
+  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data();
   return e;
 }
 

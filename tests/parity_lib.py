@@ -129,6 +129,7 @@ def compare_sample(dtype, state, size, active, ctrl=None, target=None, grip=None
             c = o.run_controller(np.asarray(target[e], np.float64), int(grip[e]), ticks)
             d.append(float(np.abs(fin[e, :sc.NQ] - o.qpos[:sc.NQ]).max())); conv_same += int(bool(conv[e]) == c)
         growth[str(5 * ticks)] = dict(max=float(np.max(d)), median=float(np.median(d)))
+        last_d = d
         extra = dict(converged_bits_equal=conv_same, osc_tau_abs_max=float(max(t[0] for t in tau_err)), osc_tau_rel_max=float(max(t[1] for t in tau_err)))
     else:
         load(); p.set_control(torch.tensor(ctrl_gpu))
@@ -147,13 +148,19 @@ def compare_sample(dtype, state, size, active, ctrl=None, target=None, grip=None
                 d[m].append(float(np.abs(snaps[m][e] - o.qpos[:sc.NQ]).max()))
         growth = {str(m): dict(max=float(np.max(v)), median=float(np.median(v))) for m, v in d.items()}
         extra = {}
+        last_d = d[marks[-1]]
     flagsH = p.status().cpu().numpy()
+    for e in range(k):      # scenes that drift apart keep what is needed to replay them on the CPU
+        rows[e]["drift"] = last_d[e]
+        if last_d[e] > (1e-9 if dtype == "f64" else 1e-3) and "replay" not in rows[e]:
+            rows[e]["replay"] = dict(state=st64[e].tolist(), size=np.asarray(size[e]).tolist(), active=np.asarray(active[e]).tolist(), ctrl=ctrl_gpu[e].tolist(),
+                                     target=None if target is None else np.asarray(target[e]).tolist(), grip=None if grip is None else int(grip[e]))
     p.close()
     agg = lambda key: dict(max=float(max(r[key] for r in rows)), median=float(np.median([r[key] for r in rows])))
     res = dict(dtype=dtype, scenes=k, single_step={f: agg(f) for f in ("qacc_abs", "qacc_rel", "qvel_abs", "qvel_rel", "qpos_abs", "qpos_rel", "contact_dist_abs", "qacc_abs_arm", "qacc_abs_gripper", "qacc_abs_props")},
                contact_sets_identical=int(sum(r["contacts_identical"] for r in rows)), nefc_equal=int(sum(r["nefc"] == r["nefc_oracle"] for r in rows)),
                nefc_max=int(max(r["nefc"] for r in rows)), niter_max=int(max(r["niter"] for r in rows)),
-               qpos_drift=growth, flags_single_step=int(np.bitwise_or.reduce(flags1)), flags_horizon=int(np.bitwise_or.reduce(flagsH)), rows=rows)
+               qpos_drift=growth, drift_scenes_above=dict(thresh=(1e-9 if dtype == "f64" else 1e-3), count=int(sum(x > (1e-9 if dtype == "f64" else 1e-3) for x in last_d))), flags_single_step=int(np.bitwise_or.reduce(flags1)), flags_horizon=int(np.bitwise_or.reduce(flagsH)), rows=rows)
     res.update(extra)
     return res
 

@@ -156,7 +156,11 @@ def test_env_pick_and_place_moves_a_prop():
     grasp = _mulquat(qz.to(torch.float32), down[None].expand(4, 4))
     pick = torch.cat([pos0, grasp], 1)
     t0 = float(env.physics.time[0])
-    env.step({"pose": pick})
+    q_before = env.physics.qpos.clone(); eef_before = env.robot.eef_pose.clone()
+    ts2 = env.step({"pose": pick})
+    # the TimeStep carries the observation taken BEFORE acting (rearrangement.py:343), not views of the live state
+    assert torch.equal(ts2.observation["qpos"], q_before) and torch.equal(ts2.observation["eef_pos"], eef_before)
+    assert not torch.equal(ts2.observation["qpos"], env.physics.qpos) and float(ts2.observation["time"][0]) == pytest.approx(t0, abs=1e-6)
     assert env.mode == "place" and abs(float(env.physics.time[0]) - t0 - 9.0) < 1e-2        # 2+2+1+2+2 s of physics
     lifted = env.physics.qpos[:, 15 + 2]
     assert int((lifted > 0.5).sum()) >= 3                                                  # cube travels with the gripper
@@ -223,6 +227,13 @@ def test_tuner_circle_and_pick_place_stages():
     assert env.num_envs == 32 and int(env.n_props.max()) == 1
     pick, place = env.random_pick_and_place()
     assert pick.shape == (32, 7) and place.shape == (32, 7)
+    # grasp quaternion = mju_mat2Quat(R_xyz(0, 180 deg, yaw)) with the SIGNED yaw atan2(R10, R00) of the block's geom_xmat (rearrangement.py:676-681)
+    from mujoco_robot_environments_b200.expert import euler_xyz_matrix, mat2quat
+    env.physics.forward(full_contacts=False)
+    R = env.physics.data.geom_xmat[:, env.physics.model.prop_geomid[0]]
+    yaw = torch.atan2(R[:, 3], R[:, 0])
+    want = mat2quat(euler_xyz_matrix(torch.zeros_like(yaw), torch.zeros_like(yaw) + np.pi, yaw)).to(pick.dtype)
+    assert float((pick[:, 3:] - want).abs().max()) < 1e-5 and float(yaw.abs().max()) > 0.3
     assert bool((pick[:, 3:] - place[:, 3:]).abs().max() == 0)
     hist = t.run(generations=2, method="pick_place")
     assert len(hist) == 2 and np.isfinite(hist[-1]["best_fitness"])
