@@ -228,7 +228,8 @@ def run_render(args, wl):
         dist.destroy_process_group()
 
 
-def run_ours(args, wl):
+def measure(args, wl, workload, n_steps):
+    """Times `n_steps` launches of one workload on this rank's GPU (+ the end-to-end leg); rank 0 gets the JSON line, others None."""
     import numpy as np
     import torch
     import torch.distributed as dist
@@ -236,11 +237,9 @@ def run_ours(args, wl):
     from mujoco_robot_environments_b200.physics import BatchedPhysics
 
     rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
-    torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
-    if world > 1:
-        dist.init_process_group("nccl", device_id=dev)
-    n = args.envs or wl["envs"]
+    n = (args.envs if workload == args.workload else 0) or wl["envs"]
+    args = argparse.Namespace(**{**vars(args), "steps": n_steps, "workload": workload})
     dtype = torch.float32 if wl["dtype"] == "f32" else torch.float64
     w = 4 if wl["dtype"] == "f32" else 8
     ticks = args.ticks
@@ -249,6 +248,8 @@ def run_ours(args, wl):
     st, size, active = sc.make_states(n, seed=1234 + rank, settled=True)
     p = BatchedPhysics(n, dtype=dtype, device=dev)
     p.state.copy_(torch.tensor(st, dtype=dtype)); p.set_env_params(torch.tensor(size), torch.tensor(active))
+    # what a caller of RobotArm.run_controller reads afterwards: the state, `converged` and the end-effector site (robot_arm.py:55-58,94)
+    p.set_out_fields("SITE")
     flush = torch.empty(192 * 1024 * 1024, dtype=torch.uint8, device=dev)   # > 126 MB L2
     # pinned host staging for the end-to-end leg
     n_t = 8
@@ -336,7 +337,8 @@ def run_ours(args, wl):
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms.item() / args.steps, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": wl["dtype"], "data": "synthetic",
                 "config": {**workload_config(args, wl),
-                           "l2": "flushed between timed iterations (192 MiB fill, untimed); the e2e leg runs back to back without the flush", "launch": p.launch_info(), "wall_s_incl_flush": wall,
+                           "l2": "flushed between timed iterations (192 MiB fill, untimed); the e2e leg runs back to back without the flush", "launch": p.launch_info(),
+                           "derived_outputs": "stepping launches refresh the end-effector site group only (b2p_set_out_mask(B2P_OUT_SITE)); state, converged and status always", "wall_s_incl_flush": wall,
                            "episode_stats": {"converged_envs": stats[0].item(), "envs": stats[1].item(), "flagged_envs": stats[2].item(),
                                              "flags": {k: stats[3 + i].item() for i, k in enumerate(FLAG_NAMES)}}},
                 "clocks": sampler.summary(), "gpu_launches": int(launches + order_launches) * world,
@@ -349,6 +351,27 @@ def run_ours(args, wl):
             v, cores = cpu_baseline(args.cpu_seconds, wl["osc"])
             line["cpu_baseline"] = {"value": v, "unit": "env-steps/s", "cores": cores, "kind": "port",
                                     "sample": "%d processes x %.0f s, one env per process, same scene/target distribution (oracle C port, %s; MuJoCo not installable here)" % (cores, args.cpu_seconds, CPU_BUILD)}
+        p.close()
+        return line
+    p.close()
+    return None
+
+
+def run_ours(args, wl):
+    import torch
+    import torch.distributed as dist
+    rank, world, local = int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1")), int(os.environ.get("LOCAL_RANK", "0"))
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    line = measure(args, wl, args.workload, args.steps)
+    if args.workload == "c3" and world == 1 and not args.no_secondary:
+        # BASELINE configs[1] (fp64 parity mode, physics only) rides along on the default line so that a driver-run record carries it
+        a2 = argparse.Namespace(**{**vars(args), "no_cpu": True})
+        l2 = measure(a2, WORKLOADS["c2"], "c2", max(3, min(5, args.steps)))
+        if line is not None and l2 is not None:
+            line["secondary"] = {k: l2[k] for k in ("metric", "value", "unit", "dtype", "steps", "ms_per_step", "config", "e2e", "roofline", "gpu_launches")}
+    if line is not None:
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.destroy_process_group()
@@ -365,6 +388,7 @@ def main():
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--cpu-seconds", type=float, default=12.0)
     ap.add_argument("--no-cpu", action="store_true")
+    ap.add_argument("--no-secondary", action="store_true", help="c3 only: skip the c2 (fp64 parity mode) measurement carried as `secondary`")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "ours":
         args.warmup = 3

@@ -60,6 +60,16 @@ int b2p_out_offset(int field, int* offset, int* count);
 int b2p_bind_state(b2p_handle h, void* state);
 /* optional caller-owned derived-output buffer [n_env][B2P_Q_OUT_STRIDE]; NULL = use the handle's own */
 int b2p_bind_out(b2p_handle h, void* out);
+/* Which groups of the derived-output record the STEPPING calls (b2p_step_physics / b2p_step_osc / b2p_settle) write at the end of a
+ * launch; b2p_forward always writes every group (that is what physics.forward() is for).  Default: all, so that any read of
+ * data.* after a step sees current values, as with mjData.  A caller that only reads the end-effector site after run_controller
+ * (RobotArm.eef_pos, models/robot_arm.py:55-58; OSC.current_position_error, osc.py:156-157) sets B2P_OUT_SITE and saves the
+ * 5.7 kB (fp32) per scene per launch the other groups cost. */
+enum {
+  B2P_OUT_SITE = 1 /* SITE_XPOS, SITE_XMAT, NCON, NEFC */, B2P_OUT_CONTACT = 2, B2P_OUT_MARM = 4, B2P_OUT_GEOM = 8 /* GEOM_XPOS, GEOM_XMAT */,
+  B2P_OUT_BIAS = 16 /* QFRC_BIAS */, B2P_OUT_DYN = 32 /* QACC, QACC_SMOOTH, CTRL, NITER */, B2P_OUT_EFC = 64 /* EFC_FORCE */, B2P_OUT_ALL = 127
+};
+int b2p_set_out_mask(b2p_handle h, int mask);
 /* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active);
 /* optional per-scene OSC gains [n_env][6] reals (position kp, kd, orientation kp, kd, nullspace kp, kd): one candidate of the

@@ -12,6 +12,8 @@
 
 using namespace b2p;
 
+static_assert((int)OUT_SITE == (int)B2P_OUT_SITE && (int)OUT_CONTACT == (int)B2P_OUT_CONTACT && (int)OUT_MARM == (int)B2P_OUT_MARM && (int)OUT_GEOM == (int)B2P_OUT_GEOM &&
+              (int)OUT_BIAS == (int)B2P_OUT_BIAS && (int)OUT_DYN == (int)B2P_OUT_DYN && (int)OUT_EFC == (int)B2P_OUT_EFC && (int)OUT_ALL == (int)B2P_OUT_ALL, "include/b2p.h and b2p_scratch.h disagree on the output groups");
 static thread_local std::string g_err;
 static int fail(int code, const std::string& msg) { g_err = msg; return code; }
 namespace b2p { int api_fail(int code, const char* msg) { return fail(code, msg); } }   // shared with b2p_render.cu
@@ -62,7 +64,7 @@ struct b2p_handle_s {
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env; void* d_jovf;
   const void* env_gains; const unsigned char* env_mask;
-  int *d_work, *d_order; int work_steps, sort_queue;   // work_steps: physics steps behind d_work (0 = none yet)
+  int *d_work, *d_order; int work_steps, sort_queue, out_mask;   // work_steps: physics steps behind d_work (0 = none yet)
 };
 
 template <typename T>
@@ -109,7 +111,7 @@ template <typename T>
 static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
-  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.gains = (const T*)h->env_gains;
+  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf};
   a.work = h->d_work; a.order = nullptr;
   if (h->sort_queue && h->work_steps > 0) {
@@ -153,6 +155,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
   HostTables ht;
   std::string err = build_model(blob, nbytes, h->hmodel, ht);
   if (!err.empty()) { delete h; return fail(B2P_ERR_MODEL, "b2p_create: " + err); }
+  h->out_mask = OUT_ALL;
   h->dtype = dtype; h->device = device; h->n_env = n_env; h->nq = h->hmodel.nq; h->nv = h->hmodel.nv; h->nu = h->hmodel.nu; h->nprop = h->hmodel.nprop; h->ngeom = h->hmodel.ngeom;
   CK(cudaSetDevice(device));
   CK(cudaMalloc(&h->d_status, (size_t)n_env * 4)); CK(cudaMemset(h->d_status, 0, (size_t)n_env * 4));
@@ -196,6 +199,7 @@ int b2p_bind_state(b2p_handle h, void* state) {
   h->state = state; return B2P_OK;
 }
 int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out = out ? out : h->own_out; return B2P_OK; }
+int b2p_set_out_mask(b2p_handle h, int mask) { if (!h || mask < 0 || mask > OUT_ALL) return fail(B2P_ERR_ARG, "b2p_set_out_mask: bad argument"); h->out_mask = mask; return B2P_OK; }
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
 int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
 int b2p_set_env_mask(b2p_handle h, const uint8_t* mask) { if (!h) return B2P_ERR_ARG; h->env_mask = mask; return B2P_OK; }

@@ -76,18 +76,19 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
   PROF_ADD(PF_INTEGRATE)
 }
 
-// Derived-output record.  The "pos" part (site / geom poses, contacts, mass matrix, bias) reads step1 buffers that share
-// storage with the solver's (Scratch unions), so it must be written after a step1 and before the next step2; the "dyn"
-// part (qacc, efc_force, solver statistics) persists.
-enum { OUT_POS = 1, OUT_DYN = 2 };
+// Derived-output record, written group by group (b2p_set_out_mask; B2P_OUT_* of include/b2p.h).  The "pos" groups (site / geom
+// poses, contacts, mass matrix, bias) read step1 buffers that share storage with the solver's (Scratch unions), so they must be
+// written after a step1 and before the next step2; the "dyn" groups (qacc, efc_force, solver statistics) persist.
 template <typename T>
 B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, const Ctx& c, T* o, int parts) {
   typedef OutLayout L;
-  if (parts & OUT_POS) {
+  if (parts & OUT_SITE) {
     for (int i = c.tid; i < 6; i += c.nt) o[L::SITE_XPOS + i] = s.site_xpos[i / 3][i % 3];
     for (int i = c.tid; i < 18; i += c.nt) o[L::SITE_XMAT + i] = s.site_xmat[i / 9][i % 9];
-    for (int i = c.tid; i < MAXNV; i += c.nt) o[L::QFRC_BIAS + i] = i < m.nv ? s.qfrc_bias[i] : T(0);
     if (c.tid == 0) { o[L::NCON] = T(s.ncon); o[L::NEFC] = T(s.nefc); }
+  }
+  if (parts & OUT_BIAS) for (int i = c.tid; i < MAXNV; i += c.nt) o[L::QFRC_BIAS + i] = i < m.nv ? s.qfrc_bias[i] : T(0);
+  if (parts & OUT_CONTACT) {
     for (int k = c.tid; k < MAXCON; k += c.nt) {
       T* q = o + L::CONTACT + k * L::CONTACT_W;
       if (k < s.ncon) {
@@ -96,7 +97,9 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
         q[7] = T(g.pair_g1[p]); q[8] = T(g.pair_g2[p]); q[9] = T(s.c_dist[k] < s.c_incl[k] ? 0 : 1);
       } else for (int i = 0; i < L::CONTACT_W; i++) q[i] = 0;
     }
-    for (int i = c.tid; i < MAXTD * MAXTD; i += c.nt) { const int r = i / MAXTD, q = i % MAXTD; o[L::MARM + i] = s.Mt[r >= q ? tri_idx(r, q) : tri_idx(q, r)]; }
+  }
+  if (parts & OUT_MARM) for (int i = c.tid; i < MAXTD * MAXTD; i += c.nt) { const int r = i / MAXTD, q = i % MAXTD; o[L::MARM + i] = s.Mt[r >= q ? tri_idx(r, q) : tri_idx(q, r)]; }
+  if (parts & OUT_GEOM) {
     for (int i = c.tid; i < MAXG * 3; i += c.nt) o[L::GPOS + i] = i / 3 < m.ngeom ? s.gpos[i / 3][i % 3] : T(0);
     for (int i = c.tid; i < MAXG * 9; i += c.nt) o[L::GMAT + i] = i / 9 < m.ngeom ? s.gmat[i / 9][i % 9] : T(0);
   }
@@ -104,8 +107,8 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
     for (int i = c.tid; i < MAXNV; i += c.nt) { o[L::QACC + i] = i < m.nv ? s.qacc[i] : T(0); o[L::QACC_SMOOTH + i] = i < m.nv ? s.qacc_smooth[i] : T(0); }
     for (int i = c.tid; i < MAXU; i += c.nt) o[L::CTRL + i] = s.ctrl[i];
     if (c.tid == 0) o[L::NITER] = T(s.niter);
-    for (int i = c.tid; i < MAXEFC_OUT; i += c.nt) o[L::EFC_FORCE + i] = i < s.nefc ? s.force[i] : T(0);
   }
+  if (parts & OUT_EFC) for (int i = c.tid; i < MAXEFC_OUT; i += c.nt) o[L::EFC_FORCE + i] = i < s.nefc ? s.force[i] : T(0);
 }
 
 // One scene, whole launch: load the state record, run the requested mode, store the record.  `active` = this warp holds
@@ -178,7 +181,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
   int work = 0;   // scheduling hint for the next launch (see StepArgs::work)
   if (a.mode == MODE_FORWARD) {
     step1(m, g, s, c, full, active);
-    if (active && a.out) { bsync(c); write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, OUT_POS); bsync(c); }
+    if (active && a.out) { bsync(c); write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, OUT_POS); bsync(c); }   // physics.forward(): every group
     step2(m, s, c, false, false, active);
   } else if (a.mode == MODE_PHYSICS) {
     for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); }
@@ -231,7 +234,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
   if (!state_preloaded) { const T* head = s.qpos; for (int i = c.tid; i < REC_SIZE; i += c.nt) rec[i] = head[i]; }
   if (c.tid == 0 && a.status) a.status[env] |= s.flags;
   if (c.tid == 0 && a.work && (a.mode == MODE_PHYSICS || a.mode == MODE_OSC) && a.n_steps > 0) a.work[env] = work;
-  if (a.out) write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, a.mode == MODE_FORWARD ? OUT_DYN : (OUT_POS | OUT_DYN));
+  if (a.out) { const int parts = a.mode == MODE_FORWARD ? (OUT_DYN | OUT_EFC) : ((a.mode == MODE_OSC && a.n_steps == 0) ? (a.out_mask | OUT_DYN | OUT_SITE) : a.out_mask); if (parts) write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, parts); }
 }
 
 }  // namespace b2p

@@ -206,6 +206,22 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     m.act_gain[a] = b.D(B2PM_F_ACT_GAIN)[a]; cp(m.act_bias[a], b.D(B2PM_F_ACT_BIAS) + 3 * a, 3);
     cp(m.act_ctrlrange[a], b.D(B2PM_F_ACT_CTRLRANGE) + 2 * a, 2); cp(m.act_forcerange[a], b.D(B2PM_F_ACT_FORCERANGE) + 2 * a, 2);
   }
+  // The kernel folds osc.py:224-236 (tau @ pinv(actuator_moment)[arm, arm]) to the identity (b2p_osc.h).  That holds exactly when
+  // the moment row of actuator a < narm is the unit vector of dof a (unit gear, joint transmission) and no other actuator reaches
+  // an arm dof; anything else is refused here rather than silently mis-scaled.  (Gain and bias do not enter actuator_moment; the
+  // reference does not compensate them either.)
+  {
+    const int narm = b.C(B2PM_C_NARM);
+    if (m.nu < narm) return "OSC needs one actuator per arm joint";
+    for (int a = 0; a < m.nu; a++) {
+      if (a < narm) {
+        if (m.act_trnnum[a] != 1 || m.act_trndof[a][0] != a || m.act_trncoef[a][0] != 1.0)
+          return "arm actuators must be unit-gear joint actuators on dofs 0..narm-1 (OSC actuator-moment inverse is folded to identity)";
+      } else {
+        for (int x = 0; x < m.act_trnnum[a]; x++) if (m.act_trndof[a][x] < narm) return "a non-arm actuator drives an arm dof (OSC actuator-moment inverse is folded to identity)";
+      }
+    }
+  }
   const double g6[6] = {350, 20, 500, 100, 200, 30}, q0[7] = {0, -0.785, 0, -2.356, 0, 1.571, 0.785};
   cp(m.osc_gains, g6, 6); cp(m.osc_null, q0, 7); m.osc_pos_thresh = 5e-3; m.osc_ori_thresh = 68e-3;
   { int e = 0; for (int a = 0; a < MAXNV - 1; a++) for (int cc = 0; cc <= a; cc++) m.tri[e++] = (unsigned short)((a << 8) | cc); }

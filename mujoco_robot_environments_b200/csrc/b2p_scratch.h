@@ -103,7 +103,7 @@ struct StepArgs {
   int* steps_done;           // MODE_SETTLE out [n_env]
   T settle_qvel_tol, settle_qacc_tol; int settle_min_steps;
   T* out;                    // MODE_FORWARD / any: optional derived-output record per env (see OutLayout)
-  int out_stride;
+  int out_stride, out_mask;   // out_mask: groups of the record the stepping modes write (OUT_* of b2p_core.h); MODE_FORWARD writes all
   const int* order;          // optional [n_env]: queue position -> scene (scenes ordered by the work they did in the previous launch)
   int* work;                 // optional [n_env] out: work proxy of this launch, sum over steps of nefc * (2 + Newton iterations)
   // MODE_PLACE (expert prop_place): per scene the prop to place and the box [lo3 | hi3] proposals are drawn from
@@ -113,6 +113,9 @@ struct StepArgs {
 };
 // derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |
 //   contacts[MAXCON] x (dist, pos3, normal3, geom1, geom2, excluded) | Marm[MAXTD*MAXTD] | gpos[MAXG][3] | gmat[MAXG][9]
+// groups of the record (B2P_OUT_* of include/b2p.h)
+enum { OUT_SITE = 1, OUT_CONTACT = 2, OUT_MARM = 4, OUT_GEOM = 8, OUT_BIAS = 16, OUT_DYN = 32, OUT_EFC = 64,
+       OUT_POS = OUT_SITE | OUT_CONTACT | OUT_MARM | OUT_GEOM | OUT_BIAS, OUT_ALL = 127 };
 struct OutLayout {
   static constexpr int SITE_XPOS = 0, SITE_XMAT = 6, QACC = 24, QFRC_BIAS = QACC + MAXNV, CTRL = QFRC_BIAS + MAXNV, NCON = CTRL + MAXU, NEFC = NCON + 1,
                        NITER = NEFC + 1, CONTACT = NITER + 1, CONTACT_W = 10, MARM = CONTACT + MAXCON * CONTACT_W, GPOS = MARM + MAXTD * MAXTD,

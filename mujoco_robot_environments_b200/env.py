@@ -51,6 +51,9 @@ class BatchedRearrangementEnv:
         self.num_envs = int(num_envs)
         self._physics = BatchedPhysics(self.num_envs, dtype=dtype, device=device)
         p = self._physics
+        # what this class reads after a stepping launch: the end-effector site (observation) and the geom poses (expert, ray-caster);
+        # contacts are only read after an explicit forward(), as in the reference (prop_initializer.py:221)
+        p.set_out_fields("SITE", "GEOM")
         if abs(p.model.opt.timestep - float(self._cfg["physics_dt"])) > 1e-12:
             raise ValueError("physics_dt=%g differs from the compiled model's timestep %g: recompile the scene blob (tools/compile_scene.py)"
                              % (self._cfg["physics_dt"], p.model.opt.timestep))
@@ -336,9 +339,11 @@ class BatchedRearrangementEnv:
         first = self.has_prop.to(torch.int64).argmax(1)
         e = torch.arange(self.num_envs, device=self.device)
         prop = torch.stack([p.qpos[:, a:a + 7] for a in p.model.prop_qposadr], 1)[e, first]
-        # the prop geom sits at the body origin with the body's orientation: geom_xmat = R(qpos[3:7]), quaternion (w, x, y, z)
-        w, x, y, z = prop[:, 3], prop[:, 4], prop[:, 5], prop[:, 6]
-        yaw = torch.atan2(2 * (x * y + w * z), 1 - 2 * (y * y + z * z))
+        # props_info is rebuilt from geom_xmat of the current state (rearrangement.py:240-258): one forward launch, then the kernel's own matrix
+        p.forward(full_contacts=False)
+        gid = torch.as_tensor(p.model.prop_geomid, device=self.device)[first]
+        R = p.data.geom_xmat[e, gid]
+        yaw = torch.atan2(R[:, 3], R[:, 0])
         zero = torch.zeros_like(yaw)
         quat = mat2quat(euler_xyz_matrix(zero, zero + math.pi, yaw)).to(self.dtype)
         ws = self._cfg["task"]["initializers"]["workspace"]

@@ -84,6 +84,7 @@ class BatchedPhysics:
             ffi.check(self._L.b2p_out_offset(fid, C.byref(o), C.byref(c)))
             self._ofs[k] = (o.value, c.value)
         self.data = _Data(self)
+        self.out_mask = ffi.OUT["ALL"]
         self.reset()
 
     # ------------------------------------------------------------------ lifetime
@@ -196,6 +197,17 @@ class BatchedPhysics:
         assert m.shape == (self.n_env,)
         self._env_mask = m                       # borrowed by the handle: keep it alive
         ffi.check(self._L.b2p_set_env_mask(self._h, m.data_ptr()))
+
+    def set_out_fields(self, *groups: str):
+        """Which groups of the derived-output record the stepping calls refresh (``b2p_set_out_mask``): any of "SITE", "CONTACT",
+        "MARM", "GEOM", "BIAS", "DYN", "EFC", or "ALL" (the default).  ``forward()`` always refreshes everything.  Groups left out
+        keep the values of the last launch that wrote them -- a caller that reads ``data.contact`` after ``step()`` must keep
+        "CONTACT" in (or call ``forward()`` first, as the reference does before it scans contacts)."""
+        mask = 0
+        for g in groups:
+            mask |= ffi.OUT[g.upper()]
+        ffi.check(self._L.b2p_set_out_mask(self._h, mask), "b2p_set_out_mask")
+        self.out_mask = mask
 
     def set_full_contacts(self, full: bool):
         ffi.check(self._L.b2p_set_full_contacts(self._h, int(full)))

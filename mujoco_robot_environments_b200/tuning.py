@@ -82,6 +82,7 @@ class BatchedTuner:
         n = self.popsize * self.tpc
         self.physics = BatchedPhysics(n, dtype=dtype, device=device)
         p = self.physics
+        p.set_out_fields("SITE")        # the fitness functions read the end-effector site only
         self.osc = BatchedOSC(p, None, self.cfg["robots"]["arm"]["controller_config"]["controller_params"])
         self.robot = BatchedRobotArm(p, self.osc, None, self.cfg["control_dt"])
         self.strategy = CMAES(6, self.popsize, sigma_init, mean_init, seed)

@@ -56,7 +56,7 @@ static int run(Emu<T>* e, const EmuArgs* a) {
   s.prop_size = (const T*)a->prop_size; s.prop_active = (const unsigned char*)a->prop_active; s.env_mask = (const unsigned char*)a->env_mask;
   s.converged = (unsigned char*)a->converged; s.status = (int*)a->status; s.steps_done = (int*)a->steps_done;
   s.settle_qvel_tol = (T)a->settle_qvel_tol; s.settle_qacc_tol = (T)a->settle_qacc_tol; s.settle_min_steps = a->settle_min_steps;
-  s.out = (T*)a->out; s.out_stride = a->out_stride; s.gains = (const T*)a->gains;
+  s.out = (T*)a->out; s.out_stride = a->out_stride; s.out_mask = OUT_ALL; s.gains = (const T*)a->gains;
   Ctx c = {0, 1};
   for (int env = 0; env < a->n_env; env++) {
     if (s.env_mask && !s.env_mask[env]) continue;

@@ -98,6 +98,24 @@ def test_bad_blob_is_rejected_before_touching_the_device(lib):
     assert b"magic" in lib.b2p_last_error()
 
 
+def test_actuator_pattern_is_checked_at_create(lib):
+    """the kernel folds osc.py:224-236 (tau @ pinv(actuator_moment)[arm, arm]) to the identity; b2p_create must refuse a
+    model where that does not hold (geared arm motor, arm actuator on another dof, gripper actuator reaching an arm dof)."""
+    from blobtools import surgery
+    from mujoco_robot_environments_b200.physics import load_default_blob
+    blob, _ = load_default_blob()
+    lib.b2p_last_error.restype = C.c_char_p
+
+    def geared(c, o, a): a["act_trncoef"][2, 0] = 2.0
+    def moved(c, o, a): a["act_trndof"][3, 0] = 4
+    def gripper_on_arm(c, o, a): a["act_trndof"][7, 1] = 6
+    for edit in (geared, moved, gripper_on_arm):
+        bad = surgery(blob, edit=edit)
+        h = C.c_void_p()
+        assert lib.b2p_create(bad, len(bad), 4, 0, 0, C.byref(h)) == -2, edit.__name__
+        assert b"actuator" in lib.b2p_last_error()
+
+
 def test_physics_backend_refuses_to_run_without_cuda():
     import torch
     if torch.cuda.is_available():

@@ -162,3 +162,26 @@ def test_coupled_blocks_parity(dtype, tol):
             o.step()
         assert np.abs(got[e, :sc.NQ] - o.qpos[:sc.NQ]).max() < tol, kinds[e]
         assert np.abs(got[e, sc.REC_QVEL:sc.REC_QVEL + sc.NV] - o.qvel[:sc.NV]).max() < 200 * tol, kinds[e]
+
+
+def test_output_mask_limits_what_a_stepping_launch_writes():
+    """b2p_set_out_mask: with only the SITE group selected a stepping launch refreshes the site poses (equal to what forward() then
+    reports for the new state) and leaves every other group of the record untouched; the state is bitwise that of an unmasked run."""
+    n = 16
+    st, size, active = sc.make_states(n, seed=21)
+    tg, grip = sc.random_targets(n, seed=22)
+    ref = _phys(n, torch.float64); _load(ref, st, size, active)
+    ref.run_controller(torch.tensor(tg), torch.tensor(grip), 3); torch.cuda.synchronize()
+    p = _phys(n, torch.float64); _load(p, st, size, active)
+    p.out.fill_(-7.0)
+    p.set_out_fields("SITE")
+    p.run_controller(torch.tensor(tg), torch.tensor(grip), 3); torch.cuda.synchronize()
+    assert (p.state == ref.state).all()
+    assert (p.data.site_xpos == ref.data.site_xpos).all() and (p.data.site_xmat == ref.data.site_xmat).all() and (p.data.ncon == ref.data.ncon).all()
+    for grp in ("CONTACT", "MARM", "GEOM_XPOS", "GEOM_XMAT", "QACC", "QFRC_BIAS", "EFC_FORCE"):
+        assert bool((p.derived(grp) == -7.0).all()), grp
+    p.forward(full_contacts=False); torch.cuda.synchronize()           # forward() always writes every group
+    assert not bool((p.derived("GEOM_XPOS") == -7.0).any())
+    assert float((p.data.site_xpos - ref.data.site_xpos).abs().max()) == 0.0
+    with pytest.raises(KeyError):
+        p.set_out_fields("NOPE")
