@@ -60,7 +60,7 @@ struct b2p_handle_s {
   LaunchGeom lg;
   long long launches, order_launches;
   DevModel<double> hmodel;
-  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
+  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void* d_geom_dop; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
   void* d_zero_ctrl; int* d_next_env; void* d_jovf;
   const void* env_gains; const unsigned char* env_mask;
@@ -84,6 +84,7 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   CK(cudaMalloc(&h->d_pair_param, pp.size() * sizeof(PairParam<T>) + 16)); CK(cudaMemcpy(h->d_pair_param, pp.data(), pp.size() * sizeof(PairParam<T>), cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_g1, g1.size() * 2 + 16)); CK(cudaMemcpy(h->d_g1, g1.data(), g1.size() * 2, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_g2, g2.size() * 2 + 16)); CK(cudaMemcpy(h->d_g2, g2.data(), g2.size() * 2, cudaMemcpyHostToDevice));
+  { std::vector<T> dop(ht.geom_dop.begin(), ht.geom_dop.end()); CK(cudaMalloc(&h->d_geom_dop, dop.size() * sizeof(T) + 16)); CK(cudaMemcpy(h->d_geom_dop, dop.data(), dop.size() * sizeof(T), cudaMemcpyHostToDevice)); }
   CK(cudaMalloc(&h->d_geom_start, ht.geom_start.size() * 4 + 16)); CK(cudaMemcpy(h->d_geom_start, ht.geom_start.data(), ht.geom_start.size() * 4, cudaMemcpyHostToDevice));
   {
     std::vector<NbrPt<T>> np(ht.mesh_nbr.size()); std::vector<NbrSpan> ns(ht.mesh_nbradr.size());
@@ -112,7 +113,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
-  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf};
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (const T*)h->d_geom_dop};
   a.work = h->d_work; a.order = nullptr;
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
@@ -167,7 +168,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_geom_dop, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;

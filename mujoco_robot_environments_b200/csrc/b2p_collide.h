@@ -29,7 +29,7 @@ template <typename T> B2P_HD int start_slot(const T* d) {
   return ((d[0] > T(0.4)) - (d[0] < T(-0.4)) + 1) * 9 + ((d[1] > T(0.4)) - (d[1] < T(-0.4)) + 1) * 3 + ((d[2] > T(0.4)) - (d[2] < T(-0.4)) + 1);
 }
 #ifdef B2P_HOST_COUNTERS
-static long g_support_calls = 0, g_climb_steps = 0, g_mpr_calls = 0;
+static long g_support_calls = 0, g_climb_steps = 0, g_mpr_calls = 0, g_cand = 0, g_bb_calls = 0, g_steps = 0, g_pair_mpr[1024] = {0};
 #endif
 template <typename T>
 B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
@@ -114,7 +114,7 @@ template <typename T> B2P_HD T point_tri_dist2(const T* a, const T* b, const T* 
 }
 // Minkowski portal refinement (libccd ccdMPRPenetration, what mjc_Convex runs in MuJoCo 3.2.x)
 template <typename T>
-B2P_HDN bool mpr_penetration(CObj<T>& o1, CObj<T>& o2, const Globals<T>& g, int maxiter, T tol, T& depth, T* dir, T* pos) {
+B2P_HDN bool mpr_penetration(CObj<T>& o1, CObj<T>& o2, const Globals<T>& g, int maxiter, T tol, T& depth, T* dir, T* pos, T* wit = nullptr) {   // wit: separation witness of a query that ends at its first test (SepCache)
   Sup<T> p[4], v4; T d[3], va[3], vb[3];
 #ifdef B2P_HOST_COUNTERS
   g_mpr_calls++;
@@ -125,7 +125,14 @@ B2P_HDN bool mpr_penetration(CObj<T>& o1, CObj<T>& o2, const Globals<T>& g, int 
   normalize3(d);
   mink_support(o1, o2, g, d, p[1]);
   T dt = dot3(p[1].v, d);
-  if (is_zero(dt) || dt < 0) return false;
+  if (is_zero(dt) || dt < 0) {
+    if (wit) {   // the objects (inflated by margin / 2 each) are -dt apart along d: d and the two exact support heights (margin taken out)
+      T a[3], b[3];
+      for (int k = 0; k < 3; k++) { a[k] = p[1].v1[k] - o1.pos[k]; b[k] = p[1].v2[k] - o2.pos[k]; }
+      cp3(wit, d); wit[3] = (dot3(a, d) - T(0.5) * o1.margin) + (-dot3(b, d) - T(0.5) * o2.margin); wit[4] = 1;
+    }
+    return false;
+  }
   cross3(d, p[0].v, p[1].v);
   if (is_zero(dot3(d, d))) {
     if (is_zero(dot3(p[1].v, p[1].v))) { depth = 0; dir[0] = dir[1] = dir[2] = 0; }
@@ -212,6 +219,38 @@ B2P_HD int plane_box(const T* ppos, const T* pmat, const T* bpos, const T* bmat,
     for (int k = 0; k < 3; k++) { w[k] += bpos[k]; dif[k] = w[k] - ppos[k]; }
     const T dist = dot3(dif, n);
     if (dist > margin) continue;
+    out.dist[cnt] = dist;
+    for (int k = 0; k < 3; k++) out.pos[cnt][k] = w[k] - T(0.5) * dist * n[k];
+    cnt++;
+  }
+  return cnt;
+}
+
+// mjc_PlaneConvex for a hull: the support vertex along -normal, then the support vertices of three directions tilted off -normal
+// (120 degrees apart), kept when they are new vertices inside the margin: at most 4 contacts (oracle: plane_convex, same constants).
+#define B2P_PLANE_TILT 0.05
+template <typename T>
+B2P_HDN int plane_convex(const T* ppos, const T* pmat, CObj<T>& hull, const Globals<T>& g, T margin, RawCon<T>& out) {
+  const T n[3] = {pmat[2], pmat[5], pmat[8]}, t1[3] = {pmat[0], pmat[3], pmat[6]}, t2[3] = {pmat[1], pmat[4], pmat[7]};
+  int cnt = 0, seen[4] = {-1, -1, -1, -1};
+  cp3(out.normal, n);
+  for (int q = 0; q < 4; q++) {
+    T dir[3];
+    if (q == 0) { for (int k = 0; k < 3; k++) dir[k] = -n[k]; }
+    else {
+      const T ca = q == 1 ? T(1) : T(-0.5), sa = q == 1 ? T(0) : (q == 2 ? T(0.8660254037844387) : T(-0.8660254037844387));   // cos / sin of 0, 120, 240 degrees
+      for (int k = 0; k < 3; k++) dir[k] = -n[k] + T(B2P_PLANE_TILT) * (ca * t1[k] + sa * t2[k]);
+      normalize3(dir);
+    }
+    T w[3];
+    support(hull, g, dir, w);
+    bool dup = false;
+    for (int i = 0; i < 4; i++) if (i < cnt && seen[i] == hull.cur) dup = true;
+    if (dup) continue;
+    const T dif[3] = {w[0] - ppos[0], w[1] - ppos[1], w[2] - ppos[2]};
+    const T dist = dot3(dif, n);
+    if (dist > margin) continue;
+    for (int i = 0; i < 4; i++) if (i == cnt) seen[i] = hull.cur;
     out.dist[cnt] = dist;
     for (int k = 0; k < 3; k++) out.pos[cnt][k] = w[k] - T(0.5) * dist * n[k];
     cnt++;
@@ -345,6 +384,52 @@ B2P_HD bool obb_separated(const T* p1, const T* m1, const T* c1, const T* h1, co
   return false;
 }
 
+// Upper bound of a geom's support height (about its frame origin, no margin) along the unit world direction d.  Boxes: exact.  Hulls:
+// the 26-DOP bound -- d in the geom frame is split into non-negative multiples of one axis, one face diagonal and one body diagonal of
+// its octant, and the support function is sublinear, so the same combination of the tabulated support values is >= the true support.
+template <typename T>
+B2P_HD T support_bound(const T* mat, const T* half, const T* dop, int type, const T* d) {
+  T l[3]; mulmtv(l, mat, d);
+  const T a0 = fabs(l[0]), a1 = fabs(l[1]), a2 = fabs(l[2]);
+  if (type == B2P_GEOM_BOX) return a0 * half[0] + a1 * half[1] + a2 * half[2];
+  const int s0 = l[0] < 0 ? -1 : 1, s1 = l[1] < 0 ? -1 : 1, s2 = l[2] < 0 ? -1 : 1;
+  // order the components: hi >= mid >= lo
+  int ih = 0, im = 1, il = 2; T hi = a0, mid = a1, lo = a2;
+  if (mid > hi) { T t = hi; hi = mid; mid = t; int k = ih; ih = im; im = k; }
+  if (lo > mid) { T t = mid; mid = lo; lo = t; int k = im; im = il; il = k; }
+  if (mid > hi) { T t = hi; hi = mid; mid = t; int k = ih; ih = im; im = k; }
+  const int w[3] = {9, 3, 1}, sg[3] = {s0, s1, s2};
+  const int q1 = 13 + sg[ih] * w[ih], q2 = q1 + sg[im] * w[im], q3 = q2 + sg[il] * w[il];
+  return (hi - mid) * dop[q1] + (mid - lo) * dop[q2] + lo * dop[q3];
+}
+// true when the geoms are certainly more than md apart along the line of centres -- exactly the first test of the MPR query
+// (mpr_penetration: dt <= 0 after the first Minkowski support), decided here from bounds without walking a hull graph
+template <typename T>
+B2P_HD bool centre_axis_separated(const T* p1, const T* m1, const T* h1, const T* dop1, int t1, const T* p2, const T* m2, const T* h2, const T* dop2, int t2, T md) {
+  T d[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+  const T len = normalize3(d);
+  if (len < T(1e-6)) return false;
+  const T nd[3] = {-d[0], -d[1], -d[2]};
+  const T gap = len - support_bound(m1, h1, dop1, t1, d) - support_bound(m2, h2, dop2, t2, nd) - md;
+  return gap > T(256) * Num<T>::eps() * (1 + len);
+}
+
+// Separation witnesses (Scratch::sep_*): a hull pair whose MPR query ended at its first test was `gap` apart along the line of
+// centres d.  The witness keeps d in BOTH geom frames (dA = RA' d, eB = RB' (-d)) and H = hA(d) + hB(-d), the exact support heights.
+// At a later step d' = RA dA is the same direction as seen from geom 1, so hA(d') = hA(d) exactly, and hB(-d') <= hB(-d) +
+// rB |d' + RB eB| (a hull of radius rB, the support function is rB-Lipschitz).  If the bound still leaves the pair more than the
+// margin apart, the query is skipped: the links of the gripper's four-bar linkage sit millimetres apart for ever, every query on
+// them used to walk two hull graphs (chains of dependent L2 loads) only to find that out.  Conservative, so contact sets are unchanged.
+template <typename T>
+B2P_HD bool witness_separated(const T* w, const T* p1, const T* m1, const T* p2, const T* m2, T rb, T md) {
+  T d[3], e[3];
+  mulmv(d, m1, w); mulmv(e, m2, w + 3);
+  const T err[3] = {d[0] + e[0], d[1] + e[1], d[2] + e[2]};
+  const T dif[3] = {p2[0] - p1[0], p2[1] - p1[1], p2[2] - p1[2]};
+  const T gap = dot3(dif, d) - w[6] - rb * norm3(err) - md;
+  return gap > T(1024) * Num<T>::eps() * (1 + fabs(w[6]));
+}
+
 constexpr int BB_CLIP_REALS = 48;   // box_box clip scratch per lane: 2 polygons x 8 vertices x 3
 // broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
 template <typename T>
@@ -372,12 +457,18 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
         T dif[3] = {s.gpos[g2][0] - s.gpos[g1][0], s.gpos[g2][1] - s.gpos[g1][1], s.gpos[g2][2] - s.gpos[g1][2]};
         if (m.geom_type[g1] == B2P_GEOM_PLANE) {
           T nrm[3] = {s.gmat[g1][2], s.gmat[g1][5], s.gmat[g1][8]};
-          flag = (m.geom_type[g2] == B2P_GEOM_BOX) && !(dot3(dif, nrm) - s.grbound[g2] > md);
+          flag = !(dot3(dif, nrm) - s.grbound[g2] > md);
         } else {
           flag = !(norm3(dif) > s.grbound[g1] + s.grbound[g2] + md);
           if (flag) {   // second filter: the geoms' oriented bounding boxes along their 6 face normals (conservative, so exact)
             const T* h1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
             flag = !obb_separated(s.gpos[g1], s.gmat[g1], m.geom_aabb_c[g1], h1, s.gpos[g2], s.gmat[g2], m.geom_aabb_c[g2], h2, md);
+            // third filter, hull pairs only (they go to MPR): the query's own first test on support bounds
+            if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH))
+              flag = !centre_axis_separated(s.gpos[g1], s.gmat[g1], h1, g.geom_dop + 27 * g1, m.geom_type[g1], s.gpos[g2], s.gmat[g2], h2, g.geom_dop + 27 * g2, m.geom_type[g2], md);
+            if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH)) {   // fourth filter: a separation witness of an earlier step
+              for (int k = 0; k < SEP_N; k++) if (s.sep_pair[k] == p) { if (witness_separated(s.sep_w[k], s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], s.grbound[g2], md)) flag = 0; }
+            }
           }
         }
       }
@@ -393,10 +484,13 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
   csync(c, LK_NARROW);
   if (!active) return;
   const int ncand = s.ncand;
+#ifdef B2P_HOST_COUNTERS
+  g_cand += ncand; g_steps++;
+#endif
   const T tol = m.ccd_tolerance > 16 * Num<T>::eps() ? m.ccd_tolerance : 16 * Num<T>::eps();
   int cbase = 0;
   for (int c0 = 0; c0 < ncand; c0 += c.nt) {
-    const int ci = c0 + c.tid; int n = 0; RawCon<T> raw; int p = -1; T md = 0;
+    const int ci = c0 + c.tid; int n = 0; RawCon<T> raw; int p = -1; T md = 0; T wit[5]; wit[4] = 0;
     // lanes that will run box_box borrow clip scratch from the FK / RNE sweep buffers (crb, cvel, cacc, cfrc), which are dead
     // once dynamics_terms has run: slot = rank among this round's box-box lanes, while slots last
     int bb_flag = 0;
@@ -415,21 +509,34 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
 #if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
       const long long nt0_ = clock64(); int nkind_ = 0;
 #endif
-      if (t1 == B2P_GEOM_PLANE) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
+      if (t1 == B2P_GEOM_PLANE) {
+        if (t2 == B2P_GEOM_BOX) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
+        else {   // an arm link that reaches the ground behind / beside the table
+          CObj<T> h = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, T(0), g.geom_start + 27 * g2};
+          n = plane_convex(s.gpos[g1], s.gmat[g1], h, g, md, raw);
+        }
+      }
       else {
         bool convex = true;
 #if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
         nkind_ = (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) ? 1 : 2;
 #endif
+#ifdef B2P_HOST_COUNTERS
+        if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) g_bb_calls++;
+#endif
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw, clip); convex = n < 0; if (n < 0) n = 0; }
+#ifdef B2P_HOST_COUNTERS
+        if (convex) g_pair_mpr[p & 1023]++;
+#endif
         if (convex) {
           CObj<T> a = {s.gpos[g1], s.gmat[g1], sz1, nullptr, t1, m.geom_vertadr[g1], m.geom_vertnum[g1], -1, md, g.geom_start + 27 * g1};
           CObj<T> b = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, md, g.geom_start + 27 * g2};
           T depth, dir[3], pos[3];
+          wit[4] = 0;
 #ifdef B2P_SKIP_MPR
           if (false) {
 #else
-          if (mpr_penetration(a, b, g, m.ccd_iterations, tol, depth, dir, pos) && depth >= 0) {
+          if (mpr_penetration(a, b, g, m.ccd_iterations, tol, depth, dir, pos, wit) && depth >= 0) {
 #endif
             raw.dist[0] = md - depth; cp3(raw.normal, dir); cp3(raw.pos[0], pos); n = 1;
           }
@@ -441,6 +548,24 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
       int keep = 0;   // drop points not strictly inside the detection margin
       for (int i = 0; i < n; i++) if (raw.dist[i] < md) { if (keep != i) { raw.dist[keep] = raw.dist[i]; cp3(raw.pos[keep], raw.pos[i]); } keep++; }
       n = keep;
+    }
+    {   // new separation witnesses -> the scene's cache: the pair's own slot if it has one, else the next slots of the ring, in lane order
+      bool fresh = wit[4] != 0; int slot = -1;
+      if (fresh) for (int k = 0; k < SEP_N; k++) if (s.sep_pair[k] == p) slot = k;
+      int nnew; const int rk = block_rank(c, fresh && slot < 0, nnew);
+      const bool own = fresh && slot >= 0;
+      if (fresh && slot < 0) slot = (s.sep_next + rk) % SEP_N;
+      bsync(c);
+      for (int phase = 0; phase < 2; phase++) {   // refreshed entries first, then the ring (which may evict any entry): no two lanes write one slot at once
+        if (fresh && own == (phase == 0) && (own || rk < SEP_N)) {
+          const int g1 = g.pair_g1[p], g2 = g.pair_g2[p];
+          const T nd[3] = {-wit[0], -wit[1], -wit[2]};
+          s.sep_pair[slot] = (short)p; mulmtv(s.sep_w[slot], s.gmat[g1], wit); mulmtv(s.sep_w[slot] + 3, s.gmat[g2], nd); s.sep_w[slot][6] = wit[3];
+        }
+        bsync(c);
+      }
+      if (c.tid == 0 && nnew) s.sep_next = (s.sep_next + (nnew < SEP_N ? nnew : SEP_N)) % SEP_N;
+      bsync(c);
     }
     int tot; const int ofs = block_scan(c, n, tot);
     for (int i = 0; i < n; i++) {

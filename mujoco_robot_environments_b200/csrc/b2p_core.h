@@ -125,7 +125,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     for (int i = c.tid; i < MAXP * 3; i += c.nt) s.psize[i / 3][i % 3] = a.prop_size ? a.prop_size[(size_t)env * MAXP * 3 + i] : m.geom_size[0][0];
     for (int i = c.tid; i < MAXP; i += c.nt) s.pactive[i] = i < m.nprop ? (a.prop_active ? a.prop_active[(size_t)env * MAXP + i] : 1) : 0;
     for (int i = c.tid; i < MAXU; i += c.nt) s.ctrl[i] = (a.ctrl && i < m.nu) ? a.ctrl[(size_t)env * m.nu + i] : T(0);
-    if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; }
+    if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; s.sp.nblk = 0; s.sep_next = 0; for (int k = 0; k < SEP_N; k++) s.sep_pair[k] = -1; }   // sp.nblk = 0: no block structure built yet (make_rows)
     bsync(c);
     if (!a.prop_size) {   // default: sizes from the model's prop geoms
       for (int g0 = c.tid; g0 < m.ngeom; g0 += c.nt) if (m.geom_prop[g0] >= 0) for (int k = 0; k < 3; k++) s.psize[m.geom_prop[g0]][k] = m.geom_size[g0][k];

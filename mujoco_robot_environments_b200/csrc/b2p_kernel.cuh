@@ -56,6 +56,8 @@ struct alignas(16) SmemLayout {
   alignas(8) unsigned long long bar[1 + KernelCfg<T>::kWarps];
 };
 
+static_assert(sizeof(SmemLayout<float>) + 128 <= 232448 && sizeof(SmemLayout<double>) + 128 <= 232448, "shared memory per CTA exceeds the 227 KB an sm_100 CTA may use: shrink Pool<T>::JPS or the warps per CTA");
+
 template <typename T, bool kPlace>
 __global__ void __launch_bounds__(32 * KernelCfg<T>::kWarps, KernelCfg<T>::kMinBlocks)
 b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int* __restrict__ next_env) {

@@ -19,7 +19,10 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
     normquat(q + 3); cp3(s.ppos[p], q); quat2mat(s.pmat[p], q + 3);
   }
   bsync(c);
-  for (int l = 0; l < m.nlevel; l++) {
+  // The tree is deep and narrow (the arm is a chain), so a level holds one or two bodies and a level-by-level pass is a serial
+  // chain run by one or two lanes.  Only what truly depends on the parent goes through such passes (A: pose, C: velocity /
+  // acceleration); the per-body inertia and force terms (B, D) run with one lane per body.
+  for (int l = 0; l < m.nlevel; l++) {     // A: pose of every tree body, joint anchor / axis -> cdof
     for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
       const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
       T pos[3], quat[4], a[3];
@@ -36,35 +39,40 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       mulquat(quat, quat, qloc); normquat(quat);
       quat2mat(mat, quat);
       mulmv(a, mat, m.jnt_pos[d]);
-      for (int k = 0; k < 3; k++) { pos[k] = xanchor[k] - a[k]; s.xpos[b][k] = pos[k]; }
+      for (int k = 0; k < 3; k++) s.xpos[b][k] = xanchor[k] - a[k];
       for (int k = 0; k < 4; k++) s.xquat[b][k] = quat[k];
       for (int k = 0; k < 9; k++) s.xmat[b][k] = mat[k];
-      // inertia about the fixed reference point, motion axis
-      T xipos[3], qi[4], ximat[9], off[3];
-      mulmv(xipos, mat, m.tb_ipos[b]);
-      for (int k = 0; k < 3; k++) off[k] = pos[k] + xipos[k] - m.ref[k];
-      mulquat(qi, quat, m.tb_iquat[b]); quat2mat(ximat, qi);
-      T cinert[10];
-      inert_com(cinert, m.tb_inertia[b], ximat, off, m.tb_mass[b]);
-      for (int k = 0; k < 10; k++) s.crb[b][k] = cinert[k];
-      T* cd = s.cdof[d];
+      T* cd = s.cdof[d]; T off[3];                       // motion axis about the fixed reference point
       cp3(cd, xaxis);
       for (int k = 0; k < 3; k++) off[k] = m.ref[k] - xanchor[k];
       cross3(cd + 3, xaxis, off);
-      // velocity: cdof_dot = cvel_parent x cdof ; cvel = cvel_parent + cdof*qvel
-      T v[6];
-      for (int k = 0; k < 6; k++) v[k] = s.cvel[p][k];
-      T cdof_dot[6];
-      cross_motion(cdof_dot, v, cd);
-      for (int k = 0; k < 6; k++) { v[k] += cd[k] * s.qvel[d]; s.cvel[b][k] = v[k]; }
-      // rne forward: cacc = cacc_parent + cdof_dot*qvel ; cfrc = I*cacc + cvel x* (I*cvel)
-      T acc[6], Ia[6], Iv[6], cf[6];
-      for (int k = 0; k < 6; k++) { acc[k] = s.cacc[p][k] + cdof_dot[k] * s.qvel[d]; s.cacc[b][k] = acc[k]; }
-      mul_inert_vec(Ia, cinert, acc); mul_inert_vec(Iv, cinert, v); cross_force(cf, v, Iv);
-      for (int k = 0; k < 6; k++) s.cfrc[b][k] = Ia[k] + cf[k];
     }
     bsync(c);
   }
+  for (int b = 1 + c.tid; b < m.ntb; b += c.nt) {   // B: inertia about the fixed reference point
+    T xipos[3], qi[4], ximat[9], off[3];
+    mulmv(xipos, s.xmat[b], m.tb_ipos[b]);
+    for (int k = 0; k < 3; k++) off[k] = s.xpos[b][k] + xipos[k] - m.ref[k];
+    mulquat(qi, s.xquat[b], m.tb_iquat[b]); quat2mat(ximat, qi);
+    inert_com(s.crb[b], m.tb_inertia[b], ximat, off, m.tb_mass[b]);
+  }
+  for (int l = 0; l < m.nlevel; l++) {     // C: cvel = cvel_parent + cdof*qvel ; cacc = cacc_parent + (cvel_parent x cdof)*qvel
+    for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
+      const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
+      const T* cd = s.cdof[d]; const T qv = s.qvel[d];
+      T v[6], cdof_dot[6];
+      for (int k = 0; k < 6; k++) v[k] = s.cvel[p][k];
+      cross_motion(cdof_dot, v, cd);
+      for (int k = 0; k < 6; k++) { s.cvel[b][k] = v[k] + cd[k] * qv; s.cacc[b][k] = s.cacc[p][k] + cdof_dot[k] * qv; }
+    }
+    bsync(c);
+  }
+  for (int b = 1 + c.tid; b < m.ntb; b += c.nt) {   // D: rne forward force  cfrc = I*cacc + cvel x* (I*cvel)
+    T Ia[6], Iv[6], cf[6];
+    mul_inert_vec(Ia, s.crb[b], s.cacc[b]); mul_inert_vec(Iv, s.crb[b], s.cvel[b]); cross_force(cf, s.cvel[b], Iv);
+    for (int k = 0; k < 6; k++) s.cfrc[b][k] = Ia[k] + cf[k];
+  }
+  bsync(c);
   // geoms + sites
   for (int g = c.tid; g < m.ngeom; g += c.nt) {
     const int b = m.geom_body[g];

@@ -43,10 +43,10 @@ constexpr int PROP_BODY0 = MAXTB;
 // (grasps, arm contacts) spill to a per-warp overflow area in global memory (L1/L2 resident): shared memory per scene is what
 // bounds the scenes in flight per SM, and the kernel is latency bound.
 #ifndef B2P_JPS_F32
-#define B2P_JPS_F32 768
+#define B2P_JPS_F32 704
 #endif
 #ifndef B2P_JPS_F64
-#define B2P_JPS_F64 704
+#define B2P_JPS_F64 640
 #endif
 template <typename T> struct Pool { static constexpr int EFC = B2P_EFC_F32, JP = B2P_JPOOL_F32, JPS = B2P_JPS_F32; };
 template <> struct Pool<double> { static constexpr int EFC = 160, JP = 2944, JPS = B2P_JPS_F64; };
@@ -106,7 +106,7 @@ struct alignas(16) DevModel {
 
 // ------------------------------------------------------------------------------------------ host builder
 struct HostTables {              // global-memory tables, always fp64 on host; converted on upload
-  std::vector<double> mesh_vert; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr, geom_start;
+  std::vector<double> mesh_vert, geom_dop; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr, geom_start;
   std::vector<int> pair_g1, pair_g2; std::vector<double> pair_param;  // 12 doubles per pair
 };
 
@@ -251,7 +251,10 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
       for (int q = ht.mesh_nbradr[v]; q < ht.mesh_nbradr[v] + ht.mesh_nbrnum[v]; q++) ht.mesh_nbr[q] += vadr[me];
   }
   // hill-climb start table: for every mesh geom and each of the 26 quantised directions the hull's extreme vertex (global index)
-  ht.geom_start.assign((size_t)MAXG * 27, 0);
+  // ... and the support VALUE along the same 26 (unnormalised) directions: a 26-DOP around the hull.  The support function is
+  // sublinear, so for any direction written as a non-negative combination of three of these the combination of the tabulated
+  // values bounds the hull's support from above -- the broad phase rejects hull pairs with it without touching the hull graph.
+  ht.geom_start.assign((size_t)MAXG * 27, 0); ht.geom_dop.assign((size_t)MAXG * 27, 0.0);
   for (int g = 0; g < m.ngeom; g++) {
     if (m.geom_vertnum[g] <= 0) continue;
     for (int q = 0; q < 27; q++) {
@@ -262,6 +265,7 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
         if (x > bd) { bd = x; best = v; }
       }
       ht.geom_start[(size_t)g * 27 + q] = best;
+      ht.geom_dop[(size_t)g * 27 + q] = q == 13 ? 0.0 : bd * (1 + 1e-6) + 1e-9;   // rounded up: stays an upper bound after the cast to float
     }
   }
   const int *p1 = b.I(B2PM_F_PAIR_GEOM1), *p2 = b.I(B2PM_F_PAIR_GEOM2), *prio = b.I(B2PM_F_GEOM_PRIORITY);

@@ -5,6 +5,8 @@ namespace b2p {
 
 // ------------------------------------------------------------------------------------------ constraints
 template <typename T>
+B2P_HDN T impedance_pow(T x, T mid, T pw) { return x <= mid ? pow(x, pw) / pow(mid, pw - 1) : 1 - pow(1 - x, pw) / pow(1 - mid, pw - 1); }
+template <typename T>
 B2P_HD T impedance(const T* si, T pos, T margin) {
   const T d0 = clampT(si[0], T(0.0001), T(0.9999)), d1 = clampT(si[1], T(0.0001), T(0.9999)), w = si[2] > 0 ? si[2] : T(0);
   const T mid = clampT(si[3], T(0.0001), T(0.9999)), pw = si[4] > 1 ? si[4] : T(1);
@@ -13,8 +15,8 @@ B2P_HD T impedance(const T* si, T pos, T margin) {
   if (x >= 1) return d1;
   if (x <= 0) return d0;
   if (pw == 1) y = x;
-  else if (x <= mid) y = pow(x, pw) / pow(mid, pw - 1);
-  else y = 1 - pow(1 - x, pw) / pow(1 - mid, pw - 1);
+  else if (pw == 2) y = x <= mid ? x * x / mid : 1 - (1 - x) * (1 - x) / (1 - mid);   // MuJoCo's default power: no pow() (x * x IS the correctly rounded pow(x, 2))
+  else y = impedance_pow(x, mid, pw);
   return d0 + y * (d1 - d0);
 }
 // K, B, imp, R for one row (mj_makeImpedance, App. B item 9)
@@ -58,10 +60,12 @@ B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
 template <typename T> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s, int r) { return row_dot(m, s, r, s.qvel); }
 
 // mj_makeConstraint + mj_referenceConstraint: equality -> limits -> contacts, rows complete incl. aref.
-// One lane builds one item (an equality, a joint limit side, or a contact = 3 rows); row numbers and packed-Jacobian
-// offsets come from warp prefix sums, so the row order is deterministic and identical to MuJoCo's.  The same pass
-// records, per dof block, which items touch it (brow lists) and which blocks share a row (cpl_pairs) -- the sparsity
-// the Newton solver exploits.
+// Pass 1, one lane per ITEM (an equality, a joint limit side, or a contact = 3 rows): which items exist, their row numbers and
+// packed-Jacobian offsets from warp prefix sums (so the row order is deterministic and identical to MuJoCo's), the per-block item
+// lists (brow) and which blocks share a row (cpl_pairs) -- the sparsity the Newton solver exploits.
+// Pass 2, one lane per ROW: the Jacobian row, impedance / regularisation and the reference acceleration.  The rows of one item are
+// independent of each other, and a row on the tree is a 15-dof loop per body: one lane per item made the two connect equalities
+// (3 rows x 2 tree bodies each) the critical path of the whole stage.
 template <typename T>
 B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
   const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
@@ -69,12 +73,12 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
   int nb[SP_MAXBLK];
   for (int b = 0; b < SP_MAXBLK; b++) nb[b] = 0;
   for (int i0 = 0; i0 < nitem; i0 += c.nt) {
-    const int it = i0 + c.tid; int nr = 0, kind = -1, id = 0, ba = 0, bb = -1, seg1 = 0, seg2 = 0; T dist = 0;
+    const int it = i0 + c.tid; int nr = 0, kind = -1, id = 0, ba = 0, bb = -1;
     if (it < nitem) {
       if (it < m.neq) { kind = ROW_EQ; id = it; nr = m.eq_type[it] == B2P_EQ_CONNECT ? 3 : 1; }
       else if (it < m.neq + nlim) {
         const int j = (it - m.neq) >> 1, side = ((it - m.neq) & 1) ? 1 : -1;
-        if (m.jnt_limited[j]) { dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]); if (dist < m.jnt_margin[j]) { kind = ROW_LIMIT; id = j * 2 + (side > 0); nr = 1; } }
+        if (m.jnt_limited[j]) { const T dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]); if (dist < m.jnt_margin[j]) { kind = ROW_LIMIT; id = j * 2 + (side > 0); nr = 1; } }
       } else {
         id = it - m.neq - nlim;
         if (s.c_dist[id] < s.c_incl[id]) {
@@ -83,8 +87,8 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
           const int p = s.c_pair[id], b1 = m.geom_body[g.pair_g1[p]], b2 = m.geom_body[g.pair_g2[p]];
           const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
           ba = (t1 || t2) ? 0 : -1;
-          if (b1 >= PROP_BODY0) { if (ba < 0) ba = 1 + b1 - PROP_BODY0; else { bb = 1 + b1 - PROP_BODY0; seg1 = block_width(m, ba); } }
-          if (b2 >= PROP_BODY0) { if (ba < 0) ba = 1 + b2 - PROP_BODY0; else { bb = 1 + b2 - PROP_BODY0; seg2 = block_width(m, ba); } }
+          if (b1 >= PROP_BODY0) { if (ba < 0) ba = 1 + b1 - PROP_BODY0; else bb = 1 + b1 - PROP_BODY0; }
+          if (b2 >= PROP_BODY0) { if (ba < 0) ba = 1 + b2 - PROP_BODY0; else bb = 1 + b2 - PROP_BODY0; }
           if (ba < 0) { kind = -1; nr = 0; }     // static-static pairs never reach here (filtered at compile time)
         }
       }
@@ -103,46 +107,8 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
         s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
         s.joff[r0 + q] = (short)(in_smem ? j0 + q * w : -(j0 + q * w) - 1);
       }
-      T* J0 = in_smem ? s.Jp + j0 : s.jovf + j0;
-      for (int k = 0; k < nr * w; k++) J0[k] = 0;
-      if (kind == ROW_EQ && nr == 3) {
-        const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];
-        mulmv(g1, s.xmat[b1], m.eq_data[id]); mulmv(g2, s.xmat[b2], m.eq_data[id] + 3);
-        for (int k = 0; k < 3; k++) { g1[k] += s.xpos[b1][k]; g2[k] += s.xpos[b2][k]; res[k] = g1[k] - g2[k]; }
-        const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
-        for (int q = 0; q < 3; q++) {
-          T ax[3] = {T(q == 0), T(q == 1), T(q == 2)};
-          add_jac(m, s, J0 + q * w, 0, b1, g1, ax, T(1)); add_jac(m, s, J0 + q * w, 0, b2, g2, ax, T(-1));
-          T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
-          s.D[r0 + q] = 1 / R; s.aref[r0 + q] = -B * row_vel(m, s, r0 + q) - K * imp * res[q];
-        }
-      } else if (kind == ROW_EQ) {
-        const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
-        const T x = s.qpos[j2] - m.qpos0[j2], pos = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
-        J0[j1] = 1; J0[j2] = -cf[1];
-        T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], pos, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
-        s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * pos;
-      } else if (kind == ROW_LIMIT) {
-        const int j = id >> 1, side = (id & 1) ? 1 : -1;
-        J0[j] = T(-side);
-        T K, B, imp, R; row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
-        s.D[r0] = 1 / R; s.aref[r0] = -B * row_vel(m, s, r0) - K * imp * (dist - m.jnt_margin[j]);
-      } else {
-        const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
-        const PairParam<T>& pp = g.pair_param[p];
-        const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
-        T K, B, imp, R0;
-        row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
-        const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
-        s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0); s.c_row[id] = (short)r0;
-        for (int q = 0; q < 3; q++) {
-          const T* ax = s.c_frame[id] + 3 * q;
-          add_jac(m, s, J0 + q * w, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0 + q * w, seg1, b1, s.c_pos[id], ax, T(-1));
-          const T vel = row_vel(m, s, r0 + q);
-          if (q == 0) { s.D[r0] = 1 / R0; s.aref[r0] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
-          else { s.D[r0 + q] = 1 / R1; s.aref[r0 + q] = -B * vel; }
-        }
-      }
+      if (kind == ROW_CONTACT) s.c_row[id] = (short)r0;
+      else if (kind == ROW_EQ) s.eq_row0[id] = (short)r0;
       if (bb >= 0) {   // solver blocks: prop p -> p, tree -> nprop
         const int sa = ba == 0 ? m.nprop : ba - 1, sb = bb - 1, hi = sa > sb ? sa : sb, lo = sa > sb ? sb : sa;
         pairs |= 1u << (hi * SP_MAXBLK + lo);
@@ -157,12 +123,63 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
   }
   first_drop = block_min(c, first_drop);
   pairs = block_or(c, pairs);
+  // the block structure depends on the coupling bits only: it is kept from step to step and rebuilt (by one lane, serially) only
+  // when a contact starts or stops coupling two blocks
+  const bool rebuild = s.sp.nblk != nblk || s.cpl_pairs != pairs;
+  const int nefc = base < first_drop ? base : first_drop;
+  bsync(c);
   if (c.tid == 0) {
-    s.nefc = base < first_drop ? base : first_drop; s.jused = jbase; s.cpl_pairs = pairs;
+    s.nefc = nefc; s.jused = jbase; s.cpl_pairs = pairs;
     for (int b = 0; b < SP_MAXBLK; b++) s.nbrow[b] = nb[b];
   }
+  for (int r = c.tid; r < nefc; r += c.nt) {
+    const int kind = s.row_type[r], id = s.row_id[r], ba = s.row_a[r], bb = s.row_b[r];
+    const int w = block_width(m, ba) + (bb >= 0 ? 6 : 0);
+    const int jo = s.joff[r];
+    T* J0 = jo >= 0 ? s.Jp + jo : s.jovf + (-jo - 1);
+    for (int k = 0; k < w; k++) J0[k] = 0;
+    if (kind == ROW_EQ && m.eq_type[id] == B2P_EQ_CONNECT) {
+      const int q = r - s.eq_row0[id];
+      const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];
+      mulmv(g1, s.xmat[b1], m.eq_data[id]); mulmv(g2, s.xmat[b2], m.eq_data[id] + 3);
+      for (int k = 0; k < 3; k++) { g1[k] += s.xpos[b1][k]; g2[k] += s.xpos[b2][k]; res[k] = g1[k] - g2[k]; }
+      const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
+      const T ax[3] = {T(q == 0), T(q == 1), T(q == 2)};
+      add_jac(m, s, J0, 0, b1, g1, ax, T(1)); add_jac(m, s, J0, 0, b2, g2, ax, T(-1));
+      T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
+      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * (q == 0 ? res[0] : (q == 1 ? res[1] : res[2]));
+    } else if (kind == ROW_EQ) {
+      const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
+      const T x = s.qpos[j2] - m.qpos0[j2], pos = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
+      J0[j1] = 1; J0[j2] = -cf[1];
+      T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], pos, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
+      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * pos;
+    } else if (kind == ROW_LIMIT) {
+      const int j = id >> 1, side = (id & 1) ? 1 : -1;
+      const T dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]);
+      J0[j] = T(-side);
+      T K, B, imp, R; row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
+      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * (dist - m.jnt_margin[j]);
+    } else {
+      const int q = r - s.c_row[id];
+      const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
+      const PairParam<T>& pp = g.pair_param[p];
+      // segment of each body inside the packed row: the tree (or the first prop) heads it, a second block follows
+      const int seg1 = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0, seg2 = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
+      const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
+      T K, B, imp, R0;
+      row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
+      const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
+      if (q == 0) s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0);
+      const T* ax = s.c_frame[id] + 3 * q;
+      add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1));
+      const T vel = row_vel(m, s, r);
+      if (q == 0) { s.D[r] = 1 / R0; s.aref[r] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
+      else { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
+    }
+  }
   bsync(c);
-  sp_build(s.sp, m.nprop, m.ntd, pairs, c);
+  if (rebuild) sp_build(s.sp, m.nprop, m.ntd, pairs, c);
 }
 
 }  // namespace b2p

@@ -7,6 +7,7 @@ namespace b2p {
 // HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
 constexpr int REC_QPOS = 0, REC_QVEL = MAXNQ, REC_QACC = MAXNQ + MAXNV, REC_TIME = MAXNQ + 2 * MAXNV, REC_SIZE = 128;
 // one hull-graph neighbour with its coordinates inline (one 16-byte load in fp32), and (first neighbour, count) per vertex
+constexpr int SEP_N = 8;             // separation witnesses kept per scene
 template <typename T> struct alignas(16) NbrPt { T x, y, z; int idx; };
 struct NbrSpan { int adr, num; };
 template <typename T>
@@ -17,6 +18,7 @@ struct Globals {                 // read-only global-memory tables
   const NbrPt<T>* nbr_pt;        // [nmeshnbr] neighbour vertex coordinates + index, same order as nbr
   const NbrSpan* nbr_span;       // [nmeshvert]
   T* jovf;                       // [warp slots][Pool<T>::JP] Jacobian rows that do not fit a scene's shared-memory pool
+  const T* geom_dop;             // [ngeom][27] hull support value along the 26 directions {-1,0,1}^3 (mesh geoms): 26-DOP bound
 };
 
 // Shared memory per scene is what bounds the number of resident warps (= scenes in flight) per SM, and the kernel is latency
@@ -46,10 +48,12 @@ struct alignas(16) Scratch {
   T Jp[Pool<T>::JPS], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
   T* jovf;                       // this warp's overflow area (global memory, Pool<T>::JP reals): joff[r] < 0 <=> row r lives at jovf[-joff[r] - 1]
   signed char row_a[Pool<T>::EFC], row_b[Pool<T>::EFC], row_type[Pool<T>::EFC], row_state[Pool<T>::EFC];
-  short row_id[Pool<T>::EFC], joff[Pool<T>::EFC];
+  short row_id[Pool<T>::EFC], joff[Pool<T>::EFC], eq_row0[MAXEQ];   // eq_row0: first row of equality e
   // per-block row lists (block 0 = tree, 1+p = prop p): first row of every item (eq/limit row, or contact triple)
   unsigned char brow0[Pool<T>::EFC], browp[MAXP][MAXCON]; int nbrow[SP_MAXBLK];
   SpStruct sp;                   // block structure of the Newton Hessian in solver order (props first, tree last)
+  // separation witnesses of hull pairs (b2p_collide.h: witness_separated): pair id (-1 = free), dA[3] | eB[3] | H ; ring cursor
+  T sep_w[SEP_N][7]; short sep_pair[SEP_N]; int sep_next;
   // settle / frozen-arm support
   T hold_q[MAXTD], hold_v[MAXTD];
   union {                        // ---- storage shared between step1-only ("pos") and step2-only ("dyn") buffers, part 1

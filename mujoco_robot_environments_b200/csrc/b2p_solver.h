@@ -248,10 +248,13 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c
   T gn2 = 0, cost = 0; bool dirty = true;
   PROF_T0
   if (has) {
-    const T cw = cost_at(m, s, c, s.qacc_ws), cs = cost_at(m, s, c, s.qacc_smooth);
-    for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = cw < cs ? s.qacc_ws[d] : s.qacc_smooth[d];
+    // warm start: the cheaper of qacc_warmstart and qacc_smooth.  The warm start wins in all but the first step of a contact, so it is
+    // evaluated LAST: s.Jaref / s.Ma then already describe the starting point and the third evaluation is only needed otherwise.
+    const T cs = cost_at(m, s, c, s.qacc_smooth), cw = cost_at(m, s, c, s.qacc_ws);
+    const bool use_ws = cw < cs;
+    for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = use_ws ? s.qacc_ws[d] : s.qacc_smooth[d];
     bsync(c);
-    cost_at(m, s, c, s.qacc);
+    if (!use_ws) cost_at(m, s, c, s.qacc);
     NANCHK(2, s.Jaref, s.nefc)
     cost = solver_update(m, s, c, gn2, dirty);
     NANCHK(3, s.grad, nv) NANCHK(4, &s.cW[0][0], 6 * s.ncon)

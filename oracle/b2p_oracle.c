@@ -582,6 +582,46 @@ static int plane_box(const double* ppos, const double* pmat, const double* bpos,
   return cnt;
 }
 
+/* mjc_PlaneConvex (engine_collision_convex.c) for a hull: the support vertex along -normal, then the support vertices of three
+ * directions tilted off -normal (120 degrees apart in the plane), kept when they are new vertices inside the margin -- at most 4
+ * contacts, all with the plane normal.  RECOLLECTION of MuJoCo 3.2.7: the tilt magnitude is not pinned;
+ * B2P_PLANE_TILT is used by the oracle and the kernel alike.  `vid` returns the chosen vertex so that duplicates are dropped by
+ * identity, not by distance. */
+#define B2P_PLANE_TILT 0.05
+static void support_vertex(cobj_t* c, const double* dir, double* res, int* vid) {
+  double keep = c->margin; c->margin = 0; support(c, dir, res); c->margin = keep;
+  double ld[3]; mulmatTvec3(ld, c->mat, dir);
+  int best = 0; double bd = -1e300;
+  for (int i = 0; i < c->nvert; i++) { double d = dot3(c->vert + 3 * i, ld); if (d > bd) { bd = d; best = i; } }
+  *vid = best;
+}
+static int plane_convex(const double* ppos, const double* pmat, cobj_t* hull, double margin, rawcon_t* out) {
+  double n[3] = {pmat[2], pmat[5], pmat[8]}, t1[3] = {pmat[0], pmat[3], pmat[6]}, t2[3] = {pmat[1], pmat[4], pmat[7]};
+  int cnt = 0, seen[4];
+  for (int q = 0; q < 4; q++) {
+    double dir[3];
+    if (q == 0) for (int k = 0; k < 3; k++) dir[k] = -n[k];
+    else {
+      const double ca = q == 1 ? 1.0 : -0.5, sa = q == 1 ? 0.0 : (q == 2 ? 0.8660254037844387 : -0.8660254037844387);   /* 0, 120, 240 degrees */
+      for (int k = 0; k < 3; k++) dir[k] = -n[k] + B2P_PLANE_TILT * (ca * t1[k] + sa * t2[k]);
+      normalize3(dir);
+    }
+    double w[3]; int vid;
+    support_vertex(hull, dir, w, &vid);
+    int dup = 0;
+    for (int i = 0; i < cnt; i++) if (seen[i] == vid) dup = 1;
+    if (dup) continue;
+    double dif[3] = {w[0] - ppos[0], w[1] - ppos[1], w[2] - ppos[2]};
+    const double dist = dot3(dif, n);
+    if (dist > margin) continue;
+    seen[cnt] = vid;
+    out[cnt].dist = dist; memcpy(out[cnt].normal, n, 24);
+    for (int k = 0; k < 3; k++) out[cnt].pos[k] = w[k] - 0.5 * dist * n[k];
+    cnt++;
+  }
+  return cnt;
+}
+
 /* Box-box: separating-axis test (15 axes) + reference-face clipping (<= 8 points) or edge-edge point.
  * returns #contacts, or -1 when the boxes are separated by 0 < s <= margin (caller falls back to the
  * margin-inflated convex routine, which reports the single closest-feature contact). */
@@ -721,7 +761,11 @@ static void collision(orc_t* o) {
       double nrm[3] = {m1[2], m1[5], m1[8]}, dif[3] = {x2[0] - x1[0], x2[1] - x1[1], x2[2] - x1[2]};
       if (dot3(dif, nrm) - o->geom_rbound[g2] > md) continue;
       if (t2 == B2P_GEOM_BOX) n = plane_box(x1, m1, x2, m2, o->geom_size + 3 * g2, md, raw);
-      else continue; /* plane-mesh: unreachable for this scene (arm cannot reach z<0); documented in DESIGN.md */
+      else if (t2 == B2P_GEOM_MESH) {   /* an arm link below the table edge reaches the ground */
+        int v0 = vadr[gmesh[g2]];
+        cobj_t h = {x2, m2, t2, o->geom_size + 3 * g2, mvert + 3 * v0, vnum[gmesh[g2]], 0, FI(o, B2PM_F_MESH_NBRADR) + v0, FI(o, B2PM_F_MESH_NBRNUM) + v0, FI(o, B2PM_F_MESH_NBR), 0};
+        n = plane_convex(x1, m1, &h, md, raw);
+      } else continue;
     } else {
       double dif[3] = {x2[0] - x1[0], x2[1] - x1[1], x2[2] - x1[2]};
       if (norm3(dif) > o->geom_rbound[g1] + o->geom_rbound[g2] + md) continue;

@@ -12,7 +12,7 @@ using namespace b2p;
 template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
-  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop;
   Globals<T> g; Scratch<T>* s;
 };
 
@@ -32,6 +32,7 @@ static Emu<T>* make(const void* blob, size_t n) {
     p.margin = (T)q[10]; p.gap = (T)q[11]; e->pp.push_back(p);
   }
   e->g.mesh_vert = e->mesh_vert.data(); e->g.nbradr = e->ht.mesh_nbradr.data(); e->g.nbrnum = e->ht.mesh_nbrnum.data(); e->g.nbr = e->ht.mesh_nbr.data(); e->g.geom_start = e->ht.geom_start.data();
+  e->geom_dop.assign(e->ht.geom_dop.begin(), e->ht.geom_dop.end()); e->g.geom_dop = e->geom_dop.data();
   e->nbr_pt.resize(e->ht.mesh_nbr.size()); e->nbr_span.resize(e->ht.mesh_nbradr.size());
   for (size_t q = 0; q < e->nbr_pt.size(); q++) { const int u = e->ht.mesh_nbr[q]; e->nbr_pt[q].x = (T)e->ht.mesh_vert[3 * u]; e->nbr_pt[q].y = (T)e->ht.mesh_vert[3 * u + 1]; e->nbr_pt[q].z = (T)e->ht.mesh_vert[3 * u + 2]; e->nbr_pt[q].idx = u; }
   for (size_t v = 0; v < e->nbr_span.size(); v++) { e->nbr_span[v].adr = e->ht.mesh_nbradr[v]; e->nbr_span[v].num = e->ht.mesh_nbrnum[v]; }
@@ -76,4 +77,20 @@ int emu_out_size() { return OutLayout::SIZE; }
 int emu_scratch_bytes(int dtype) { return dtype == 0 ? (int)sizeof(Scratch<double>) : (int)sizeof(Scratch<float>); }
 int emu_model_bytes(int dtype) { return dtype == 0 ? (int)sizeof(DevModel<double>) : (int)sizeof(DevModel<float>); }
 void emu_destroy(void* h, int dtype) { if (dtype == 0) { auto* e = (Emu<double>*)h; delete e->s; delete e; } else { auto* e = (Emu<float>*)h; delete e->s; delete e; } }
+}
+// narrow-phase census of a run (tools/narrow_census.py; built with -DB2P_HOST_COUNTERS): support calls, hill-climb steps, MPR queries
+extern "C" void emu_pair_mpr(long* out) {
+#ifdef B2P_HOST_COUNTERS
+  for (int i = 0; i < 1024; i++) { out[i] = b2p::g_pair_mpr[i]; b2p::g_pair_mpr[i] = 0; }
+#else
+  for (int i = 0; i < 1024; i++) out[i] = 0;
+#endif
+}
+extern "C" void emu_counters(long* out, int reset) {
+#ifdef B2P_HOST_COUNTERS
+  out[0] = b2p::g_support_calls; out[1] = b2p::g_climb_steps; out[2] = b2p::g_mpr_calls; out[3] = b2p::g_cand; out[4] = b2p::g_bb_calls; out[5] = b2p::g_steps;
+  if (reset) b2p::g_support_calls = b2p::g_climb_steps = b2p::g_mpr_calls = b2p::g_cand = b2p::g_bb_calls = b2p::g_steps = 0;
+#else
+  for (int i = 0; i < 6; i++) out[i] = -1; (void)reset;
+#endif
 }
