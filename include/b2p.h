@@ -70,6 +70,12 @@ enum {
   B2P_OUT_BIAS = 16 /* QFRC_BIAS */, B2P_OUT_DYN = 32 /* QACC, QACC_SMOOTH, CTRL, NITER */, B2P_OUT_EFC = 64 /* EFC_FORCE */, B2P_OUT_ALL = 127
 };
 int b2p_set_out_mask(b2p_handle h, int mask);
+/* Constraint solver of the stepping calls (mjOption.solver; the reference never sets it, tasks/rearrangement.py:77-78, so MuJoCo's
+ * default -- Newton -- is this library's default too).  PGS is MuJoCo's projected Gauss-Seidel on the dual problem (elliptic cones),
+ * offered as the independent minimiser of the same objective and because BASELINE.json names it; it runs as its own kernel
+ * instantiation and is several times slower than Newton on this model class. */
+enum { B2P_SOLVER_NEWTON = 0, B2P_SOLVER_PGS = 1 };
+int b2p_set_solver(b2p_handle h, int solver);
 /* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active);
 /* optional per-scene OSC gains [n_env][6] reals (position kp, kd, orientation kp, kd, nullspace kp, kd): one candidate of the

@@ -62,7 +62,7 @@ struct b2p_handle_s {
   DevModel<double> hmodel;
   void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void* d_geom_dop; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
-  void* d_zero_ctrl; int* d_next_env; void* d_jovf;
+  void* d_zero_ctrl; int* d_next_env; void* d_jovf; void* d_xpool; int solver;
   const void* env_gains; const unsigned char* env_mask;
   int *d_work, *d_order; int work_steps, sort_queue, out_mask;   // work_steps: physics steps behind d_work (0 = none yet)
 };
@@ -113,8 +113,8 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
-  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (const T*)h->d_geom_dop};
-  a.work = h->d_work; a.order = nullptr;
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (T*)h->d_xpool, (const T*)h->d_geom_dop};
+  a.work = h->d_work; a.order = nullptr; a.solver = h->solver;
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
     CK(cudaGetLastError());
@@ -168,7 +168,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_geom_dop, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_geom_dop, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf, h->d_xpool};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;
@@ -201,6 +201,15 @@ int b2p_bind_state(b2p_handle h, void* state) {
 }
 int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out = out ? out : h->own_out; return B2P_OK; }
 int b2p_set_out_mask(b2p_handle h, int mask) { if (!h || mask < 0 || mask > OUT_ALL) return fail(B2P_ERR_ARG, "b2p_set_out_mask: bad argument"); h->out_mask = mask; return B2P_OK; }
+int b2p_set_solver(b2p_handle h, int solver) {
+  if (!h || (solver != B2P_SOLVER_NEWTON && solver != B2P_SOLVER_PGS)) return fail(B2P_ERR_ARG, "b2p_set_solver: bad argument");
+  if (solver == B2P_SOLVER_PGS && !h->d_xpool) {   // M^-1 J' per resident warp, J's packed layout
+    CK(cudaSetDevice(h->device));
+    const size_t w = h->dtype == B2P_F64 ? 8 : 4, jp = h->dtype == B2P_F64 ? Pool<double>::JP : Pool<float>::JP;
+    CK(cudaMalloc(&h->d_xpool, (size_t)h->lg.grid * h->lg.warps_per_cta * jp * w));
+  }
+  h->solver = solver; return B2P_OK;
+}
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
 int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
 int b2p_set_env_mask(b2p_handle h, const uint8_t* mask) { if (!h) return B2P_ERR_ARG; h->env_mask = mask; return B2P_OK; }

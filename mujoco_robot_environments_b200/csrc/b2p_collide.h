@@ -442,12 +442,13 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
     s.grbound[q] = p >= 0 ? norm3(s.psize[p]) : m.geom_rbound[q];
   }
   bsync(c);
+  // Pass 1 over the static pair table (global memory; the next round's entries are fetched while this round is tested): bounding
+  // spheres / plane distance only -- a handful of instructions per pair, every lane busy -- compacted into s.cand by ballot.
   int base = 0;
-  // the pair table lives in global memory: the next round's entries are fetched while this round is tested
   int ng1 = 0, ng2 = 0; T nmd = 0;
   if (c.tid < m.npair) { ng1 = g.pair_g1[c.tid]; ng2 = g.pair_g2[c.tid]; const PairParam<T>& pp = g.pair_param[c.tid]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
   for (int p0 = 0; p0 < m.npair; p0 += c.nt) {
-    const int p = p0 + c.tid; int flag = 0;
+    const int p = p0 + c.tid; bool flag = false;
     if (!B2P_BP_PREFETCH && p < m.npair) { ng1 = g.pair_g1[p]; ng2 = g.pair_g2[p]; const PairParam<T>& pp = g.pair_param[p]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
     const int g1 = ng1, g2 = ng2; const T md = nmd;
     if (B2P_BP_PREFETCH && p + c.nt < m.npair) { const int pn = p + c.nt; ng1 = g.pair_g1[pn]; ng2 = g.pair_g2[pn]; const PairParam<T>& pp = g.pair_param[pn]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
@@ -459,25 +460,46 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
           T nrm[3] = {s.gmat[g1][2], s.gmat[g1][5], s.gmat[g1][8]};
           flag = !(dot3(dif, nrm) - s.grbound[g2] > md);
         } else {
-          flag = !(norm3(dif) > s.grbound[g1] + s.grbound[g2] + md);
-          if (flag) {   // second filter: the geoms' oriented bounding boxes along their 6 face normals (conservative, so exact)
-            const T* h1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
-            flag = !obb_separated(s.gpos[g1], s.gmat[g1], m.geom_aabb_c[g1], h1, s.gpos[g2], s.gmat[g2], m.geom_aabb_c[g2], h2, md);
-            // third filter, hull pairs only (they go to MPR): the query's own first test on support bounds
-            if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH))
-              flag = !centre_axis_separated(s.gpos[g1], s.gmat[g1], h1, g.geom_dop + 27 * g1, m.geom_type[g1], s.gpos[g2], s.gmat[g2], h2, g.geom_dop + 27 * g2, m.geom_type[g2], md);
-            if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH)) {   // fourth filter: a separation witness of an earlier step
-              for (int k = 0; k < SEP_N; k++) if (s.sep_pair[k] == p) { if (witness_separated(s.sep_w[k], s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], s.grbound[g2], md)) flag = 0; }
-            }
-          }
+          const T rr = s.grbound[g1] + s.grbound[g2] + md;
+          flag = !(dot3(dif, dif) > rr * rr);
         }
       }
     }
-    int tot; const int ofs = block_scan(c, flag, tot);
+    int tot; const int ofs = block_rank(c, flag, tot);
     if (flag && base + ofs < MAXCAND) s.cand[base + ofs] = (short)p;
     base += tot;
   }
-  if (c.tid == 0) { s.ncand = base < MAXCAND ? base : MAXCAND; if (base > MAXCAND) s.flags |= FLAG_CANDFULL; }
+  unsigned full = base > MAXCAND ? FLAG_CANDFULL : 0;
+  const int n1 = base < MAXCAND ? base : MAXCAND;
+  bsync(c);
+  // Pass 2 over the survivors, lanes full again: oriented bounding boxes along their 6 face normals, then -- hull pairs only, they
+  // would go to MPR -- the query's own first test on support bounds and the separation witnesses of earlier steps.  All three are
+  // conservative, so the contact set is exactly that of the unfiltered table.  Compaction is in place (a round reads its 32 entries
+  // before it writes, and never writes past what it has read).
+  base = 0;
+  for (int i0 = 0; i0 < n1; i0 += c.nt) {
+    const int i = i0 + c.tid; bool flag = false; int p = 0;
+    if (i < n1) {
+      p = s.cand[i];
+      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p]; const PairParam<T>& pp = g.pair_param[p]; const T md = full_contacts ? pp.margin : pp.margin - pp.gap;
+      if (m.geom_type[g1] == B2P_GEOM_PLANE) flag = true;
+      else {
+        const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
+        const T* h1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+        flag = !obb_separated(s.gpos[g1], s.gmat[g1], m.geom_aabb_c[g1], h1, s.gpos[g2], s.gmat[g2], m.geom_aabb_c[g2], h2, md);
+        if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH)) {
+          flag = !centre_axis_separated(s.gpos[g1], s.gmat[g1], h1, g.geom_dop + 27 * g1, m.geom_type[g1], s.gpos[g2], s.gmat[g2], h2, g.geom_dop + 27 * g2, m.geom_type[g2], md);
+          if (flag) for (int k = 0; k < SEP_N; k++) if (s.sep_pair[k] == p) { if (witness_separated(s.sep_w[k], s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], s.grbound[g2], md)) flag = false; }
+        }
+      }
+    }
+    int tot; const int ofs = block_rank(c, flag, tot);
+    bsync(c);
+    if (flag) s.cand[base + ofs] = (short)p;
+    base += tot;
+  }
+  if (c.tid == 0 && full) s.flags |= full;
+  if (c.tid == 0) s.ncand = base;
   bsync(c);
   }
   PROF_ADD(PF_BROAD)

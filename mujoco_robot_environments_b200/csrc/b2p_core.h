@@ -18,6 +18,7 @@
 #include "b2p_rows.h"
 #include "b2p_solver.h"
 #include "b2p_osc.h"
+#include "b2p_pgs.h"
 
 namespace b2p {
 
@@ -47,7 +48,7 @@ B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, con
   if (active) make_rows(m, g, s, c);
   PROF_ADD(PF_ROWS)
 }
-template <typename T>
+template <typename T, bool kPgs = false>
 B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
   PROF_T0
   csync(c, LK_STEP2);
@@ -59,7 +60,7 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
   }
   PROF_ADD(PF_SMOOTH)
   csync(c, LK_SOLVE);
-  solve_constraints(m, s, c, active);
+  if constexpr (kPgs) solve_pgs(m, s, c, active); else solve_constraints(m, s, c, active);
   PROF_RESET
   if (active) {
     // mj_checkAcc / checkVel / checkPos equivalents -> per-env status bits
@@ -113,8 +114,12 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
 
 // One scene, whole launch: load the state record, run the requested mode, store the record.  `active` = this warp holds
 // a scene; an idle warp of a lockstep CTA still walks the same stage barriers.
-template <typename T, bool kPlace = false>   // kPlace: the placement-search kernel (MODE_PLACE) is its own instantiation, so the step kernels' code is untouched by it
+// kVar: 0 = the step kernel, 1 = the placement search (MODE_PLACE), 2 = the step kernel with the PGS solver.  Each is its own
+// instantiation, so the default step kernel's code (and its layout in the instruction cache) is untouched by the other two.
+enum { VAR_STEP = 0, VAR_PLACE = 1, VAR_PGS = 2 };
+template <typename T, int kVar = VAR_STEP>
 B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded, bool active = true) {
+  constexpr bool kPlace = kVar == VAR_PLACE, kPgs = kVar == VAR_PGS;
   const int nv = m.nv;
   T* rec = a.state + (size_t)(active ? env : 0) * a.state_stride;
   if (active) {
@@ -182,9 +187,9 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
   if (a.mode == MODE_FORWARD) {
     step1(m, g, s, c, full, active);
     if (active && a.out) { bsync(c); write_out(m, g, s, c, a.out + (size_t)env * a.out_stride, OUT_POS); bsync(c); }   // physics.forward(): every group
-    step2(m, s, c, false, false, active);
+    step2<T, kPgs>(m, s, c, false, false, active);
   } else if (a.mode == MODE_PHYSICS) {
-    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); }
+    for (int k = 0; k < a.n_steps; k++) { step1(m, g, s, c, full, active); step2<T, kPgs>(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); }
     step1(m, g, s, c, full, active);   // leave derived quantities consistent with the final state (dm_control legacy step order)
   } else if (a.mode == MODE_OSC) {
     // RobotArm.run_controller (robot_arm.py:61-94): per tick OSC torque + gripper command, control_steps x physics.step()
@@ -207,7 +212,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
         osc_torque(m, s, tg, grip, c, gn);
       }
       PROF_ADD(PF_OSC)
-      for (int k = 0; k < a.control_steps; k++) { step2(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); step1(m, g, s, c, full, active); }
+      for (int k = 0; k < a.control_steps; k++) { step2<T, kPgs>(m, s, c, true, false, active); if (active) work += s.nefc * (2 + s.niter); step1(m, g, s, c, full, active); }
       if (active && osc_converged(m, s, tg)) conv = true;
     }
     if (active && c.tid == 0 && a.converged) a.converged[env] = conv ? 1 : 0;
@@ -217,7 +222,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     int done = 0; bool fin = !active;
     for (int k = 0; k < a.n_steps; k++) {
       if (csync_and(c, fin)) break;
-      step1(m, g, s, c, full, !fin); step2(m, s, c, true, true, !fin);
+      step1(m, g, s, c, full, !fin); step2<T, kPgs>(m, s, c, true, true, !fin);
       if (!fin) {
         done = k + 1;
         T mx[2] = {0, 0};   // max |qvel|, |qacc| over ACTIVE prop dofs: computed redundantly by every lane (nv is tiny)

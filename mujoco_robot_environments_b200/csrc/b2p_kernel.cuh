@@ -58,7 +58,7 @@ struct alignas(16) SmemLayout {
 
 static_assert(sizeof(SmemLayout<float>) + 128 <= 232448 && sizeof(SmemLayout<double>) + 128 <= 232448, "shared memory per CTA exceeds the 227 KB an sm_100 CTA may use: shrink Pool<T>::JPS or the warps per CTA");
 
-template <typename T, bool kPlace>
+template <typename T, int kVar>
 __global__ void __launch_bounds__(32 * KernelCfg<T>::kWarps, KernelCfg<T>::kMinBlocks)
 b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int* __restrict__ next_env) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
@@ -82,7 +82,8 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   if (threadIdx.x == 0) { mbar_expect_tx(&sm.bar[0], kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar[0]); }
   mbar_wait(&sm.bar[0], 0);
   Scratch<T>& s = sm.scratch[warp];
-  if (lane == 0) s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP;
+  constexpr bool kPlace = kVar == VAR_PLACE;
+  if (lane == 0) { s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP; s.xpool = g.xpool ? g.xpool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP : nullptr; }
   __syncwarp();
   unsigned long long* bar = &sm.bar[1 + warp];
   unsigned phase = 0;
@@ -100,7 +101,7 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
       mbar_wait(bar, phase); phase ^= 1;
     }
     PROF_T0
-    run_env<T, kPlace>(sm.model, g, s, a, env, c, true, active);
+    run_env<T, kVar>(sm.model, g, s, a, env, c, true, active);
     if (active) PROF_ADD(PF_TOTAL)
     if (active) {
       __syncwarp();
@@ -129,13 +130,15 @@ template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<
 template <typename T>
 static cudaError_t step_configure(int device, int n_env, LaunchGeom* out) {
   const size_t smem = step_smem_size<T>();
-  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(b2p_step_kernel<T, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PLACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0, sms = 0;
   const int threads = 32 * KernelCfg<T>::kWarps;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T, false>, threads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T, VAR_STEP>, threads, smem);
   if (e != cudaSuccess) return e;
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) return e;
@@ -151,8 +154,9 @@ template <typename T>
 static cudaError_t step_launch(const LaunchGeom& lg, const void* d_model, const Globals<T>& g, const StepArgs<T>& a, int* next_env, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(next_env, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
-  if (a.mode == MODE_PLACE) b2p_step_kernel<T, true><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
-  else b2p_step_kernel<T, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  if (a.mode == MODE_PLACE) b2p_step_kernel<T, VAR_PLACE><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  else if (a.solver == 1) b2p_step_kernel<T, VAR_PGS><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  else b2p_step_kernel<T, VAR_STEP><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
   return cudaGetLastError();
 }
 

@@ -18,6 +18,7 @@ struct Globals {                 // read-only global-memory tables
   const NbrPt<T>* nbr_pt;        // [nmeshnbr] neighbour vertex coordinates + index, same order as nbr
   const NbrSpan* nbr_span;       // [nmeshvert]
   T* jovf;                       // [warp slots][Pool<T>::JP] Jacobian rows that do not fit a scene's shared-memory pool
+  T* xpool;                      // [warp slots][Pool<T>::JP] PGS only: X = M^-1 J' in J's packed layout (NULL until b2p_set_solver(PGS))
   const T* geom_dop;             // [ngeom][27] hull support value along the 26 directions {-1,0,1}^3 (mesh geoms): 26-DOP bound
 };
 
@@ -46,6 +47,7 @@ struct alignas(16) Scratch {
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
   // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
   T Jp[Pool<T>::JPS], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
+  T* xpool;                      // this warp's M^-1 J' area (PGS)
   T* jovf;                       // this warp's overflow area (global memory, Pool<T>::JP reals): joff[r] < 0 <=> row r lives at jovf[-joff[r] - 1]
   signed char row_a[Pool<T>::EFC], row_b[Pool<T>::EFC], row_type[Pool<T>::EFC], row_state[Pool<T>::EFC];
   short row_id[Pool<T>::EFC], joff[Pool<T>::EFC], eq_row0[MAXEQ];   // eq_row0: first row of equality e
@@ -94,7 +96,7 @@ template <typename T> B2P_HD const unsigned char* block_rows(const Scratch<T>& s
 // launch parameters shared by kernel and host emulation
 template <typename T>
 struct StepArgs {
-  int mode, n_env, n_steps, control_steps, state_stride, full_contacts, lockstep, lock_group;   // lock_group: warps per lockstep group (0 = whole CTA)
+  int mode, n_env, n_steps, control_steps, state_stride, full_contacts, lockstep, lock_group, solver;   // solver: 0 Newton, 1 PGS   // lock_group: warps per lockstep group (0 = whole CTA)
   T* state;                  // [n_env][state_stride]: qpos | qvel | qacc_warmstart | time
   const T* ctrl;             // MODE_PHYSICS / SETTLE: [n_env][nu]
   const T* target;           // MODE_OSC: [n_env][13] pos3 vel3 quat4(wxyz) angvel3

@@ -209,6 +209,10 @@ class BatchedPhysics:
         ffi.check(self._L.b2p_set_out_mask(self._h, mask), "b2p_set_out_mask")
         self.out_mask = mask
 
+    def set_solver(self, name: str):
+        """mjOption.solver for the stepping calls: "newton" (MuJoCo's and this backend's default) or "pgs" (``b2p_set_solver``)."""
+        ffi.check(self._L.b2p_set_solver(self._h, ffi.SOLVER[name.lower()]), "b2p_set_solver")
+
     def set_full_contacts(self, full: bool):
         ffi.check(self._L.b2p_set_full_contacts(self._h, int(full)))
 

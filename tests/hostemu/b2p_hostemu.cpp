@@ -12,7 +12,7 @@ using namespace b2p;
 template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
-  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop, xpool;
   Globals<T> g; Scratch<T>* s;
 };
 
@@ -39,7 +39,8 @@ static Emu<T>* make(const void* blob, size_t n) {
   e->g.nbr_pt = e->nbr_pt.data(); e->g.nbr_span = e->nbr_span.data();
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
   e->jovf.assign(Pool<T>::JP, T(0)); e->g.jovf = e->jovf.data();
-  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data();
+  e->xpool.assign(Pool<T>::JP, T(0)); e->g.xpool = e->xpool.data();
+  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data(); e->s->xpool = e->xpool.data();
   return e;
 }
 
@@ -47,6 +48,7 @@ struct EmuArgs {   // mirrors the ctypes struct in tests/hostemu.py
   int mode, n_env, n_steps, control_steps, state_stride, full_contacts, settle_min_steps, out_stride;
   double settle_qvel_tol, settle_qacc_tol;
   void *state, *ctrl, *target, *grip, *prop_size, *prop_active, *env_mask, *converged, *status, *steps_done, *out, *gains;
+  int solver;
 };
 
 template <typename T>
@@ -61,7 +63,7 @@ static int run(Emu<T>* e, const EmuArgs* a) {
   Ctx c = {0, 1};
   for (int env = 0; env < a->n_env; env++) {
     if (s.env_mask && !s.env_mask[env]) continue;
-    run_env(e->model, e->g, *e->s, s, env, c, false);
+    if (a->solver == 1) run_env<T, VAR_PGS>(e->model, e->g, *e->s, s, env, c, false); else run_env(e->model, e->g, *e->s, s, env, c, false);
   }
   return 0;
 }

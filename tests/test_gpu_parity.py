@@ -185,3 +185,84 @@ def test_output_mask_limits_what_a_stepping_launch_writes():
     assert float((p.data.site_xpos - ref.data.site_xpos).abs().max()) == 0.0
     with pytest.raises(KeyError):
         p.set_out_fields("NOPE")
+
+
+@pytest.mark.parametrize("dtype,tol", [(torch.float64, 1e-8), (torch.float32, 5e-3)])
+def test_euler_integrator_parity(dtype, tol):
+    """R6.12: the scene compiled with integrator = Euler (joint damping alone is implicit) on the GPU against the oracle's mj_Euler
+    branch, gripper closing so that the actuator's velocity term -- which implicitfast would put into the integrator matrix -- is live."""
+    import blobtools as bt
+    from mujoco_robot_environments_b200.compile import blob as B
+    from mujoco_robot_environments_b200.physics import BatchedPhysics, load_default_blob
+    blob, names = load_default_blob()
+    eb = bt.surgery(blob, opts=dict(integrator=B.INT_EULER))
+    n, steps = 8, 60
+    st, size, active = sc.make_states(n, seed=13, settled=False)
+    o = Oracle(eb)
+    sc.oracle_load(o, st[0], size[0], active[0]); o.step1(); bias = o.qfrc_bias[:7].copy()
+    ctrl = sc.halton_ctrl(n, 0, bias); ctrl[:, 7] = 200.0
+    p = BatchedPhysics(n, dtype=dtype, blob=eb, names=names); _load(p, st, size, active)
+    p.set_control(torch.tensor(ctrl)); p.step(steps); torch.cuda.synchronize()
+    got = p.state.cpu().numpy().astype(np.float64)
+    assert int(p.status().cpu().max()) == 0
+    ref = _phys(n, dtype); _load(ref, st, size, active); ref.set_control(torch.tensor(ctrl)); ref.step(steps); torch.cuda.synchronize()
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0); o.ctrl[:] = ctrl[i]
+        for _ in range(steps):
+            o.step()
+        assert np.abs(got[i, :sc.NQ] - o.qpos[:sc.NQ]).max() < tol
+    if dtype == torch.float64:
+        assert float((p.qpos - ref.qpos).abs().max()) > 1e-6         # not the implicitfast trajectory
+
+
+def test_plane_convex_contacts_on_gpu():
+    """R6.6 plane-convex: arm links below the table edge touch the ground plane; same contact list as the oracle, and stepping from
+    there raises no bad-state flag."""
+    st, size, active = sc.make_states(1, seed=3)
+    poses = np.array([[-2.97, 2.3, -0.27, -0.19, -0.11, 2.36, 0.7], [-2.57, 1.89, -0.03, -0.87, -0.47, 2.45, 0.83], [-2.8, 2.03, 0.05, -0.6, 0.63, 2.42, 1.3]])
+    n = len(poses)
+    S = np.repeat(st, n, 0); S[:, :7] = poses
+    p = _phys(n, torch.float64); _load(p, S, np.repeat(size, n, 0), np.repeat(active, n, 0))
+    p.forward(full_contacts=False); torch.cuda.synchronize()
+    ncon = p.data.ncon.cpu().numpy(); con = {k: v.cpu().numpy() for k, v in p.data.contact.items()}
+    o = Oracle(sc.default_blob()); seen = 0
+    for e in range(n):
+        sc.oracle_load(o, S[e], size[0], active[0]); o.set_option("full_contacts", 0); o.forward()
+        oc = o.contacts()
+        assert ncon[e] == len(oc["dist"])
+        assert (con["geom1"][e, :ncon[e]] == oc["geom"][:, 0]).all() and (con["geom2"][e, :ncon[e]] == oc["geom"][:, 1]).all()
+        assert np.abs(con["dist"][e, :ncon[e]] - oc["dist"]).max() < 1e-12 and np.abs(con["pos"][e, :ncon[e]] - oc["pos"]).max() < 1e-12
+        seen += int(((oc["geom"][:, 0] == 0) & (oc["geom"][:, 1] > 1)).sum())
+    assert seen >= 40
+    p.step(20); torch.cuda.synchronize()
+    assert int((p.status().cpu() & 7).max()) == 0
+
+
+def test_pgs_solver_on_gpu():
+    """b2p_set_solver(B2P_SOLVER_PGS): the matrix-free PGS kernel instantiation run to its tolerance (iterations / tolerance raised in
+    the blob, as the oracle-side cross-check does) against the oracle's NEWTON on the resting / landing / sliding / grasping / stacked /
+    flailing scenes of tests/test_solver_crosscheck.py: qacc within 1e-6 relative (SURVEY 8c fixture 3), forces in the true cones.
+    Then 25 steps at MuJoCo's default settings (100 sweeps, 1e-8): the PGS trajectory stays within 1e-4 of the Newton one."""
+    from test_solver_crosscheck import _pgs_blob, _scenes
+    from mujoco_robot_environments_b200.physics import BatchedPhysics, load_default_blob
+    _, names = load_default_blob()
+    scenes = _scenes(); n = len(scenes)
+    st = np.stack([s[1] for s in scenes]); size = np.stack([s[2] for s in scenes]); active = np.stack([s[3] for s in scenes]); ctrl = np.stack([s[4] for s in scenes])
+    p = BatchedPhysics(n, dtype=torch.float64, blob=_pgs_blob(), names=names); _load(p, st, size, active)
+    p.set_solver("pgs"); p.set_control(torch.tensor(ctrl))
+    o = Oracle(sc.default_blob()); o.set_option("tolerance", 1e-12)
+    # one PGS solve per scene: MODE_PHYSICS with one step, then compare the step's qacc (= qacc_warmstart of the record)
+    p.step(1); torch.cuda.synchronize()
+    assert int((p.status().cpu() & 64).max()) == 0                      # met its tolerance before the sweep cap
+    got = p.qacc_warmstart.cpu().numpy()
+    for i, (label, s0, z, a, c) in enumerate(scenes):
+        sc.oracle_load(o, s0, z, a); o.set_option("full_contacts", 0); o.ctrl[:sc.NU] = c; o.forward()
+        rel = np.abs(got[i, :sc.NV] - o.qacc[:sc.NV]).max() / max(1.0, np.abs(o.qacc[:sc.NV]).max())
+        assert rel < 1e-6, (label, rel)
+    # default solver settings: a short trajectory with each solver
+    res = []
+    for name in ("newton", "pgs"):
+        q = _phys(n, torch.float64); _load(q, st, size, active); q.set_solver(name); q.set_control(torch.tensor(ctrl)); q.step(25); torch.cuda.synchronize()
+        assert int((q.status().cpu() & 7).max()) == 0
+        res.append(q.qpos.cpu().numpy().copy())
+    assert np.abs(res[0] - res[1]).max() < 1e-4

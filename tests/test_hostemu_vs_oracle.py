@@ -124,3 +124,51 @@ def test_per_scene_gains(blob):
         o.run_controller(tg[i], int(grip[i]), ticks)
         assert np.abs(got[i, :sc.NQ] - o.qpos[:sc.NQ]).max() < 1e-8, i
     assert np.abs(got[0, :7] - got[1, :7]).max() > 1e-4        # and the rows really differ
+
+
+def test_euler_integrator(blob):
+    """SURVEY R6.12 / mj_Euler (the MEN-A menagerie snapshot's integrator family): the same scene compiled with integrator = Euler --
+    joint damping alone enters the integrator matrix, the gripper actuator's velocity term does not (b2p_model.h impl_hD) -- against
+    the oracle's mj_Euler branch, and it must differ from the implicitfast trajectory (else the test would not see the branch)."""
+    import blobtools as bt
+    from mujoco_robot_environments_b200.compile import blob as B
+    eb = bt.surgery(blob, opts=dict(integrator=B.INT_EULER))
+    n, steps = 2, 60
+    st, size, active = sc.make_states(n, seed=13, settled=False)
+    o = Oracle(eb)
+    sc.oracle_load(o, st[0], size[0], active[0]); o.step1(); bias = o.qfrc_bias[:7].copy()
+    ctrl = sc.halton_ctrl(n, 0, bias); ctrl[:, 7] = 200.0            # gripper closing: the actuator's -10 * velocity term is live
+    got = st.copy()
+    r = HostEmu(eb, np.float64).run(MODE_PHYSICS, got, n_steps=steps, ctrl=ctrl, prop_size=size, prop_active=active)
+    ref = st.copy()
+    HostEmu(blob, np.float64).run(MODE_PHYSICS, ref, n_steps=steps, ctrl=ctrl, prop_size=size, prop_active=active)
+    assert r["status"].max() == 0
+    for i in range(n):
+        sc.oracle_load(o, st[i], size[i], active[i]); o.set_option("full_contacts", 0); o.ctrl[:] = ctrl[i]
+        for _ in range(steps):
+            o.step()
+        want = sc.oracle_state(o)
+        assert np.abs(got[i, :sc.NQ] - want[:sc.NQ]).max() < 1e-8
+        assert np.abs(got[i, sc.REC_QVEL:sc.REC_QVEL + sc.NV] - want[sc.REC_QVEL:sc.REC_QVEL + sc.NV]).max() < 1e-6
+    assert np.abs(got[:, :sc.NQ] - ref[:, :sc.NQ]).max() > 1e-6
+
+
+def test_plane_convex_contacts(blob):
+    """R6.6 plane-convex: an arm driven past its joint limits to below the table edge touches the ground plane with hull vertices --
+    same contact list (geoms, distances, points) as the oracle's plane_convex, and a step from there stays finite."""
+    st, size, active = sc.make_states(1, seed=3)
+    o = Oracle(blob); e = HostEmu(blob, np.float64)
+    poses = np.array([[-2.97, 2.3, -0.27, -0.19, -0.11, 2.36, 0.7], [-2.57, 1.89, -0.03, -0.87, -0.47, 2.45, 0.83], [-2.8, 2.03, 0.05, -0.6, 0.63, 2.42, 1.3]])
+    seen = 0
+    for q7 in poses:
+        q = st[0].copy(); q[:7] = q7
+        sc.oracle_load(o, q, size[0], active[0]); o.set_option("full_contacts", 0); o.forward()
+        oc = o.contacts()
+        r = e.run(MODE_FORWARD, q[None].copy(), prop_size=size, prop_active=active, full_contacts=False)
+        out = r["out"][0]; nc = int(out[S["ncon"]][0]); c = out[S["contact"]].reshape(-1, 10)[:nc]
+        assert r["status"][0] == 0 and nc == len(oc["dist"]) and (c[:, 7].astype(int) == oc["geom"][:, 0]).all() and (c[:, 8].astype(int) == oc["geom"][:, 1]).all()
+        assert np.abs(c[:, 0] - oc["dist"]).max() < 1e-12 and np.abs(c[:, 1:4] - oc["pos"]).max() < 1e-12
+        ground = (oc["geom"][:, 0] == 0) & (oc["geom"][:, 1] > 1)
+        seen += int(ground.sum())
+        assert (np.abs(c[ground, 4:7] - np.array([0, 0, 1.0])).max() < 1e-15) if ground.any() else True
+    assert seen >= 4

@@ -141,3 +141,29 @@ def test_zero_duality_gap_at_the_newton_solution(scenes):
         dual = 0.5 * fn @ A @ fn + fn @ (J @ a0 - aref)
         assert abs(primal + dual) < 1e-7 * max(1.0, abs(primal)), (label, primal, dual)
         assert np.abs((a0 + Mi @ J.T @ fn - qn)[act]).max() < 1e-6 * max(1.0, np.abs(qn).max()), label
+
+
+def _pgs_blob():
+    import blobtools as bt
+    return bt.surgery(sc.default_blob(), opts=dict(iterations=50000.0, tolerance=1e-17))
+
+
+def test_kernel_pgs_agrees_with_newton_on_the_host_build(scenes):
+    """The kernel's own PGS (csrc/b2p_pgs.h, matrix-free: b2p_set_solver(B2P_SOLVER_PGS)) compiled for the host, run to its tolerance on
+    every scene, against the ORACLE's Newton: qacc within 1e-6 relative.  The product default stays Newton; the GPU leg is
+    tests/test_gpu_parity.py::test_pgs_solver_on_gpu."""
+    from hostemu import MODE_FORWARD, HostEmu, out_slices
+    S = out_slices()
+    o = Oracle(sc.default_blob()); o.set_option("tolerance", 1e-12)
+    e = HostEmu(_pgs_blob(), np.float64)
+    for label, st, size, active, ctrl in scenes:
+        sc.oracle_load(o, st, size, active); o.set_option("full_contacts", 0); o.ctrl[:sc.NU] = ctrl; o.forward()
+        r = e.run(MODE_FORWARD, st[None].copy(), ctrl=ctrl[None], prop_size=size[None], prop_active=active[None], solver=1)
+        out = r["out"][0]
+        qn, qp = o.qacc[:sc.NV], out[S["qacc"]][:sc.NV]
+        assert int(out[S["niter"]][0]) < 50000 and (r["status"][0] & 64) == 0, label
+        assert int(out[S["nefc"]][0]) == o.dim("nefc"), label
+        rel = np.abs(qn - qp).max() / max(1.0, np.abs(qn).max())
+        assert rel < 1e-6, (label, rel)
+        fo = out[S["efc_force"]][:o.dim("nefc")]
+        assert np.abs(fo - o.efc_force).max() < 1e-5 * max(1.0, np.abs(o.efc_force).max()), label
