@@ -78,6 +78,12 @@ enum { B2P_SOLVER_NEWTON = 0, B2P_SOLVER_PGS = 1 };
 int b2p_set_solver(b2p_handle h, int solver);
 /* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active);
+/* optional collider class per prop and scene: device [n_env][MAXPROP] bytes, B2P_GEOM_BOX (6, the compiled box with the scene's half
+ * sizes), B2P_GEOM_SPHERE (2; prop_size[.][0] = radius) or B2P_GEOM_CYLINDER (5; prop_size[.][0] = radius, [1] = half height, axis z);
+ * NULL = every prop is the compiled box.  Replaces what add_objects (environment/props.py:520-617) does when it draws a shape per
+ * prop: the classes' contact parameters (cylinder: condim 6, friction 1 1 1, solref 0.01 1.1; GalaApple: a default sphere) are in
+ * include/b2p_prop_types.h.  The pointer is borrowed. */
+int b2p_set_env_prop_types(b2p_handle h, const uint8_t* prop_type);
 /* optional per-scene OSC gains [n_env][6] reals (position kp, kd, orientation kp, kd, nullspace kp, kd): one candidate of the
  * controller tuner per scene (automated_controller_tuning/rearrangement_controller_tuning.py:145-168 mutates
  * `controller_gains` between roll-outs); NULL = every scene uses b2p_osc_config's gains.  The pointer is borrowed. */

@@ -60,9 +60,9 @@ struct b2p_handle_s {
   LaunchGeom lg;
   long long launches, order_launches;
   DevModel<double> hmodel;
-  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void* d_geom_dop; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
+  void* d_model; void* d_mesh_vert; int *d_nbradr, *d_nbrnum, *d_nbr, *d_geom_start; void* d_geom_dop; void* d_geom_raw; const unsigned char* prop_type; void *d_nbr_pt, *d_nbr_span; short *d_g1, *d_g2; void* d_pair_param;
   void* state; void* out; void* own_out; const void* prop_size; const unsigned char* prop_active; int* d_status;
-  void* d_zero_ctrl; int* d_next_env; void* d_jovf; void* d_xpool; int solver;
+  void* d_zero_ctrl; int* d_next_env; void* d_jovf; void* d_xpool; void* d_w6pool; int solver;
   const void* env_gains; const unsigned char* env_mask;
   int *d_work, *d_order; int work_steps, sort_queue, out_mask;   // work_steps: physics steps behind d_work (0 = none yet)
 };
@@ -85,6 +85,18 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   CK(cudaMalloc(&h->d_g1, g1.size() * 2 + 16)); CK(cudaMemcpy(h->d_g1, g1.data(), g1.size() * 2, cudaMemcpyHostToDevice));
   CK(cudaMalloc(&h->d_g2, g2.size() * 2 + 16)); CK(cudaMemcpy(h->d_g2, g2.data(), g2.size() * 2, cudaMemcpyHostToDevice));
   { std::vector<T> dop(ht.geom_dop.begin(), ht.geom_dop.end()); CK(cudaMalloc(&h->d_geom_dop, dop.size() * sizeof(T) + 16)); CK(cudaMemcpy(h->d_geom_dop, dop.data(), dop.size() * sizeof(T), cudaMemcpyHostToDevice)); }
+  {
+    std::vector<GeomRaw<T>> gr(ht.geom_raw.size());
+    for (size_t i = 0; i < gr.size(); i++) {
+      const GeomRaw<double>& a = ht.geom_raw[i]; GeomRaw<T>& b = gr[i];
+      b.priority = a.priority; b.condim = a.condim;
+      for (int k = 0; k < 3; k++) b.friction[k] = (T)a.friction[k];
+      for (int k = 0; k < 2; k++) b.solref[k] = (T)a.solref[k];
+      for (int k = 0; k < 5; k++) b.solimp[k] = (T)a.solimp[k];
+      b.solmix = (T)a.solmix; b.margin = (T)a.margin; b.gap = (T)a.gap;
+    }
+    CK(cudaMalloc(&h->d_geom_raw, gr.size() * sizeof(GeomRaw<T>) + 16)); CK(cudaMemcpy(h->d_geom_raw, gr.data(), gr.size() * sizeof(GeomRaw<T>), cudaMemcpyHostToDevice));
+  }
   CK(cudaMalloc(&h->d_geom_start, ht.geom_start.size() * 4 + 16)); CK(cudaMemcpy(h->d_geom_start, ht.geom_start.data(), ht.geom_start.size() * 4, cudaMemcpyHostToDevice));
   {
     std::vector<NbrPt<T>> np(ht.mesh_nbr.size()); std::vector<NbrSpan> ns(ht.mesh_nbradr.size());
@@ -102,6 +114,7 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   CK(cudaMalloc(&h->d_next_env, sizeof(int)));
   CK(sizeof(T) == 8 ? configure_f64(h->device, h->n_env, &h->lg) : configure_f32(h->device, h->n_env, &h->lg));
   CK(cudaMalloc(&h->d_jovf, (size_t)h->lg.grid * h->lg.warps_per_cta * Pool<T>::JP * sizeof(T)));   // Jacobian overflow: one area per resident warp
+  CK(cudaMalloc(&h->d_w6pool, (size_t)h->lg.grid * h->lg.warps_per_cta * MAXCON * W6_STRIDE * sizeof(T)));
   CK(cudaMalloc(&h->d_work, (size_t)h->n_env * 4)); CK(cudaMemset(h->d_work, 0, (size_t)h->n_env * 4));
   CK(cudaMalloc(&h->d_order, (size_t)h->n_env * 4));
   { const char* sq = getenv("B2P_SORT_QUEUE"); h->sort_queue = sq ? atoi(sq) : (h->n_env > h->lg.grid * h->lg.warps_per_cta); }   // pays off once there is more than one round
@@ -111,9 +124,9 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
 template <typename T>
 static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   if (!h->state) return fail(B2P_ERR_STATE, "b2p_bind_state has not been called");
-  a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active;
+  a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = h->prop_type;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
-  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (T*)h->d_xpool, (const T*)h->d_geom_dop};
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (T*)h->d_w6pool, (T*)h->d_xpool, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};
   a.work = h->d_work; a.order = nullptr; a.solver = h->solver;
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
@@ -168,7 +181,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
 int b2p_destroy(b2p_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_geom_dop, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf, h->d_xpool};
+  void* ptrs[] = {h->d_model, h->d_mesh_vert, h->d_geom_start, h->d_geom_dop, h->d_geom_raw, h->d_nbr_pt, h->d_nbr_span, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, h->d_pair_param, h->own_out, h->d_status, h->d_zero_ctrl, h->d_next_env, h->d_work, h->d_order, h->d_jovf, h->d_xpool, h->d_w6pool};
   for (void* p : ptrs) if (p) cudaFree(p);
   delete h;
   return B2P_OK;
@@ -211,6 +224,7 @@ int b2p_set_solver(b2p_handle h, int solver) {
   h->solver = solver; return B2P_OK;
 }
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
+int b2p_set_env_prop_types(b2p_handle h, const uint8_t* prop_type) { if (!h) return B2P_ERR_ARG; h->prop_type = prop_type; return B2P_OK; }
 int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
 int b2p_set_env_mask(b2p_handle h, const uint8_t* mask) { if (!h) return B2P_ERR_ARG; h->env_mask = mask; return B2P_OK; }
 int b2p_set_full_contacts(b2p_handle h, int full) { if (!h) return B2P_ERR_ARG; h->full_contacts = full; return B2P_OK; }

@@ -40,6 +40,11 @@ B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {
   mulmtv(ld, o.mat, dir);
   if (o.type == B2P_GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? o.size[k] : -o.size[k];
+  } else if (o.type == B2P_GEOM_SPHERE) {
+    for (int k = 0; k < 3; k++) lp[k] = o.size[0] * ld[k];
+  } else if (o.type == B2P_GEOM_CYLINDER) {   // disc of radius size[0] swept along local z by +- size[1]
+    const T rho = sqrt(ld[0] * ld[0] + ld[1] * ld[1]), sc = rho > Num<T>::minval() ? o.size[0] / rho : T(0);
+    lp[0] = sc * ld[0]; lp[1] = sc * ld[1]; lp[2] = ld[2] >= 0 ? o.size[1] : -o.size[1];
   } else {
     int v = o.cur;
     if (v < 0) v = o.start[start_slot(ld)];
@@ -226,6 +231,122 @@ B2P_HD int plane_box(const T* ppos, const T* pmat, const T* bpos, const T* bmat,
   return cnt;
 }
 
+// ---- analytic pairs of the sphere / cylinder prop classes (oracle: plane_sphere, plane_cylinder, sphere_sphere, sphere_solid).  The
+// normal points from the pair's first geom to its second in the PAIR TABLE's order (MuJoCo re-sorts a pair by geom type: same
+// contact with normal and geom1 / geom2 swapped).
+template <typename T>
+B2P_HD int plane_sphere(const T* ppos, const T* pmat, const T* c, T r, T margin, RawCon<T>& out) {
+  const T n[3] = {pmat[2], pmat[5], pmat[8]}, dif[3] = {c[0] - ppos[0], c[1] - ppos[1], c[2] - ppos[2]};
+  const T dist = dot3(dif, n) - r;
+  if (dist > margin) return 0;
+  out.dist[0] = dist; cp3(out.normal, n);
+  for (int k = 0; k < 3; k++) out.pos[0][k] = c[k] - n[k] * (r + T(0.5) * dist);
+  return 1;
+}
+template <typename T>
+B2P_HD int plane_cylinder(const T* ppos, const T* pmat, const T* c, const T* mat, T r, T h, T margin, RawCon<T>& out) {
+  const T n[3] = {pmat[2], pmat[5], pmat[8]}, a[3] = {mat[2], mat[5], mat[8]};
+  const T na = dot3(n, a), sg = na > 0 ? T(-1) : T(1);
+  T v[3] = {-n[0] + na * a[0], -n[1] + na * a[1], -n[2] + na * a[2]};
+  if (normalize3(v) < T(1e-9)) { v[0] = mat[0]; v[1] = mat[3]; v[2] = mat[6]; }
+  T u[3]; cross3(u, a, v);
+  int cnt = 0;
+  cp3(out.normal, n);
+  for (int q = 0; q < 4; q++) {
+    const T cap = q == 1 ? -sg : sg, ca = q < 2 ? T(1) : T(-0.5), sa = q < 2 ? T(0) : (q == 2 ? T(0.8660254037844387) : T(-0.8660254037844387));
+    T pt[3];
+    for (int k = 0; k < 3; k++) pt[k] = c[k] + cap * h * a[k] + r * (ca * v[k] + sa * u[k]);
+    const T dif[3] = {pt[0] - ppos[0], pt[1] - ppos[1], pt[2] - ppos[2]}, dist = dot3(dif, n);
+    if (dist > margin) continue;
+    out.dist[cnt] = dist;
+    for (int k = 0; k < 3; k++) out.pos[cnt][k] = pt[k] - T(0.5) * dist * n[k];
+    cnt++;
+  }
+  return cnt;
+}
+template <typename T>
+B2P_HD int sphere_sphere(const T* c1, T r1, const T* c2, T r2, T margin, RawCon<T>& out) {
+  T d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+  const T L = normalize3(d), dist = L - r1 - r2;
+  if (dist > margin) return 0;
+  out.dist[0] = dist; cp3(out.normal, d);
+  for (int k = 0; k < 3; k++) out.pos[0][k] = c1[k] + d[k] * (r1 + T(0.5) * dist);
+  return 1;
+}
+// closest point of a solid (box / cylinder) to the sphere centre; normal from the SOLID to the sphere
+template <typename T>
+B2P_HDN int sphere_solid(int solid_type, const T* cs, T rs, const T* cb, const T* mb, const T* hs, T margin, RawCon<T>& out) {
+  const T dif[3] = {cs[0] - cb[0], cs[1] - cb[1], cs[2] - cb[2]};
+  T lc[3], q[3], nl[3] = {0, 0, 0}, depth = 0;
+  mulmtv(lc, mb, dif);
+  bool inside;
+  if (solid_type == B2P_GEOM_BOX) {
+    inside = true;
+    for (int k = 0; k < 3; k++) { q[k] = lc[k] < -hs[k] ? -hs[k] : (lc[k] > hs[k] ? hs[k] : lc[k]); if (q[k] != lc[k]) inside = false; }
+    if (inside) {
+      int best = 0; T bd = Num<T>::big();
+      for (int k = 0; k < 3; k++) { const T d = hs[k] - fabs(lc[k]); if (d < bd) { bd = d; best = k; } }
+      for (int k = 0; k < 3; k++) if (k == best) { nl[k] = lc[k] >= 0 ? T(1) : T(-1); q[k] = nl[k] * hs[k]; }
+      depth = -bd;
+    }
+  } else {
+    const T rho = sqrt(lc[0] * lc[0] + lc[1] * lc[1]), r = hs[0], h = hs[1];
+    inside = rho < r && fabs(lc[2]) < h;
+    if (inside) {
+      if (r - rho < h - fabs(lc[2])) { const T ir = rho > Num<T>::minval() ? 1 / rho : T(0); nl[0] = rho > Num<T>::minval() ? lc[0] * ir : T(1); nl[1] = lc[1] * ir; nl[2] = 0; q[0] = nl[0] * r; q[1] = nl[1] * r; q[2] = lc[2]; depth = -(r - rho); }
+      else { nl[0] = nl[1] = 0; nl[2] = lc[2] >= 0 ? T(1) : T(-1); q[0] = lc[0]; q[1] = lc[1]; q[2] = nl[2] * h; depth = -(h - fabs(lc[2])); }
+    } else {
+      const T sc = rho > r ? r / rho : T(1);
+      q[0] = lc[0] * sc; q[1] = lc[1] * sc; q[2] = lc[2] < -h ? -h : (lc[2] > h ? h : lc[2]);
+    }
+  }
+  if (!inside) { for (int k = 0; k < 3; k++) nl[k] = lc[k] - q[k]; depth = normalize3(nl); }
+  const T dist = depth - rs;
+  if (dist > margin) return 0;
+  T nw[3], qw[3];
+  mulmv(nw, mb, nl); mulmv(qw, mb, q);
+  out.dist[0] = dist; cp3(out.normal, nw);
+  for (int k = 0; k < 3; k++) out.pos[0][k] = cb[k] + qw[k] + T(0.5) * dist * nw[k];
+  return 1;
+}
+
+// Contact parameters of pair p.  The host mixed them per pair for the compiled (box) props; a pair that involves a re-classed prop
+// (sphere / cylinder: per-scene data) is mixed here by the same rule (App. B item 10: priority wins, else max friction,
+// solmix-weighted solref / solimp, max condim, max margin / gap).
+template <typename T> struct PairMix { PairParam<T> pp; int condim; };
+template <typename T>
+B2P_HDN void pair_mix(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, int p, int g1, int g2, PairMix<T>& o) {
+  const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
+  const bool re1 = pr1 >= 0 && s.ptype[pr1] != B2P_GEOM_BOX, re2 = pr2 >= 0 && s.ptype[pr2] != B2P_GEOM_BOX;
+  if (!re1 && !re2) { o.pp = g.pair_param[p]; o.condim = 3; return; }
+  const GeomRaw<T>& a = re1 ? m.pclass[s.ptype[pr1] == B2P_GEOM_SPHERE ? 0 : 1] : g.geom_raw[g1];
+  const GeomRaw<T>& b = re2 ? m.pclass[s.ptype[pr2] == B2P_GEOM_SPHERE ? 0 : 1] : g.geom_raw[g2];
+  if (a.priority != b.priority) {
+    const GeomRaw<T>& w = a.priority > b.priority ? a : b;
+    o.condim = w.condim;
+    for (int k = 0; k < 3; k++) o.pp.friction[k] = w.friction[k];
+    for (int k = 0; k < 2; k++) o.pp.solref[k] = w.solref[k];
+    for (int k = 0; k < 5; k++) o.pp.solimp[k] = w.solimp[k];
+  } else {
+    o.condim = a.condim > b.condim ? a.condim : b.condim;
+    for (int k = 0; k < 3; k++) o.pp.friction[k] = a.friction[k] > b.friction[k] ? a.friction[k] : b.friction[k];
+    T mix;
+    if (a.solmix >= T(1e-15) && b.solmix >= T(1e-15)) mix = a.solmix / (a.solmix + b.solmix);
+    else if (a.solmix < T(1e-15) && b.solmix < T(1e-15)) mix = T(0.5); else mix = a.solmix < T(1e-15) ? T(0) : T(1);
+    if (a.solref[0] > 0 && b.solref[0] > 0) for (int k = 0; k < 2; k++) o.pp.solref[k] = mix * a.solref[k] + (1 - mix) * b.solref[k];
+    else for (int k = 0; k < 2; k++) o.pp.solref[k] = a.solref[k] < b.solref[k] ? a.solref[k] : b.solref[k];
+    for (int k = 0; k < 5; k++) o.pp.solimp[k] = mix * a.solimp[k] + (1 - mix) * b.solimp[k];
+  }
+  o.pp.margin = a.margin > b.margin ? a.margin : b.margin; o.pp.gap = a.gap > b.gap ? a.gap : b.gap;
+}
+// detection distance of pair p in this scene
+template <typename T>
+B2P_HD T pair_md(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, int p, int g1, int g2, bool full_contacts) {
+  if (!s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; return full_contacts ? pp.margin : pp.margin - pp.gap; }
+  PairMix<T> mx; pair_mix(m, g, s, p, g1, g2, mx);
+  return full_contacts ? mx.pp.margin : mx.pp.margin - mx.pp.gap;
+}
+
 // mjc_PlaneConvex for a hull: the support vertex along -normal, then the support vertices of three directions tilted off -normal
 // (120 degrees apart), kept when they are new vertices inside the margin: at most 4 contacts (oracle: plane_convex, same constants).
 #define B2P_PLANE_TILT 0.05
@@ -392,6 +513,8 @@ B2P_HD T support_bound(const T* mat, const T* half, const T* dop, int type, cons
   T l[3]; mulmtv(l, mat, d);
   const T a0 = fabs(l[0]), a1 = fabs(l[1]), a2 = fabs(l[2]);
   if (type == B2P_GEOM_BOX) return a0 * half[0] + a1 * half[1] + a2 * half[2];
+  if (type == B2P_GEOM_SPHERE) return half[0];
+  if (type == B2P_GEOM_CYLINDER) return half[0] * sqrt(l[0] * l[0] + l[1] * l[1]) + a2 * half[2];   // half = bounding half extents (r, r, h)
   const int s0 = l[0] < 0 ? -1 : 1, s1 = l[1] < 0 ? -1 : 1, s2 = l[2] < 0 ? -1 : 1;
   // order the components: hi >= mid >= lo
   int ih = 0, im = 1, il = 2; T hi = a0, mid = a1, lo = a2;
@@ -439,7 +562,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
   if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
   for (int q = c.tid; q < m.ngeom; q += c.nt) {
     const int p = m.geom_prop[q];
-    s.grbound[q] = p >= 0 ? norm3(s.psize[p]) : m.geom_rbound[q];
+    s.grbound[q] = p >= 0 ? (s.ptype[p] == B2P_GEOM_SPHERE ? s.psize[p][0] : norm3(s.phalf[p])) : m.geom_rbound[q];
   }
   bsync(c);
   // Pass 1 over the static pair table (global memory; the next round's entries are fetched while this round is tested): bounding
@@ -456,7 +579,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
       if (!((pr1 >= 0 && !s.pactive[pr1]) || (pr2 >= 0 && !s.pactive[pr2]))) {
         T dif[3] = {s.gpos[g2][0] - s.gpos[g1][0], s.gpos[g2][1] - s.gpos[g1][1], s.gpos[g2][2] - s.gpos[g1][2]};
-        if (m.geom_type[g1] == B2P_GEOM_PLANE) {
+        if (m.geom_type[g1] == B2P_GEOM_PLANE) {   // (md here is the compiled pair's: the box class carries the largest margin of the prop classes, so this stays conservative)
           T nrm[3] = {s.gmat[g1][2], s.gmat[g1][5], s.gmat[g1][8]};
           flag = !(dot3(dif, nrm) - s.grbound[g2] > md);
         } else {
@@ -481,14 +604,14 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
     const int i = i0 + c.tid; bool flag = false; int p = 0;
     if (i < n1) {
       p = s.cand[i];
-      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p]; const PairParam<T>& pp = g.pair_param[p]; const T md = full_contacts ? pp.margin : pp.margin - pp.gap;
-      if (m.geom_type[g1] == B2P_GEOM_PLANE) flag = true;
+      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p]; const T md = pair_md(m, g, s, p, g1, g2, full_contacts);
+      if (s.gtype[g1] == B2P_GEOM_PLANE) flag = true;
       else {
         const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
-        const T* h1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+        const T* h1 = pr1 >= 0 ? s.phalf[pr1] : m.geom_size[g1]; const T* h2 = pr2 >= 0 ? s.phalf[pr2] : m.geom_size[g2];
         flag = !obb_separated(s.gpos[g1], s.gmat[g1], m.geom_aabb_c[g1], h1, s.gpos[g2], s.gmat[g2], m.geom_aabb_c[g2], h2, md);
-        if (flag && (m.geom_type[g1] == B2P_GEOM_MESH || m.geom_type[g2] == B2P_GEOM_MESH)) {
-          flag = !centre_axis_separated(s.gpos[g1], s.gmat[g1], h1, g.geom_dop + 27 * g1, m.geom_type[g1], s.gpos[g2], s.gmat[g2], h2, g.geom_dop + 27 * g2, m.geom_type[g2], md);
+        if (flag && (s.gtype[g1] == B2P_GEOM_MESH || s.gtype[g2] == B2P_GEOM_MESH)) {
+          flag = !centre_axis_separated(s.gpos[g1], s.gmat[g1], h1, g.geom_dop + 27 * g1, (int)s.gtype[g1], s.gpos[g2], s.gmat[g2], h2, g.geom_dop + 27 * g2, (int)s.gtype[g2], md);
           if (flag) for (int k = 0; k < SEP_N; k++) if (s.sep_pair[k] == p) { if (witness_separated(s.sep_w[k], s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], s.grbound[g2], md)) flag = false; }
         }
       }
@@ -516,15 +639,14 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
     // lanes that will run box_box borrow clip scratch from the FK / RNE sweep buffers (crb, cvel, cacc, cfrc), which are dead
     // once dynamics_terms has run: slot = rank among this round's box-box lanes, while slots last
     int bb_flag = 0;
-    if (ci < ncand) { const int pq = s.cand[ci]; bb_flag = m.geom_type[g.pair_g1[pq]] == B2P_GEOM_BOX && m.geom_type[g.pair_g2[pq]] == B2P_GEOM_BOX; }
+    if (ci < ncand) { const int pq = s.cand[ci]; bb_flag = s.gtype[g.pair_g1[pq]] == B2P_GEOM_BOX && s.gtype[g.pair_g2[pq]] == B2P_GEOM_BOX; }
     int bb_tot; const int bb_slot = block_scan(c, bb_flag, bb_tot);
     // (measured on B200: +4 % in fp64, where the local arrays are twice as large; -8 % in fp32, so fp32 keeps its local arrays)
     T* clip = (B2P_BB_SMEM && sizeof(T) == 8 && bb_flag && bb_slot < (MAXTB * 28) / BB_CLIP_REALS) ? &s.crb[0][0] + bb_slot * BB_CLIP_REALS : nullptr;
     if (ci < ncand) {
       p = s.cand[ci];
-      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], t1 = m.geom_type[g1], t2 = m.geom_type[g2];
-      const PairParam<T>& pp = g.pair_param[p];
-      md = full_contacts ? pp.margin : pp.margin - pp.gap;
+      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], t1 = s.gtype[g1], t2 = s.gtype[g2];
+      md = pair_md(m, g, s, p, g1, g2, full_contacts);
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
       const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1];
       const T* sz2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
@@ -533,6 +655,8 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
 #endif
       if (t1 == B2P_GEOM_PLANE) {
         if (t2 == B2P_GEOM_BOX) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
+        else if (t2 == B2P_GEOM_SPHERE) n = plane_sphere(s.gpos[g1], s.gmat[g1], s.gpos[g2], sz2[0], md, raw);
+        else if (t2 == B2P_GEOM_CYLINDER) n = plane_cylinder(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2[0], sz2[1], md, raw);
         else {   // an arm link that reaches the ground behind / beside the table
           CObj<T> h = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, T(0), g.geom_start + 27 * g2};
           n = plane_convex(s.gpos[g1], s.gmat[g1], h, g, md, raw);
@@ -547,6 +671,13 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) g_bb_calls++;
 #endif
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw, clip); convex = n < 0; if (n < 0) n = 0; }
+        else if (t1 == B2P_GEOM_SPHERE || t2 == B2P_GEOM_SPHERE) {   // the sphere class against sphere / box / cylinder is analytic; against a hull it goes to MPR
+          if (t1 == B2P_GEOM_SPHERE && t2 == B2P_GEOM_SPHERE) { n = sphere_sphere(s.gpos[g1], sz1[0], s.gpos[g2], sz2[0], md, raw); convex = false; }
+          else if (t1 == B2P_GEOM_SPHERE && (t2 == B2P_GEOM_BOX || t2 == B2P_GEOM_CYLINDER)) {
+            n = sphere_solid(t2, s.gpos[g1], sz1[0], s.gpos[g2], s.gmat[g2], sz2, md, raw); convex = false;
+            for (int k = 0; k < 3; k++) raw.normal[k] = -raw.normal[k];      // solid -> sphere is second -> first here
+          } else if (t2 == B2P_GEOM_SPHERE && (t1 == B2P_GEOM_BOX || t1 == B2P_GEOM_CYLINDER)) { n = sphere_solid(t1, s.gpos[g2], sz2[0], s.gpos[g1], s.gmat[g1], sz1, md, raw); convex = false; }
+        }
 #ifdef B2P_HOST_COUNTERS
         if (convex) g_pair_mpr[p & 1023]++;
 #endif
@@ -593,9 +724,14 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
     for (int i = 0; i < n; i++) {
       const int k = cbase + ofs + i;
       if (k >= MAXCON) break;
-      const PairParam<T>& pp = g.pair_param[p];
       s.c_dist[k] = raw.dist[i]; cp3(s.c_pos[k], raw.pos[i]); cp3(s.c_frame[k], raw.normal); make_frame(s.c_frame[k]);
-      s.c_pair[k] = (short)p; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k] = pp.friction[0]; s.c_row[k] = -1;
+      if (!s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k] = pp.friction[0]; s.c_dim[k] = 3; }
+      else {
+        PairMix<T> mx; pair_mix(m, g, s, p, g.pair_g1[p], g.pair_g2[p], mx);
+        s.c_incl[k] = mx.pp.margin - mx.pp.gap; s.c_fric[k] = mx.pp.friction[0]; s.c_dim[k] = (unsigned char)(mx.condim == 6 ? 6 : 3);
+        if (mx.condim == 6) { s.w6[k * W6_STRIDE + 21] = mx.pp.friction[1]; s.w6[k * W6_STRIDE + 22] = mx.pp.friction[2]; }
+      }
+      s.c_pair[k] = (short)p; s.c_row[k] = -1;
     }
     cbase += tot;
   }

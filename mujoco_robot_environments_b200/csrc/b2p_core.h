@@ -25,10 +25,23 @@ namespace b2p {
 // ------------------------------------------------------------------------------------------ pipeline
 template <typename T>
 B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+  // mass, principal inertia, invweight0 and bounding half extents per collider class (include/b2p_prop_types.h: b2p_prop_inertia)
   for (int p = c.tid; p < m.nprop; p += c.nt) {
-    const T* z = s.psize[p]; const T mass = m.prop_mass[p];
-    T I[3] = {mass / 3 * (z[1] * z[1] + z[2] * z[2]), mass / 3 * (z[0] * z[0] + z[2] * z[2]), mass / 3 * (z[0] * z[0] + z[1] * z[1])};
-    for (int k = 0; k < 3; k++) s.pinertia[p][k] = I[k];
+    const T* z = s.psize[p]; const int tp = s.ptype[p];
+    T mass, I[3], hf[3];
+    if (tp == B2P_GEOM_SPHERE) {
+      const T r = z[0]; mass = m.pclass_mass[0] > 0 ? m.pclass_mass[0] : T(1000.0 * 4.0 / 3.0 * 3.14159265358979323846) * r * r * r;
+      I[0] = I[1] = I[2] = T(0.4) * mass * r * r; hf[0] = hf[1] = hf[2] = r;
+    } else if (tp == B2P_GEOM_CYLINDER) {
+      const T r = z[0], h = z[1]; mass = m.pclass_mass[1] > 0 ? m.pclass_mass[1] : T(1000.0 * 3.14159265358979323846) * r * r * 2 * h;
+      I[0] = I[1] = mass * (T(0.25) * r * r + h * h / 3); I[2] = T(0.5) * mass * r * r; hf[0] = hf[1] = r; hf[2] = h;
+    } else {
+      mass = m.prop_mass[p];
+      I[0] = mass / 3 * (z[1] * z[1] + z[2] * z[2]); I[1] = mass / 3 * (z[0] * z[0] + z[2] * z[2]); I[2] = mass / 3 * (z[0] * z[0] + z[1] * z[1]);
+      hf[0] = z[0]; hf[1] = z[1]; hf[2] = z[2];
+    }
+    for (int k = 0; k < 3; k++) { s.pinertia[p][k] = I[k]; s.phalf[p][k] = hf[k]; }
+    s.pmass[p] = mass;
     s.pinvw[p][0] = 1 / mass; s.pinvw[p][1] = (1 / I[0] + 1 / I[1] + 1 / I[2]) / 3;
   }
   bsync(c);
@@ -129,6 +142,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     }
     for (int i = c.tid; i < MAXP * 3; i += c.nt) s.psize[i / 3][i % 3] = a.prop_size ? a.prop_size[(size_t)env * MAXP * 3 + i] : m.geom_size[0][0];
     for (int i = c.tid; i < MAXP; i += c.nt) s.pactive[i] = i < m.nprop ? (a.prop_active ? a.prop_active[(size_t)env * MAXP + i] : 1) : 0;
+    for (int i = c.tid; i < MAXP; i += c.nt) { const int tp = (a.prop_type && i < m.nprop) ? a.prop_type[(size_t)env * MAXP + i] : B2P_GEOM_BOX; s.ptype[i] = (unsigned char)((tp == B2P_GEOM_SPHERE || tp == B2P_GEOM_CYLINDER) ? tp : B2P_GEOM_BOX); }
     for (int i = c.tid; i < MAXU; i += c.nt) s.ctrl[i] = (a.ctrl && i < m.nu) ? a.ctrl[(size_t)env * m.nu + i] : T(0);
     if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; s.sp.nblk = 0; s.sep_next = 0; for (int k = 0; k < SEP_N; k++) s.sep_pair[k] = -1; }   // sp.nblk = 0: no block structure built yet (make_rows)
     bsync(c);
@@ -136,6 +150,8 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       for (int g0 = c.tid; g0 < m.ngeom; g0 += c.nt) if (m.geom_prop[g0] >= 0) for (int k = 0; k < 3; k++) s.psize[m.geom_prop[g0]][k] = m.geom_size[g0][k];
       bsync(c);
     }
+    for (int g0 = c.tid; g0 < MAXG; g0 += c.nt) s.gtype[g0] = (unsigned char)(g0 < m.ngeom ? (m.geom_prop[g0] >= 0 ? s.ptype[m.geom_prop[g0]] : m.geom_type[g0]) : 0);
+    if (c.tid == 0) { int any = 0; for (int p = 0; p < m.nprop; p++) any |= s.ptype[p] != B2P_GEOM_BOX; s.reclassed = any; }
     prop_params(m, s, c);
   }
   if constexpr (kPlace) {

@@ -83,7 +83,7 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   mbar_wait(&sm.bar[0], 0);
   Scratch<T>& s = sm.scratch[warp];
   constexpr bool kPlace = kVar == VAR_PLACE;
-  if (lane == 0) { s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP; s.xpool = g.xpool ? g.xpool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP : nullptr; }
+  if (lane == 0) { s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP; s.xpool = g.xpool ? g.xpool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP : nullptr; s.w6 = g.w6pool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * MAXCON * W6_STRIDE; }
   __syncwarp();
   unsigned long long* bar = &sm.bar[1 + warp];
   unsigned phase = 0;

@@ -131,7 +131,7 @@ B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       s.qfrc_bias[d] = v;
       s.qfrc_passive[d] = -m.dof_damping[d] * s.qvel[d] - m.jnt_stiffness[d] * (s.qpos[d] - m.qpos_spring[d]);
     } else {
-      const int p = (d - n) / 6, k = (d - n) % 6; const T mass = m.prop_mass[p];
+      const int p = (d - n) / 6, k = (d - n) % 6; const T mass = s.pmass[p];
       if (k < 3) { s.Mdiag[d] = mass; s.qfrc_bias[d] = -mass * m.gravity[k]; }
       else {
         const T* w = s.qvel + n + 6 * p + 3; const T* I = s.pinertia[p];

@@ -14,6 +14,7 @@
 #include <vector>
 
 #include "../../include/b2p_model_layout.h"
+#include "../../include/b2p_prop_types.h"
 
 namespace b2p {
 
@@ -43,10 +44,10 @@ constexpr int PROP_BODY0 = MAXTB;
 // (grasps, arm contacts) spill to a per-warp overflow area in global memory (L1/L2 resident): shared memory per scene is what
 // bounds the scenes in flight per SM, and the kernel is latency bound.
 #ifndef B2P_JPS_F32
-#define B2P_JPS_F32 704
+#define B2P_JPS_F32 640
 #endif
 #ifndef B2P_JPS_F64
-#define B2P_JPS_F64 640
+#define B2P_JPS_F64 576
 #endif
 template <typename T> struct Pool { static constexpr int EFC = B2P_EFC_F32, JP = B2P_JPOOL_F32, JPS = B2P_JPS_F32; };
 template <> struct Pool<double> { static constexpr int EFC = 160, JP = 2944, JPS = B2P_JPS_F64; };
@@ -68,6 +69,11 @@ template <typename T>
 struct PairParam {               // per candidate geom pair, mixed contact parameters (App. B item 10)
   T friction[3]; T solref[2]; T solimp[5]; T margin; T gap;
 };
+template <typename T>
+struct GeomRaw {                 // a geom's own contact parameters: mixed on the device for pairs with a re-classed prop (sphere / cylinder)
+  int priority, condim; T friction[3]; T solref[2]; T solimp[5]; T solmix, margin, gap;
+};
+constexpr int NPCLASS = 2;       // re-classable prop colliders beyond the box: 0 sphere, 1 cylinder (include/b2p_prop_types.h)
 
 template <typename T>
 struct alignas(16) DevModel {
@@ -85,6 +91,7 @@ struct alignas(16) DevModel {
   int jnt_limited[MAXTD];
   // props
   T prop_mass[MAXP];
+  GeomRaw<T> pclass[NPCLASS]; T pclass_mass[NPCLASS];   // the sphere / cylinder prop classes (mass < 0: density 1000 x volume)
   // geoms
   int geom_type[MAXG], geom_body[MAXG], geom_vertadr[MAXG], geom_vertnum[MAXG], geom_prop[MAXG];
   T geom_size[MAXG][3], geom_pos[MAXG][3], geom_quat[MAXG][4], geom_rbound[MAXG], geom_invweight0[MAXG][2];
@@ -108,6 +115,7 @@ struct alignas(16) DevModel {
 struct HostTables {              // global-memory tables, always fp64 on host; converted on upload
   std::vector<double> mesh_vert, geom_dop; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr, geom_start;
   std::vector<int> pair_g1, pair_g2; std::vector<double> pair_param;  // 12 doubles per pair
+  std::vector<GeomRaw<double>> geom_raw;
 };
 
 struct BlobView {
@@ -175,6 +183,16 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   // spatial reference point: the (world-fixed) anchor of dof 0 at qpos0 = parent-chain of static frames
   cp(m.ref, b.D(B2PM_F_BODY_POS) + 3 * 1, 3);   // body 1's parent is the (fused) world
   for (int p = 0; p < nprop; p++) m.prop_mass[p] = b.D(B2PM_F_PROP_MASS)[p];
+  {
+    const b2p_prop_class* cls[NPCLASS] = {&B2P_PROP_CLASS_SPHERE, &B2P_PROP_CLASS_CYLINDER};
+    for (int k = 0; k < NPCLASS; k++) {
+      GeomRaw<double>& r = m.pclass[k]; r.priority = cls[k]->priority; r.condim = cls[k]->condim;
+      for (int q = 0; q < 3; q++) r.friction[q] = cls[k]->friction[q];
+      for (int q = 0; q < 2; q++) r.solref[q] = cls[k]->solref[q];
+      for (int q = 0; q < 5; q++) r.solimp[q] = cls[k]->solimp[q];
+      r.solmix = cls[k]->solmix; r.margin = cls[k]->margin; r.gap = cls[k]->gap; m.pclass_mass[k] = cls[k]->mass;
+    }
+  }
   const int *gt = b.I(B2PM_F_GEOM_TYPE), *gb = b.I(B2PM_F_GEOM_BODYID), *gm = b.I(B2PM_F_GEOM_MESHID), *gp = b.I(B2PM_F_GEOM_PROPID), *condim = b.I(B2PM_F_GEOM_CONDIM);
   const int *vadr = b.I(B2PM_F_MESH_VERTADR), *vnum = b.I(B2PM_F_MESH_VERTNUM);
   for (int g = 0; g < ngeom; g++) {
@@ -271,6 +289,14 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   const int *p1 = b.I(B2PM_F_PAIR_GEOM1), *p2 = b.I(B2PM_F_PAIR_GEOM2), *prio = b.I(B2PM_F_GEOM_PRIORITY);
   const double *fr = b.D(B2PM_F_GEOM_FRICTION), *sr = b.D(B2PM_F_GEOM_SOLREF), *si = b.D(B2PM_F_GEOM_SOLIMP), *sm = b.D(B2PM_F_GEOM_SOLMIX);
   const double *mg = b.D(B2PM_F_GEOM_MARGIN), *gg = b.D(B2PM_F_GEOM_GAP);
+  ht.geom_raw.resize(m.ngeom);
+  for (int q = 0; q < m.ngeom; q++) {
+    GeomRaw<double>& r = ht.geom_raw[q]; r.priority = prio[q]; r.condim = condim[q];
+    for (int k = 0; k < 3; k++) r.friction[k] = fr[3 * q + k];
+    for (int k = 0; k < 2; k++) r.solref[k] = sr[2 * q + k];
+    for (int k = 0; k < 5; k++) r.solimp[k] = si[5 * q + k];
+    r.solmix = sm[q]; r.margin = mg[q]; r.gap = gg[q];
+  }
   for (int p = 0; p < m.npair; p++) {
     int g1 = p1[p], g2 = p2[p]; double pp[12];
     if (prio[g1] != prio[g2]) {
@@ -303,7 +329,8 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
   CI(tb_parent); CI(level_start); CI(level_body); CI(child_start); CI(child_list); CI(anc_mask);
   CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0);
   CR(jnt_pos); CR(jnt_axis); CR(jnt_stiffness); CR(jnt_range); CR(jnt_margin); CR(jnt_solref); CR(jnt_solimp); CR(qpos0); CR(qpos_spring);
-  CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass);
+  CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass); CR(pclass_mass);
+  for (int k = 0; k < NPCLASS; k++) { d.pclass[k].priority = s.pclass[k].priority; d.pclass[k].condim = s.pclass[k].condim; for (int q = 0; q < 3; q++) d.pclass[k].friction[q] = (T)s.pclass[k].friction[q]; for (int q = 0; q < 2; q++) d.pclass[k].solref[q] = (T)s.pclass[k].solref[q]; for (int q = 0; q < 5; q++) d.pclass[k].solimp[q] = (T)s.pclass[k].solimp[q]; d.pclass[k].solmix = (T)s.pclass[k].solmix; d.pclass[k].margin = (T)s.pclass[k].margin; d.pclass[k].gap = (T)s.pclass[k].gap; }
   CI(geom_type); CI(geom_body); CI(geom_vertadr); CI(geom_vertnum); CI(geom_prop);
   CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(geom_aabb_c); CR(site_pos); CR(site_quat);
   CI(eq_type); CI(eq_obj1); CI(eq_obj2); CR(eq_data); CR(eq_solref); CR(eq_solimp);

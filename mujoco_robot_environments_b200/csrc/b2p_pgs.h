@@ -72,6 +72,11 @@ B2P_HDN void solve_pgs(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool a
     bsync(c);
   }
   if (!has) return;
+  {   // condim-6 contacts (cylinder class): this PGS, like the oracle's, covers condim 1 and 3 -- such a step is solved by Newton and flagged
+    unsigned six = 0;
+    for (int k = c.tid; k < s.ncon; k += c.nt) if (s.c_row[k] >= 0 && s.c_dim[k] == 6) six = 1;
+    if (block_or(c, six)) { if (c.tid == 0) s.flags |= FLAG_PGS_CONDIM6; solve_constraints(m, s, c, active); return; }
+  }
   const int n = s.nefc;
   const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
   // ---- X = M^-1 J' (prop segments: diagonal; tree segments: one triangular solve with the factor of M per row)

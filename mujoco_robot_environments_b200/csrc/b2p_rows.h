@@ -1,5 +1,6 @@
 #pragma once
 #include "b2p_linalg.h"
+#include "b2p_collide.h"
 
 namespace b2p {
 
@@ -48,6 +49,18 @@ B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0,
     }
   }
 }
+// ... and of its angular velocity (rows 3..5 of a condim-6 contact: torsional and rolling friction)
+template <typename T>
+B2P_HD void add_jac_rot(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0, int body, const T* ax, T sign) {
+  if (body == 0) return;
+  if (body >= PROP_BODY0) {
+    const int p = body - PROP_BODY0;
+    for (int k = 0; k < 3; k++) row[seg0 + 3 + k] += sign * (ax[0] * s.pmat[p][k] + ax[1] * s.pmat[p][3 + k] + ax[2] * s.pmat[p][6 + k]);
+  } else {
+    const unsigned mask = m.anc_mask[body];
+    for (int d = 0; d < m.ntd; d++) if (mask & (1u << d)) row[seg0 + d] += sign * dot3(ax, s.cdof[d]);
+  }
+}
 template <typename T>
 B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
   const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a);
@@ -82,7 +95,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       } else {
         id = it - m.neq - nlim;
         if (s.c_dist[id] < s.c_incl[id]) {
-          kind = ROW_CONTACT; nr = 3;
+          kind = ROW_CONTACT; nr = s.c_dim[id];
           // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
           const int p = s.c_pair[id], b1 = m.geom_body[g.pair_g1[p]], b2 = m.geom_body[g.pair_g2[p]];
           const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
@@ -163,7 +176,9 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
     } else {
       const int q = r - s.c_row[id];
       const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
-      const PairParam<T>& pp = g.pair_param[p];
+      PairMix<T> mx;
+      if (!s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
+      const PairParam<T>& pp = mx.pp;
       // segment of each body inside the packed row: the tree (or the first prop) heads it, a second block follows
       const int seg1 = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0, seg2 = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
       const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
@@ -171,11 +186,16 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
       const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
       if (q == 0) s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0);
-      const T* ax = s.c_frame[id] + 3 * q;
-      add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1));
+      const T* ax = s.c_frame[id] + 3 * (q < 3 ? q : q - 3);
+      if (q < 3) { add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1)); }
+      else { add_jac_rot(m, s, J0, seg2, b2, ax, T(1)); add_jac_rot(m, s, J0, seg1, b1, ax, T(-1)); }
       const T vel = row_vel(m, s, r);
       if (q == 0) { s.D[r] = 1 / R0; s.aref[r] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
-      else { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
+      else if (q < 3) { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
+      else {   // App. B item 9: R_k = R_1 mu_0^2 / mu_k^2 for the torsional (k = 3) and rolling (k = 4, 5) rows
+        const T fk = s.w6[id * W6_STRIDE + (q == 3 ? 21 : 22)], f0 = s.c_fric[id];
+        s.D[r] = 1 / (R1 * f0 * f0 / (fk * fk)); s.aref[r] = -B * vel;
+      }
     }
   }
   bsync(c);

@@ -7,6 +7,7 @@ namespace b2p {
 // HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
 constexpr int REC_QPOS = 0, REC_QVEL = MAXNQ, REC_QACC = MAXNQ + MAXNV, REC_TIME = MAXNQ + 2 * MAXNV, REC_SIZE = 128;
 // one hull-graph neighbour with its coordinates inline (one 16-byte load in fp32), and (first neighbour, count) per vertex
+constexpr int W6_STRIDE = 24;        // reals per condim-6 contact in the w6 area: 21 (packed lower triangle) + torsional, rolling friction + pad
 constexpr int SEP_N = 8;             // separation witnesses kept per scene
 template <typename T> struct alignas(16) NbrPt { T x, y, z; int idx; };
 struct NbrSpan { int adr, num; };
@@ -18,7 +19,9 @@ struct Globals {                 // read-only global-memory tables
   const NbrPt<T>* nbr_pt;        // [nmeshnbr] neighbour vertex coordinates + index, same order as nbr
   const NbrSpan* nbr_span;       // [nmeshvert]
   T* jovf;                       // [warp slots][Pool<T>::JP] Jacobian rows that do not fit a scene's shared-memory pool
+  T* w6pool;                     // [warp slots][MAXCON][W6_STRIDE] condim-6 contacts: cone Hessian blocks + friction coefficients
   T* xpool;                      // [warp slots][Pool<T>::JP] PGS only: X = M^-1 J' in J's packed layout (NULL until b2p_set_solver(PGS))
+  const GeomRaw<T>* geom_raw;    // [ngeom] unmixed contact parameters (pairs with a re-classed prop are mixed on the device)
   const T* geom_dop;             // [ngeom][27] hull support value along the 26 directions {-1,0,1}^3 (mesh geoms): 26-DOP bound
 };
 
@@ -32,6 +35,7 @@ struct alignas(16) Scratch {
   T qpos[MAXNQ], qvel[MAXNV], qacc_ws[MAXNV], time, rec_pad[REC_SIZE - (MAXNQ + 2 * MAXNV + 1)], ctrl[MAXU];
   // per-env prop parameters
   T psize[MAXP][3], pinertia[MAXP][3], pinvw[MAXP][2]; int pactive[MAXP];
+  T phalf[MAXP][3], pmass[MAXP]; unsigned char ptype[MAXP], gtype[MAXG]; int reclassed;   // collider class per prop (B2P_GEOM_*), bounding half extents, mass; gtype: this scene's geom types
   // tree (spatial quantities about the fixed reference point m.ref)
   T xpos[MAXTB][3], xmat[MAXTB][9], cdof[MAXTD][6];
   T ppos[MAXP][3], pmat[MAXP][9];
@@ -43,11 +47,12 @@ struct alignas(16) Scratch {
   // contacts
   int ncand, ncon, nefc, flags, niter, jused, nmpr; unsigned cpl_pairs;
   T c_dist[MAXCON], c_mu[MAXCON], c_fric[MAXCON], c_incl[MAXCON];
-  short c_pair[MAXCON], c_row[MAXCON];
+  short c_pair[MAXCON], c_row[MAXCON]; unsigned char c_dim[MAXCON];   // c_dim: 3, or 6 for a contact of the cylinder class (torsional + rolling rows)
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A
   // (block row_a: ntd tree slots or 6 prop slots) followed by segment B (block row_b: 6 prop slots, or absent).
   T Jp[Pool<T>::JPS], D[Pool<T>::EFC], aref[Pool<T>::EFC], force[Pool<T>::EFC];
   T* xpool;                      // this warp's M^-1 J' area (PGS)
+  T* w6;                         // this warp's condim-6 area (global memory, [MAXCON][W6_STRIDE]): packed 6 x 6 cone Hessian, torsional and rolling friction
   T* jovf;                       // this warp's overflow area (global memory, Pool<T>::JP reals): joff[r] < 0 <=> row r lives at jovf[-joff[r] - 1]
   signed char row_a[Pool<T>::EFC], row_b[Pool<T>::EFC], row_type[Pool<T>::EFC], row_state[Pool<T>::EFC];
   short row_id[Pool<T>::EFC], joff[Pool<T>::EFC], eq_row0[MAXEQ];   // eq_row0: first row of equality e
@@ -103,6 +108,7 @@ struct StepArgs {
   const unsigned char* grip; // MODE_OSC: [n_env] 0 = min, 1 = max
   const T* prop_size;        // [n_env][MAXP][3] half sizes
   const unsigned char* prop_active; // [n_env][MAXP]
+  const unsigned char* prop_type;   // optional [n_env][MAXP] collider class per prop: B2P_GEOM_BOX (as compiled) / SPHERE / CYLINDER; NULL = boxes
   const unsigned char* env_mask;    // optional [n_env]: 0 = skip env
   unsigned char* converged;  // MODE_OSC out [n_env]
   int* status;               // out [n_env] OR-ed flags

@@ -12,6 +12,63 @@ B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, c
     else r[d] = s.Mdiag[d] * v[d];
   }
 }
+// ---- condim-6 contacts (the cylinder prop class: normal, 2 tangential, torsional, 2 rolling rows).  Rare, so they live in their own
+// out-of-line functions with plain loops over the 6 rows, and their 6 x 6 cone Hessian sits in the warp's global w6 area; the
+// condim-3 code above / below stays unrolled and in shared memory.
+template <typename T> B2P_HD int tri6(int a, int b) { return a >= b ? (a * (a + 1)) / 2 + b : (b * (b + 1)) / 2 + a; }
+template <typename T> B2P_HD void friction5(const Scratch<T>& s, int k, T* fr) { const T f0 = s.c_fric[k], ft = s.w6[k * W6_STRIDE + 21], fl = s.w6[k * W6_STRIDE + 22]; fr[0] = f0; fr[1] = f0; fr[2] = ft; fr[3] = fl; fr[4] = fl; }
+template <typename T>
+B2P_HDN T cone6_update(Scratch<T>& s, int k, int r, bool want_hess, unsigned& chg) {
+  const T mu = s.c_mu[k]; T fr[5]; friction5(s, k, fr);
+  T U[6], Tt = 0, cost = 0;
+  U[0] = s.Jaref[r] * mu;
+  for (int i = 1; i < 6; i++) { U[i] = s.Jaref[r + i] * fr[i - 1]; Tt += U[i] * U[i]; }
+  Tt = sqrt(Tt); const T N = U[0];
+  T* W = s.w6 + k * W6_STRIDE;
+  const int old = s.row_state[r];
+  if (N >= mu * Tt || (Tt <= 0 && N >= 0)) {
+    for (int q = 0; q < 6; q++) { s.force[r + q] = 0; s.row_state[r + q] = ST_SATISFIED; }
+    if (want_hess) for (int q = 0; q < 21; q++) W[q] = 0;
+  } else if (mu * N + Tt <= 0 || (Tt <= 0 && N < 0)) {
+    for (int q = 0; q < 6; q++) { const T jq = s.Jaref[r + q]; s.force[r + q] = -s.D[r + q] * jq; s.row_state[r + q] = ST_QUADRATIC; cost += T(0.5) * s.D[r + q] * jq * jq; }
+    if (want_hess) { for (int q = 0; q < 21; q++) W[q] = 0; for (int q = 0; q < 6; q++) W[tri6<T>(q, q)] = s.D[r + q]; }
+  } else {
+    const T mv = Num<T>::minval(), dn = mu * mu * (1 + mu * mu), Dm = s.D[r] / (dn > mv ? dn : mv), NmT = N - mu * Tt;
+    cost += T(0.5) * Dm * NmT * NmT;
+    const T fn = -Dm * NmT * mu;
+    s.force[r] = fn;
+    for (int i = 1; i < 6; i++) s.force[r + i] = -fn / Tt * U[i] * fr[i - 1];
+    for (int q = 0; q < 6; q++) s.row_state[r + q] = ST_CONE;
+    if (want_hess) {
+      T sc[6]; sc[0] = mu; for (int i = 1; i < 6; i++) sc[i] = fr[i - 1];
+      const T iT = 1 / Tt, iT2 = iT * iT, iT3 = iT2 * iT;
+      W[0] = Dm * sc[0] * sc[0];
+      for (int a = 1; a < 6; a++) {
+        W[tri6<T>(a, 0)] = -Dm * mu * U[a] * iT * sc[a] * sc[0];
+        for (int b = 1; b <= a; b++) W[tri6<T>(a, b)] = (Dm * mu * mu * U[a] * U[b] * iT2 - Dm * mu * NmT * ((a == b ? iT : T(0)) - U[a] * U[b] * iT3)) * sc[a] * sc[b];
+      }
+    }
+  }
+  chg |= (unsigned)(old != s.row_state[r] || s.row_state[r] == ST_CONE);
+  return cost;
+}
+// line-search terms of one condim-6 contact at step a: (quadratic q0 q1 q2 when the whole contact is quadratic) or (cone ec e1 e2)
+template <typename T>
+B2P_HDN void cone6_ls(const Scratch<T>& s, int k, int r, T a, T* q, T* e) {
+  const T mu = s.c_mu[k]; T fr[5]; friction5(s, k, fr);
+  T t0 = 0, t1 = 0, t2 = 0, UU = 0, UV = 0, VV = 0;
+  for (int i = 0; i < 6; i++) { const T D = s.D[r + i], j0 = s.Jaref[r + i], jv = s.Jv[r + i]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }
+  for (int i = 1; i < 6; i++) { const T u = s.Jaref[r + i] * fr[i - 1], v = s.Jv[r + i] * fr[i - 1]; UU += u * u; UV += u * v; VV += v * v; }
+  const T U0 = s.Jaref[r] * mu, V0 = s.Jv[r] * mu, N = U0 + a * V0, Tsqr = UU + a * (2 * UV + a * VV);
+  if (Tsqr <= 0) { if (N < 0) { q[0] += t0; q[1] += t1; q[2] += t2; } return; }
+  const T Tt = sqrt(Tsqr);
+  if (N >= mu * Tt) return;
+  if (mu * N + Tt <= 0) { q[0] += t0; q[1] += t1; q[2] += t2; return; }
+  const T mv = Num<T>::minval(), dn = mu * mu * (1 + mu * mu), Dm = s.D[r] / (dn > mv ? dn : mv);
+  const T N1 = V0, T1 = (UV + a * VV) / Tt, T2 = VV / Tt - (UV + a * VV) * T1 / (Tt * Tt), NmT = N - mu * Tt;
+  e[0] += T(0.5) * Dm * NmT * NmT; e[1] += Dm * NmT * (N1 - mu * T1); e[2] += Dm * ((N1 - mu * T1) * (N1 - mu * T1) + NmT * (-mu * T2));
+}
+
 // per-item (rows of eq/limit, whole contacts) force/state/cost from s.Jaref; returns this thread's cost part
 template <typename T>
 B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess, unsigned* dirty = nullptr) {
@@ -30,6 +87,7 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, b
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
+    if (s.c_dim[k] == 6) { cost += cone6_update(s, k, r, want_hess, chg); continue; }
     const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     const T j0 = s.Jaref[r], j1 = s.Jaref[r + 1], j2 = s.Jaref[r + 2];
     const T N = j0 * mu, U1 = j1 * f1, U2 = j2 * f2, Tt = sqrt(U1 * U1 + U2 * U2);
@@ -67,7 +125,7 @@ B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
     const unsigned char* lst = block_rows(s, blk);
     T a = 0;
     for (int q = 0; q < n; q++) {
-      const int r = lst[q], tp = s.row_type[r], nr = (tp == ROW_CONTACT || (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT)) ? 3 : 1;
+      const int r = lst[q], tp = s.row_type[r], nr = tp == ROW_CONTACT ? s.c_dim[s.row_id[r]] : ((tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1);
       const T* seg = row_seg(m, s, r, blk);
       const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
       for (int k = 0; k < nr; k++) { const T f = s.force[r + k]; if (f != 0) a += seg[k * w + o] * f; }
@@ -98,7 +156,12 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
         const T* si = row_seg(m, s, r, bi);
         if (bi == bj) sj = si;
         const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
-        if (tp == ROW_CONTACT) {
+        if (tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
+          if (s.row_state[r] != ST_SATISFIED) {
+            const T* W = s.w6 + s.row_id[r] * W6_STRIDE;
+            for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi]; if (ai != 0) for (int b = 0; b < 6; b++) h += W[tri6<T>(a, b)] * ai * sj[b * w + oj]; }
+          }
+        } else if (tp == ROW_CONTACT) {
           if (s.row_state[r] != ST_SATISFIED) {
             const T* W = s.cW[s.row_id[r]];
             const T a0 = si[oi], a1 = si[w + oi], a2 = si[2 * w + oi], b0 = sj[oj], b1 = sj[w + oj], b2 = sj[2 * w + oj];
@@ -126,6 +189,7 @@ B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, 
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
+    if (s.c_dim[k] == 6) { T qq[3] = {0, 0, 0}, ee[3] = {0, 0, 0}; cone6_ls(s, k, r, a, qq, ee); q0 += qq[0]; q1 += qq[1]; q2 += qq[2]; ec += ee[0]; e1 += ee[1]; e2 += ee[2]; continue; }
     const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     T t0 = 0, t1 = 0, t2 = 0;
     for (int q = 0; q < 3; q++) { const T D = s.D[r + q], j0 = s.Jaref[r + q], jv = s.Jv[r + q]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }

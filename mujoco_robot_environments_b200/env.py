@@ -22,6 +22,7 @@ import numpy as np
 import torch
 
 from . import config as cfglib
+from . import ffi
 from .controllers import BatchedMinMax, BatchedOSC
 from .expert import Camera, SortColoursExpert, euler_xyz_matrix, mat2quat, sample_prop_colours
 from .physics import BatchedPhysics
@@ -70,6 +71,8 @@ class BatchedRearrangementEnv:
         self.n_props = torch.zeros(self.num_envs, dtype=torch.int64, device=self.device)
         self.has_prop = torch.zeros(self.num_envs, self.max_props, dtype=torch.bool, device=self.device)
         self.prop_half_size = torch.zeros(self.num_envs, self.max_props, 3, device=self.device, dtype=self.dtype)
+        self.prop_type = torch.full((self.num_envs, self.max_props), ffi.GEOM["box"], dtype=torch.uint8, device=self.device)   # collider class per prop
+        self.props_clamped = 0
         self.prop_colour = torch.zeros(self.num_envs, self.max_props, dtype=torch.int64, device=self.device)
         self.prop_rgba = torch.zeros(self.num_envs, self.max_props, 4, dtype=torch.float32, device=self.device)
         self.resample_scenes()
@@ -108,18 +111,40 @@ class BatchedRearrangementEnv:
             return
         lo, hi = int(pc["min_objects"]), int(pc["max_objects"])
         n = np.full(k, lo) if lo == hi else self._crng.integers(lo, hi, k)                    # np.random.randint(lo, hi): hi exclusive
-        if n.max() > self.max_props:
-            raise ValueError("prop set needs %d props, the compiled model has %d" % (n.max(), self.max_props))
-        half = self._crng.uniform(pc["min_object_size"], pc["max_object_size"], (k, self.max_props, 1)).repeat(3, axis=2)
+        if lo > self.max_props:
+            raise ValueError("prop set needs at least %d props, the compiled model has %d" % (lo, self.max_props))
+        # itl_rearrangement draws 4 or 5 props; the compiled model class holds 4 (MAXP): a fifth is not placed, and counted here
+        self.props_clamped += int((n > self.max_props).sum())
+        n = np.minimum(n, self.max_props)
+        # shape per prop (add_objects, props.py:604-617: random.choice(shapes)) -> collider class and its size parameters
+        #   cube: 3 x [U]; rectangle: U(3) (props.py:277-284); cylinder: (radius, half height) = U(2) (:360-364); apple: the asset's sphere
+        shapes = list(pc.get("shapes", ["cube"]))
+        unknown = [x for x in shapes if x not in cfglib.SHAPES]
+        if unknown:
+            raise ValueError("prop shapes %r are not among the collider classes %r" % (unknown, cfglib.SHAPES))
+        sidx = self._crng.integers(0, len(shapes), (k, self.max_props))
+        u = self._crng.uniform(pc["min_object_size"], pc["max_object_size"], (k, self.max_props, 3))
+        half = np.zeros((k, self.max_props, 3)); ptype = np.full((k, self.max_props), ffi.GEOM["box"], np.uint8)
+        for si, name in enumerate(shapes):
+            sel = sidx == si
+            if name == "cube":
+                half[sel] = u[sel][:, :1].repeat(3, axis=1)
+            elif name == "rectangle":
+                half[sel] = u[sel]
+            elif name == "cylinder":
+                half[sel] = np.concatenate([u[sel][:, :2], np.zeros((int(sel.sum()), 1))], 1); ptype[sel] = ffi.GEOM["cylinder"]
+            else:
+                half[sel] = [cfglib.APPLE_RADIUS, 0.0, 0.0]; ptype[sel] = ffi.GEOM["sphere"]
         # "grey" of single_block has no COLOURS entry in the reference either
         cidx, rgba = sample_prop_colours(k, self.max_props, [c for c in pc["colours"] if c != "grey"], self._crng)
         di = torch.as_tensor(idx, device=self.device)
         self.n_props[di] = torch.tensor(n, device=self.device)
         self.has_prop[di] = torch.arange(self.max_props, device=self.device)[None, :] < self.n_props[di][:, None]
         self.prop_half_size[di] = torch.tensor(half, device=self.device, dtype=self.dtype)
+        self.prop_type[di] = torch.tensor(ptype, device=self.device)
         self.prop_colour[di] = torch.tensor(cidx, device=self.device)
         self.prop_rgba[di] = torch.tensor(rgba, device=self.device)
-        self._physics.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8))
+        self._physics.set_env_params(self.prop_half_size, self.has_prop.to(torch.uint8), self.prop_type)
 
     # ------------------------------------------------------------------ accessors
     @property
@@ -198,9 +223,10 @@ class BatchedRearrangementEnv:
                     if (self._sampler != "device" or attempt % 4 == 3) and not bool(todo.any()):
                         break
                 else:
-                    if self.strict:
-                        raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
-                    stuck |= todo
+                    if bool(todo.any()):          # (the device sampler looks at `todo` every 4th try only: the last tries may have succeeded)
+                        if self.strict:
+                            raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
+                        stuck |= todo
             if not bool(stuck.any()):
                 return
             # park every prop of the stuck scenes and start their placement over

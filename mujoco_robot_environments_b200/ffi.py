@@ -26,10 +26,11 @@ Q = dict(NQ=0, NV=1, NU=2, NPROP=3, STATE_STRIDE=4, OUT_STRIDE=5, MAXPROP=6, REC
          REC_TIME=10, LAUNCHES=11, SMEM_BYTES=12, BLOCKS_PER_SM=13, THREADS=14, GRID=15, MAXCON=16, NGEOM=17, ORDER_LAUNCHES=18)
 O = dict(SITE_XPOS=0, SITE_XMAT=1, QACC=2, QFRC_BIAS=3, CTRL=4, NCON=5, NEFC=6, NITER=7, CONTACT=8, MARM=9, GEOM_XPOS=10,
          GEOM_XMAT=11, QACC_SMOOTH=12, EFC_FORCE=13)
-SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params", "b2p_set_out_mask", "b2p_set_solver",
+SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params", "b2p_set_out_mask", "b2p_set_solver", "b2p_set_env_prop_types",
            "b2p_osc_config", "b2p_set_env_gains", "b2p_set_env_mask", "b2p_set_full_contacts", "b2p_step_physics", "b2p_step_osc", "b2p_settle", "b2p_forward", "b2p_place_search", "b2p_get",
            "b2p_status", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error",
            "b2p_render_create", "b2p_render_destroy", "b2p_render_query", "b2p_render"]          # include/b2p_render.h
+GEOM = dict(box=6, sphere=2, cylinder=5)            # B2P_GEOM_* of include/b2p_model_layout.h (MuJoCo's mjtGeom numbering)
 SOLVER = dict(newton=0, pgs=1)
 OUT = dict(SITE=1, CONTACT=2, MARM=4, GEOM=8, BIAS=16, DYN=32, EFC=64, ALL=127)
 RQ = dict(WIDTH=0, HEIGHT=1, NGEOM=2, LAUNCHES=3, TILES_COPIED=4, TILES_CAST=5)
@@ -81,6 +82,7 @@ def lib() -> C.CDLL:
     L.b2p_set_env_params.argtypes = [vp, vp, u8p]
     L.b2p_set_out_mask.argtypes = [vp, i32]
     L.b2p_set_solver.argtypes = [vp, i32]
+    L.b2p_set_env_prop_types.argtypes = [vp, u8p]
     L.b2p_osc_config.argtypes = [vp, C.POINTER(C.c_double), C.POINTER(C.c_double), C.c_double, C.c_double]
     L.b2p_set_full_contacts.argtypes = [vp, i32]
     L.b2p_set_env_gains.argtypes = [vp, vp]

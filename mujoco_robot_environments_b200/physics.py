@@ -72,12 +72,14 @@ class BatchedPhysics:
             pad = torch.ones(self.n_env, self.maxprop - self.prop_size.shape[1], 3, **kw) * 0.0155
             self.prop_size = torch.cat([self.prop_size, pad], 1).contiguous()
         self.prop_active = torch.ones(self.n_env, self.maxprop, device=self.device, dtype=torch.uint8)
+        self.prop_type = torch.full((self.n_env, self.maxprop), ffi.GEOM["box"], device=self.device, dtype=torch.uint8)   # collider class per prop
         self.converged = torch.zeros(self.n_env, device=self.device, dtype=torch.uint8)
         self.steps_done = torch.zeros(self.n_env, device=self.device, dtype=torch.int32)
         self._status = torch.zeros(self.n_env, device=self.device, dtype=torch.int32)
         ffi.check(self._L.b2p_bind_state(self._h, self.state.data_ptr()), "b2p_bind_state")
         ffi.check(self._L.b2p_bind_out(self._h, self.out.data_ptr()), "b2p_bind_out")
         ffi.check(self._L.b2p_set_env_params(self._h, self.prop_size.data_ptr(), self.prop_active.data_ptr()), "b2p_set_env_params")
+        ffi.check(self._L.b2p_set_env_prop_types(self._h, self.prop_type.data_ptr()), "b2p_set_env_prop_types")
         self._ofs = {}
         for k, fid in ffi.O.items():
             o, c = C.c_int(), C.c_int()
@@ -216,14 +218,19 @@ class BatchedPhysics:
     def set_full_contacts(self, full: bool):
         ffi.check(self._L.b2p_set_full_contacts(self._h, int(full)))
 
-    def set_env_params(self, prop_size: Optional[torch.Tensor] = None, prop_active: Optional[torch.Tensor] = None):
+    def set_env_params(self, prop_size: Optional[torch.Tensor] = None, prop_active: Optional[torch.Tensor] = None,
+                       prop_type: Optional[torch.Tensor] = None):
+        """Per-scene prop parameters: half sizes [n, P, 3] (sphere: [r, -, -]; cylinder: [r, half height, -]), active flags [n, P] and
+        collider class [n, P] (``ffi.GEOM``: box 6 / sphere 2 / cylinder 5; environment/props.py draws a shape per prop)."""
+        if prop_type is not None:
+            self.prop_type.copy_(prop_type.to(self.prop_type))
         if prop_size is not None:
             self.prop_size.copy_(prop_size.to(self.prop_size))
         if prop_active is not None:
             self.prop_active.copy_(prop_active.to(self.prop_active))
 
     # bit k of status(): the first three are mj_checkPos / Vel / Acc, the rest capacity / iteration-cap notes (csrc/b2p_math.h)
-    STATUS_FLAGS = ("badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter")
+    STATUS_FLAGS = ("badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter", "pgs_condim6")
 
     def status(self, clear: bool = False) -> torch.Tensor:
         """Per-env OR of bad-state flags (dm_control check_invalid_state equivalent)."""

@@ -7,6 +7,7 @@
  */
 #include "b2p_oracle.h"
 #include "../include/b2p_model_layout.h"
+#include "../include/b2p_prop_types.h"
 #include <math.h>
 #include <stdint.h>
 #include <stdio.h>
@@ -31,7 +32,7 @@ enum { ROW_EQ, ROW_LIMIT, ROW_CONTACT };
 enum { ST_SATISFIED, ST_QUADRATIC, ST_CONE };
 
 struct orc_t {
-  unsigned char* blob;
+  unsigned char* blob; unsigned char* blob0;   /* blob: this instance's copy (prop geoms re-classed by orc_set_prop_type); blob0: as compiled */
   const int* hdr; const double* opt; const int* table;
   int nq, nv, nu, nbody, njnt, ngeom, nsite, neq, npair, nmesh, nprop;
   double timestep, gravity[3], impratio, tolerance, ls_tolerance, ccd_tolerance, meaninertia;
@@ -39,7 +40,8 @@ struct orc_t {
   /* per-scene mutable model params (props) */
   double geom_size[3 * MAXGEOM], geom_rbound[MAXGEOM], body_mass[MAXBODY], body_inertia[3 * MAXBODY];
   double body_invweight0[2 * MAXBODY], geom_invweight0[2 * MAXGEOM], dof_invweight0[MAXNV];
-  double prop_size[3 * MAXPROP]; int prop_active[MAXPROP];
+  double prop_size[3 * MAXPROP]; int prop_active[MAXPROP], prop_type[MAXPROP];
+  double geom_half[3 * MAXGEOM];   /* bounding half extents in the geom frame (mid phase of the timing build) */
   /* state */
   double qpos[MAXNV + 8], qvel[MAXNV], ctrl[16], qacc_warmstart[MAXNV], time;
   /* derived */
@@ -170,11 +172,11 @@ static void apply_prop_params(orc_t* o) {
   const int* pb = FI(o, B2PM_F_PROP_BODYID); const int* pg = FI(o, B2PM_F_PROP_GEOMID);
   const double* pm = FD(o, B2PM_F_PROP_MASS); const int* pd = FI(o, B2PM_F_PROP_DOFADR);
   for (int p = 0; p < o->nprop; p++) {
-    const double* s = o->prop_size + 3 * p; int b = pb[p], g = pg[p]; double m = pm[p];
-    memcpy(o->geom_size + 3 * g, s, 24);
-    o->geom_rbound[g] = norm3(s);
+    const double* s = o->prop_size + 3 * p; int b = pb[p], g = pg[p]; double m, I[3], half[3];
+    b2p_prop_inertia(o->prop_type[p], s, pm[p], &m, I, half);   /* box: m/3 (b^2 + c^2); sphere 2/5 m r^2; cylinder m (r^2/4 + h^2/3), m r^2/2 */
+    memcpy(o->geom_size + 3 * g, s, 24); memcpy(o->geom_half + 3 * g, half, 24);
+    o->geom_rbound[g] = norm3(half) ; if (o->prop_type[p] == B2P_GEOM_SPHERE) o->geom_rbound[g] = s[0];
     o->body_mass[b] = m;
-    double I[3] = {m / 3 * (s[1] * s[1] + s[2] * s[2]), m / 3 * (s[0] * s[0] + s[2] * s[2]), m / 3 * (s[0] * s[0] + s[1] * s[1])};
     memcpy(o->body_inertia + 3 * b, I, 24);
     /* mj_setConst for a lone free body: invweight0 = (1/m, mean(1/I)) (App. B item 9) */
     double tr = 1 / m, rot = (1 / I[0] + 1 / I[1] + 1 / I[2]) / 3;
@@ -184,12 +186,33 @@ static void apply_prop_params(orc_t* o) {
     for (int k = 0; k < 6; k++) o->dof_active[pd[p] + k] = o->prop_active[p];
   }
 }
+/* re-class prop p's collision geom (box as compiled / sphere / cylinder): the instance's blob copy gets the class's MJCF fields */
+void orc_set_prop_type(orc_t* o, int p, int geom_type) {
+  if (p < 0 || p >= o->nprop) return;
+  const int g = FI(o, B2PM_F_PROP_GEOMID)[p];
+  static const int fields[] = {B2PM_F_GEOM_TYPE, B2PM_F_GEOM_CONDIM, B2PM_F_GEOM_PRIORITY, B2PM_F_GEOM_FRICTION, B2PM_F_GEOM_SOLREF, B2PM_F_GEOM_SOLIMP,
+                               B2PM_F_GEOM_SOLMIX, B2PM_F_GEOM_MARGIN, B2PM_F_GEOM_GAP};
+  static const int width[] = {4, 4, 4, 24, 16, 40, 8, 8, 8};
+  for (int f = 0; f < 9; f++) memcpy(o->blob + o->table[2 * fields[f]] + (size_t)width[f] * g, o->blob0 + o->table[2 * fields[f]] + (size_t)width[f] * g, width[f]);
+  if (geom_type == B2P_GEOM_SPHERE || geom_type == B2P_GEOM_CYLINDER) {
+    const b2p_prop_class* c = geom_type == B2P_GEOM_SPHERE ? &B2P_PROP_CLASS_SPHERE : &B2P_PROP_CLASS_CYLINDER;
+    ((int*)(o->blob + o->table[2 * B2PM_F_GEOM_TYPE]))[g] = c->geom_type; ((int*)(o->blob + o->table[2 * B2PM_F_GEOM_CONDIM]))[g] = c->condim;
+    ((int*)(o->blob + o->table[2 * B2PM_F_GEOM_PRIORITY]))[g] = c->priority;
+    memcpy(o->blob + o->table[2 * B2PM_F_GEOM_FRICTION] + 24 * (size_t)g, c->friction, 24); memcpy(o->blob + o->table[2 * B2PM_F_GEOM_SOLREF] + 16 * (size_t)g, c->solref, 16);
+    memcpy(o->blob + o->table[2 * B2PM_F_GEOM_SOLIMP] + 40 * (size_t)g, c->solimp, 40);
+    ((double*)(o->blob + o->table[2 * B2PM_F_GEOM_SOLMIX]))[g] = c->solmix; ((double*)(o->blob + o->table[2 * B2PM_F_GEOM_MARGIN]))[g] = c->margin;
+    ((double*)(o->blob + o->table[2 * B2PM_F_GEOM_GAP]))[g] = c->gap;
+    o->prop_type[p] = geom_type;
+  } else o->prop_type[p] = B2P_GEOM_BOX;
+  apply_prop_params(o);
+}
 
 orc_t* orc_create(const void* blob, size_t nbytes) {
   const int* hdr = (const int*)blob;
   if (nbytes < 1024 || (unsigned)hdr[0] != B2PM_MAGIC || hdr[1] != B2PM_VERSION) return NULL;
   orc_t* o = (orc_t*)calloc(1, sizeof(orc_t));
   o->blob = (unsigned char*)malloc(nbytes); memcpy(o->blob, blob, nbytes);
+  o->blob0 = (unsigned char*)malloc(nbytes); memcpy(o->blob0, blob, nbytes);
   o->hdr = (const int*)o->blob; o->opt = (const double*)(o->blob + B2PM_HEADER_BYTES);
   o->table = (const int*)(o->blob + B2PM_TABLE_OFFSET);
   o->nq = hdr[B2PM_C_NQ]; o->nv = hdr[B2PM_C_NV]; o->nu = hdr[B2PM_C_NU]; o->nbody = hdr[B2PM_C_NBODY];
@@ -212,7 +235,8 @@ orc_t* orc_create(const void* blob, size_t nbytes) {
   memcpy(o->dof_invweight0, FD(o, B2PM_F_DOF_INVWEIGHT0), 8 * o->nv);
   for (int i = 0; i < o->nv; i++) o->dof_active[i] = 1;
   const int* pg = FI(o, B2PM_F_PROP_GEOMID);
-  for (int p = 0; p < o->nprop; p++) { memcpy(o->prop_size + 3 * p, o->geom_size + 3 * pg[p], 24); o->prop_active[p] = 1; }
+  { const double* ab = FD(o, B2PM_F_GEOM_AABB); for (int g = 0; g < o->ngeom; g++) memcpy(o->geom_half + 3 * g, ab + 6 * g + 3, 24); }
+  for (int p = 0; p < o->nprop; p++) { memcpy(o->prop_size + 3 * p, o->geom_size + 3 * pg[p], 24); o->prop_active[p] = 1; o->prop_type[p] = B2P_GEOM_BOX; }
   apply_prop_params(o);
   o->efc_J = (double*)calloc((size_t)ORC_MAXEFC * MAXNV, sizeof(double));
   o->efc_ind = (unsigned char*)calloc((size_t)ORC_MAXEFC * MAXNV, 1);
@@ -223,7 +247,7 @@ orc_t* orc_create(const void* blob, size_t nbytes) {
   orc_reset(o);
   return o;
 }
-void orc_destroy(orc_t* o) { if (o) { free(o->efc_J); free(o->efc_ind); free(o->jacbuf); free(o->solbuf); free(o->blob); free(o); } }
+void orc_destroy(orc_t* o) { if (o) { free(o->efc_J); free(o->efc_ind); free(o->jacbuf); free(o->solbuf); free(o->blob); free(o->blob0); free(o); } }
 void orc_reset(orc_t* o) {
   memcpy(o->qpos, FD(o, B2PM_F_QPOS0), 8 * o->nq);
   memset(o->qvel, 0, sizeof o->qvel); memset(o->ctrl, 0, sizeof o->ctrl);
@@ -415,6 +439,11 @@ static void support(cobj_t* c, const double* dir, double* res) {
   mulmatTvec3(ld, c->mat, dir);
   if (c->type == B2P_GEOM_BOX) {
     for (int k = 0; k < 3; k++) lp[k] = ld[k] >= 0 ? c->size[k] : -c->size[k];
+  } else if (c->type == B2P_GEOM_SPHERE) {
+    for (int k = 0; k < 3; k++) lp[k] = c->size[0] * ld[k];
+  } else if (c->type == B2P_GEOM_CYLINDER) {   /* disc of radius size[0] swept along local z by +- size[1] */
+    const double rho = sqrt(ld[0] * ld[0] + ld[1] * ld[1]);
+    lp[0] = rho > MINVAL ? c->size[0] * ld[0] / rho : 0; lp[1] = rho > MINVAL ? c->size[0] * ld[1] / rho : 0; lp[2] = ld[2] >= 0 ? c->size[1] : -c->size[1];
   } else {
 #ifdef ORC_FAST
     int v = c->cur; double bd = dot3(c->vert + 3 * v, ld);
@@ -723,6 +752,82 @@ static int box_box(const double* p1, const double* m1, const double* s1, const d
   return cnt;
 }
 
+
+/* ---- analytic pairs of the sphere / cylinder prop classes (mjc_PlaneSphere, mjc_PlaneCylinder, mjc_SphereSphere, mjc_SphereBox,
+ * mjc_SphereCylinder restated from their geometry; RECOLLECTION of MuJoCo 3.2.7, unpinned like the rest).  The normal always points
+ * from the pair's first geom to its second, in the PAIR TABLE's order (MuJoCo re-sorts a pair by geom type; the contact is the same
+ * with normal and geom1 / geom2 swapped). */
+static int plane_sphere(const double* ppos, const double* pmat, const double* c, double r, double margin, rawcon_t* out) {
+  const double n[3] = {pmat[2], pmat[5], pmat[8]}, dif[3] = {c[0] - ppos[0], c[1] - ppos[1], c[2] - ppos[2]};
+  const double dist = dot3(dif, n) - r;
+  if (dist > margin) return 0;
+  out[0].dist = dist; memcpy(out[0].normal, n, 24);
+  for (int k = 0; k < 3; k++) out[0].pos[k] = c[k] - n[k] * (r + 0.5 * dist);
+  return 1;
+}
+/* rim points of the two end discs that lie lowest along -n (a cylinder on its side rests on a line: two points), plus two more
+ * points of the nearer disc 120 degrees around (a standing cylinder rests on a tripod); each kept when inside the margin */
+static int plane_cylinder(const double* ppos, const double* pmat, const double* c, const double* mat, double r, double h, double margin, rawcon_t* out) {
+  const double n[3] = {pmat[2], pmat[5], pmat[8]}, a[3] = {mat[2], mat[5], mat[8]};
+  const double na = dot3(n, a), sg = na > 0 ? -1.0 : 1.0;
+  double v[3] = {-n[0] + na * a[0], -n[1] + na * a[1], -n[2] + na * a[2]};
+  if (normalize3(v) < 1e-9) { v[0] = mat[0]; v[1] = mat[3]; v[2] = mat[6]; }   /* axis along the normal: any radial direction (local x) */
+  double u[3]; cross3(u, a, v);
+  int cnt = 0;
+  for (int q = 0; q < 4; q++) {
+    const double cap = q == 1 ? -sg : sg, ca = q < 2 ? 1.0 : -0.5, sa = q < 2 ? 0.0 : (q == 2 ? 0.8660254037844387 : -0.8660254037844387);
+    double pt[3];
+    for (int k = 0; k < 3; k++) pt[k] = c[k] + cap * h * a[k] + r * (ca * v[k] + sa * u[k]);
+    const double dif[3] = {pt[0] - ppos[0], pt[1] - ppos[1], pt[2] - ppos[2]}, dist = dot3(dif, n);
+    if (dist > margin) continue;
+    out[cnt].dist = dist; memcpy(out[cnt].normal, n, 24);
+    for (int k = 0; k < 3; k++) out[cnt].pos[k] = pt[k] - 0.5 * dist * n[k];
+    cnt++;
+  }
+  return cnt;
+}
+static int sphere_sphere(const double* c1, double r1, const double* c2, double r2, double margin, rawcon_t* out) {
+  double d[3] = {c2[0] - c1[0], c2[1] - c1[1], c2[2] - c1[2]};
+  const double L = normalize3(d), dist = L - r1 - r2;
+  if (dist > margin) return 0;
+  out[0].dist = dist; memcpy(out[0].normal, d, 24);
+  for (int k = 0; k < 3; k++) out[0].pos[k] = c1[k] + d[k] * (r1 + 0.5 * dist);
+  return 1;
+}
+/* closest point of a solid (box: half extents hs; cylinder: radius hs[0], half height hs[1], axis z) to the sphere centre, in the
+ * solid's frame; a centre inside the solid is pushed out through the nearest face.  normal: from the SOLID to the sphere. */
+static int sphere_solid(int solid_type, const double* cs, double rs, const double* cb, const double* mb, const double* hs, double margin, rawcon_t* out) {
+  double dif[3] = {cs[0] - cb[0], cs[1] - cb[1], cs[2] - cb[2]}, lc[3], q[3], nl[3], depth;
+  mulmatTvec3(lc, mb, dif);
+  int inside;
+  if (solid_type == B2P_GEOM_BOX) {
+    inside = 1;
+    for (int k = 0; k < 3; k++) { q[k] = lc[k] < -hs[k] ? -hs[k] : (lc[k] > hs[k] ? hs[k] : lc[k]); if (q[k] != lc[k]) inside = 0; }
+    if (inside) {
+      int best = 0; double bd = 1e300;
+      for (int k = 0; k < 3; k++) { const double d = hs[k] - fabs(lc[k]); if (d < bd) { bd = d; best = k; } }
+      nl[0] = nl[1] = nl[2] = 0; nl[best] = lc[best] >= 0 ? 1 : -1; q[best] = nl[best] * hs[best]; depth = -bd;
+    }
+  } else {
+    const double rho = sqrt(lc[0] * lc[0] + lc[1] * lc[1]), r = hs[0], h = hs[1];
+    inside = rho < r && fabs(lc[2]) < h;
+    if (inside) {
+      if (r - rho < h - fabs(lc[2])) { const double ir = rho > MINVAL ? 1 / rho : 0; nl[0] = rho > MINVAL ? lc[0] * ir : 1; nl[1] = lc[1] * ir; nl[2] = 0; q[0] = nl[0] * r; q[1] = nl[1] * r; q[2] = lc[2]; depth = -(r - rho); }
+      else { nl[0] = nl[1] = 0; nl[2] = lc[2] >= 0 ? 1 : -1; q[0] = lc[0]; q[1] = lc[1]; q[2] = nl[2] * h; depth = -(h - fabs(lc[2])); }
+    } else {
+      const double sc = rho > r ? r / rho : 1.0;
+      q[0] = lc[0] * sc; q[1] = lc[1] * sc; q[2] = lc[2] < -h ? -h : (lc[2] > h ? h : lc[2]);
+    }
+  }
+  if (!inside) { for (int k = 0; k < 3; k++) nl[k] = lc[k] - q[k]; depth = normalize3(nl); }
+  const double dist = depth - rs;
+  if (dist > margin) return 0;
+  double nw[3], qw[3];
+  mulmatvec3(nw, mb, nl); mulmatvec3(qw, mb, q);
+  out[0].dist = dist; memcpy(out[0].normal, nw, 24);
+  for (int k = 0; k < 3; k++) out[0].pos[k] = cb[k] + qw[k] + 0.5 * dist * nw[k];
+  return 1;
+}
 static void mix_params(orc_t* o, int g1, int g2, contact_t* c) {
   /* App. B item 10: priority wins; equal priority -> max friction, solmix-weighted solref/solimp, max condim */
   const int *prio = FI(o, B2PM_F_GEOM_PRIORITY), *condim = FI(o, B2PM_F_GEOM_CONDIM);
@@ -761,6 +866,8 @@ static void collision(orc_t* o) {
       double nrm[3] = {m1[2], m1[5], m1[8]}, dif[3] = {x2[0] - x1[0], x2[1] - x1[1], x2[2] - x1[2]};
       if (dot3(dif, nrm) - o->geom_rbound[g2] > md) continue;
       if (t2 == B2P_GEOM_BOX) n = plane_box(x1, m1, x2, m2, o->geom_size + 3 * g2, md, raw);
+      else if (t2 == B2P_GEOM_SPHERE) n = plane_sphere(x1, m1, x2, o->geom_size[3 * g2], md, raw);
+      else if (t2 == B2P_GEOM_CYLINDER) n = plane_cylinder(x1, m1, x2, m2, o->geom_size[3 * g2], o->geom_size[3 * g2 + 1], md, raw);
       else if (t2 == B2P_GEOM_MESH) {   /* an arm link below the table edge reaches the ground */
         int v0 = vadr[gmesh[g2]];
         cobj_t h = {x2, m2, t2, o->geom_size + 3 * g2, mvert + 3 * v0, vnum[gmesh[g2]], 0, FI(o, B2PM_F_MESH_NBRADR) + v0, FI(o, B2PM_F_MESH_NBRNUM) + v0, FI(o, B2PM_F_MESH_NBR), 0};
@@ -772,7 +879,7 @@ static void collision(orc_t* o) {
 #ifdef ORC_FAST
       { /* mid phase of the timing build: the geoms' oriented bounding boxes along their 6 face normals (conservative: never drops a contact) */
         const double* ab = FD(o, B2PM_F_GEOM_AABB);
-        const double *c1 = ab + 6 * g1, *c2 = ab + 6 * g2, *h1 = gprop[g1] >= 0 ? o->geom_size + 3 * g1 : ab + 6 * g1 + 3, *h2 = gprop[g2] >= 0 ? o->geom_size + 3 * g2 : ab + 6 * g2 + 3;
+        const double *c1 = ab + 6 * g1, *c2 = ab + 6 * g2, *h1 = o->geom_half + 3 * g1, *h2 = o->geom_half + 3 * g2;
         double w1[3], w2[3], t[3], sep = 0; mulmatvec3(w1, m1, c1); mulmatvec3(w2, m2, c2);
         for (int k = 0; k < 3; k++) t[k] = (x2[k] + w2[k]) - (x1[k] + w1[k]);
         for (int i = 0; i < 3 && !sep; i++) {
@@ -792,7 +899,11 @@ static void collision(orc_t* o) {
       if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) {
         n = box_box(x1, m1, o->geom_size + 3 * g1, x2, m2, o->geom_size + 3 * g2, md, raw);
         convex = (n < 0); if (n < 0) n = 0;
-      }
+      } else if (t1 == B2P_GEOM_SPHERE && t2 == B2P_GEOM_SPHERE) { n = sphere_sphere(x1, o->geom_size[3 * g1], x2, o->geom_size[3 * g2], md, raw); convex = 0; }
+      else if (t1 == B2P_GEOM_SPHERE && (t2 == B2P_GEOM_BOX || t2 == B2P_GEOM_CYLINDER)) {     /* normal solid -> sphere = second -> first: flip */
+        n = sphere_solid(t2, x1, o->geom_size[3 * g1], x2, m2, o->geom_size + 3 * g2, md, raw); convex = 0;
+        for (int i = 0; i < n; i++) for (int k = 0; k < 3; k++) raw[i].normal[k] = -raw[i].normal[k];
+      } else if (t2 == B2P_GEOM_SPHERE && (t1 == B2P_GEOM_BOX || t1 == B2P_GEOM_CYLINDER)) { n = sphere_solid(t1, x2, o->geom_size[3 * g2], x1, m1, o->geom_size + 3 * g1, md, raw); convex = 0; }
       if (convex) {
         cobj_t a = {x1, m1, t1, o->geom_size + 3 * g1, NULL, 0, md, NULL, NULL, NULL, 0}, b = {x2, m2, t2, o->geom_size + 3 * g2, NULL, 0, md, NULL, NULL, NULL, 0};
         const int *nadr = FI(o, B2PM_F_MESH_NBRADR), *nnum = FI(o, B2PM_F_MESH_NBRNUM), *nbr = FI(o, B2PM_F_MESH_NBR);

@@ -41,6 +41,7 @@ double* orc_ptr(orc_t* o, int field);       /* NULL if unknown */
 int orc_dim(orc_t* o, int what);            /* 0 nq 1 nv 2 nu 3 nbody 4 ngeom 5 nsite 6 ncon 7 nefc 8 nprop 9 solver iters */
 void orc_reset(orc_t* o);                   /* mj_resetData: qpos=qpos0, rest 0 */
 void orc_set_prop(orc_t* o, int prop, const double half[3], int active);
+void orc_set_prop_type(orc_t* o, int prop, int geom_type); /* B2P_GEOM_BOX (as compiled) / B2P_GEOM_SPHERE / B2P_GEOM_CYLINDER: include/b2p_prop_types.h */
 void orc_set_option(orc_t* o, int what, double v); /* 0 full contact list (1) / solver-active only (0); 1 integrator; 2 tolerance; 3 iterations; 4 solver (0 Newton, 1 PGS) */
 
 void orc_step1(orc_t* o);                   /* mj_step1: position + velocity stages */

@@ -14,7 +14,7 @@ class EmuArgs(C.Structure):
     _fields_ = [(n, C.c_int) for n in ("mode", "n_env", "n_steps", "control_steps", "state_stride", "full_contacts", "settle_min_steps", "out_stride")] + \
                [("settle_qvel_tol", C.c_double), ("settle_qacc_tol", C.c_double)] + \
                [(n, C.c_void_p) for n in ("state", "ctrl", "target", "grip", "prop_size", "prop_active", "env_mask", "converged", "status", "steps_done", "out", "gains")] + \
-               [("solver", C.c_int)]
+               [("solver", C.c_int), ("prop_type", C.c_void_p)]
 
 
 def lib():
@@ -70,7 +70,7 @@ class HostEmu:
         self.L.emu_osc_config(self.h, self.dt, g.ctypes.data, q.ctypes.data, pt, ot)
 
     def run(self, mode, state, n_steps=1, control_steps=5, ctrl=None, target=None, grip=None, prop_size=None, prop_active=None,
-            full_contacts=False, want_out=True, settle=(1e-3, 1e-2, 300), gains=None, solver=0):
+            full_contacts=False, want_out=True, settle=(1e-3, 1e-2, 300), gains=None, solver=0, prop_type=None):
         """state: [n_env, stride] array of self.np (modified in place). Returns dict(out, status, converged, steps_done)."""
         assert state.dtype == self.np and state.flags.c_contiguous
         n = state.shape[0]
@@ -88,6 +88,6 @@ class HostEmu:
                     settle_min_steps=settle[2], out_stride=self.out_size, settle_qvel_tol=settle[0], settle_qacc_tol=settle[1],
                     state=state.ctypes.data, ctrl=ptr(ctrl, self.np), target=ptr(target, self.np), grip=ptr(grip, np.uint8),
                     prop_size=ptr(prop_size, self.np), prop_active=ptr(prop_active, np.uint8), env_mask=None,
-                    converged=conv.ctypes.data, status=status.ctypes.data, steps_done=done.ctypes.data, out=out.ctypes.data if want_out else None, gains=ptr(gains, self.np), solver=int(solver))
+                    converged=conv.ctypes.data, status=status.ctypes.data, steps_done=done.ctypes.data, out=out.ctypes.data if want_out else None, gains=ptr(gains, self.np), solver=int(solver), prop_type=ptr(prop_type, np.uint8))
         self.L.emu_run(self.h, self.dt, C.byref(a))
         return dict(out=out, status=status, converged=conv, steps_done=done)

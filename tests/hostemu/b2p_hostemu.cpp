@@ -12,7 +12,7 @@ using namespace b2p;
 template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
-  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop, xpool;
+  std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop, xpool, w6; std::vector<GeomRaw<T>> geom_raw;
   Globals<T> g; Scratch<T>* s;
 };
 
@@ -40,7 +40,17 @@ static Emu<T>* make(const void* blob, size_t n) {
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
   e->jovf.assign(Pool<T>::JP, T(0)); e->g.jovf = e->jovf.data();
   e->xpool.assign(Pool<T>::JP, T(0)); e->g.xpool = e->xpool.data();
-  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data(); e->s->xpool = e->xpool.data();
+  e->geom_raw.resize(e->ht.geom_raw.size());
+  for (size_t i = 0; i < e->geom_raw.size(); i++) {
+    const GeomRaw<double>& a = e->ht.geom_raw[i]; GeomRaw<T>& b = e->geom_raw[i];
+    b.priority = a.priority; b.condim = a.condim;
+    for (int k = 0; k < 3; k++) b.friction[k] = (T)a.friction[k];
+    for (int k = 0; k < 2; k++) b.solref[k] = (T)a.solref[k];
+    for (int k = 0; k < 5; k++) b.solimp[k] = (T)a.solimp[k];
+    b.solmix = (T)a.solmix; b.margin = (T)a.margin; b.gap = (T)a.gap;
+  }
+  e->g.geom_raw = e->geom_raw.data();
+  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data(); e->s->xpool = e->xpool.data(); e->w6.assign((size_t)MAXCON * W6_STRIDE, T(0)); e->g.w6pool = e->w6.data(); e->s->w6 = e->w6.data();
   return e;
 }
 
@@ -48,7 +58,7 @@ struct EmuArgs {   // mirrors the ctypes struct in tests/hostemu.py
   int mode, n_env, n_steps, control_steps, state_stride, full_contacts, settle_min_steps, out_stride;
   double settle_qvel_tol, settle_qacc_tol;
   void *state, *ctrl, *target, *grip, *prop_size, *prop_active, *env_mask, *converged, *status, *steps_done, *out, *gains;
-  int solver;
+  int solver; void* prop_type;
 };
 
 template <typename T>
@@ -59,7 +69,7 @@ static int run(Emu<T>* e, const EmuArgs* a) {
   s.prop_size = (const T*)a->prop_size; s.prop_active = (const unsigned char*)a->prop_active; s.env_mask = (const unsigned char*)a->env_mask;
   s.converged = (unsigned char*)a->converged; s.status = (int*)a->status; s.steps_done = (int*)a->steps_done;
   s.settle_qvel_tol = (T)a->settle_qvel_tol; s.settle_qacc_tol = (T)a->settle_qacc_tol; s.settle_min_steps = a->settle_min_steps;
-  s.out = (T*)a->out; s.out_stride = a->out_stride; s.out_mask = OUT_ALL; s.gains = (const T*)a->gains;
+  s.out = (T*)a->out; s.out_stride = a->out_stride; s.out_mask = OUT_ALL; s.gains = (const T*)a->gains; s.prop_type = (const unsigned char*)a->prop_type;
   Ctx c = {0, 1};
   for (int env = 0; env < a->n_env; env++) {
     if (s.env_mask && !s.env_mask[env]) continue;

@@ -32,6 +32,7 @@ def lib():
             getattr(L, fn).restype = None
         L.orc_dim.argtypes = [C.c_void_p, C.c_int]
         L.orc_set_prop.argtypes = [C.c_void_p, C.c_int, C.POINTER(C.c_double), C.c_int]
+        L.orc_set_prop_type.argtypes = [C.c_void_p, C.c_int, C.c_int]
         L.orc_set_option.argtypes = [C.c_void_p, C.c_int, C.c_double]
         L.orc_contacts.argtypes = [C.c_void_p] + [C.c_void_p] * 5
         L.orc_osc_config.argtypes = [C.c_void_p, C.c_void_p, C.c_void_p, C.c_double, C.c_double]
@@ -98,6 +99,10 @@ class Oracle:
     def set_prop(self, p, half, active=True):
         a = (C.c_double * 3)(*[float(x) for x in half])
         self.L.orc_set_prop(self.h, p, a, int(active))
+
+    def set_prop_type(self, p, geom_type):
+        """re-class prop p's collider: blob.GEOM_BOX (as compiled) / GEOM_SPHERE / GEOM_CYLINDER (include/b2p_prop_types.h)"""
+        self.L.orc_set_prop_type(self.h, int(p), int(geom_type))
 
     def set_option(self, what, v):
         self.L.orc_set_option(self.h, dict(full_contacts=0, integrator=1, tolerance=2, iterations=3, solver=4)[what], float(v))

@@ -261,3 +261,36 @@ def test_device_sampler_reset_and_scene_resampling():
     assert not torch.equal(n0, env.n_props) and not torch.equal(c0, env.prop_colour)
     assert bool((env.n_props >= 2).all() & (env.n_props <= 4).all())
     assert torch.equal(p.prop_active.bool(), env.has_prop)
+
+
+@pytest.mark.parametrize("group", ["itl_rearrangement", "apple", "itl_agent_demo"])
+def test_env_with_the_other_prop_groups(group):
+    """The prop groups round 1 rejected (config/arena/props/{itl_rearrangement,apple,itl_agent_demo}.yaml): the env draws a shape per prop
+    (cube / rectangle / cylinder; apple; cube), the kernels step the matching collider classes, reset leaves every prop at rest on the
+    table at the height its class implies, and a pick-and-place of the first prop raises no bad-state flag."""
+    from mujoco_robot_environments_b200 import ffi
+    from mujoco_robot_environments_b200.env import BatchedRearrangementEnv
+    env = BatchedRearrangementEnv(num_envs=32, dtype=torch.float32, overrides=["arena/props=" + group], seed=5)
+    ts = env.reset()
+    has = env.has_prop.cpu().numpy(); tp = env.prop_type.cpu().numpy(); hs = env.prop_half_size.cpu().numpy()
+    pos = ts.observation["prop_pos"].cpu().numpy(); quat = ts.observation["prop_quat"].cpu().numpy()
+    if group == "itl_rearrangement":
+        assert (env.n_props == 4).all() and env.props_clamped > 0                 # randint(4, 6) draws 4 or 5; the model class holds 4
+        assert (tp[has] == ffi.GEOM["cylinder"]).any() and (tp[has] == ffi.GEOM["box"]).any()
+        assert (np.ptp(hs[has & (tp == ffi.GEOM["box"])], axis=1) > 1e-4).any()     # rectangles: three different half sizes
+    elif group == "apple":
+        assert (tp[has] == ffi.GEOM["sphere"]).all() and ((env.n_props == 2) | (env.n_props == 3)).all()
+    else:
+        assert (tp[has] == ffi.GEOM["box"]).all() and (env.n_props == 2).all()
+    assert not bool(env.failed.any())
+    # resting height: box -> its half height along the axis that ended up vertical; sphere -> radius; cylinder -> half height (upright) or radius (fallen)
+    z = pos[..., 2] - 0.4
+    sph = has & (tp == ffi.GEOM["sphere"]); cyl = has & (tp == ffi.GEOM["cylinder"]); box = has & (tp == ffi.GEOM["box"])
+    assert np.abs(z[sph] - hs[sph][:, 0]).max(initial=0) < 2e-3
+    assert np.minimum(np.abs(z[cyl] - hs[cyl][:, 1]), np.abs(z[cyl] - hs[cyl][:, 0])).max(initial=0) < 3e-3
+    assert np.abs(z[box][:, None] - hs[box]).min(axis=1).max(initial=0) < 2e-3
+    assert int((env.physics.status().cpu() & 7).max()) == 0
+    pick, place = env.random_pick_and_place()
+    env.step({"pose": pick}); env.step({"pose": place})
+    assert int((env.physics.status().cpu() & 7).max()) == 0
+    assert bool(torch.isfinite(env.physics.qpos).all())
