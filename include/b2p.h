@@ -110,8 +110,18 @@ int b2p_forward(b2p_handle h, int full_contacts, void* stream);
  * of the physics); scenes with env_mask 0 are skipped and their out row is not written. */
 int b2p_place_search(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* env_mask /* NULL = all */, int max_attempts,
                      double dist, int table_geom, unsigned seed, void* out, void* stream);
+/* PropPlacer.__call__ for ONE prop of every scene in one launch (environment/prop_initializer.py:197-236, driven by the arena's
+ * workspace box and `rotation = pi * U about z`, tasks/rearrangement.py:189-197): like b2p_place_search, but every proposal also
+ * draws the yaw, and the accepted orientation comes back in quat_out (device [n_env][4], w x y z).  The collision rule is the
+ * placer's "_has_collisions_with_prop": any listed contact of the prop closer than `dist` with anything but `table_geom`, with the
+ * props not placed yet switched off through prop_active (prop_initializer.py:142-162,183-185).  The caller writes the accepted pose
+ * into the state (the search itself runs on the warp's scratch copy) and moves on to the next prop: a reset places N props in N launches. */
+int b2p_place_props(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* env_mask /* NULL = all */, int max_attempts,
+                    double dist, int table_geom, unsigned seed, void* out, void* quat_out, void* stream);
 int b2p_get(b2p_handle h, int field, void* dst /* [n_env][count] */, void* stream);
 int b2p_status(b2p_handle h, int32_t* flags /* device [n_env] */, int clear, void* stream);
+/* overwrite the per-scene status words (device [n_env]): a masked reset clears the flags of the scenes it resets and of no other */
+int b2p_status_set(b2p_handle h, const int32_t* flags, void* stream);
 
 /* developer aid: per-stage cycle counters summed over scenes, [B2P_PROF_N] entries; all zero unless the library was built
  * with -DB2P_PROF (the product build has no counters in the kernel).  Synchronises the device. */

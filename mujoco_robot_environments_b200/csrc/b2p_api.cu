@@ -152,11 +152,11 @@ static int run_mode(b2p_handle h, int mode, int n_steps, int control_steps, int 
   return launch<T>(h, a, (cudaStream_t)stream);
 }
 template <typename T>
-static int place_mode(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* mask, int max_attempts, double dist, int table_geom, unsigned seed, void* out, void* stream) {
+static int place_mode(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* mask, int max_attempts, double dist, int table_geom, unsigned seed, void* out, void* stream, int yaw = 0, void* quat_out = nullptr) {
   StepArgs<T> a; std::memset(&a, 0, sizeof a);
   { const char* ls = getenv("B2P_LOCKSTEP"); a.lockstep = ls ? atoi(ls) : LK_DEFAULT; }
   a.mode = MODE_PLACE; a.n_steps = max_attempts; a.control_steps = 1; a.full_contacts = 1; a.env_mask = mask;
-  a.place_prop = prop; a.place_box = (const T*)box; a.place_dist = (T)dist; a.place_table = table_geom; a.place_seed = seed; a.place_out = (T*)out;
+  a.place_prop = prop; a.place_box = (const T*)box; a.place_dist = (T)dist; a.place_table = table_geom; a.place_seed = seed; a.place_out = (T*)out; a.place_yaw = yaw; a.place_quat = (T*)quat_out;
   return launch<T>(h, a, (cudaStream_t)stream);
 }
 extern "C" {
@@ -216,6 +216,7 @@ int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out =
 int b2p_set_out_mask(b2p_handle h, int mask) { if (!h || mask < 0 || mask > OUT_ALL) return fail(B2P_ERR_ARG, "b2p_set_out_mask: bad argument"); h->out_mask = mask; return B2P_OK; }
 int b2p_set_solver(b2p_handle h, int solver) {
   if (!h || (solver != B2P_SOLVER_NEWTON && solver != B2P_SOLVER_PGS)) return fail(B2P_ERR_ARG, "b2p_set_solver: bad argument");
+  if (solver == B2P_SOLVER_PGS && h->prop_type) return fail(B2P_ERR_ARG, "b2p_set_solver: PGS covers condim 1 and 3; it is not offered while prop classes are bound (b2p_set_env_prop_types)");
   if (solver == B2P_SOLVER_PGS && !h->d_xpool) {   // M^-1 J' per resident warp, J's packed layout
     CK(cudaSetDevice(h->device));
     const size_t w = h->dtype == B2P_F64 ? 8 : 4, jp = h->dtype == B2P_F64 ? Pool<double>::JP : Pool<float>::JP;
@@ -224,7 +225,11 @@ int b2p_set_solver(b2p_handle h, int solver) {
   h->solver = solver; return B2P_OK;
 }
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
-int b2p_set_env_prop_types(b2p_handle h, const uint8_t* prop_type) { if (!h) return B2P_ERR_ARG; h->prop_type = prop_type; return B2P_OK; }
+int b2p_set_env_prop_types(b2p_handle h, const uint8_t* prop_type) {
+  if (!h) return B2P_ERR_ARG;
+  if (prop_type && h->solver == B2P_SOLVER_PGS) return fail(B2P_ERR_ARG, "b2p_set_env_prop_types: not offered with the PGS solver (condim 1 and 3 only)");
+  h->prop_type = prop_type; return B2P_OK;
+}
 int b2p_set_env_gains(b2p_handle h, const void* gains) { if (!h) return B2P_ERR_ARG; h->env_gains = gains; return B2P_OK; }
 int b2p_set_env_mask(b2p_handle h, const uint8_t* mask) { if (!h) return B2P_ERR_ARG; h->env_mask = mask; return B2P_OK; }
 int b2p_set_full_contacts(b2p_handle h, int full) { if (!h) return B2P_ERR_ARG; h->full_contacts = full; return B2P_OK; }
@@ -254,6 +259,11 @@ int b2p_place_search(b2p_handle h, const int32_t* prop, const void* box, const u
   return h->dtype == B2P_F64 ? place_mode<double>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream)
                              : place_mode<float>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream);
 }
+int b2p_place_props(b2p_handle h, const int32_t* prop, const void* box, const uint8_t* mask, int max_attempts, double dist, int table_geom, unsigned seed, void* out, void* quat_out, void* stream) {
+  if (!h || !prop || !box || !out || !quat_out || max_attempts < 0) return fail(B2P_ERR_ARG, "b2p_place_props: bad argument");
+  return h->dtype == B2P_F64 ? place_mode<double>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream, 1, quat_out)
+                             : place_mode<float>(h, prop, box, mask, max_attempts, dist, table_geom, seed, out, stream, 1, quat_out);
+}
 int b2p_settle(b2p_handle h, const uint8_t* mask, int max_steps, int min_steps, double vt, double at, int32_t* steps_done, void* stream) {
   if (!h || max_steps < 0) return fail(B2P_ERR_ARG, "b2p_settle: bad argument");
   return DISPATCH(h, MODE_SETTLE, max_steps, 1, h->full_contacts, nullptr, nullptr, nullptr, mask, nullptr, steps_done, vt, at, min_steps, stream);
@@ -274,6 +284,11 @@ int b2p_status(b2p_handle h, int32_t* flags, int clear, void* stream) {
   if (!h) return B2P_ERR_ARG;
   if (flags) CK(cudaMemcpyAsync(flags, h->d_status, (size_t)h->n_env * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   if (clear) CK(cudaMemsetAsync(h->d_status, 0, (size_t)h->n_env * 4, (cudaStream_t)stream));
+  return B2P_OK;
+}
+int b2p_status_set(b2p_handle h, const int32_t* flags, void* stream) {
+  if (!h || !flags) return fail(B2P_ERR_ARG, "b2p_status_set: null");
+  CK(cudaMemcpyAsync(h->d_status, flags, (size_t)h->n_env * 4, cudaMemcpyDeviceToDevice, (cudaStream_t)stream));
   return B2P_OK;
 }
 int b2p_prof_read(b2p_handle h, unsigned long long* out, int reset) {

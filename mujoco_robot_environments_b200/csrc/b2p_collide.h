@@ -314,8 +314,8 @@ B2P_HDN int sphere_solid(int solid_type, const T* cs, T rs, const T* cb, const T
 // (sphere / cylinder: per-scene data) is mixed here by the same rule (App. B item 10: priority wins, else max friction,
 // solmix-weighted solref / solimp, max condim, max margin / gap).
 template <typename T> struct PairMix { PairParam<T> pp; int condim; };
-template <typename T>
-B2P_HDN void pair_mix(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, int p, int g1, int g2, PairMix<T>& o) {
+template <typename T, bool C>
+B2P_HDN void pair_mix(const DevModel<T>& m, const Globals<T>& g, const Scratch<T, C>& s, int p, int g1, int g2, PairMix<T>& o) {
   const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
   const bool re1 = pr1 >= 0 && s.ptype[pr1] != B2P_GEOM_BOX, re2 = pr2 >= 0 && s.ptype[pr2] != B2P_GEOM_BOX;
   if (!re1 && !re2) { o.pp = g.pair_param[p]; o.condim = 3; return; }
@@ -340,9 +340,9 @@ B2P_HDN void pair_mix(const DevModel<T>& m, const Globals<T>& g, const Scratch<T
   o.pp.margin = a.margin > b.margin ? a.margin : b.margin; o.pp.gap = a.gap > b.gap ? a.gap : b.gap;
 }
 // detection distance of pair p in this scene
-template <typename T>
-B2P_HD T pair_md(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, int p, int g1, int g2, bool full_contacts) {
-  if (!s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; return full_contacts ? pp.margin : pp.margin - pp.gap; }
+template <typename T, bool C>
+B2P_HD T pair_md(const DevModel<T>& m, const Globals<T>& g, const Scratch<T, C>& s, int p, int g1, int g2, bool full_contacts) {
+  if (!C || !s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; return full_contacts ? pp.margin : pp.margin - pp.gap; }
   PairMix<T> mx; pair_mix(m, g, s, p, g1, g2, mx);
   return full_contacts ? mx.pp.margin : mx.pp.margin - mx.pp.gap;
 }
@@ -555,14 +555,14 @@ B2P_HD bool witness_separated(const T* w, const T* p1, const T* m1, const T* p2,
 
 constexpr int BB_CLIP_REALS = 48;   // box_box clip scratch per lane: 2 polygons x 8 vertices x 3
 // broad phase (bounding spheres over the static pair table) + narrow phase, deterministic contact order
-template <typename T>
-B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
+template <typename T, bool C>
+B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const Ctx& c, bool full_contacts, bool active) {
   PROF_T0
   if (active) {
   if (c.tid == 0) { s.ncand = 0; s.ncon = 0; }
   for (int q = c.tid; q < m.ngeom; q += c.nt) {
     const int p = m.geom_prop[q];
-    s.grbound[q] = p >= 0 ? (s.ptype[p] == B2P_GEOM_SPHERE ? s.psize[p][0] : norm3(s.phalf[p])) : m.geom_rbound[q];
+    s.grbound[q] = p >= 0 ? ((C && s.ptype[p] == B2P_GEOM_SPHERE) ? s.psize[p][0] : norm3(s.phalf[p])) : m.geom_rbound[q];
   }
   bsync(c);
   // Pass 1 over the static pair table (global memory; the next round's entries are fetched while this round is tested): bounding
@@ -655,8 +655,8 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
 #endif
       if (t1 == B2P_GEOM_PLANE) {
         if (t2 == B2P_GEOM_BOX) n = plane_box(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2, md, raw);
-        else if (t2 == B2P_GEOM_SPHERE) n = plane_sphere(s.gpos[g1], s.gmat[g1], s.gpos[g2], sz2[0], md, raw);
-        else if (t2 == B2P_GEOM_CYLINDER) n = plane_cylinder(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2[0], sz2[1], md, raw);
+        else if (C && t2 == B2P_GEOM_SPHERE) n = plane_sphere(s.gpos[g1], s.gmat[g1], s.gpos[g2], sz2[0], md, raw);
+        else if (C && t2 == B2P_GEOM_CYLINDER) n = plane_cylinder(s.gpos[g1], s.gmat[g1], s.gpos[g2], s.gmat[g2], sz2[0], sz2[1], md, raw);
         else {   // an arm link that reaches the ground behind / beside the table
           CObj<T> h = {s.gpos[g2], s.gmat[g2], sz2, nullptr, t2, m.geom_vertadr[g2], m.geom_vertnum[g2], -1, T(0), g.geom_start + 27 * g2};
           n = plane_convex(s.gpos[g1], s.gmat[g1], h, g, md, raw);
@@ -671,7 +671,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) g_bb_calls++;
 #endif
         if (t1 == B2P_GEOM_BOX && t2 == B2P_GEOM_BOX) { n = box_box(s.gpos[g1], s.gmat[g1], sz1, s.gpos[g2], s.gmat[g2], sz2, md, raw, clip); convex = n < 0; if (n < 0) n = 0; }
-        else if (t1 == B2P_GEOM_SPHERE || t2 == B2P_GEOM_SPHERE) {   // the sphere class against sphere / box / cylinder is analytic; against a hull it goes to MPR
+        else if (C && (t1 == B2P_GEOM_SPHERE || t2 == B2P_GEOM_SPHERE)) {   // the sphere class against sphere / box / cylinder is analytic; against a hull it goes to MPR
           if (t1 == B2P_GEOM_SPHERE && t2 == B2P_GEOM_SPHERE) { n = sphere_sphere(s.gpos[g1], sz1[0], s.gpos[g2], sz2[0], md, raw); convex = false; }
           else if (t1 == B2P_GEOM_SPHERE && (t2 == B2P_GEOM_BOX || t2 == B2P_GEOM_CYLINDER)) {
             n = sphere_solid(t2, s.gpos[g1], sz1[0], s.gpos[g2], s.gmat[g2], sz2, md, raw); convex = false;
@@ -725,7 +725,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, c
       const int k = cbase + ofs + i;
       if (k >= MAXCON) break;
       s.c_dist[k] = raw.dist[i]; cp3(s.c_pos[k], raw.pos[i]); cp3(s.c_frame[k], raw.normal); make_frame(s.c_frame[k]);
-      if (!s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k] = pp.friction[0]; s.c_dim[k] = 3; }
+      if (!C || !s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; s.c_incl[k] = pp.margin - pp.gap; s.c_fric[k] = pp.friction[0]; s.c_dim[k] = 3; }
       else {
         PairMix<T> mx; pair_mix(m, g, s, p, g.pair_g1[p], g.pair_g2[p], mx);
         s.c_incl[k] = mx.pp.margin - mx.pp.gap; s.c_fric[k] = mx.pp.friction[0]; s.c_dim[k] = (unsigned char)(mx.condim == 6 ? 6 : 3);

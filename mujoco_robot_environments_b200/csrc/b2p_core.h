@@ -23,16 +23,16 @@
 namespace b2p {
 
 // ------------------------------------------------------------------------------------------ pipeline
-template <typename T>
-B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HD void prop_params(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   // mass, principal inertia, invweight0 and bounding half extents per collider class (include/b2p_prop_types.h: b2p_prop_inertia)
   for (int p = c.tid; p < m.nprop; p += c.nt) {
     const T* z = s.psize[p]; const int tp = s.ptype[p];
     T mass, I[3], hf[3];
-    if (tp == B2P_GEOM_SPHERE) {
+    if (C && tp == B2P_GEOM_SPHERE) {
       const T r = z[0]; mass = m.pclass_mass[0] > 0 ? m.pclass_mass[0] : T(1000.0 * 4.0 / 3.0 * 3.14159265358979323846) * r * r * r;
       I[0] = I[1] = I[2] = T(0.4) * mass * r * r; hf[0] = hf[1] = hf[2] = r;
-    } else if (tp == B2P_GEOM_CYLINDER) {
+    } else if (C && tp == B2P_GEOM_CYLINDER) {
       const T r = z[0], h = z[1]; mass = m.pclass_mass[1] > 0 ? m.pclass_mass[1] : T(1000.0 * 3.14159265358979323846) * r * r * 2 * h;
       I[0] = I[1] = mass * (T(0.25) * r * r + h * h / 3); I[2] = T(0.5) * mass * r * r; hf[0] = hf[1] = r; hf[2] = h;
     } else {
@@ -46,8 +46,8 @@ B2P_HD void prop_params(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   }
   bsync(c);
 }
-template <typename T>
-B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c, bool full_contacts, bool active) {
+template <typename T, bool C>
+B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const Ctx& c, bool full_contacts, bool active) {
   PROF_T0
   csync(c, LK_FK);
   PROF_ADD(PF_BARRIER)
@@ -61,8 +61,8 @@ B2P_HDN void step1(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, con
   if (active) make_rows(m, g, s, c);
   PROF_ADD(PF_ROWS)
 }
-template <typename T, bool kPgs = false>
-B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
+template <typename T, bool kPgs = false, bool C>
+B2P_HDN void step2(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool do_integrate, bool freeze_tree, bool active) {
   PROF_T0
   csync(c, LK_STEP2);
   PROF_ADD(PF_BARRIER)
@@ -93,8 +93,8 @@ B2P_HDN void step2(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool do_in
 // Derived-output record, written group by group (b2p_set_out_mask; B2P_OUT_* of include/b2p.h).  The "pos" groups (site / geom
 // poses, contacts, mass matrix, bias) read step1 buffers that share storage with the solver's (Scratch unions), so they must be
 // written after a step1 and before the next step2; the "dyn" groups (qacc, efc_force, solver statistics) persist.
-template <typename T>
-B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<T>& s, const Ctx& c, T* o, int parts) {
+template <typename T, bool C>
+B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<T, C>& s, const Ctx& c, T* o, int parts) {
   typedef OutLayout L;
   if (parts & OUT_SITE) {
     for (int i = c.tid; i < 6; i += c.nt) o[L::SITE_XPOS + i] = s.site_xpos[i / 3][i % 3];
@@ -130,8 +130,8 @@ B2P_HDN void write_out(const DevModel<T>& m, const Globals<T>& g, const Scratch<
 // kVar: 0 = the step kernel, 1 = the placement search (MODE_PLACE), 2 = the step kernel with the PGS solver.  Each is its own
 // instantiation, so the default step kernel's code (and its layout in the instruction cache) is untouched by the other two.
 enum { VAR_STEP = 0, VAR_PLACE = 1, VAR_PGS = 2 };
-template <typename T, int kVar = VAR_STEP>
-B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded, bool active = true) {
+template <typename T, int kVar = VAR_STEP, bool C>
+B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const StepArgs<T>& a, int env, const Ctx& c, bool state_preloaded, bool active = true) {
   constexpr bool kPlace = kVar == VAR_PLACE, kPgs = kVar == VAR_PGS;
   const int nv = m.nv;
   T* rec = a.state + (size_t)(active ? env : 0) * a.state_stride;
@@ -142,7 +142,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
     }
     for (int i = c.tid; i < MAXP * 3; i += c.nt) s.psize[i / 3][i % 3] = a.prop_size ? a.prop_size[(size_t)env * MAXP * 3 + i] : m.geom_size[0][0];
     for (int i = c.tid; i < MAXP; i += c.nt) s.pactive[i] = i < m.nprop ? (a.prop_active ? a.prop_active[(size_t)env * MAXP + i] : 1) : 0;
-    for (int i = c.tid; i < MAXP; i += c.nt) { const int tp = (a.prop_type && i < m.nprop) ? a.prop_type[(size_t)env * MAXP + i] : B2P_GEOM_BOX; s.ptype[i] = (unsigned char)((tp == B2P_GEOM_SPHERE || tp == B2P_GEOM_CYLINDER) ? tp : B2P_GEOM_BOX); }
+    for (int i = c.tid; i < MAXP; i += c.nt) { const int tp = (C && a.prop_type && i < m.nprop) ? a.prop_type[(size_t)env * MAXP + i] : B2P_GEOM_BOX; s.ptype[i] = (unsigned char)((tp == B2P_GEOM_SPHERE || tp == B2P_GEOM_CYLINDER) ? tp : B2P_GEOM_BOX); }
     for (int i = c.tid; i < MAXU; i += c.nt) s.ctrl[i] = (a.ctrl && i < m.nu) ? a.ctrl[(size_t)env * m.nu + i] : T(0);
     if (c.tid == 0) { s.flags = 0; s.niter = 0; s.ncon = 0; s.nefc = 0; s.sp.nblk = 0; s.sep_next = 0; for (int k = 0; k < SEP_N; k++) s.sep_pair[k] = -1; }   // sp.nblk = 0: no block structure built yet (make_rows)
     bsync(c);
@@ -171,7 +171,10 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
         if (c.tid == 0) {
           T* q = s.qpos + qa;
           for (int d = 0; d < 3; d++) q[d] = lo[d] + (hi[d] - lo[d]) * (T)uniform01(a.place_seed, (unsigned)env, (unsigned)k, (unsigned)d);
-          q[3] = 0; q[4] = 0; q[5] = 1; q[6] = 0;
+          if (a.place_yaw) {   // PropPlacer (rearrangement.py:189-197): yaw = pi * U about z, quaternion (cos, 0, 0, sin)
+            const T ang = T(3.14159265358979323846) * (T)uniform01(a.place_seed, (unsigned)env, (unsigned)k, 3u);
+            q[3] = cos(T(0.5) * ang); q[4] = 0; q[5] = 0; q[6] = sin(T(0.5) * ang);
+          } else { q[3] = 0; q[4] = 0; q[5] = 1; q[6] = 0; }
         }
         bsync(c);
       }
@@ -195,6 +198,7 @@ B2P_HD void run_env(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, co
       T* o = a.place_out + (size_t)env * 4;
       for (int d = 0; d < 3; d++) o[d] = s.qpos[qa + d];
       o[3] = found ? T(used) : T(-used - 1);
+      if (a.place_quat) for (int d = 0; d < 4; d++) a.place_quat[(size_t)env * 4 + d] = s.qpos[qa + 3 + d];
     }
     return;
   }

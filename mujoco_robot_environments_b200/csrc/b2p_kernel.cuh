@@ -49,24 +49,25 @@ __device__ __forceinline__ void tma_store_1d(void* dst, const void* src, unsigne
 }
 __device__ __forceinline__ void fence_async_smem() { asm volatile("fence.proxy.async.shared::cta;" ::: "memory"); }
 
-template <typename T>
+template <typename T, bool C = false>
 struct alignas(16) SmemLayout {
   DevModel<T> model;
-  alignas(16) Scratch<T> scratch[KernelCfg<T>::kWarps];
+  alignas(16) Scratch<T, C> scratch[KernelCfg<T>::kWarps];
   alignas(8) unsigned long long bar[1 + KernelCfg<T>::kWarps];
 };
 
-static_assert(sizeof(SmemLayout<float>) + 128 <= 232448 && sizeof(SmemLayout<double>) + 128 <= 232448, "shared memory per CTA exceeds the 227 KB an sm_100 CTA may use: shrink Pool<T>::JPS or the warps per CTA");
+static_assert(sizeof(SmemLayout<float>) + 128 <= 232448 && sizeof(SmemLayout<double>) + 128 <= 232448 && sizeof(SmemLayout<float, true>) == sizeof(SmemLayout<float, false>), "shared memory per CTA exceeds the 227 KB an sm_100 CTA may use: shrink Pool<T>::JPS or the warps per CTA");
 
-template <typename T, int kVar>
+template <typename T, int kVar, bool C>
 __global__ void __launch_bounds__(32 * KernelCfg<T>::kWarps, KernelCfg<T>::kMinBlocks)
 b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T> a, int* __restrict__ next_env) {
   extern __shared__ __align__(128) unsigned char smem_raw[];
-  SmemLayout<T>& sm = *reinterpret_cast<SmemLayout<T>*>(smem_raw);
+  SmemLayout<T, C>& sm = *reinterpret_cast<SmemLayout<T, C>*>(smem_raw);
   constexpr unsigned kModelBytes = (unsigned)sizeof(DevModel<T>);
   constexpr unsigned kRecBytes = REC_SIZE * sizeof(T);
   static_assert(sizeof(DevModel<T>) % 16 == 0, "DevModel must be a multiple of 16 bytes for cp.async.bulk");
-  static_assert(offsetof(Scratch<T>, qpos) == 0 && sizeof(Scratch<T>) % 16 == 0, "state record must head a 16-byte aligned Scratch");
+  typedef Scratch<T, C> ScratchT;
+  static_assert(offsetof(ScratchT, qpos) == 0 && sizeof(ScratchT) % 16 == 0, "state record must head a 16-byte aligned Scratch");
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   // lockstep groups: the CTA's warps walk the stage barriers in groups of a.lock_group warps (named barriers 1..), so that a
   // warp waits for the slowest solve of its group only; the whole CTA meets once per scene at the queue
@@ -81,7 +82,7 @@ b2p_step_kernel(const DevModel<T>* __restrict__ gmodel, Globals<T> g, StepArgs<T
   __syncthreads();
   if (threadIdx.x == 0) { mbar_expect_tx(&sm.bar[0], kModelBytes); tma_load_1d(&sm.model, gmodel, kModelBytes, &sm.bar[0]); }
   mbar_wait(&sm.bar[0], 0);
-  Scratch<T>& s = sm.scratch[warp];
+  Scratch<T, C>& s = sm.scratch[warp];
   constexpr bool kPlace = kVar == VAR_PLACE;
   if (lane == 0) { s.jovf = g.jovf + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP; s.xpool = g.xpool ? g.xpool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * Pool<T>::JP : nullptr; s.w6 = g.w6pool + (size_t)(blockIdx.x * KernelCfg<T>::kWarps + warp) * MAXCON * W6_STRIDE; }
   __syncwarp();
@@ -124,21 +125,25 @@ static cudaError_t step_prof_read(unsigned long long* out, int reset) {
 #endif
 }
 
-template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<T>) + 128; }
+template <typename T> static size_t step_smem_size() { return sizeof(SmemLayout<T, false>) + 128; }
 
 // occupancy query + attribute setup (once per handle)
 template <typename T>
 static cudaError_t step_configure(int device, int n_env, LaunchGeom* out) {
   const size_t smem = step_smem_size<T>();
-  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_STEP>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  cudaError_t e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_STEP, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PLACE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PLACE, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
-  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PGS>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PGS, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_STEP, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+  if (e != cudaSuccess) return e;
+  e = cudaFuncSetAttribute(b2p_step_kernel<T, VAR_PLACE, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
   if (e != cudaSuccess) return e;
   int per_sm = 0, sms = 0;
   const int threads = 32 * KernelCfg<T>::kWarps;
-  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T, VAR_STEP>, threads, smem);
+  e = cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, b2p_step_kernel<T, VAR_STEP, false>, threads, smem);
   if (e != cudaSuccess) return e;
   e = cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, device);
   if (e != cudaSuccess) return e;
@@ -154,9 +159,14 @@ template <typename T>
 static cudaError_t step_launch(const LaunchGeom& lg, const void* d_model, const Globals<T>& g, const StepArgs<T>& a, int* next_env, cudaStream_t st) {
   cudaError_t e = cudaMemsetAsync(next_env, 0, sizeof(int), st);
   if (e != cudaSuccess) return e;
-  if (a.mode == MODE_PLACE) b2p_step_kernel<T, VAR_PLACE><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
-  else if (a.solver == 1) b2p_step_kernel<T, VAR_PGS><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
-  else b2p_step_kernel<T, VAR_STEP><<<lg.grid, lg.threads, lg.smem_bytes, st>>>((const DevModel<T>*)d_model, g, a, next_env);
+  // five instantiations: {step, place} x {box props only, prop classes} + PGS (box props only).  The box-only step kernel is the
+  // throughput path; a handle with prop classes bound (b2p_set_env_prop_types) launches the class-capable ones.
+  const bool cls = a.prop_type != nullptr;
+  const DevModel<T>* dm = (const DevModel<T>*)d_model;
+  if (a.mode == MODE_PLACE) { if (cls) b2p_step_kernel<T, VAR_PLACE, true><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env); else b2p_step_kernel<T, VAR_PLACE, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env); }
+  else if (a.solver == 1 && !cls) b2p_step_kernel<T, VAR_PGS, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env);
+  else if (cls) b2p_step_kernel<T, VAR_STEP, true><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env);
+  else b2p_step_kernel<T, VAR_STEP, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env);
   return cudaGetLastError();
 }
 

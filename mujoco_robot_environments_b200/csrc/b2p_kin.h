@@ -4,8 +4,8 @@
 namespace b2p {
 
 // ------------------------------------------------------------------------------------------ mj_kinematics + comPos + comVel + rne (forward sweep)
-template <typename T>
-B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   if (c.tid == 0) {
     for (int k = 0; k < 3; k++) s.xpos[0][k] = 0;
     s.xquat[0][0] = 1; s.xquat[0][1] = 0; s.xquat[0][2] = 0; s.xquat[0][3] = 0;
@@ -22,6 +22,9 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   // The tree is deep and narrow (the arm is a chain), so a level holds one or two bodies and a level-by-level pass is a serial
   // chain run by one or two lanes.  Only what truly depends on the parent goes through such passes (A: pose, C: velocity /
   // acceleration); the per-body inertia and force terms (B, D) run with one lane per body.
+  // (the half-angle sine / cosine of every joint, one lane per joint, ahead of the serial pass; parked in cfrc, which pass D rewrites)
+  for (int d = c.tid; d < m.ntd; d += c.nt) { const T ha = T(0.5) * (s.qpos[d] - m.qpos0[d]); s.cfrc[d + 1][0] = cos(ha); s.cfrc[d + 1][1] = sin(ha); }
+  bsync(c);
   for (int l = 0; l < m.nlevel; l++) {     // A: pose of every tree body, joint anchor / axis -> cdof
     for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
       const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
@@ -34,8 +37,8 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
       mulmv(a, mat, m.jnt_pos[d]);
       for (int k = 0; k < 3; k++) xanchor[k] = pos[k] + a[k];
       mulmv(xaxis, mat, m.jnt_axis[d]);
-      const T ang = s.qpos[d] - m.qpos0[d], sn = sin(T(0.5) * ang);
-      T qloc[4] = {cos(T(0.5) * ang), sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
+      const T cs = s.cfrc[b][0], sn = s.cfrc[b][1];
+      T qloc[4] = {cs, sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
       mulquat(quat, quat, qloc); normquat(quat);
       quat2mat(mat, quat);
       mulmv(a, mat, m.jnt_pos[d]);
@@ -93,25 +96,30 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   bsync(c);
 }
 
-// backward sweep: composite inertias (mj_crb) and rne force accumulation, parent gathers children
-template <typename T>
-B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
-  for (int l = m.nlevel - 2; l >= 0; l--) {
-    for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
-      const int b = m.level_body[idx];
-      for (int q = m.child_start[b]; q < m.child_start[b + 1]; q++) {
-        const int ch = m.child_list[q];
-        for (int k = 0; k < 10; k++) s.crb[b][k] += s.crb[ch][k];
-        for (int k = 0; k < 6; k++) s.cfrc[b][k] += s.cfrc[ch][k];
+// backward sweep: composite inertias (mj_crb) and rne force accumulation.  The sum over a body's subtree is taken directly -- one
+// lane per body over the bodies whose ancestor mask holds it -- instead of parent-gathers-children level by level (nine dependent
+// rounds with a barrier each on this chain-shaped tree).
+template <typename T, bool C>
+B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
+  T acc[16];
+  for (int b0 = 1; b0 < m.ntb; b0 += c.nt) {
+    const int b = b0 + c.tid;
+    if (b < m.ntb) {
+      for (int k = 0; k < 16; k++) acc[k] = 0;
+      for (int j = b; j < m.ntb; j++) if ((m.anc_mask[j] >> (b - 1)) & 1u) {       // descendants have larger ids (parent < child)
+        for (int k = 0; k < 10; k++) acc[k] += s.crb[j][k];
+        for (int k = 0; k < 6; k++) acc[10 + k] += s.cfrc[j][k];
       }
     }
+    bsync(c);
+    if (b < m.ntb) { for (int k = 0; k < 10; k++) s.crb[b][k] = acc[k]; for (int k = 0; k < 6; k++) s.cfrc[b][k] = acc[10 + k]; }
     bsync(c);
   }
 }
 
 // mass matrix (tree block dense, props diagonal), bias forces, passive forces
-template <typename T>
-B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   const int n = m.ntd;
   for (int e = c.tid; e < n * n; e += c.nt) {
     const int i = e / n, j = e % n;
@@ -147,8 +155,8 @@ B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
 }
 
 // ------------------------------------------------------------------------------------------ actuation + smooth acceleration
-template <typename T>
-B2P_HDN void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void actuation_and_smooth(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) s.qfrc_act[d] = 0;
   bsync(c);
   if (c.tid == 0) {
@@ -175,8 +183,8 @@ B2P_HDN void actuation_and_smooth(const DevModel<T>& m, Scratch<T>& s, const Ctx
 }
 
 // ------------------------------------------------------------------------------------------ integrator (mj_implicit / mj_Euler + mj_advance)
-template <typename T>
-B2P_HDN void integrate(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool freeze_tree) {
+template <typename T, bool C>
+B2P_HDN void integrate(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool freeze_tree) {
   const int n = m.ntd; const T h = m.timestep;
   // M - h * d(qfrc_passive + qfrc_actuator)/d(qvel): the velocity-derivative part is a model constant (joint damping
   // on the diagonal; for implicitfast the affine actuator's -bias_vel * moment' moment inside M's sparsity), built on the host

@@ -13,7 +13,7 @@ namespace b2p {
 
 enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
 enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
-enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64, FLAG_PGS_CONDIM6 = 128 };
+enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3, MODE_PLACE = 4 };
 // counter-based uniform in [0, 1): placement proposals are a function of (seed, scene, attempt, coordinate) only
 B2P_HD unsigned hash32(unsigned x) { x ^= x >> 16; x *= 0x7feb352dU; x ^= x >> 15; x *= 0x846ca68bU; x ^= x >> 16; return x; }

@@ -42,8 +42,8 @@ B2P_HD void small_inv_col(const T* L, T* Ainv, int col) {
 // s.ctrl[7], min_max.py:14-19).  Warp-cooperative: the small matrices live in shared memory (the part of the H / FK-sweep
 // union that is dead between step1 and step2) and their entries / columns are spread over the lanes; the two tiny Cholesky
 // factorisations and the PD terms run on lane 0.
-template <typename T>
-B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T>& s, const T* tg, bool grip, const Ctx& c, const T* gn) {
+template <typename T, bool C>
+B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T, C>& s, const T* tg, bool grip, const Ctx& c, const T* gn) {
   T* w = s.H;
   T *J = w, *Ma = w + 42, *Minv = w + 91, *MiJt = w + 140, *Lxi = w + 182, *L = w + 218, *Lx = w + 254, *Nb = w + 290;
   T *dx = w + 332, *pd = w + 338, *Lpd = w + 344, *ne = w + 350, *A = w + 360, *V = w + 396;
@@ -112,8 +112,8 @@ B2P_HDN void osc_torque(const DevModel<T>& m, Scratch<T>& s, const T* tg, bool g
   if (c.tid == 0) s.ctrl[7] = grip ? T(255) : T(0);                                                                  // min_max.py:14-19
   bsync(c);
 }
-template <typename T>
-B2P_HD bool osc_converged(const DevModel<T>& m, const Scratch<T>& s, const T* tg) {   // osc.py:240-247
+template <typename T, bool C>
+B2P_HD bool osc_converged(const DevModel<T>& m, const Scratch<T, C>& s, const T* tg) {   // osc.py:240-247
   T q[4], e[3], d[3], qd[4] = {tg[6], tg[7], tg[8], tg[9]};
   normquat(qd); mat2quat(q, s.site_xmat[0]); osc_ori_error(q, qd, e);
   for (int k = 0; k < 3; k++) d[k] = s.site_xpos[0][k] - tg[k];

@@ -17,7 +17,7 @@
 
 namespace b2p {
 
-template <typename T> B2P_HD T* xrow(const Scratch<T>& s, int r) { const int o = s.joff[r]; return s.xpool + (o >= 0 ? o : -o - 1); }
+template <typename T, bool C> B2P_HD T* xrow(const Scratch<T, C>& s, int r) { const int o = s.joff[r]; return s.xpool + (o >= 0 ? o : -o - 1); }
 
 // min 1/2 x'Ax + x'b  s.t. (x0/d0)^2 + (x1/d1)^2 <= r^2  (mju_QCQP2): Newton on the multiplier of the scaled problem y = x / d
 template <typename T>
@@ -40,8 +40,8 @@ B2P_HD void qcqp2(const T* A, const T* b, const T* d, T r, T* x) {
 }
 
 // J_r . x with the warp's lanes across the row's columns (deterministic butterfly sum: every lane ends with the same bits)
-template <typename T, int K>
-B2P_HD void rows_dot(const DevModel<T>& m, const Scratch<T>& s, const Ctx& c, int r, const T* x, T (&out)[K]) {
+template <typename T, int K, bool C>
+B2P_HD void rows_dot(const DevModel<T>& m, const Scratch<T, C>& s, const Ctx& c, int r, const T* x, T (&out)[K]) {
   const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a), w = wa + (b >= 0 ? 6 : 0), sb = b >= 0 ? block_start(m, b) : 0;
   for (int k = 0; k < K; k++) out[k] = 0;
   for (int e = c.tid; e < w; e += c.nt) {
@@ -51,8 +51,8 @@ B2P_HD void rows_dot(const DevModel<T>& m, const Scratch<T>& s, const Ctx& c, in
   block_sum(c, out);
 }
 // a += sum_k X_{r+k} * df_k
-template <typename T, int K>
-B2P_HD void rows_axpy(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, int r, const T (&df)[K], T* acc) {
+template <typename T, int K, bool C>
+B2P_HD void rows_axpy(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, int r, const T (&df)[K], T* acc) {
   const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a), w = wa + (b >= 0 ? 6 : 0), sb = b >= 0 ? block_start(m, b) : 0;
   for (int e = c.tid; e < w; e += c.nt) {
     T v = 0;
@@ -62,8 +62,8 @@ B2P_HD void rows_axpy(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, int r, 
   bsync(c);
 }
 
-template <typename T>
-B2P_HDN void solve_pgs(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool active) {
+template <typename T, bool C>
+B2P_HDN void solve_pgs(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool active) {
   const int nv = m.nv;
   const bool has = active && s.nefc > 0;
   if (active && !has) {
@@ -72,11 +72,6 @@ B2P_HDN void solve_pgs(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool a
     bsync(c);
   }
   if (!has) return;
-  {   // condim-6 contacts (cylinder class): this PGS, like the oracle's, covers condim 1 and 3 -- such a step is solved by Newton and flagged
-    unsigned six = 0;
-    for (int k = c.tid; k < s.ncon; k += c.nt) if (s.c_row[k] >= 0 && s.c_dim[k] == 6) six = 1;
-    if (block_or(c, six)) { if (c.tid == 0) s.flags |= FLAG_PGS_CONDIM6; solve_constraints(m, s, c, active); return; }
-  }
   const int n = s.nefc;
   const T scale = 1 / (m.meaninertia * (nv > 1 ? nv : 1));
   // ---- X = M^-1 J' (prop segments: diagonal; tree segments: one triangular solve with the factor of M per row)

@@ -33,8 +33,8 @@ B2P_HD void row_params(const DevModel<T>& m, const T* solref_in, const T* solimp
   R = (1 - imp) / imp * diag; if (R < mv) R = mv;
 }
 // add sign * ax . d(point velocity of unified body `body` at world point pt)/d(qvel) into a compressed row
-template <typename T>
-B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0, int body, const T* pt, const T* ax, T sign) {
+template <typename T, bool C>
+B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T, C>& s, T* row, int seg0, int body, const T* pt, const T* ax, T sign) {
   if (body == 0) return;
   if (body >= PROP_BODY0) {
     const int p = body - PROP_BODY0; T r[3] = {pt[0] - s.ppos[p][0], pt[1] - s.ppos[p][1], pt[2] - s.ppos[p][2]};
@@ -50,8 +50,8 @@ B2P_HD void add_jac(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0,
   }
 }
 // ... and of its angular velocity (rows 3..5 of a condim-6 contact: torsional and rolling friction)
-template <typename T>
-B2P_HD void add_jac_rot(const DevModel<T>& m, const Scratch<T>& s, T* row, int seg0, int body, const T* ax, T sign) {
+template <typename T, bool C>
+B2P_HD void add_jac_rot(const DevModel<T>& m, const Scratch<T, C>& s, T* row, int seg0, int body, const T* ax, T sign) {
   if (body == 0) return;
   if (body >= PROP_BODY0) {
     const int p = body - PROP_BODY0;
@@ -61,8 +61,8 @@ B2P_HD void add_jac_rot(const DevModel<T>& m, const Scratch<T>& s, T* row, int s
     for (int d = 0; d < m.ntd; d++) if (mask & (1u << d)) row[seg0 + d] += sign * dot3(ax, s.cdof[d]);
   }
 }
-template <typename T>
-B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
+template <typename T, bool C>
+B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T, C>& s, int r, const T* x) {
   const int a = s.row_a[r], b = s.row_b[r], wa = block_width(m, a), sa = block_start(m, a);
   const T* j = jrow(s, r);
   T v = 0;
@@ -70,7 +70,7 @@ B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T>& s, int r, const T* x) {
   if (b >= 0) { const int sb = block_start(m, b); for (int k = 0; k < 6; k++) v += j[wa + k] * x[sb + k]; }
   return v;
 }
-template <typename T> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s, int r) { return row_dot(m, s, r, s.qvel); }
+template <typename T, bool C> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T, C>& s, int r) { return row_dot(m, s, r, s.qvel); }
 
 // mj_makeConstraint + mj_referenceConstraint: equality -> limits -> contacts, rows complete incl. aref.
 // Pass 1, one lane per ITEM (an equality, a joint limit side, or a contact = 3 rows): which items exist, their row numbers and
@@ -79,8 +79,8 @@ template <typename T> B2P_HD T row_vel(const DevModel<T>& m, const Scratch<T>& s
 // Pass 2, one lane per ROW: the Jacobian row, impedance / regularisation and the reference acceleration.  The rows of one item are
 // independent of each other, and a row on the tree is a 15-dof loop per body: one lane per item made the two connect equalities
 // (3 rows x 2 tree bodies each) the critical path of the whole stage.
-template <typename T>
-B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const Ctx& c) {
   const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
   int base = 0, jbase = 0, first_drop = Pool<T>::EFC + 1; unsigned pairs = 0;
   int nb[SP_MAXBLK];
@@ -95,7 +95,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       } else {
         id = it - m.neq - nlim;
         if (s.c_dist[id] < s.c_incl[id]) {
-          kind = ROW_CONTACT; nr = s.c_dim[id];
+          kind = ROW_CONTACT; nr = C ? s.c_dim[id] : 3;
           // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
           const int p = s.c_pair[id], b1 = m.geom_body[g.pair_g1[p]], b2 = m.geom_body[g.pair_g2[p]];
           const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
@@ -177,7 +177,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       const int q = r - s.c_row[id];
       const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
       PairMix<T> mx;
-      if (!s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
+      if (!C || !s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
       const PairParam<T>& pp = mx.pp;
       // segment of each body inside the packed row: the tree (or the first prop) heads it, a second block follows
       const int seg1 = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0, seg2 = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
@@ -187,11 +187,11 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T>& s,
       const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
       if (q == 0) s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0);
       const T* ax = s.c_frame[id] + 3 * (q < 3 ? q : q - 3);
-      if (q < 3) { add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1)); }
+      if (!C || q < 3) { add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1)); }
       else { add_jac_rot(m, s, J0, seg2, b2, ax, T(1)); add_jac_rot(m, s, J0, seg1, b1, ax, T(-1)); }
       const T vel = row_vel(m, s, r);
       if (q == 0) { s.D[r] = 1 / R0; s.aref[r] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
-      else if (q < 3) { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
+      else if (!C || q < 3) { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
       else {   // App. B item 9: R_k = R_1 mu_0^2 / mu_k^2 for the torsional (k = 3) and rolling (k = 4, 5) rows
         const T fk = s.w6[id * W6_STRIDE + (q == 3 ? 21 : 22)], f0 = s.c_fric[id];
         s.D[r] = 1 / (R1 * f0 * f0 / (fk * fk)); s.aref[r] = -B * vel;

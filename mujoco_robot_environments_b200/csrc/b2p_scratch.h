@@ -29,7 +29,9 @@ struct Globals {                 // read-only global-memory tables
 // bound, so Scratch is kept small: buffers whose lifetimes never overlap share storage.  "pos" members are produced by step1
 // (kinematics, collision, row construction) and are dead once make_rows / the derived-output write have run; "dyn" members
 // live only inside step2 (solver, integrator).  Everything outside the two unions persists across both.
-template <typename T>
+// C: the scene may hold re-classed props (sphere / cylinder colliders, condim-6 contacts).  The layout does not depend on it; the flag
+// selects, at compile time, whether the stepping code carries those paths -- the box-only instantiation is the throughput kernel.
+template <typename T, bool C = false>
 struct alignas(16) Scratch {
   // persisted state (one HBM record per env: qpos | qvel | qacc_warmstart | time)
   T qpos[MAXNQ], qvel[MAXNV], qacc_ws[MAXNV], time, rec_pad[REC_SIZE - (MAXNQ + 2 * MAXNV + 1)], ctrl[MAXU];
@@ -87,15 +89,15 @@ template <typename T> B2P_HD int dof_block(const DevModel<T>& m, int d) { return
 template <typename T> B2P_HD int block_start(const DevModel<T>& m, int blk) { return blk == 0 ? 0 : m.ntd + 6 * (blk - 1); }
 template <typename T> B2P_HD int block_width(const DevModel<T>& m, int blk) { return blk == 0 ? m.ntd : 6; }
 // first slot of packed Jacobian row r: shared-memory pool, or the warp's global overflow area
-template <typename T> B2P_HD const T* jrow(const Scratch<T>& s, int r) { const int o = s.joff[r]; return o >= 0 ? s.Jp + o : s.jovf + (-o - 1); }
+template <typename T, bool C> B2P_HD const T* jrow(const Scratch<T, C>& s, int r) { const int o = s.joff[r]; return o >= 0 ? s.Jp + o : s.jovf + (-o - 1); }
 // pointer to the slots of block `blk` inside row r, or nullptr when the row does not touch the block
-template <typename T> B2P_HD const T* row_seg(const DevModel<T>& m, const Scratch<T>& s, int r, int blk) {
+template <typename T, bool C> B2P_HD const T* row_seg(const DevModel<T>& m, const Scratch<T, C>& s, int r, int blk) {
   const int a = s.row_a[r];
   if (a == blk) return jrow(s, r);
   if (s.row_b[r] == blk) return jrow(s, r) + block_width(m, a);
   return nullptr;
 }
-template <typename T> B2P_HD const unsigned char* block_rows(const Scratch<T>& s, int blk) { return blk == 0 ? s.brow0 : s.browp[blk - 1]; }
+template <typename T, bool C> B2P_HD const unsigned char* block_rows(const Scratch<T, C>& s, int blk) { return blk == 0 ? s.brow0 : s.browp[blk - 1]; }
 
 // HBM state record of one env = the head of Scratch<T>: qpos[MAXNQ] | qvel[MAXNV] | qacc_warmstart[MAXNV] | time | pad
 // launch parameters shared by kernel and host emulation
@@ -121,6 +123,7 @@ struct StepArgs {
   // MODE_PLACE (expert prop_place): per scene the prop to place and the box [lo3 | hi3] proposals are drawn from
   const int* place_prop; const T* place_box; T place_dist; int place_table; unsigned place_seed;
   T* place_out;              // [n_env][4]: accepted position xyz, attempts used (negative: none accepted within n_steps attempts)
+  int place_yaw; T* place_quat;   // place_yaw: draw a yaw about z per proposal (PropPlacer) instead of the gripper-down orientation; place_quat: optional [n_env][4] out
   const T* gains;            // MODE_OSC: optional [n_env][6] per-scene OSC gains (pos kp kd, ori kp kd, null kp kd); NULL = the model's
 };
 // derived-output record (reals): site_xpos[2][3] site_xmat[2][9] qacc[MAXNV] qfrc_bias[MAXNV] ctrl[MAXU] ncon nefc niter |

@@ -5,8 +5,8 @@
 namespace b2p {
 
 // ------------------------------------------------------------------------------------------ Newton solver
-template <typename T>
-B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, const Ctx& c) {
+template <typename T, bool C>
+B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T, C>& s, T* r, const T* v, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) {
     if (d < m.ntd) { T a = 0; for (int j = 0; j < m.ntd; j++) a += s.Mt[j <= d ? tri_idx(d, j) : tri_idx(j, d)] * v[j]; r[d] = a; }
     else r[d] = s.Mdiag[d] * v[d];
@@ -16,9 +16,9 @@ B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T>& s, T* r, const T* v, c
 // out-of-line functions with plain loops over the 6 rows, and their 6 x 6 cone Hessian sits in the warp's global w6 area; the
 // condim-3 code above / below stays unrolled and in shared memory.
 template <typename T> B2P_HD int tri6(int a, int b) { return a >= b ? (a * (a + 1)) / 2 + b : (b * (b + 1)) / 2 + a; }
-template <typename T> B2P_HD void friction5(const Scratch<T>& s, int k, T* fr) { const T f0 = s.c_fric[k], ft = s.w6[k * W6_STRIDE + 21], fl = s.w6[k * W6_STRIDE + 22]; fr[0] = f0; fr[1] = f0; fr[2] = ft; fr[3] = fl; fr[4] = fl; }
-template <typename T>
-B2P_HDN T cone6_update(Scratch<T>& s, int k, int r, bool want_hess, unsigned& chg) {
+template <typename T, bool C> B2P_HD void friction5(const Scratch<T, C>& s, int k, T* fr) { const T f0 = s.c_fric[k], ft = s.w6[k * W6_STRIDE + 21], fl = s.w6[k * W6_STRIDE + 22]; fr[0] = f0; fr[1] = f0; fr[2] = ft; fr[3] = fl; fr[4] = fl; }
+template <typename T, bool C>
+B2P_HDN T cone6_update(Scratch<T, C>& s, int k, int r, bool want_hess, unsigned& chg) {
   const T mu = s.c_mu[k]; T fr[5]; friction5(s, k, fr);
   T U[6], Tt = 0, cost = 0;
   U[0] = s.Jaref[r] * mu;
@@ -53,8 +53,8 @@ B2P_HDN T cone6_update(Scratch<T>& s, int k, int r, bool want_hess, unsigned& ch
   return cost;
 }
 // line-search terms of one condim-6 contact at step a: (quadratic q0 q1 q2 when the whole contact is quadratic) or (cone ec e1 e2)
-template <typename T>
-B2P_HDN void cone6_ls(const Scratch<T>& s, int k, int r, T a, T* q, T* e) {
+template <typename T, bool C>
+B2P_HDN void cone6_ls(const Scratch<T, C>& s, int k, int r, T a, T* q, T* e) {
   const T mu = s.c_mu[k]; T fr[5]; friction5(s, k, fr);
   T t0 = 0, t1 = 0, t2 = 0, UU = 0, UV = 0, VV = 0;
   for (int i = 0; i < 6; i++) { const T D = s.D[r + i], j0 = s.Jaref[r + i], jv = s.Jv[r + i]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }
@@ -70,8 +70,8 @@ B2P_HDN void cone6_ls(const Scratch<T>& s, int k, int r, T a, T* q, T* e) {
 }
 
 // per-item (rows of eq/limit, whole contacts) force/state/cost from s.Jaref; returns this thread's cost part
-template <typename T>
-B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool want_hess, unsigned* dirty = nullptr) {
+template <typename T, bool C>
+B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool want_hess, unsigned* dirty = nullptr) {
   // dirty: this thread saw a row change state, or a contact in the cone's middle zone (whose Hessian block moves with the point):
   // when no thread did, the Newton Hessian of the previous iteration -- and its factor in s.H -- is still exact
   T cost = 0; unsigned chg = 0;
@@ -87,7 +87,7 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, b
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
-    if (s.c_dim[k] == 6) { cost += cone6_update(s, k, r, want_hess, chg); continue; }
+    if (C && s.c_dim[k] == 6) { cost += cone6_update(s, k, r, want_hess, chg); continue; }
     const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     const T j0 = s.Jaref[r], j1 = s.Jaref[r + 1], j2 = s.Jaref[r + 2];
     const T N = j0 * mu, U1 = j1 * f1, U2 = j2 * f2, Tt = sqrt(U1 * U1 + U2 * U2);
@@ -118,14 +118,14 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, b
   return cost;
 }
 // qfrc_con = J' force: one lane per dof, walking only the items of the dof's block
-template <typename T>
-B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) {
     const int blk = dof_block(m, d), o = d - block_start(m, blk), n = s.nbrow[blk];
     const unsigned char* lst = block_rows(s, blk);
     T a = 0;
     for (int q = 0; q < n; q++) {
-      const int r = lst[q], tp = s.row_type[r], nr = tp == ROW_CONTACT ? s.c_dim[s.row_id[r]] : ((tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1);
+      const int r = lst[q], tp = s.row_type[r], nr = tp == ROW_CONTACT ? (C ? s.c_dim[s.row_id[r]] : 3) : ((tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1);
       const T* seg = row_seg(m, s, r, blk);
       const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
       for (int k = 0; k < nr; k++) { const T f = s.force[r + k]; if (f != 0) a += seg[k * w + o] * f; }
@@ -135,8 +135,8 @@ B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
 }
 // H = M + J' W J on the packed lower triangle in solver order (props first, tree last), only inside the block
 // structure s.sp: one lane per matrix element, walking the item list of the element's row block.
-template <typename T>
-B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
+template <typename T, bool C>
+B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   const int np = m.nprop, np6 = 6 * np, ntd = m.ntd;
   for (int sbi = 0; sbi <= np; sbi++) for (int sbj = 0; sbj <= sbi; sbj++) {
     if (!sp_coupled(s.sp, sbi, sbj)) continue;
@@ -156,7 +156,7 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
         const T* si = row_seg(m, s, r, bi);
         if (bi == bj) sj = si;
         const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
-        if (tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
+        if (C && tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
           if (s.row_state[r] != ST_SATISFIED) {
             const T* W = s.w6 + s.row_id[r] * W6_STRIDE;
             for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi]; if (ai != 0) for (int b = 0; b < 6; b++) h += W[tri6<T>(a, b)] * ai * sj[b * w + oj]; }
@@ -177,8 +177,8 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T>& s, const Ctx& c) {
   }
 }
 template <typename T> struct LsPt { T alpha, cost, d1, d2; };
-template <typename T>
-B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, const T* qg) {
+template <typename T, bool C>
+B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, T a, const T* qg) {
   T q0 = 0, q1 = 0, q2 = 0, ec = 0, e1 = 0, e2 = 0;
   for (int r = c.tid; r < s.nefc; r += c.nt) {
     const int tp = s.row_type[r];
@@ -189,7 +189,7 @@ B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, 
   for (int k = c.tid; k < s.ncon; k += c.nt) {
     const int r = s.c_row[k];
     if (r < 0) continue;
-    if (s.c_dim[k] == 6) { T qq[3] = {0, 0, 0}, ee[3] = {0, 0, 0}; cone6_ls(s, k, r, a, qq, ee); q0 += qq[0]; q1 += qq[1]; q2 += qq[2]; ec += ee[0]; e1 += ee[1]; e2 += ee[2]; continue; }
+    if (C && s.c_dim[k] == 6) { T qq[3] = {0, 0, 0}, ee[3] = {0, 0, 0}; cone6_ls(s, k, r, a, qq, ee); q0 += qq[0]; q1 += qq[1]; q2 += qq[2]; ec += ee[0]; e1 += ee[1]; e2 += ee[2]; continue; }
     const T mu = s.c_mu[k], f1 = s.c_fric[k], f2 = f1;
     T t0 = 0, t1 = 0, t2 = 0;
     for (int q = 0; q < 3; q++) { const T D = s.D[r + q], j0 = s.Jaref[r + q], jv = s.Jv[r + q]; t0 += T(0.5) * D * j0 * j0; t1 += D * j0 * jv; t2 += T(0.5) * D * jv * jv; }
@@ -215,8 +215,8 @@ B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T a, 
   return p;
 }
 // Jaref = J*x - aref, Ma = M*x, returns total cost (all threads)
-template <typename T>
-B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x) {
+template <typename T, bool C>
+B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, const T* x) {
   for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] = row_dot(m, s, r, x) - s.aref[r];
   mul_M(m, s, s.Ma, x, c);
   bsync(c);
@@ -226,8 +226,8 @@ B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, const T* x)
   return v[0];
 }
 // cost and gradient at s.qacc (s.Jaref / s.Ma consistent with it); also the per-contact cone Hessian weights
-template <typename T>
-B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gradnorm2, bool& hess_dirty) {
+template <typename T, bool C>
+B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, T& gradnorm2, bool& hess_dirty) {
   unsigned chg = 0;
   T v[2] = {constraint_update(m, s, c, true, &chg), 0};
   hess_dirty = block_or(c, chg) != 0;
@@ -244,8 +244,8 @@ B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T& gr
   return v[0];
 }
 // Newton direction: search = -H^-1 grad with H = M + J' W J factored on its block structure
-template <typename T>
-B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool refactor) {
+template <typename T, bool C>
+B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool refactor) {
   PROF_T0
   if (refactor) {   // otherwise s.H still holds the factor of the identical Hessian of the previous iteration
     assemble_H(m, s, c);
@@ -261,8 +261,8 @@ B2P_HDN void newton_direction(const DevModel<T>& m, Scratch<T>& s, const Ctx& c,
   bsync(c);
   PROF_ADD(PF_SOLVE)
 }
-template <typename T>
-B2P_HDN T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale) {
+template <typename T, bool C>
+B2P_HDN T line_search(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, T scale) {
   T v[4] = {0, 0, 0, 0};
   mul_M(m, s, s.Mv, s.search, c);
   for (int r = c.tid; r < s.nefc; r += c.nt) s.Jv[r] = row_dot(m, s, r, s.search);
@@ -299,8 +299,8 @@ B2P_HDN T line_search(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, T scale
   }
   return best.alpha;
 }
-template <typename T>
-B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T>& s, const Ctx& c, bool active) {
+template <typename T, bool C>
+B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, bool active) {
   const int nv = m.nv;
   const bool has = active && s.nefc > 0;
   if (active && !has) {

@@ -93,6 +93,7 @@ class BatchedRearrangementEnv:
         self._dgen = torch.Generator(device=self.device); self._dgen.manual_seed(tseed)
         self._rs = [np.random.RandomState(seed=tseed + e) for e in range(self.num_envs)] if self._sampler == "per_env" else None
         self._vrng = np.random.default_rng(tseed)
+        self._place_seed = (tseed * 2654435761) & 0x7FFFFFFF   # counter-based proposals of the device-side placer: a new stream per launch
         self._table_gid = p.geom_id(TABLE_GEOM)
         self._prop_gid = torch.tensor(p.model.prop_geomid, device=self.device)
         self.mode = None
@@ -203,30 +204,36 @@ class BatchedRearrangementEnv:
                 if not bool(todo.any()):
                     continue
                 active[todo, k] = 1
-                for attempt in range(int(pcfg["max_attempts_per_prop"])):
-                    if self._sampler == "device":
-                        # every scene draws; only the scenes still searching take the proposal (no nonzero / host sync per try)
-                        w = self._cfg["task"]["initializers"]["workspace"]
-                        lo = torch.tensor(w["min_pose"], device=self.device, dtype=self.dtype); hi = torch.tensor(w["max_pose"], device=self.device, dtype=self.dtype)
-                        u = torch.rand(self.num_envs, 4, device=self.device, dtype=self.dtype, generator=self._dgen)
-                        ang = math.pi * u[:, 3]
-                        pose = torch.cat([lo + (hi - lo) * u[:, :3], torch.cos(ang / 2)[:, None], torch.zeros(self.num_envs, 2, device=self.device, dtype=self.dtype),
-                                          torch.sin(ang / 2)[:, None]], 1)
-                        p.qpos[:, qadr[k]:qadr[k] + 7] = torch.where(todo[:, None], pose, p.qpos[:, qadr[k]:qadr[k] + 7])
-                    else:
-                        envs = torch.nonzero(todo).flatten()
-                        pos, quat = self._sample_poses(envs.cpu().numpy())
-                        pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
-                        p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
-                    p.forward(full_contacts=True)
-                    todo = todo & self._collides(k)
-                    if (self._sampler != "device" or attempt % 4 == 3) and not bool(todo.any()):
-                        break
-                else:
-                    if bool(todo.any()):          # (the device sampler looks at `todo` every 4th try only: the last tries may have succeeded)
+                if self._sampler == "device":
+                    # one launch per prop: every scene's warp loops proposal -> kinematics -> collision pass -> rule on the device
+                    w = self._cfg["task"]["initializers"]["workspace"]
+                    lo = torch.tensor(w["min_pose"], device=self.device, dtype=self.dtype).expand(self.num_envs, 3)
+                    hi = torch.tensor(w["max_pose"], device=self.device, dtype=self.dtype).expand(self.num_envs, 3)
+                    self._place_seed += 1
+                    out, quat = p.place_props(torch.full((self.num_envs,), k, device=self.device), lo, hi, self._table_gid, 0.6,
+                                              int(pcfg["max_attempts_per_prop"]), self._place_seed, mask=todo)
+                    ok = todo & (out[:, 3] > 0)
+                    pose = torch.cat([out[:, :3], quat], 1)
+                    p.qpos[:, qadr[k]:qadr[k] + 7] = torch.where(ok[:, None], pose, p.qpos[:, qadr[k]:qadr[k] + 7])
+                    bad = todo & ~ok
+                    if bool(bad.any()):
                         if self.strict:
                             raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
-                        stuck |= todo
+                        stuck |= bad
+                    continue
+                for attempt in range(int(pcfg["max_attempts_per_prop"])):   # per-scene RandomState streams (reference draw order), one query launch per round
+                    envs = torch.nonzero(todo).flatten()
+                    pos, quat = self._sample_poses(envs.cpu().numpy())
+                    pose = torch.tensor(np.concatenate([pos, quat], 1), device=self.device, dtype=self.dtype)
+                    p.qpos[envs, qadr[k]:qadr[k] + 7] = pose
+                    p.forward(full_contacts=True)
+                    todo = todo & self._collides(k)
+                    if not bool(todo.any()):
+                        break
+                else:
+                    if self.strict:
+                        raise RuntimeError("Failed to find a non-colliding pose for prop_%d after %d attempts" % (k, pcfg["max_attempts_per_prop"]))
+                    stuck |= todo
             if not bool(stuck.any()):
                 return
             # park every prop of the stuck scenes and start their placement over
@@ -288,7 +295,7 @@ class BatchedRearrangementEnv:
             self.eef_home_pose = home_pose
         else:
             self.eef_home_pose[m] = home_pose[m]
-        p.status(clear=True)
+        p.status(clear=m)                                                                     # the reset scenes' flags only
         self.mode = "pick"                                                                    # :331
         return TimeStep(StepType.FIRST, 0.0, 0.0, self._compute_observation())
 

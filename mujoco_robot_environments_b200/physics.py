@@ -79,7 +79,7 @@ class BatchedPhysics:
         ffi.check(self._L.b2p_bind_state(self._h, self.state.data_ptr()), "b2p_bind_state")
         ffi.check(self._L.b2p_bind_out(self._h, self.out.data_ptr()), "b2p_bind_out")
         ffi.check(self._L.b2p_set_env_params(self._h, self.prop_size.data_ptr(), self.prop_active.data_ptr()), "b2p_set_env_params")
-        ffi.check(self._L.b2p_set_env_prop_types(self._h, self.prop_type.data_ptr()), "b2p_set_env_prop_types")
+        self._classes_bound = False        # the class-capable kernels are selected only once a scene holds a sphere / cylinder prop
         self._ofs = {}
         for k, fid in ffi.O.items():
             o, c = C.c_int(), C.c_int()
@@ -172,6 +172,21 @@ class BatchedPhysics:
         self._keep = (pid, box, m)
         return out
 
+    def place_props(self, prop_id: torch.Tensor, lo: torch.Tensor, hi: torch.Tensor, table_geom: int, dist: float, max_attempts: int,
+                    seed: int, mask: Optional[torch.Tensor] = None):
+        """PropPlacer for one prop per scene in one launch (``b2p_place_props``): proposals = position ~ U(lo, hi), yaw = pi * U about z
+        -> (out [n_env, 4] = accepted xyz, attempts used (negative: none accepted), quat [n_env, 4]).  The state is not written."""
+        pid = prop_id.to(device=self.device, dtype=torch.int32).contiguous()
+        box = torch.cat([lo, hi], 1).to(device=self.device, dtype=self.dtype).contiguous()
+        m = None if mask is None else mask.to(device=self.device, dtype=torch.uint8).contiguous()
+        assert pid.shape == (self.n_env,) and box.shape == (self.n_env, 6)
+        out = torch.zeros(self.n_env, 4, device=self.device, dtype=self.dtype)
+        quat = torch.zeros(self.n_env, 4, device=self.device, dtype=self.dtype)
+        ffi.check(self._L.b2p_place_props(self._h, pid.data_ptr(), box.data_ptr(), None if m is None else m.data_ptr(), int(max_attempts), float(dist),
+                                          int(table_geom), int(seed) & 0xFFFFFFFF, out.data_ptr(), quat.data_ptr(), self._stream()), "b2p_place_props")
+        self._keep = (pid, box, m)
+        return out, quat
+
     def osc_config(self, gains6, nullspace7, pos_thresh=5e-3, ori_thresh=68e-3):
         g = (C.c_double * 6)(*[float(x) for x in gains6])
         q = (C.c_double * 7)(*[float(x) for x in nullspace7])
@@ -224,16 +239,27 @@ class BatchedPhysics:
         collider class [n, P] (``ffi.GEOM``: box 6 / sphere 2 / cylinder 5; environment/props.py draws a shape per prop)."""
         if prop_type is not None:
             self.prop_type.copy_(prop_type.to(self.prop_type))
+            want = bool((self.prop_type != ffi.GEOM["box"]).any())
+            if want != self._classes_bound:       # box-only batches keep the throughput kernel (b2p_set_env_prop_types(NULL))
+                ffi.check(self._L.b2p_set_env_prop_types(self._h, self.prop_type.data_ptr() if want else None), "b2p_set_env_prop_types")
+                self._classes_bound = want
         if prop_size is not None:
             self.prop_size.copy_(prop_size.to(self.prop_size))
         if prop_active is not None:
             self.prop_active.copy_(prop_active.to(self.prop_active))
 
     # bit k of status(): the first three are mj_checkPos / Vel / Acc, the rest capacity / iteration-cap notes (csrc/b2p_math.h)
-    STATUS_FLAGS = ("badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter", "pgs_condim6")
+    STATUS_FLAGS = ("badqpos", "badqvel", "badqacc", "contactfull", "efcfull", "candfull", "solver_maxiter")
 
-    def status(self, clear: bool = False) -> torch.Tensor:
-        """Per-env OR of bad-state flags (dm_control check_invalid_state equivalent)."""
+    def status(self, clear=False) -> torch.Tensor:
+        """Per-env OR of bad-state flags (dm_control check_invalid_state equivalent).  ``clear``: True clears every scene's flags after
+        the read, a bool tensor [n_env] clears those scenes' only (a masked reset must not wipe what the other scenes raised)."""
+        if isinstance(clear, torch.Tensor):
+            ffi.check(self._L.b2p_status(self._h, self._status.data_ptr(), 0, self._stream()))
+            kept = torch.where(clear.to(self.device, torch.bool), torch.zeros_like(self._status), self._status)
+            ffi.check(self._L.b2p_status_set(self._h, kept.data_ptr(), self._stream()))
+            self._keep_status = kept
+            return self._status
         ffi.check(self._L.b2p_status(self._h, self._status.data_ptr(), int(clear), self._stream()))
         return self._status
 

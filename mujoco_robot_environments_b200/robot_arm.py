@@ -37,8 +37,14 @@ class BatchedRobotArm:
         return self.physics.data.site_xpos[:, 1]
 
     def ticks_for(self, duration: float) -> int:
-        """Number of passes of ``while time - start < duration`` (robot_arm.py:68) when every pass advances time by
-        control_steps * timestep: 200 for 1.0 s, 400 for 2.0 s."""
+        """Number of passes of ``while time - start < duration`` (robot_arm.py:68) when every pass advances time by EXACTLY
+        control_steps * timestep: 200 for 1.0 s, 400 for 2.0 s.
+
+        Deviation, on purpose: the reference's ``data.time`` is a float64 accumulated 0.001 at a time, so ``time - start`` after 400
+        passes is 2.0 -+ a few ulp, and for most start times the rounding falls on the low side -- the reference then runs a 401st
+        (201st) pass, five more physics steps (0.25 % of the phase), depending on the scene's start time.  A batch runs one tick count
+        for all scenes, so the exact-arithmetic count is used.  (``physics_env_steps`` of the data generator is
+        sum(time) / h; in fp32 mode the record's time field is an fp32 accumulation, so that statistic is approximate.)"""
         return max(0, int(math.ceil(duration / self._tick_dt - 1e-9)))
 
     def run_controller(self, duration: float) -> torch.Tensor:

@@ -13,7 +13,7 @@ template <typename T>
 struct Emu {
   DevModel<T> model; HostTables ht;
   std::vector<T> mesh_vert; std::vector<short> g1, g2; std::vector<PairParam<T>> pp; std::vector<NbrPt<T>> nbr_pt; std::vector<NbrSpan> nbr_span; std::vector<T> jovf, geom_dop, xpool, w6; std::vector<GeomRaw<T>> geom_raw;
-  Globals<T> g; Scratch<T>* s;
+  Globals<T> g; Scratch<T, false>* s; Scratch<T, true>* sc;   // box-only and class-capable instantiations of the stepping code
 };
 
 template <typename T>
@@ -50,7 +50,9 @@ static Emu<T>* make(const void* blob, size_t n) {
     b.solmix = (T)a.solmix; b.margin = (T)a.margin; b.gap = (T)a.gap;
   }
   e->g.geom_raw = e->geom_raw.data();
-  e->s = new Scratch<T>(); e->s->jovf = e->jovf.data(); e->s->xpool = e->xpool.data(); e->w6.assign((size_t)MAXCON * W6_STRIDE, T(0)); e->g.w6pool = e->w6.data(); e->s->w6 = e->w6.data();
+  e->w6.assign((size_t)MAXCON * W6_STRIDE, T(0)); e->g.w6pool = e->w6.data();
+  e->s = new Scratch<T, false>(); e->s->jovf = e->jovf.data(); e->s->xpool = e->xpool.data(); e->s->w6 = e->w6.data();
+  e->sc = new Scratch<T, true>(); e->sc->jovf = e->jovf.data(); e->sc->xpool = e->xpool.data(); e->sc->w6 = e->w6.data();
   return e;
 }
 
@@ -73,7 +75,9 @@ static int run(Emu<T>* e, const EmuArgs* a) {
   Ctx c = {0, 1};
   for (int env = 0; env < a->n_env; env++) {
     if (s.env_mask && !s.env_mask[env]) continue;
-    if (a->solver == 1) run_env<T, VAR_PGS>(e->model, e->g, *e->s, s, env, c, false); else run_env(e->model, e->g, *e->s, s, env, c, false);
+    if (a->prop_type) run_env<T, VAR_STEP>(e->model, e->g, *e->sc, s, env, c, false);
+    else if (a->solver == 1) run_env<T, VAR_PGS>(e->model, e->g, *e->s, s, env, c, false);
+    else run_env<T, VAR_STEP>(e->model, e->g, *e->s, s, env, c, false);
   }
   return 0;
 }
@@ -88,7 +92,7 @@ void emu_osc_config(void* h, int dtype, const double* gains6, const double* null
 int emu_out_size() { return OutLayout::SIZE; }
 int emu_scratch_bytes(int dtype) { return dtype == 0 ? (int)sizeof(Scratch<double>) : (int)sizeof(Scratch<float>); }
 int emu_model_bytes(int dtype) { return dtype == 0 ? (int)sizeof(DevModel<double>) : (int)sizeof(DevModel<float>); }
-void emu_destroy(void* h, int dtype) { if (dtype == 0) { auto* e = (Emu<double>*)h; delete e->s; delete e; } else { auto* e = (Emu<float>*)h; delete e->s; delete e; } }
+void emu_destroy(void* h, int dtype) { if (dtype == 0) { auto* e = (Emu<double>*)h; delete e->s; delete e->sc; delete e; } else { auto* e = (Emu<float>*)h; delete e->s; delete e->sc; delete e; } }
 }
 // narrow-phase census of a run (tools/narrow_census.py; built with -DB2P_HOST_COUNTERS): support calls, hill-climb steps, MPR queries
 extern "C" void emu_pair_mpr(long* out) {
