@@ -113,7 +113,7 @@ static int upload(b2p_handle_s* h, const HostTables& ht) {
   h->out = h->own_out;
   CK(cudaMalloc(&h->d_next_env, sizeof(int)));
   CK(sizeof(T) == 8 ? configure_f64(h->device, h->n_env, &h->lg) : configure_f32(h->device, h->n_env, &h->lg));
-  CK(cudaMalloc(&h->d_jovf, (size_t)h->lg.grid * h->lg.warps_per_cta * Pool<T>::JP * sizeof(T)));   // Jacobian overflow: one area per resident warp
+  CK(cudaMalloc(&h->d_jovf, ((size_t)h->lg.grid * h->lg.warps_per_cta * Pool<T>::JP + 16) * sizeof(T)));   // + 16: row_dot reads a tree row in 16 guarded slots   // Jacobian overflow: one area per resident warp
   CK(cudaMalloc(&h->d_w6pool, (size_t)h->lg.grid * h->lg.warps_per_cta * MAXCON * W6_STRIDE * sizeof(T)));
   CK(cudaMalloc(&h->d_work, (size_t)h->n_env * 4)); CK(cudaMemset(h->d_work, 0, (size_t)h->n_env * 4));
   CK(cudaMalloc(&h->d_order, (size_t)h->n_env * 4));

@@ -22,24 +22,23 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c)
   // The tree is deep and narrow (the arm is a chain), so a level holds one or two bodies and a level-by-level pass is a serial
   // chain run by one or two lanes.  Only what truly depends on the parent goes through such passes (A: pose, C: velocity /
   // acceleration); the per-body inertia and force terms (B, D) run with one lane per body.
-  // (the half-angle sine / cosine of every joint, one lane per joint, ahead of the serial pass; parked in cfrc, which pass D rewrites)
-  for (int d = c.tid; d < m.ntd; d += c.nt) { const T ha = T(0.5) * (s.qpos[d] - m.qpos0[d]); s.cfrc[d + 1][0] = cos(ha); s.cfrc[d + 1][1] = sin(ha); }
+  // Everything about a joint that does not depend on the parent's pose is done ahead of the serial pass, one lane per joint: the
+  // rotation of the body relative to its parent, q_rel = tb_quat * (cos a/2, sin a/2 axis)  (parked in cfrc, which pass D rewrites).
+  // The joint's anchor and axis in the parent frame are model constants (tb_anchor, tb_axis).
+  for (int d = c.tid; d < m.ntd; d += c.nt) {
+    const T ha = T(0.5) * (s.qpos[d] - m.qpos0[d]), sn = sin(ha);
+    const T qloc[4] = {cos(ha), sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
+    mulquat(s.cfrc[d + 1], m.tb_quat[d + 1], qloc);
+  }
   bsync(c);
   for (int l = 0; l < m.nlevel; l++) {     // A: pose of every tree body, joint anchor / axis -> cdof
     for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
       const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
-      T pos[3], quat[4], a[3];
-      mulmv(pos, s.xmat[p], m.tb_pos[b]);
-      for (int k = 0; k < 3; k++) pos[k] += s.xpos[p][k];
-      mulquat(quat, s.xquat[p], m.tb_quat[b]);
-      T mat[9]; quat2mat(mat, quat);
-      T xanchor[3], xaxis[3];
-      mulmv(a, mat, m.jnt_pos[d]);
-      for (int k = 0; k < 3; k++) xanchor[k] = pos[k] + a[k];
-      mulmv(xaxis, mat, m.jnt_axis[d]);
-      const T cs = s.cfrc[b][0], sn = s.cfrc[b][1];
-      T qloc[4] = {cs, sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
-      mulquat(quat, quat, qloc); normquat(quat);
+      T quat[4], mat[9], xanchor[3], xaxis[3], a[3];
+      mulmv(xanchor, s.xmat[p], m.tb_anchor[b]);
+      for (int k = 0; k < 3; k++) xanchor[k] += s.xpos[p][k];
+      mulmv(xaxis, s.xmat[p], m.tb_axis[b]);
+      mulquat(quat, s.xquat[p], s.cfrc[b]); normquat(quat);
       quat2mat(mat, quat);
       mulmv(a, mat, m.jnt_pos[d]);
       for (int k = 0; k < 3; k++) s.xpos[b][k] = xanchor[k] - a[k];

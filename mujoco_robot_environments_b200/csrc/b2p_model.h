@@ -85,6 +85,7 @@ struct alignas(16) DevModel {
   unsigned anc_mask[MAXTB];      // bit d set <=> tree dof d is on the chain of body b (incl. its own)
   T tb_pos[MAXTB][3], tb_quat[MAXTB][4], tb_ipos[MAXTB][3], tb_iquat[MAXTB][4], tb_mass[MAXTB], tb_inertia[MAXTB][3];
   T tb_invweight0[MAXTB][2];
+  T tb_anchor[MAXTB][3], tb_axis[MAXTB][3];   // joint anchor and axis of body b's hinge in the PARENT body's frame: pos + R(quat) jnt_pos, R(quat) jnt_axis
   T jnt_pos[MAXTD][3], jnt_axis[MAXTD][3], jnt_stiffness[MAXTD], jnt_range[MAXTD][2], jnt_margin[MAXTD];
   T jnt_solref[MAXTD][2], jnt_solimp[MAXTD][5], qpos0[MAXTD], qpos_spring[MAXTD];
   T dof_armature[MAXTD], dof_damping[MAXTD], dof_invweight0[MAXTD];
@@ -179,6 +180,16 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     m.qpos0[d] = b.D(B2PM_F_QPOS0)[d]; m.qpos_spring[d] = b.D(B2PM_F_QPOS_SPRING)[d];
     m.dof_armature[d] = b.D(B2PM_F_DOF_ARMATURE)[d]; m.dof_damping[d] = b.D(B2PM_F_DOF_DAMPING)[d]; m.dof_invweight0[d] = b.D(B2PM_F_DOF_INVWEIGHT0)[d];
     m.jnt_limited[d] = b.I(B2PM_F_JNT_LIMITED)[d];
+  }
+  for (int i = 1; i < ntb; i++) {   // constants of the kinematic pass: the hinge of body i as seen from its parent
+    const double* q = m.tb_quat[i]; const int d = i - 1;
+    const double w = q[0], x = q[1], y = q[2], z = q[3];
+    const double R[9] = {w * w + x * x - y * y - z * z, 2 * (x * y - w * z), 2 * (x * z + w * y), 2 * (x * y + w * z), w * w - x * x + y * y - z * z, 2 * (y * z - w * x),
+                         2 * (x * z - w * y), 2 * (y * z + w * x), w * w - x * x - y * y + z * z};
+    for (int r = 0; r < 3; r++) {
+      m.tb_anchor[i][r] = m.tb_pos[i][r] + R[3 * r] * m.jnt_pos[d][0] + R[3 * r + 1] * m.jnt_pos[d][1] + R[3 * r + 2] * m.jnt_pos[d][2];
+      m.tb_axis[i][r] = R[3 * r] * m.jnt_axis[d][0] + R[3 * r + 1] * m.jnt_axis[d][1] + R[3 * r + 2] * m.jnt_axis[d][2];
+    }
   }
   // spatial reference point: the (world-fixed) anchor of dof 0 at qpos0 = parent-chain of static frames
   cp(m.ref, b.D(B2PM_F_BODY_POS) + 3 * 1, 3);   // body 1's parent is the (fused) world
@@ -327,7 +338,7 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
   CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body);
   CR(timestep); CR(gravity); CR(impratio); CR(tolerance); CR(ls_tolerance); CR(ccd_tolerance); CR(meaninertia); CR(ref);
   CI(tb_parent); CI(level_start); CI(level_body); CI(child_start); CI(child_list); CI(anc_mask);
-  CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0);
+  CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0); CR(tb_anchor); CR(tb_axis);
   CR(jnt_pos); CR(jnt_axis); CR(jnt_stiffness); CR(jnt_range); CR(jnt_margin); CR(jnt_solref); CR(jnt_solimp); CR(qpos0); CR(qpos_spring);
   CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass); CR(pclass_mass);
   for (int k = 0; k < NPCLASS; k++) { d.pclass[k].priority = s.pclass[k].priority; d.pclass[k].condim = s.pclass[k].condim; for (int q = 0; q < 3; q++) d.pclass[k].friction[q] = (T)s.pclass[k].friction[q]; for (int q = 0; q < 2; q++) d.pclass[k].solref[q] = (T)s.pclass[k].solref[q]; for (int q = 0; q < 5; q++) d.pclass[k].solimp[q] = (T)s.pclass[k].solimp[q]; d.pclass[k].solmix = (T)s.pclass[k].solmix; d.pclass[k].margin = (T)s.pclass[k].margin; d.pclass[k].gap = (T)s.pclass[k].gap; }

@@ -47,7 +47,7 @@ struct alignas(16) Scratch {
   T qfrc_bias[MAXNV], qfrc_passive[MAXNV], qfrc_act[MAXNV], qfrc_smooth[MAXNV], qacc_smooth[MAXNV], qacc[MAXNV], qfrc_con[MAXNV];
   T act_force[MAXU];
   // contacts
-  int ncand, ncon, nefc, flags, niter, jused, nmpr; unsigned cpl_pairs;
+  int ncand, ncon, nefc, flags, niter, jused, nmpr, nrow_nc; unsigned cpl_pairs;   // nrow_nc: rows ahead of the first contact row (equality + limit rows)
   T c_dist[MAXCON], c_mu[MAXCON], c_fric[MAXCON], c_incl[MAXCON];
   short c_pair[MAXCON], c_row[MAXCON]; unsigned char c_dim[MAXCON];   // c_dim: 3, or 6 for a contact of the cylinder class (torsional + rolling rows)
   // constraint rows.  Jacobian rows are packed: row r occupies Jp[joff[r] .. joff[r] + wa + wb) with segment A

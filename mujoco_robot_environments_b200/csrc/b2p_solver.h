@@ -75,9 +75,8 @@ B2P_HDN T constraint_update(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c
   // dirty: this thread saw a row change state, or a contact in the cone's middle zone (whose Hessian block moves with the point):
   // when no thread did, the Newton Hessian of the previous iteration -- and its factor in s.H -- is still exact
   T cost = 0; unsigned chg = 0;
-  for (int r = c.tid; r < s.nefc; r += c.nt) {
+  for (int r = c.tid; r < s.nrow_nc; r += c.nt) {   // equality and limit rows come first (MuJoCo's row order): no pass over the contact rows
     const int tp = s.row_type[r];
-    if (tp == ROW_CONTACT) continue;
     const T j = s.Jaref[r];
     const int old = s.row_state[r];
     if (tp == ROW_EQ || j < 0) { s.force[r] = -s.D[r] * j; s.row_state[r] = ST_QUADRATIC; cost += T(0.5) * s.D[r] * j * j; }
@@ -144,11 +143,19 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
     const int ni = block_width(m, bi), nj = block_width(m, bj), ui0 = sbi == np ? np6 : 6 * sbi, uj0 = sbj == np ? np6 : 6 * sbj;
     const int cnt = sbi == sbj ? (ni * (ni + 1)) >> 1 : ni * nj, n = s.nbrow[bi];
     const unsigned char* lst = block_rows(s, bi);
-    for (int e = c.tid; e < cnt; e += c.nt) {
-      int oi, oj;
-      if (sbi == sbj) { const unsigned t = m.tri[e]; oi = t >> 8; oj = t & 255u; } else { oi = e / nj; oj = e - oi * nj; }
-      T h = 0;
-      if (sbi == sbj) h = bi == 0 ? s.Mt[tri_idx(oi, oj)] : (oi == oj ? s.Mdiag[ntd + 6 * (bi - 1) + oi] : T(0));
+    // item loop OUTSIDE, up to 4 elements per lane in registers: a row's type / state / segment pointers are decoded once per
+    // lane and item instead of once per matrix element (same summation order per element, so the same bits)
+    constexpr int EPL = 4;
+    for (int e0 = 0; e0 < cnt; e0 += EPL * c.nt) {
+      int oi[EPL], oj[EPL]; T h[EPL]; bool on[EPL];
+#pragma unroll
+      for (int k = 0; k < EPL; k++) {
+        const int e = e0 + k * c.nt + c.tid; on[k] = e < cnt; oi[k] = 0; oj[k] = 0; h[k] = 0;
+        if (on[k]) {
+          if (sbi == sbj) { const unsigned t = m.tri[e]; oi[k] = t >> 8; oj[k] = t & 255u; } else { oi[k] = e / nj; oj[k] = e - oi[k] * nj; }
+          if (sbi == sbj) h[k] = bi == 0 ? s.Mt[tri_idx(oi[k], oj[k])] : (oi[k] == oj[k] ? s.Mdiag[ntd + 6 * (bi - 1) + oi[k]] : T(0));
+        }
+      }
       for (int q = 0; q < n; q++) {
         const int r = lst[q], tp = s.row_type[r];
         const T* sj = bi == bj ? nullptr : row_seg(m, s, r, bj);
@@ -159,20 +166,31 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
         if (C && tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
           if (s.row_state[r] != ST_SATISFIED) {
             const T* W = s.w6 + s.row_id[r] * W6_STRIDE;
-            for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi]; if (ai != 0) for (int b = 0; b < 6; b++) h += W[tri6<T>(a, b)] * ai * sj[b * w + oj]; }
+#pragma unroll
+            for (int k = 0; k < EPL; k++) if (on[k])
+              for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi[k]]; if (ai != 0) for (int b = 0; b < 6; b++) h[k] += W[tri6<T>(a, b)] * ai * sj[b * w + oj[k]]; }
           }
         } else if (tp == ROW_CONTACT) {
           if (s.row_state[r] != ST_SATISFIED) {
             const T* W = s.cW[s.row_id[r]];
-            const T a0 = si[oi], a1 = si[w + oi], a2 = si[2 * w + oi], b0 = sj[oj], b1 = sj[w + oj], b2 = sj[2 * w + oj];
-            h += W[0] * a0 * b0 + W[1] * a1 * b1 + W[2] * a2 * b2 + W[3] * (a0 * b1 + a1 * b0) + W[4] * (a0 * b2 + a2 * b0) + W[5] * (a1 * b2 + a2 * b1);
+            const T W0 = W[0], W1 = W[1], W2 = W[2], W3 = W[3], W4 = W[4], W5 = W[5];
+#pragma unroll
+            for (int k = 0; k < EPL; k++) if (on[k]) {
+              const T a0 = si[oi[k]], a1 = si[w + oi[k]], a2 = si[2 * w + oi[k]], b0 = sj[oj[k]], b1 = sj[w + oj[k]], b2 = sj[2 * w + oj[k]];
+              h[k] += W0 * a0 * b0 + W1 * a1 * b1 + W2 * a2 * b2 + W3 * (a0 * b1 + a1 * b0) + W4 * (a0 * b2 + a2 * b0) + W5 * (a1 * b2 + a2 * b1);
+            }
           }
         } else {
           const int nr = (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1;
-          for (int k = 0; k < nr; k++) if (s.row_state[r + k] == ST_QUADRATIC) h += s.D[r + k] * si[k * w + oi] * sj[k * w + oj];
+          for (int kk = 0; kk < nr; kk++) if (s.row_state[r + kk] == ST_QUADRATIC) {
+            const T D = s.D[r + kk];
+#pragma unroll
+            for (int k = 0; k < EPL; k++) if (on[k]) h[k] += D * si[kk * w + oi[k]] * sj[kk * w + oj[k]];
+          }
         }
       }
-      s.H[tri_idx(ui0 + oi, uj0 + oj)] = h;
+#pragma unroll
+      for (int k = 0; k < EPL; k++) if (on[k]) s.H[tri_idx(ui0 + oi[k], uj0 + oj[k])] = h[k];
     }
   }
 }
@@ -180,9 +198,8 @@ template <typename T> struct LsPt { T alpha, cost, d1, d2; };
 template <typename T, bool C>
 B2P_HDN LsPt<T> ls_eval(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, T a, const T* qg) {
   T q0 = 0, q1 = 0, q2 = 0, ec = 0, e1 = 0, e2 = 0;
-  for (int r = c.tid; r < s.nefc; r += c.nt) {
+  for (int r = c.tid; r < s.nrow_nc; r += c.nt) {
     const int tp = s.row_type[r];
-    if (tp == ROW_CONTACT) continue;
     const T D = s.D[r], j0 = s.Jaref[r], jv = s.Jv[r];
     if (tp == ROW_EQ || j0 + a * jv < 0) { q0 += T(0.5) * D * j0 * j0; q1 += D * j0 * jv; q2 += T(0.5) * D * jv * jv; }
   }

@@ -151,10 +151,17 @@ def generate(num_envs: int = 1024, episodes_per_env: int = 1, cfg: Optional[dict
                          dtype=torch.float64, device=env.device)
     wall_t = distlib.max_over_ranks(torch.tensor([wall], dtype=torch.float64, device=env.device))
     distlib.reduce_stats(stats)
+    torch.cuda.synchronize(env.device)
+    tg0 = time.perf_counter()
     gathered = {k: distlib.gather_demos(v.to(torch.uint8) if v.dtype == torch.bool else v) for k, v in local.items()}
+    torch.cuda.synchronize(env.device)
+    gather_s = distlib.max_over_ranks(torch.tensor([time.perf_counter() - tg0], dtype=torch.float64, device=env.device)).item()
+    nbytes = torch.tensor([float(sum(v.numel() * v.element_size() for v in local.values()))], dtype=torch.float64, device=env.device)
+    distlib.reduce_stats(nbytes)                           # bytes of demonstration records over all ranks (what rank 0 ends up holding)
     s = stats.tolist()
     stat = {"episodes": s[0], "successes": s[1], "pick_place_rounds": s[2], "failed": s[3], "physics_env_steps_last_episode": s[4], "kernel_launches": s[5],
-            "wall_s": wall_t.item(), "world_size": world, "envs_per_gpu": num_envs,
+            "wall_s": wall_t.item(), "world_size": world, "envs_per_gpu": num_envs, "episodes_per_s": s[0] / max(wall_t.item(), 1e-9),
+            "gather_s": gather_s, "gathered_bytes": nbytes.item(), "frames_rendered": bool(render),
             "flagged_episodes": {k: s[6 + i] for i, k in enumerate(env.physics.STATUS_FLAGS)}}
     env.close()
     return (gathered if rank == 0 else None), stat

@@ -38,7 +38,7 @@ static Emu<T>* make(const void* blob, size_t n) {
   for (size_t v = 0; v < e->nbr_span.size(); v++) { e->nbr_span[v].adr = e->ht.mesh_nbradr[v]; e->nbr_span[v].num = e->ht.mesh_nbrnum[v]; }
   e->g.nbr_pt = e->nbr_pt.data(); e->g.nbr_span = e->nbr_span.data();
   e->g.pair_g1 = e->g1.data(); e->g.pair_g2 = e->g2.data(); e->g.pair_param = e->pp.data();
-  e->jovf.assign(Pool<T>::JP, T(0)); e->g.jovf = e->jovf.data();
+  e->jovf.assign(Pool<T>::JP + 16, T(0)); e->g.jovf = e->jovf.data();
   e->xpool.assign(Pool<T>::JP, T(0)); e->g.xpool = e->xpool.data();
   e->geom_raw.resize(e->ht.geom_raw.size());
   for (size_t i = 0; i < e->geom_raw.size(); i++) {
