@@ -3,6 +3,12 @@
 #ifndef B2P_BB_SMEM
 #define B2P_BB_SMEM 1
 #endif
+#ifndef B2P_BB_SMEM_F32
+#define B2P_BB_SMEM_F32 1
+#endif
+#ifndef B2P_RAW_SMEM
+#define B2P_RAW_SMEM 0
+#endif
 #ifndef B2P_BP_PREFETCH
 #define B2P_BP_PREFETCH 1
 #endif
@@ -565,16 +571,16 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
     s.grbound[q] = p >= 0 ? ((C && s.ptype[p] == B2P_GEOM_SPHERE) ? s.psize[p][0] : norm3(s.phalf[p])) : m.geom_rbound[q];
   }
   bsync(c);
-  // Pass 1 over the static pair table (global memory; the next round's entries are fetched while this round is tested): bounding
-  // spheres / plane distance only -- a handful of instructions per pair, every lane busy -- compacted into s.cand by ballot.
+  // Pass 1 over the static pair table (a packed copy in the model constants, i.e. shared memory: no global loads in this pass):
+  // bounding spheres / plane distance only -- a handful of instructions per pair, every lane busy -- compacted into s.cand by ballot.
   int base = 0;
-  int ng1 = 0, ng2 = 0; T nmd = 0;
-  if (c.tid < m.npair) { ng1 = g.pair_g1[c.tid]; ng2 = g.pair_g2[c.tid]; const PairParam<T>& pp = g.pair_param[c.tid]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
   for (int p0 = 0; p0 < m.npair; p0 += c.nt) {
     const int p = p0 + c.tid; bool flag = false;
-    if (!B2P_BP_PREFETCH && p < m.npair) { ng1 = g.pair_g1[p]; ng2 = g.pair_g2[p]; const PairParam<T>& pp = g.pair_param[p]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
-    const int g1 = ng1, g2 = ng2; const T md = nmd;
-    if (B2P_BP_PREFETCH && p + c.nt < m.npair) { const int pn = p + c.nt; ng1 = g.pair_g1[pn]; ng2 = g.pair_g2[pn]; const PairParam<T>& pp = g.pair_param[pn]; nmd = full_contacts ? pp.margin : pp.margin - pp.gap; }
+    const unsigned pk = p < m.npair ? m.pair_pk[p] : 0u;
+    const int g1 = pk & 255u, g2 = pk >> 8;
+    // detection distance from the geoms' own margins (the pair's mixed value is max(margin) - max(gap), App. B item 10)
+    const T mg1 = m.geom_margin[g1], mg2 = m.geom_margin[g2], gp1 = m.geom_gap[g1], gp2 = m.geom_gap[g2];
+    const T md = (mg1 > mg2 ? mg1 : mg2) - (full_contacts ? T(0) : (gp1 > gp2 ? gp1 : gp2));
     if (p < m.npair) {
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
       if (!((pr1 >= 0 && !s.pactive[pr1]) || (pr2 >= 0 && !s.pactive[pr2]))) {
@@ -635,14 +641,18 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
   const T tol = m.ccd_tolerance > 16 * Num<T>::eps() ? m.ccd_tolerance : 16 * Num<T>::eps();
   int cbase = 0;
   for (int c0 = 0; c0 < ncand; c0 += c.nt) {
-    const int ci = c0 + c.tid; int n = 0; RawCon<T> raw; int p = -1; T md = 0; T wit[5]; wit[4] = 0;
-    // lanes that will run box_box borrow clip scratch from the FK / RNE sweep buffers (crb, cvel, cacc, cfrc), which are dead
-    // once dynamics_terms has run: slot = rank among this round's box-box lanes, while slots last
+    const int ci = c0 + c.tid; int n = 0; RawCon<T> raw_local; int p = -1; T md = 0; T wit[5]; wit[4] = 0;
+    // lanes that will run box_box borrow their clip polygons from the FK / RNE sweep buffers (crb, cvel, cacc, cfrc), which are dead
+    // once dynamics_terms has run: slot = rank among this round's box-box lanes, while slots last.  The polygons are dynamically
+    // indexed arrays, i.e. local memory otherwise.  Same-box A/B on B200 (tools/gpu_ab.sh, c3, 12 scenes per SM): local 8.06 M, lent
+    // 8.27 M env-steps/s; lending the raw contact record as well (B2P_RAW_SMEM) 8.20 M -- it turns every access to it into a generic load.
     int bb_flag = 0;
     if (ci < ncand) { const int pq = s.cand[ci]; bb_flag = s.gtype[g.pair_g1[pq]] == B2P_GEOM_BOX && s.gtype[g.pair_g2[pq]] == B2P_GEOM_BOX; }
-    int bb_tot; const int bb_slot = block_scan(c, bb_flag, bb_tot);
-    // (measured on B200: +4 % in fp64, where the local arrays are twice as large; -8 % in fp32, so fp32 keeps its local arrays)
-    T* clip = (B2P_BB_SMEM && sizeof(T) == 8 && bb_flag && bb_slot < (MAXTB * 28) / BB_CLIP_REALS) ? &s.crb[0][0] + bb_slot * BB_CLIP_REALS : nullptr;
+    int bb_tot; const int bb_slot = block_rank(c, bb_flag != 0, bb_tot);
+    constexpr int RAW_REALS = (int)((sizeof(RawCon<T>) + sizeof(T) - 1) / sizeof(T)), SLOT_REALS = BB_CLIP_REALS + RAW_REALS;
+    const bool lend = B2P_BB_SMEM && (sizeof(T) == 8 || B2P_BB_SMEM_F32) && bb_flag && bb_slot < (MAXTB * 28) / SLOT_REALS;
+    T* clip = lend ? &s.crb[0][0] + bb_slot * SLOT_REALS : nullptr;
+    RawCon<T>& raw = (B2P_RAW_SMEM && lend) ? *reinterpret_cast<RawCon<T>*>(clip + BB_CLIP_REALS) : raw_local;
     if (ci < ncand) {
       p = s.cand[ci];
       const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], t1 = s.gtype[g1], t2 = s.gtype[g2];

@@ -26,6 +26,7 @@ constexpr int MAXNQ = MAXTD + 7 * MAXP;   // 44
 constexpr int MAXG = 32;         // collidable geoms
 constexpr int MAXCON = 48;       // contacts kept per env
 constexpr int MAXCAND = 160;     // narrow-phase candidates per env
+constexpr int MAXPAIR = 448;     // geom pairs of the static pair table (386 in the 4-prop scene)
 constexpr int MAXEQ = 4;
 constexpr int MAXU = 8;
 constexpr int MAXLEVEL = 12;
@@ -44,7 +45,7 @@ constexpr int PROP_BODY0 = MAXTB;
 // (grasps, arm contacts) spill to a per-warp overflow area in global memory (L1/L2 resident): shared memory per scene is what
 // bounds the scenes in flight per SM, and the kernel is latency bound.
 #ifndef B2P_JPS_F32
-#define B2P_JPS_F32 640
+#define B2P_JPS_F32 624
 #endif
 #ifndef B2P_JPS_F64
 #define B2P_JPS_F64 576
@@ -97,6 +98,8 @@ struct alignas(16) DevModel {
   int geom_type[MAXG], geom_body[MAXG], geom_vertadr[MAXG], geom_vertnum[MAXG], geom_prop[MAXG];
   T geom_size[MAXG][3], geom_pos[MAXG][3], geom_quat[MAXG][4], geom_rbound[MAXG], geom_invweight0[MAXG][2];
   T geom_aabb_c[MAXG][3];        // centre of the geom-frame bounding box (half extents = geom_size for boxes AND meshes)
+  T geom_margin[MAXG], geom_gap[MAXG];
+  unsigned short pair_pk[MAXPAIR];   // the pair table for the first broad-phase pass, g1 | g2 << 8: in shared memory with the rest of the model, so that pass has no global loads
   // sites: 0 attachment_site, 1 pinch
   T site_pos[2][3], site_quat[2][4];
   // equality
@@ -138,6 +141,7 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   const int ntd = b.C(B2PM_C_NARM) + b.C(B2PM_C_NGRIP), ntb = nbody - nprop;
   if (nprop > MAXP || ntd > MAXTD - 1 || ntb > MAXTB || ngeom > MAXG || nv != ntd + 6 * nprop) return "model exceeds kernel maxima";
   if (b.C(B2PM_C_NEQ) > MAXEQ || b.C(B2PM_C_NU) > MAXU) return "too many equalities / actuators";
+  if (b.C(B2PM_C_NPAIR) > MAXPAIR) return "too many geom pairs";
   if ((int)b.opt[B2PM_O_CONE] != B2P_CONE_ELLIPTIC) return "only elliptic cones are implemented";
   m.nv = nv; m.nq = b.C(B2PM_C_NQ); m.ntd = ntd; m.ntb = ntb; m.nprop = nprop; m.ngeom = ngeom; m.npair = b.C(B2PM_C_NPAIR);
   m.neq = b.C(B2PM_C_NEQ); m.nu = b.C(B2PM_C_NU);
@@ -308,6 +312,8 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     for (int k = 0; k < 5; k++) r.solimp[k] = si[5 * q + k];
     r.solmix = sm[q]; r.margin = mg[q]; r.gap = gg[q];
   }
+  for (int q = 0; q < m.ngeom; q++) { m.geom_margin[q] = mg[q]; m.geom_gap[q] = gg[q]; }
+  for (int p = 0; p < m.npair; p++) m.pair_pk[p] = (unsigned short)(p1[p] | (p2[p] << 8));
   for (int p = 0; p < m.npair; p++) {
     int g1 = p1[p], g2 = p2[p]; double pp[12];
     if (prio[g1] != prio[g2]) {
@@ -343,7 +349,7 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
   CR(dof_armature); CR(dof_damping); CR(dof_invweight0); CI(jnt_limited); CR(prop_mass); CR(pclass_mass);
   for (int k = 0; k < NPCLASS; k++) { d.pclass[k].priority = s.pclass[k].priority; d.pclass[k].condim = s.pclass[k].condim; for (int q = 0; q < 3; q++) d.pclass[k].friction[q] = (T)s.pclass[k].friction[q]; for (int q = 0; q < 2; q++) d.pclass[k].solref[q] = (T)s.pclass[k].solref[q]; for (int q = 0; q < 5; q++) d.pclass[k].solimp[q] = (T)s.pclass[k].solimp[q]; d.pclass[k].solmix = (T)s.pclass[k].solmix; d.pclass[k].margin = (T)s.pclass[k].margin; d.pclass[k].gap = (T)s.pclass[k].gap; }
   CI(geom_type); CI(geom_body); CI(geom_vertadr); CI(geom_vertnum); CI(geom_prop);
-  CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(geom_aabb_c); CR(site_pos); CR(site_quat);
+  CR(geom_size); CR(geom_pos); CR(geom_quat); CR(geom_rbound); CR(geom_invweight0); CR(geom_aabb_c); CR(geom_margin); CR(geom_gap); CI(pair_pk); CR(site_pos); CR(site_quat);
   CI(eq_type); CI(eq_obj1); CI(eq_obj2); CR(eq_data); CR(eq_solref); CR(eq_solimp);
   CI(act_trnnum); CI(act_trndof); CI(act_ctrllimited); CI(act_forcelimited);
   CR(act_trncoef); CR(act_gain); CR(act_bias); CR(act_ctrlrange); CR(act_forcerange);
