@@ -9,6 +9,7 @@ import scenarios as sc
 from orc import Oracle
 
 pytestmark = pytest.mark.gpu
+PINV_F32_TOL = 5e-2
 torch = pytest.importorskip("torch")
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
@@ -36,12 +37,20 @@ def test_osc_golden_compute_control_output(dtype, tol):
     tau = osc.compute_control_output().cpu().numpy().astype(np.float64); conv = osc.is_converged().cpu().numpy()
     assert p.launches == launches + 1
     assert np.abs(p.state.cpu().numpy()[:, :15] - st[:, :15]).max() < 1e-6      # zero-tick launch: no stepping
+    worst_pinv = 0.0
     for i in range(n):
+        err = np.abs(tau[i] - g["tau"][i]).max() / max(1.0, np.abs(g["tau"][i]).max())
         if dtype == torch.float32 and not g["branch"][i]:
+            # osc.py:113-115, pinv(rcond = 1e-2) of a near-singular task-space inertia in fp32: the kept eigenvalues are >= 1e-2 of the
+            # largest, so the branch is conditioned like 1e2 x fp32 rounding; its own tolerance (measured on B200: see the printed line)
+            worst_pinv = max(worst_pinv, err)
+            assert err < PINV_F32_TOL, (i, err)
             continue
-        assert np.abs(tau[i] - g["tau"][i]).max() / max(1.0, np.abs(g["tau"][i]).max()) < tol, i
+        assert err < tol, i
         if dtype == torch.float64:
             assert bool(conv[i]) == bool(g["converged"][i])
+    if dtype == torch.float32:
+        print("fp32 pinv-branch rows: worst relative torque error %.3e over %d rows" % (worst_pinv, int((~g["branch"].astype(bool)).sum())))
     # diagnostics agree with the golden inputs
     pe = osc.current_position_error().cpu().numpy()
     assert np.abs(pe - np.linalg.norm(g["target"][:, :3] - g["xpos"], axis=1)).max() < (1e-9 if dtype == torch.float64 else 1e-5)
