@@ -57,9 +57,14 @@ def max_over_ranks(x: torch.Tensor) -> torch.Tensor:
     return x
 
 
+HOST_ABOVE_BYTES = 4 << 30      # a gathered field larger than this is assembled in rank 0's HOST memory, message by message
+
+
 def gather_demos(local: torch.Tensor, dst: int = 0) -> Optional[torch.Tensor]:
     """Concatenate per-rank demo records ``[B_rank, ...]`` (same trailing shape, any B_rank) on ``dst`` in rank order.
-    Returns the concatenation on ``dst`` and None elsewhere.  Messages are cut to <= MAX_MSG_BYTES."""
+    Returns the concatenation on ``dst`` and None elsewhere.  Messages are cut to <= MAX_MSG_BYTES.  The frames of a whole box do
+    not fit one GPU next to its own (8 x 1024 scenes x 3 rounds of 480 x 640 rgb + depth = 56 GiB on rank 0: the first 8-GPU run
+    died there), so a field above HOST_ABOVE_BYTES is copied to the host as its messages arrive and returned as a CPU tensor."""
     world = _world()
     if world == 1:
         return local
@@ -74,6 +79,7 @@ def gather_demos(local: torch.Tensor, dst: int = 0) -> Optional[torch.Tensor]:
         row *= int(d)
     rows_per_msg = max(1, MAX_MSG_BYTES // max(1, row * local.element_size()))
     nmax = max(sizes)
+    to_host = sum(sizes) * row * local.element_size() > HOST_ABOVE_BYTES
     parts: List[List[torch.Tensor]] = [[] for _ in range(world)]
     for lo in range(0, nmax, rows_per_msg):
         hi = min(nmax, lo + rows_per_msg)
@@ -87,7 +93,7 @@ def gather_demos(local: torch.Tensor, dst: int = 0) -> Optional[torch.Tensor]:
             for r in range(world):
                 kr = max(0, min(sizes[r], hi) - lo)
                 if kr > 0:
-                    parts[r].append(out[r][:kr])
+                    parts[r].append(out[r][:kr].cpu() if to_host else out[r][:kr])
     if rank != dst:
         return None
     flat = [t for r in range(world) for t in parts[r]]

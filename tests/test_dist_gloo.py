@@ -32,6 +32,10 @@ def _worker(rank, world, port, q):
     old = D.MAX_MSG_BYTES
     D.MAX_MSG_BYTES = 2 * 9 * 4          # force chunking: 2 rows per message
     got = D.gather_demos(demos, dst=0)
+    D.HOST_ABOVE_BYTES, keep = 1, D.HOST_ABOVE_BYTES          # force the host-assembly path (fields too large for rank 0's GPU)
+    got_host = D.gather_demos(demos, dst=0)
+    D.HOST_ABOVE_BYTES = keep
+    assert (got is None) == (got_host is None) and (got is None or (got_host.device.type == "cpu" and bool((got_host == got.cpu()).all())))
     D.MAX_MSG_BYTES = old
     empty = D.gather_demos(demos[:0] if rank == 1 else demos[:1], dst=0)
     q.put((rank, lo, hi, stats.tolist(), t.item(), None if got is None else got[:, 0].tolist(), None if empty is None else empty[:, 0].tolist()))
