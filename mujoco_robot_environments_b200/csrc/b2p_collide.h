@@ -35,7 +35,7 @@ template <typename T> B2P_HD int start_slot(const T* d) {
   return ((d[0] > T(0.4)) - (d[0] < T(-0.4)) + 1) * 9 + ((d[1] > T(0.4)) - (d[1] < T(-0.4)) + 1) * 3 + ((d[2] > T(0.4)) - (d[2] < T(-0.4)) + 1);
 }
 #ifdef B2P_HOST_COUNTERS
-static long g_support_calls = 0, g_climb_steps = 0, g_mpr_calls = 0, g_cand = 0, g_bb_calls = 0, g_steps = 0, g_pair_mpr[1024] = {0};
+static long g_support_calls = 0, g_climb_steps = 0, g_mpr_calls = 0, g_cand = 0, g_bb_calls = 0, g_steps = 0, g_pair_mpr[1024] = {0}, g_newton_iters = 0, g_newton_solves = 0;
 #endif
 template <typename T>
 B2P_HDN void support(CObj<T>& o, const Globals<T>& g, const T* dir, T* res) {

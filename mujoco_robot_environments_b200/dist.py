@@ -81,6 +81,14 @@ def gather_demos(local: torch.Tensor, dst: int = 0) -> Optional[torch.Tensor]:
     nmax = max(sizes)
     to_host = sum(sizes) * row * local.element_size() > HOST_ABOVE_BYTES
     parts: List[List[torch.Tensor]] = [[] for _ in range(world)]
+    host, starts = None, [0] * world
+    if to_host and rank == dst:      # one pinned buffer for the whole field: message parts land in it with asynchronous copies
+        for r in range(1, world):
+            starts[r] = starts[r - 1] + sizes[r - 1]
+        try:
+            host = torch.empty((sum(sizes),) + tuple(local.shape[1:]), dtype=local.dtype, pin_memory=local.is_cuda)
+        except RuntimeError:
+            host = torch.empty((sum(sizes),) + tuple(local.shape[1:]), dtype=local.dtype)
     for lo in range(0, nmax, rows_per_msg):
         hi = min(nmax, lo + rows_per_msg)
         buf = torch.zeros((hi - lo,) + tuple(local.shape[1:]), device=local.device, dtype=local.dtype)
@@ -92,9 +100,15 @@ def gather_demos(local: torch.Tensor, dst: int = 0) -> Optional[torch.Tensor]:
         if rank == dst:
             for r in range(world):
                 kr = max(0, min(sizes[r], hi) - lo)
-                if kr > 0:
-                    parts[r].append(out[r][:kr].cpu() if to_host else out[r][:kr])
+                if kr > 0 and to_host:
+                    host[starts[r] + lo:starts[r] + lo + kr].copy_(out[r][:kr], non_blocking=True)
+                elif kr > 0:
+                    parts[r].append(out[r][:kr])
+            if to_host and local.is_cuda:
+                torch.cuda.current_stream(local.device).synchronize()     # the message buffers are reused by the next round
     if rank != dst:
         return None
+    if to_host:
+        return host
     flat = [t for r in range(world) for t in parts[r]]
     return torch.cat(flat, 0) if flat else local[:0]

@@ -95,6 +95,13 @@ int emu_model_bytes(int dtype) { return dtype == 0 ? (int)sizeof(DevModel<double
 void emu_destroy(void* h, int dtype) { if (dtype == 0) { auto* e = (Emu<double>*)h; delete e->s; delete e->sc; delete e; } else { auto* e = (Emu<float>*)h; delete e->s; delete e->sc; delete e; } }
 }
 // narrow-phase census of a run (tools/narrow_census.py; built with -DB2P_HOST_COUNTERS): support calls, hill-climb steps, MPR queries
+extern "C" void emu_newton(long* out) {
+#ifdef B2P_HOST_COUNTERS
+  out[0] = b2p::g_newton_iters; out[1] = b2p::g_newton_solves; b2p::g_newton_iters = b2p::g_newton_solves = 0;
+#else
+  out[0] = out[1] = -1;
+#endif
+}
 extern "C" void emu_pair_mpr(long* out) {
 #ifdef B2P_HOST_COUNTERS
   for (int i = 0; i < 1024; i++) { out[i] = b2p::g_pair_mpr[i]; b2p::g_pair_mpr[i] = 0; }

@@ -9,7 +9,7 @@ import scenarios as sc
 from orc import Oracle
 
 pytestmark = pytest.mark.gpu
-PINV_F32_TOL = 5e-2
+PINV_F32_TOL = 1e-4          # measured on B200: 4.6e-6 over the 18 pinv-branch rows of the golden file
 torch = pytest.importorskip("torch")
 GOLD = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
 
