@@ -19,38 +19,55 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c)
     normquat(q + 3); cp3(s.ppos[p], q); quat2mat(s.pmat[p], q + 3);
   }
   bsync(c);
-  // The tree is deep and narrow (the arm is a chain), so a level holds one or two bodies and a level-by-level pass is a serial
-  // chain run by one or two lanes.  Only what truly depends on the parent goes through such passes (A: pose, C: velocity /
-  // acceleration); the per-body inertia and force terms (B, D) run with one lane per body.
-  // Everything about a joint that does not depend on the parent's pose is done ahead of the serial pass, one lane per joint: the
-  // rotation of the body relative to its parent, q_rel = tb_quat * (cos a/2, sin a/2 axis)  (parked in cfrc, which pass D rewrites).
-  // The joint's anchor and axis in the parent frame are model constants (tb_anchor, tb_axis).
-  for (int d = c.tid; d < m.ntd; d += c.nt) {
+  // The tree is deep and narrow (the arm is a chain of 7, the gripper adds 3 more levels), so level-by-level passes are serial chains
+  // run by one or two lanes.  A: the poses come from POINTER JUMPING instead -- every body first gets its transform relative to its
+  // parent (one lane per body: nothing there depends on the parent's pose), then ceil(log2(depth)) rounds compose
+  // T_b <- T_ptr(b) o T_b, ptr(b) <- ptr(ptr(b)) for all bodies at once: 4 rounds instead of 10 levels.  (Quaternions are normalised
+  // once at the end instead of at every body: a difference of rounding order, ~1 ulp.)  C: the velocity / acceleration recursion
+  // stays level by level (six-vectors, cheap).  B, D: inertia and force terms, one lane per body.
+  for (int b = 1 + c.tid; b < m.ntb; b += c.nt) {
+    const int d = b - 1;
     const T ha = T(0.5) * (s.qpos[d] - m.qpos0[d]), sn = sin(ha);
     const T qloc[4] = {cos(ha), sn * m.jnt_axis[d][0], sn * m.jnt_axis[d][1], sn * m.jnt_axis[d][2]};
-    mulquat(s.cfrc[d + 1], m.tb_quat[d + 1], qloc);
+    T q[4], rj[3];
+    mulquat(q, m.tb_quat[b], qloc);                       // body frame relative to the parent frame
+    rotquat(rj, q, m.jnt_pos[d]);
+    for (int k = 0; k < 4; k++) s.xquat[b][k] = q[k];
+    for (int k = 0; k < 3; k++) s.xpos[b][k] = m.tb_anchor[b][k] - rj[k];    // the joint anchor stays put: origin = anchor - R jnt_pos
+    s.fkptr[b] = (unsigned char)m.tb_parent[b];
+  }
+  if (c.tid == 0) s.fkptr[0] = 0;
+  bsync(c);
+  for (int round = 0; round < m.fk_rounds; round++) {
+    for (int b0 = 1; b0 < m.ntb; b0 += c.nt) {
+      const int b = b0 + c.tid; const bool on = b < m.ntb;
+      T q[4] = {1, 0, 0, 0}, t[3] = {0, 0, 0}; int pp = 0;
+      if (on) {
+        const int a = s.fkptr[b]; T rt[3];
+        mulquat(q, s.xquat[a], s.xquat[b]);
+        rotquat(rt, s.xquat[a], s.xpos[b]);
+        for (int k = 0; k < 3; k++) t[k] = s.xpos[a][k] + rt[k];
+        pp = s.fkptr[a];
+      }
+      bsync(c);                                           // every lane has read its ancestor's (transform, pointer) pair
+      if (on) { for (int k = 0; k < 4; k++) s.xquat[b][k] = q[k]; for (int k = 0; k < 3; k++) s.xpos[b][k] = t[k]; s.fkptr[b] = (unsigned char)pp; }
+      bsync(c);
+    }
+  }
+  for (int b = 1 + c.tid; b < m.ntb; b += c.nt) { normquat(s.xquat[b]); quat2mat(s.xmat[b], s.xquat[b]); }
+  bsync(c);
+  for (int b = 1 + c.tid; b < m.ntb; b += c.nt) {       // joint anchor / axis in the world -> cdof (motion axis about the fixed reference point)
+    const int p = m.tb_parent[b], d = b - 1;
+    T xanchor[3], xaxis[3], off[3];
+    mulmv(xanchor, s.xmat[p], m.tb_anchor[b]);
+    for (int k = 0; k < 3; k++) xanchor[k] += s.xpos[p][k];
+    mulmv(xaxis, s.xmat[p], m.tb_axis[b]);
+    T* cd = s.cdof[d];
+    cp3(cd, xaxis);
+    for (int k = 0; k < 3; k++) off[k] = m.ref[k] - xanchor[k];
+    cross3(cd + 3, xaxis, off);
   }
   bsync(c);
-  for (int l = 0; l < m.nlevel; l++) {     // A: pose of every tree body, joint anchor / axis -> cdof
-    for (int idx = m.level_start[l] + c.tid; idx < m.level_start[l + 1]; idx += c.nt) {
-      const int b = m.level_body[idx], p = m.tb_parent[b], d = b - 1;
-      T quat[4], mat[9], xanchor[3], xaxis[3], a[3];
-      mulmv(xanchor, s.xmat[p], m.tb_anchor[b]);
-      for (int k = 0; k < 3; k++) xanchor[k] += s.xpos[p][k];
-      mulmv(xaxis, s.xmat[p], m.tb_axis[b]);
-      mulquat(quat, s.xquat[p], s.cfrc[b]); normquat(quat);
-      quat2mat(mat, quat);
-      mulmv(a, mat, m.jnt_pos[d]);
-      for (int k = 0; k < 3; k++) s.xpos[b][k] = xanchor[k] - a[k];
-      for (int k = 0; k < 4; k++) s.xquat[b][k] = quat[k];
-      for (int k = 0; k < 9; k++) s.xmat[b][k] = mat[k];
-      T* cd = s.cdof[d]; T off[3];                       // motion axis about the fixed reference point
-      cp3(cd, xaxis);
-      for (int k = 0; k < 3; k++) off[k] = m.ref[k] - xanchor[k];
-      cross3(cd + 3, xaxis, off);
-    }
-    bsync(c);
-  }
   for (int b = 1 + c.tid; b < m.ntb; b += c.nt) {   // B: inertia about the fixed reference point
     T xipos[3], qi[4], ximat[9], off[3];
     mulmv(xipos, s.xmat[b], m.tb_ipos[b]);

@@ -178,6 +178,12 @@ template <typename T> B2P_HD void mulquat(T* r, const T* a, const T* b) {
   T y = a[0] * b[2] - a[1] * b[3] + a[2] * b[0] + a[3] * b[1], z = a[0] * b[3] + a[1] * b[2] - a[2] * b[1] + a[3] * b[0];
   r[0] = w; r[1] = x; r[2] = y; r[3] = z;
 }
+// v rotated by the unit quaternion q: v + 2 w (u x v) + 2 u x (u x v)
+template <typename T> B2P_HD void rotquat(T* r, const T* q, const T* v) {
+  T uv[3], uuv[3];
+  cross3(uv, q + 1, v); cross3(uuv, q + 1, uv);
+  for (int k = 0; k < 3; k++) r[k] = v[k] + 2 * (q[0] * uv[k] + uuv[k]);
+}
 template <typename T> B2P_HD void normquat(T* q) {
   T n = sqrt(q[0] * q[0] + q[1] * q[1] + q[2] * q[2] + q[3] * q[3]);
   if (n < Num<T>::minval()) { q[0] = 1; q[1] = q[2] = q[3] = 0; } else { T i = 1 / n; q[0] *= i; q[1] *= i; q[2] *= i; q[3] *= i; }

@@ -79,7 +79,7 @@ constexpr int NPCLASS = 2;       // re-classable prop colliders beyond the box: 
 template <typename T>
 struct alignas(16) DevModel {
   int nv, nq, ntd, ntb, nprop, ngeom, npair, neq, nu, nlevel;
-  int iterations, ls_iterations, integrator, ccd_iterations, site_body[2], pad_[2];
+  int iterations, ls_iterations, integrator, ccd_iterations, site_body[2], fk_rounds, pad_[1];   // fk_rounds = ceil(log2(tree depth))
   T timestep, gravity[3], impratio, tolerance, ls_tolerance, ccd_tolerance, meaninertia, ref[3];
   // tree
   int tb_parent[MAXTB], level_start[MAXLEVEL + 1], level_body[MAXTB], child_start[MAXTB + 1], child_list[MAXTB];
@@ -173,6 +173,7 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   }
   if (maxd > MAXLEVEL) return "tree too deep";
   m.nlevel = maxd; int k = 0;
+  m.fk_rounds = 0; while ((1 << m.fk_rounds) < maxd) m.fk_rounds++;
   for (int l = 1; l <= maxd; l++) { m.level_start[l - 1] = k; for (int i = 1; i < ntb; i++) if (depth[i] == l) m.level_body[k++] = i; }
   m.level_start[maxd] = k; k = 0;
   for (int i = 0; i < ntb; i++) { m.child_start[i] = k; for (int c = 1; c < ntb; c++) if (par[c] == i) m.child_list[k++] = c; }
@@ -341,7 +342,7 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
 #define CI(f) std::memcpy(&d.f, &s.f, sizeof d.f)
 #define CR(f) do { const double* a = (const double*)&s.f; T* o = (T*)&d.f; for (size_t i = 0; i < sizeof(s.f) / sizeof(double); i++) o[i] = (T)a[i]; } while (0)
   CI(nv); CI(nq); CI(ntd); CI(ntb); CI(nprop); CI(ngeom); CI(npair); CI(neq); CI(nu); CI(nlevel);
-  CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body);
+  CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body); CI(fk_rounds);
   CR(timestep); CR(gravity); CR(impratio); CR(tolerance); CR(ls_tolerance); CR(ccd_tolerance); CR(meaninertia); CR(ref);
   CI(tb_parent); CI(level_start); CI(level_body); CI(child_start); CI(child_list); CI(anc_mask);
   CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0); CR(tb_anchor); CR(tb_axis);

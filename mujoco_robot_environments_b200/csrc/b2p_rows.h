@@ -90,7 +90,16 @@ template <typename T, bool C> B2P_HD T row_vel(const DevModel<T>& m, const Scrat
 // (3 rows x 2 tree bodies each) the critical path of the whole stage.
 template <typename T, bool C>
 B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const Ctx& c) {
-  const int nlim = 2 * m.ntd, nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
+  // joint-limit sides that are inside their margin (rarely more than one of the 30): found up front, so that the item list below is
+  // equalities + ACTIVE limit sides + contacts and usually fits one round of 32 lanes
+  unsigned limmask = 0;
+  for (int i = c.tid; i < 2 * m.ntd; i += c.nt) {
+    const int j = i >> 1, side = (i & 1) ? 1 : -1;
+    if (m.jnt_limited[j] && side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]) < m.jnt_margin[j]) limmask |= 1u << i;
+  }
+  limmask = block_or(c, limmask);
+  int nlim = 0; for (unsigned t = limmask; t; t &= t - 1) nlim++;
+  const int nitem = m.neq + nlim + s.ncon, nblk = m.nprop + 1;
   int base = 0, jbase = 0, first_drop = Pool<T>::EFC + 1; unsigned pairs = 0;
   int nb[SP_MAXBLK];
   for (int b = 0; b < SP_MAXBLK; b++) nb[b] = 0;
@@ -99,8 +108,9 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
     if (it < nitem) {
       if (it < m.neq) { kind = ROW_EQ; id = it; nr = m.eq_type[it] == B2P_EQ_CONNECT ? 3 : 1; }
       else if (it < m.neq + nlim) {
-        const int j = (it - m.neq) >> 1, side = ((it - m.neq) & 1) ? 1 : -1;
-        if (m.jnt_limited[j]) { const T dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]); if (dist < m.jnt_margin[j]) { kind = ROW_LIMIT; id = j * 2 + (side > 0); nr = 1; } }
+        unsigned t = limmask; for (int k = it - m.neq; k > 0; k--) t &= t - 1;      // the (it - neq)-th set bit, ascending: MuJoCo's order
+        int i = 0; while (!((t >> i) & 1u)) i++;
+        kind = ROW_LIMIT; id = (i >> 1) * 2 + (i & 1); nr = 1;
       } else {
         id = it - m.neq - nlim;
         if (s.c_dist[id] < s.c_incl[id]) {

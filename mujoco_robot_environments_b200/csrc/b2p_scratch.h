@@ -41,7 +41,7 @@ struct alignas(16) Scratch {
   // tree (spatial quantities about the fixed reference point m.ref)
   T xpos[MAXTB][3], xmat[MAXTB][9], cdof[MAXTD][6];
   T ppos[MAXP][3], pmat[MAXP][9];
-  T site_xpos[2][3], site_xmat[2][9];
+  T site_xpos[2][3], site_xmat[2][9]; unsigned char fkptr[MAXTB];   // fkptr: ancestor pointer of the pointer-jumping kinematics pass
   // dynamics: tree mass matrix (packed lower triangle; OSC, M*x) + its packed Cholesky factor; props diagonal
   T Mt[MPACK], Larm[MPACK], Mdiag[MAXNV];
   T qfrc_bias[MAXNV], qfrc_passive[MAXNV], qfrc_act[MAXNV], qfrc_smooth[MAXNV], qacc_smooth[MAXNV], qacc[MAXNV], qfrc_con[MAXNV];

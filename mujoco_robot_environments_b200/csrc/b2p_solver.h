@@ -12,7 +12,17 @@ namespace b2p {
 template <typename T, bool C>
 B2P_HD void mul_M(const DevModel<T>& m, const Scratch<T, C>& s, T* r, const T* v, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) {
-    if (d < m.ntd) { T a = 0; for (int j = 0; j < m.ntd; j++) a += s.Mt[j <= d ? tri_idx(d, j) : tri_idx(j, d)] * v[j]; r[d] = a; }
+    if (d < m.ntd) {   // fixed trip count and four partial sums (the packed triangle is padded to MAXTD rows; slots past ntd multiply zeros of v's padding away)
+      T a0 = 0, a1 = 0, a2 = 0, a3 = 0; const int ntd = m.ntd;
+#pragma unroll
+      for (int j = 0; j < MAXTD; j += 4) {
+        a0 += (j < ntd ? s.Mt[j <= d ? tri_idx(d, j) : tri_idx(j, d)] * v[j] : T(0));
+        a1 += (j + 1 < ntd ? s.Mt[j + 1 <= d ? tri_idx(d, j + 1) : tri_idx(j + 1, d)] * v[j + 1] : T(0));
+        a2 += (j + 2 < ntd ? s.Mt[j + 2 <= d ? tri_idx(d, j + 2) : tri_idx(j + 2, d)] * v[j + 2] : T(0));
+        a3 += (j + 3 < ntd ? s.Mt[j + 3 <= d ? tri_idx(d, j + 3) : tri_idx(j + 3, d)] * v[j + 3] : T(0));
+      }
+      r[d] = (a0 + a1) + (a2 + a3);
+    }
     else r[d] = s.Mdiag[d] * v[d];
   }
 }
@@ -137,18 +147,72 @@ B2P_HDN void mul_JT_force(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) 
   }
 }
 // H = M + J' W J on the packed lower triangle in solver order (props first, tree last), only inside the block
-// structure s.sp: one lane per matrix element, walking the item list of the element's row block.
+// structure s.sp.  A lane keeps up to EPL matrix elements of ONE block pair in registers and walks the row block's items once: a row's
+// type / state / segment pointers are decoded once per lane and item, not once per element (same summation order per element).
+template <typename T, bool C, int EPL>
+B2P_HD void accum_items(const DevModel<T>& m, const Scratch<T, C>& s, int bi, int bj, const unsigned char* lst, int n, const int* oi, const int* oj, const bool* on, T* h) {
+  for (int q = 0; q < n; q++) {
+    const int r = lst[q], tp = s.row_type[r];
+    const T* sj = bi == bj ? nullptr : row_seg(m, s, r, bj);
+    if (bi != bj && !sj) continue;
+    const T* si = row_seg(m, s, r, bi);
+    if (bi == bj) sj = si;
+    const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
+    if (C && tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
+      if (s.row_state[r] != ST_SATISFIED) {
+        const T* W = s.w6 + s.row_id[r] * W6_STRIDE;
+#pragma unroll
+        for (int k = 0; k < EPL; k++) if (on[k])
+          for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi[k]]; if (ai != 0) for (int b = 0; b < 6; b++) h[k] += W[tri6<T>(a, b)] * ai * sj[b * w + oj[k]]; }
+      }
+    } else if (tp == ROW_CONTACT) {
+      if (s.row_state[r] != ST_SATISFIED) {
+        const T* W = s.cW[s.row_id[r]];
+        const T W0 = W[0], W1 = W[1], W2 = W[2], W3 = W[3], W4 = W[4], W5 = W[5];
+#pragma unroll
+        for (int k = 0; k < EPL; k++) if (on[k]) {
+          const T a0 = si[oi[k]], a1 = si[w + oi[k]], a2 = si[2 * w + oi[k]], b0 = sj[oj[k]], b1 = sj[w + oj[k]], b2 = sj[2 * w + oj[k]];
+          h[k] += W0 * a0 * b0 + W1 * a1 * b1 + W2 * a2 * b2 + W3 * (a0 * b1 + a1 * b0) + W4 * (a0 * b2 + a2 * b0) + W5 * (a1 * b2 + a2 * b1);
+        }
+      }
+    } else {
+      const int nr = (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1;
+      for (int kk = 0; kk < nr; kk++) if (s.row_state[r + kk] == ST_QUADRATIC) {
+        const T D = s.D[r + kk];
+#pragma unroll
+        for (int k = 0; k < EPL; k++) if (on[k]) h[k] += D * si[kk * w + oi[k]] * sj[kk * w + oj[k]];
+      }
+    }
+  }
+}
 template <typename T, bool C>
 B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   const int np = m.nprop, np6 = 6 * np, ntd = m.ntd;
+  // the props' diagonal 6 x 6 blocks (21 elements each) in ONE pass: 8 lanes per prop, 3 elements per lane -- instead of four passes
+  // that keep 21 lanes busy each
+  const bool merged = c.nt >= 8 * MAXP;
+  if (merged) {
+    const int p = c.tid >> 3, l8 = c.tid & 7;
+    if (p < np) {
+      const int bi = p + 1, n = s.nbrow[bi];
+      int oi[3], oj[3]; T h[3]; bool on[3];
+#pragma unroll
+      for (int k = 0; k < 3; k++) {
+        const int e = l8 + 8 * k; on[k] = e < 21; oi[k] = 0; oj[k] = 0; h[k] = 0;
+        if (on[k]) { const unsigned t = m.tri[e]; oi[k] = t >> 8; oj[k] = t & 255u; h[k] = oi[k] == oj[k] ? s.Mdiag[ntd + 6 * p + oi[k]] : T(0); }
+      }
+      accum_items<T, C, 3>(m, s, bi, bi, block_rows(s, bi), n, oi, oj, on, h);
+#pragma unroll
+      for (int k = 0; k < 3; k++) if (on[k]) s.H[tri_idx(6 * p + oi[k], 6 * p + oj[k])] = h[k];
+    }
+  }
   for (int sbi = 0; sbi <= np; sbi++) for (int sbj = 0; sbj <= sbi; sbj++) {
     if (!sp_coupled(s.sp, sbi, sbj)) continue;
+    if (merged && sbi == sbj && sbi < np) continue;
     const int bi = sbi == np ? 0 : sbi + 1, bj = sbj == np ? 0 : sbj + 1;      // dof blocks (0 = tree, 1+p = prop p)
     const int ni = block_width(m, bi), nj = block_width(m, bj), ui0 = sbi == np ? np6 : 6 * sbi, uj0 = sbj == np ? np6 : 6 * sbj;
     const int cnt = sbi == sbj ? (ni * (ni + 1)) >> 1 : ni * nj, n = s.nbrow[bi];
     const unsigned char* lst = block_rows(s, bi);
-    // item loop OUTSIDE, up to 4 elements per lane in registers: a row's type / state / segment pointers are decoded once per
-    // lane and item instead of once per matrix element (same summation order per element, so the same bits)
     constexpr int EPL = 4;
     for (int e0 = 0; e0 < cnt; e0 += EPL * c.nt) {
       int oi[EPL], oj[EPL]; T h[EPL]; bool on[EPL];
@@ -160,39 +224,7 @@ B2P_HDN void assemble_H(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
           if (sbi == sbj) h[k] = bi == 0 ? s.Mt[tri_idx(oi[k], oj[k])] : (oi[k] == oj[k] ? s.Mdiag[ntd + 6 * (bi - 1) + oi[k]] : T(0));
         }
       }
-      for (int q = 0; q < n; q++) {
-        const int r = lst[q], tp = s.row_type[r];
-        const T* sj = bi == bj ? nullptr : row_seg(m, s, r, bj);
-        if (bi != bj && !sj) continue;
-        const T* si = row_seg(m, s, r, bi);
-        if (bi == bj) sj = si;
-        const int w = block_width(m, s.row_a[r]) + (s.row_b[r] >= 0 ? 6 : 0);
-        if (C && tp == ROW_CONTACT && s.c_dim[s.row_id[r]] == 6) {
-          if (s.row_state[r] != ST_SATISFIED) {
-            const T* W = s.w6 + s.row_id[r] * W6_STRIDE;
-#pragma unroll
-            for (int k = 0; k < EPL; k++) if (on[k])
-              for (int a = 0; a < 6; a++) { const T ai = si[a * w + oi[k]]; if (ai != 0) for (int b = 0; b < 6; b++) h[k] += W[tri6<T>(a, b)] * ai * sj[b * w + oj[k]]; }
-          }
-        } else if (tp == ROW_CONTACT) {
-          if (s.row_state[r] != ST_SATISFIED) {
-            const T* W = s.cW[s.row_id[r]];
-            const T W0 = W[0], W1 = W[1], W2 = W[2], W3 = W[3], W4 = W[4], W5 = W[5];
-#pragma unroll
-            for (int k = 0; k < EPL; k++) if (on[k]) {
-              const T a0 = si[oi[k]], a1 = si[w + oi[k]], a2 = si[2 * w + oi[k]], b0 = sj[oj[k]], b1 = sj[w + oj[k]], b2 = sj[2 * w + oj[k]];
-              h[k] += W0 * a0 * b0 + W1 * a1 * b1 + W2 * a2 * b2 + W3 * (a0 * b1 + a1 * b0) + W4 * (a0 * b2 + a2 * b0) + W5 * (a1 * b2 + a2 * b1);
-            }
-          }
-        } else {
-          const int nr = (tp == ROW_EQ && m.eq_type[s.row_id[r]] == B2P_EQ_CONNECT) ? 3 : 1;
-          for (int kk = 0; kk < nr; kk++) if (s.row_state[r + kk] == ST_QUADRATIC) {
-            const T D = s.D[r + kk];
-#pragma unroll
-            for (int k = 0; k < EPL; k++) if (on[k]) h[k] += D * si[kk * w + oi[k]] * sj[kk * w + oj[k]];
-          }
-        }
-      }
+      accum_items<T, C, EPL>(m, s, bi, bj, lst, n, oi, oj, on, h);
 #pragma unroll
       for (int k = 0; k < EPL; k++) if (on[k]) s.H[tri_idx(ui0 + oi[k], uj0 + oj[k])] = h[k];
     }

@@ -242,7 +242,9 @@ def test_tuner_circle_and_pick_place_stages():
     R = env.physics.data.geom_xmat[:, env.physics.model.prop_geomid[0]]
     yaw = torch.atan2(R[:, 3], R[:, 0])
     want = mat2quat(euler_xyz_matrix(torch.zeros_like(yaw), torch.zeros_like(yaw) + np.pi, yaw)).to(pick.dtype)
-    assert float((pick[:, 3:] - want).abs().max()) < 1e-5 and float(yaw.abs().max()) > 0.3
+    flat = torch.hypot(R[:, 0], R[:, 3]) > 0.1      # a cube left on its side has R00 ~ R10 ~ 0: atan2 of rounding noise, not a yaw
+    assert int(flat.sum()) >= 24
+    assert float((pick[:, 3:] - want)[flat].abs().max()) < 1e-5 and float(yaw[flat].abs().max()) > 0.3
     assert bool((pick[:, 3:] - place[:, 3:]).abs().max() == 0)
     hist = t.run(generations=2, method="pick_place")
     assert len(hist) == 2 and np.isfinite(hist[-1]["best_fitness"])
