@@ -125,7 +125,7 @@ int b2p_status_set(b2p_handle h, const int32_t* flags, void* stream);
 
 /* developer aid: per-stage cycle counters summed over scenes, [B2P_PROF_N] entries; all zero unless the library was built
  * with -DB2P_PROF (the product build has no counters in the kernel).  Synchronises the device. */
-enum { B2P_PROF_N = 20 };
+enum { B2P_PROF_N = 24 };
 int b2p_prof_read(b2p_handle h, unsigned long long* out, int reset);
 
 /* micro-benchmark: register-resident FMA chain, returns TFLOP/s of the handle-independent device (dtype 0/1) */

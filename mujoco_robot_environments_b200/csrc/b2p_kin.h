@@ -175,18 +175,18 @@ template <typename T, bool C>
 B2P_HDN void actuation_and_smooth(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   for (int d = c.tid; d < m.nv; d += c.nt) s.qfrc_act[d] = 0;
   bsync(c);
-  if (c.tid == 0) {
-    for (int a = 0; a < m.nu; a++) {
-      T len = 0, vel = 0;
-      for (int k = 0; k < m.act_trnnum[a]; k++) { const int d = m.act_trndof[a][k]; len += m.act_trncoef[a][k] * s.qpos[d]; vel += m.act_trncoef[a][k] * s.qvel[d]; }
-      T u = s.ctrl[a];
-      if (m.act_ctrllimited[a]) u = clampT(u, m.act_ctrlrange[a][0], m.act_ctrlrange[a][1]);
-      T f = m.act_gain[a] * u + m.act_bias[a][0] + m.act_bias[a][1] * len + m.act_bias[a][2] * vel;
-      if (m.act_forcelimited[a]) f = clampT(f, m.act_forcerange[a][0], m.act_forcerange[a][1]);
-      s.act_force[a] = f;
-      for (int k = 0; k < m.act_trnnum[a]; k++) s.qfrc_act[m.act_trndof[a][k]] += m.act_trncoef[a][k] * f;
-    }
+  for (int a = c.tid; a < m.nu; a += c.nt) {     // one lane per actuator: length, velocity, clamps, force
+    T len = 0, vel = 0;
+    for (int k = 0; k < m.act_trnnum[a]; k++) { const int d = m.act_trndof[a][k]; len += m.act_trncoef[a][k] * s.qpos[d]; vel += m.act_trncoef[a][k] * s.qvel[d]; }
+    T u = s.ctrl[a];
+    if (m.act_ctrllimited[a]) u = clampT(u, m.act_ctrlrange[a][0], m.act_ctrlrange[a][1]);
+    T f = m.act_gain[a] * u + m.act_bias[a][0] + m.act_bias[a][1] * len + m.act_bias[a][2] * vel;
+    if (m.act_forcelimited[a]) f = clampT(f, m.act_forcerange[a][0], m.act_forcerange[a][1]);
+    s.act_force[a] = f;
   }
+  bsync(c);
+  if (c.tid == 0)                                 // moment' * force, in actuator order (two actuators may share a dof)
+    for (int a = 0; a < m.nu; a++) for (int k = 0; k < m.act_trnnum[a]; k++) s.qfrc_act[m.act_trndof[a][k]] += m.act_trncoef[a][k] * s.act_force[a];
   bsync(c);
   for (int d = c.tid; d < m.nv; d += c.nt) {
     bool active = d < m.ntd || s.pactive[(d - m.ntd) / 6];

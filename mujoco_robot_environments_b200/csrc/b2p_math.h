@@ -22,7 +22,7 @@ B2P_HD double uniform01(unsigned seed, unsigned env, unsigned k, unsigned d) { r
 struct Ctx { int tid, nt; int lock; int bar_id, bar_n; };   // bar_n > 0: the lockstep group is bar_n threads on named barrier bar_id (a sub-group of the CTA's warps)   // lock: bit mask of the CTA-wide stage barriers in use (LK_*), 0 = warps run free
 
 // Optional per-stage cycle counters (build with -DB2P_PROF; read back through b2p_prof_read).  Off in the product build.
-enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_TOTAL, PF_N };
+enum { PF_FK = 0, PF_DYN, PF_COLLIDE, PF_ROWS, PF_OSC, PF_SMOOTH, PF_SOLVE_INIT, PF_ASSEMBLE, PF_CHOL, PF_SOLVE, PF_LS, PF_UPDATE, PF_INTEGRATE, PF_BARRIER, PF_MISC, PF_NITER, PF_NSTEP, PF_BROAD, PF_NARROW, PF_TOTAL, PF_SUB0, PF_SUB1, PF_SUB2, PF_SUB3, PF_N };   // PF_SUBk: scratch counters for whatever stage is under the microscope
 #if defined(B2P_PROF) && defined(__CUDACC__)
 static __device__ unsigned long long g_prof[PF_N];
 #endif

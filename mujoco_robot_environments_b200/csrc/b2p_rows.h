@@ -90,6 +90,7 @@ template <typename T, bool C> B2P_HD T row_vel(const DevModel<T>& m, const Scrat
 // (3 rows x 2 tree bodies each) the critical path of the whole stage.
 template <typename T, bool C>
 B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s, const Ctx& c) {
+  PROF_T0
   // joint-limit sides that are inside their margin (rarely more than one of the 30): found up front, so that the item list below is
   // equalities + ACTIVE limit sides + contacts and usually fits one round of 32 lanes
   unsigned limmask = 0;
@@ -165,34 +166,42 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
     { int nc = nefc; for (int r = 0; r < nefc; r++) if (s.row_type[r] == ROW_CONTACT) { nc = r; break; } s.nrow_nc = nc; }
     for (int b = 0; b < SP_MAXBLK; b++) s.nbrow[b] = nb[b];
   }
+  PROF_ADD(PF_SUB0)
+  // Every row kind is brought to ONE shape first -- (body, point, sign) twice, an axis, impedance parameters -- so that the warp runs the
+  // expensive part (two point Jacobians, the row's velocity) once for all its lanes instead of once per kind: a round used to cost
+  // connect-equality path + contact path + ..., one after the other, because divergent branches serialise.
   for (int r = c.tid; r < nefc; r += c.nt) {
     const int kind = s.row_type[r], id = s.row_id[r], ba = s.row_a[r], bb = s.row_b[r];
     const int w = block_width(m, ba) + (bb >= 0 ? 6 : 0);
     const int jo = s.joff[r];
     T* J0 = jo >= 0 ? s.Jp + jo : s.jovf + (-jo - 1);
     for (int k = 0; k < w; k++) J0[k] = 0;
+    // body_p / pt_p / seg_p get +ax, body_n / pt_n / seg_n get -ax (both skipped for the scalar rows, which write their entries directly)
+    int body_p = 0, body_n = 0, seg_p = 0, seg_n = 0; bool rot = false;
+    T pt_p[3] = {0, 0, 0}, pt_n[3] = {0, 0, 0}, ax[3] = {0, 0, 0};
+    T K = 0, B = 0, imp = 0, R = 1, posterm = 0;
     if (kind == ROW_EQ && m.eq_type[id] == B2P_EQ_CONNECT) {
       const int q = r - s.eq_row0[id];
-      const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T g1[3], g2[3], res[3];
-      mulmv(g1, s.xmat[b1], m.eq_data[id]); mulmv(g2, s.xmat[b2], m.eq_data[id] + 3);
-      for (int k = 0; k < 3; k++) { g1[k] += s.xpos[b1][k]; g2[k] += s.xpos[b2][k]; res[k] = g1[k] - g2[k]; }
+      const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T res[3];
+      mulmv(pt_p, s.xmat[b1], m.eq_data[id]); mulmv(pt_n, s.xmat[b2], m.eq_data[id] + 3);
+      for (int k = 0; k < 3; k++) { pt_p[k] += s.xpos[b1][k]; pt_n[k] += s.xpos[b2][k]; res[k] = pt_p[k] - pt_n[k]; }
       const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
-      const T ax[3] = {T(q == 0), T(q == 1), T(q == 2)};
-      add_jac(m, s, J0, 0, b1, g1, ax, T(1)); add_jac(m, s, J0, 0, b2, g2, ax, T(-1));
-      T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
-      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * (q == 0 ? res[0] : (q == 1 ? res[1] : res[2]));
+      ax[0] = T(q == 0); ax[1] = T(q == 1); ax[2] = T(q == 2);
+      body_p = b1; body_n = b2;
+      row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
+      posterm = q == 0 ? res[0] : (q == 1 ? res[1] : res[2]);
     } else if (kind == ROW_EQ) {
       const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
-      const T x = s.qpos[j2] - m.qpos0[j2], pos = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
+      const T x = s.qpos[j2] - m.qpos0[j2];
+      posterm = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
       J0[j1] = 1; J0[j2] = -cf[1];
-      T K, B, imp, R; row_params(m, m.eq_solref[id], m.eq_solimp[id], pos, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
-      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * pos;
+      row_params(m, m.eq_solref[id], m.eq_solimp[id], posterm, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
     } else if (kind == ROW_LIMIT) {
       const int j = id >> 1, side = (id & 1) ? 1 : -1;
       const T dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]);
       J0[j] = T(-side);
-      T K, B, imp, R; row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
-      s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * (dist - m.jnt_margin[j]);
+      row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
+      posterm = dist - m.jnt_margin[j];
     } else {
       const int q = r - s.c_row[id];
       const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
@@ -200,26 +209,29 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
       if (!C || !s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
       const PairParam<T>& pp = mx.pp;
       // segment of each body inside the packed row: the tree (or the first prop) heads it, a second block follows
-      const int seg1 = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0, seg2 = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
+      seg_n = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0; seg_p = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
       const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
-      T K, B, imp, R0;
+      T R0;
       row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
       const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
       if (q == 0) s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0);
-      const T* ax = s.c_frame[id] + 3 * (q < 3 ? q : q - 3);
-      if (!C || q < 3) { add_jac(m, s, J0, seg2, b2, s.c_pos[id], ax, T(1)); add_jac(m, s, J0, seg1, b1, s.c_pos[id], ax, T(-1)); }
-      else { add_jac_rot(m, s, J0, seg2, b2, ax, T(1)); add_jac_rot(m, s, J0, seg1, b1, ax, T(-1)); }
-      const T vel = row_vel(m, s, r);
-      if (q == 0) { s.D[r] = 1 / R0; s.aref[r] = -B * vel - K * imp * (s.c_dist[id] - s.c_incl[id]); }
-      else if (!C || q < 3) { s.D[r] = 1 / R1; s.aref[r] = -B * vel; }
+      cp3(ax, s.c_frame[id] + 3 * (q < 3 ? q : q - 3)); cp3(pt_p, s.c_pos[id]); cp3(pt_n, s.c_pos[id]);
+      body_p = b2; body_n = b1; rot = C && q >= 3;
+      if (q == 0) { R = R0; posterm = s.c_dist[id] - s.c_incl[id]; }
+      else if (!C || q < 3) { R = R1; K = 0; }
       else {   // App. B item 9: R_k = R_1 mu_0^2 / mu_k^2 for the torsional (k = 3) and rolling (k = 4, 5) rows
         const T fk = s.w6[id * W6_STRIDE + (q == 3 ? 21 : 22)], f0 = s.c_fric[id];
-        s.D[r] = 1 / (R1 * f0 * f0 / (fk * fk)); s.aref[r] = -B * vel;
+        R = R1 * f0 * f0 / (fk * fk); K = 0;
       }
     }
+    if (C && rot) { add_jac_rot(m, s, J0, seg_p, body_p, ax, T(1)); add_jac_rot(m, s, J0, seg_n, body_n, ax, T(-1)); }
+    else { add_jac(m, s, J0, seg_p, body_p, pt_p, ax, T(1)); add_jac(m, s, J0, seg_n, body_n, pt_n, ax, T(-1)); }   // body 0: nothing to add
+    s.D[r] = 1 / R; s.aref[r] = -B * row_vel(m, s, r) - K * imp * posterm;
   }
   bsync(c);
+  PROF_ADD(PF_SUB1)
   if (rebuild) sp_build(s.sp, m.nprop, m.ntd, pairs, c);
+  PROF_ADD(PF_SUB2)
 }
 
 }  // namespace b2p

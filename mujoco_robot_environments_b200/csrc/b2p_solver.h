@@ -373,6 +373,7 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T, C>& s, const Ctx
     for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = use_ws ? s.qacc_ws[d] : s.qacc_smooth[d];
     bsync(c);
     if (!use_ws) cost_at(m, s, c, s.qacc);
+    PROF_ADD(PF_SUB3)
     NANCHK(2, s.Jaref, s.nefc)
     cost = solver_update(m, s, c, gn2, dirty, gs2);
     NANCHK(3, s.grad, nv) NANCHK(4, &s.cW[0][0], 6 * s.ncon)

@@ -24,12 +24,13 @@ def go():
     if a.workload == "c3": p.run_controller(torch.tensor(tg), torch.tensor(grip), a.ticks)
     else: p.step(5 * a.ticks)
 go(); go()
-buf = (C.c_ulonglong * 20)()
+buf = (C.c_ulonglong * 24)()
 ffi.check(p._L.b2p_prof_read(p._h, buf, 1))
 go()
 ffi.check(p._L.b2p_prof_read(p._h, buf, 1))
 v = list(buf); nstep = max(1, v[16]); tot = sum(v[:15])
 print("run_env total cycles/env-step: %.0f" % (v[19] / nstep))
 print("env-steps profiled: %d   mean Newton iterations/step: %.2f   cycles/env-step (warp timeline): %.0f" % (nstep, v[15] / nstep, tot / nstep))
-for i in list(range(15)) + [17, 18]:
+NAMES += ["total", "  sub0", "  sub1", "  sub2", "  sub3"]
+for i in list(range(15)) + [17, 18, 20, 21, 22, 23]:
     print("  %-22s %9.0f cycles/step  %5.1f %%" % (NAMES[i], v[i] / nstep, 100.0 * v[i] / max(1, tot)))
