@@ -278,6 +278,41 @@ B2P_HDN T cost_at(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, const T*
   block_sum(c, v);
   return v[0];
 }
+// constraint cost alone of the residuals jar (the cost part of constraint_update, same terms in the same order; no force / state writes)
+template <typename T, bool C>
+B2P_HD T constraint_cost(const Scratch<T, C>& s, const Ctx& c, const T* jar) {
+  T cost = 0;
+  for (int r = c.tid; r < s.nrow_nc; r += c.nt) { const T j = jar[r]; if (s.row_type[r] == ROW_EQ || j < 0) cost += T(0.5) * s.D[r] * j * j; }
+  for (int k = c.tid; k < s.ncon; k += c.nt) {
+    const int r = s.c_row[k];
+    if (r < 0) continue;
+    const T mu = s.c_mu[k], f1 = s.c_fric[k];
+    const T N = jar[r] * mu, U1 = jar[r + 1] * f1, U2 = jar[r + 2] * f1, Tt = sqrt(U1 * U1 + U2 * U2);
+    if (N >= mu * Tt || (Tt <= 0 && N >= 0)) { }
+    else if (mu * N + Tt <= 0 || (Tt <= 0 && N < 0)) { for (int q = 0; q < 3; q++) { const T jq = jar[r + q]; cost += T(0.5) * s.D[r + q] * jq * jq; } }
+    else { const T mv = Num<T>::minval(), dn = mu * mu * (1 + mu * mu), Dm = s.D[r] / (dn > mv ? dn : mv), NmT = N - mu * Tt; cost += T(0.5) * Dm * NmT * NmT; }
+  }
+  return cost;
+}
+// The warm-start choice in one pass: costs at qacc_smooth and at qacc_warmstart with every row decoded once for both points
+// (box-prop instantiation; the class-capable one keeps two cost_at calls).  Leaves s.Jaref / s.Ma describing the chosen point.
+template <typename T, bool C>
+B2P_HDN bool choose_start(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
+  for (int r = c.tid; r < s.nefc; r += c.nt) { s.Jv[r] = row_dot(m, s, r, s.qacc_smooth) - s.aref[r]; s.Jaref[r] = row_dot(m, s, r, s.qacc_ws) - s.aref[r]; }
+  mul_M(m, s, s.Ma, s.qacc_ws, c);       // (the Gauss term at qacc_smooth is zero whatever M qacc_smooth is: its factor x - qacc_smooth is)
+  bsync(c);
+  T v[2] = {constraint_cost(s, c, s.Jv), constraint_cost(s, c, s.Jaref)};
+  for (int d = c.tid; d < m.nv; d += c.nt) v[1] += T(0.5) * (s.Ma[d] - s.qfrc_smooth[d]) * (s.qacc_ws[d] - s.qacc_smooth[d]);
+  block_sum(c, v);
+  const bool use_ws = v[1] < v[0];
+  if (!use_ws) {
+    bsync(c);
+    for (int r = c.tid; r < s.nefc; r += c.nt) s.Jaref[r] = s.Jv[r];
+    mul_M(m, s, s.Ma, s.qacc_smooth, c);
+  }
+  bsync(c);
+  return use_ws;
+}
 // cost and gradient at s.qacc (s.Jaref / s.Ma consistent with it); also the per-contact cone Hessian weights
 template <typename T, bool C>
 B2P_HDN T solver_update(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c, T& gradnorm2, bool& hess_dirty, T& gradscale2) {   // gradscale2: squared size of the terms the gradient is the difference of
@@ -368,11 +403,14 @@ B2P_HDN void solve_constraints(const DevModel<T>& m, Scratch<T, C>& s, const Ctx
   if (has) {
     // warm start: the cheaper of qacc_warmstart and qacc_smooth.  The warm start wins in all but the first step of a contact, so it is
     // evaluated LAST: s.Jaref / s.Ma then already describe the starting point and the third evaluation is only needed otherwise.
-    const T cs = cost_at(m, s, c, s.qacc_smooth), cw = cost_at(m, s, c, s.qacc_ws);
-    const bool use_ws = cw < cs;
+    bool use_ws;
+    if constexpr (C) {
+      const T cs = cost_at(m, s, c, s.qacc_smooth), cw = cost_at(m, s, c, s.qacc_ws);
+      use_ws = cw < cs;
+    } else use_ws = choose_start(m, s, c);
     for (int d = c.tid; d < nv; d += c.nt) s.qacc[d] = use_ws ? s.qacc_ws[d] : s.qacc_smooth[d];
     bsync(c);
-    if (!use_ws) cost_at(m, s, c, s.qacc);
+    if (C && !use_ws) cost_at(m, s, c, s.qacc);
     PROF_ADD(PF_SUB3)
     NANCHK(2, s.Jaref, s.nefc)
     cost = solver_update(m, s, c, gn2, dirty, gs2);
