@@ -348,7 +348,11 @@ B2P_HDN void pair_mix(const DevModel<T>& m, const Globals<T>& g, const Scratch<T
 // detection distance of pair p in this scene
 template <typename T, bool C>
 B2P_HD T pair_md(const DevModel<T>& m, const Globals<T>& g, const Scratch<T, C>& s, int p, int g1, int g2, bool full_contacts) {
-  if (!C || !s.reclassed) { const PairParam<T>& pp = g.pair_param[p]; return full_contacts ? pp.margin : pp.margin - pp.gap; }
+  if (!C || !s.reclassed) {   // max(margin) - max(gap) from the per-geom values in the model constants (shared memory): the same reals the host-mixed table holds
+    const T mg1 = m.geom_margin[g1], mg2 = m.geom_margin[g2], gp1 = m.geom_gap[g1], gp2 = m.geom_gap[g2];
+    const T mg = mg1 > mg2 ? mg1 : mg2;
+    return full_contacts ? mg : mg - (gp1 > gp2 ? gp1 : gp2);
+  }
   PairMix<T> mx; pair_mix(m, g, s, p, g1, g2, mx);
   return full_contacts ? mx.pp.margin : mx.pp.margin - mx.pp.gap;
 }
@@ -610,7 +614,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
     const int i = i0 + c.tid; bool flag = false; int p = 0;
     if (i < n1) {
       p = s.cand[i];
-      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p]; const T md = pair_md(m, g, s, p, g1, g2, full_contacts);
+      const unsigned pk = m.pair_pk[p]; const int g1 = pk & 255u, g2 = pk >> 8; const T md = pair_md(m, g, s, p, g1, g2, full_contacts);
       if (s.gtype[g1] == B2P_GEOM_PLANE) flag = true;
       else {
         const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
@@ -647,7 +651,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
     // indexed arrays, i.e. local memory otherwise.  Same-box A/B on B200 (tools/gpu_ab.sh, c3, 12 scenes per SM): local 8.06 M, lent
     // 8.27 M env-steps/s; lending the raw contact record as well (B2P_RAW_SMEM) 8.20 M -- it turns every access to it into a generic load.
     int bb_flag = 0;
-    if (ci < ncand) { const int pq = s.cand[ci]; bb_flag = s.gtype[g.pair_g1[pq]] == B2P_GEOM_BOX && s.gtype[g.pair_g2[pq]] == B2P_GEOM_BOX; }
+    if (ci < ncand) { const unsigned pk = m.pair_pk[s.cand[ci]]; bb_flag = s.gtype[pk & 255u] == B2P_GEOM_BOX && s.gtype[pk >> 8] == B2P_GEOM_BOX; }
     int bb_tot; const int bb_slot = block_rank(c, bb_flag != 0, bb_tot);
     constexpr int RAW_REALS = (int)((sizeof(RawCon<T>) + sizeof(T) - 1) / sizeof(T)), SLOT_REALS = BB_CLIP_REALS + RAW_REALS;
     const bool lend = B2P_BB_SMEM && (sizeof(T) == 8 || B2P_BB_SMEM_F32) && bb_flag && bb_slot < (MAXTB * 28) / SLOT_REALS;
@@ -655,7 +659,7 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
     RawCon<T>& raw = (B2P_RAW_SMEM && lend) ? *reinterpret_cast<RawCon<T>*>(clip + BB_CLIP_REALS) : raw_local;
     if (ci < ncand) {
       p = s.cand[ci];
-      const int g1 = g.pair_g1[p], g2 = g.pair_g2[p], t1 = s.gtype[g1], t2 = s.gtype[g2];
+      const unsigned pk = m.pair_pk[p]; const int g1 = pk & 255u, g2 = pk >> 8, t1 = s.gtype[g1], t2 = s.gtype[g2];
       md = pair_md(m, g, s, p, g1, g2, full_contacts);
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
       const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1];

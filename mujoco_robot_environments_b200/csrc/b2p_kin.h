@@ -114,7 +114,8 @@ B2P_HDN void forward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c)
 
 // backward sweep: composite inertias (mj_crb) and rne force accumulation.  The sum over a body's subtree is taken directly -- one
 // lane per body over the bodies whose ancestor mask holds it -- instead of parent-gathers-children level by level (nine dependent
-// rounds with a barrier each on this chain-shaped tree).
+// rounds with a barrier each on this chain-shaped tree).  (One lane per (body, component) was tried: more instructions in total --
+// every item re-walks the mask -- and slower.)
 template <typename T, bool C>
 B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   T acc[16];
@@ -137,16 +138,19 @@ B2P_HD void backward_sweep(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c)
 template <typename T, bool C>
 B2P_HDN void dynamics_terms(const DevModel<T>& m, Scratch<T, C>& s, const Ctx& c) {
   const int n = m.ntd;
-  for (int e = c.tid; e < n * n; e += c.nt) {
-    const int i = e / n, j = e % n;
-    if (j > i) continue;
+  // M_ij = cdof_j . (Ic_i cdof_i) for j on i's chain: the composite-inertia product once per dof (parked in cvel, dead since the force
+  // pass), then one lane per element of the packed triangle
+  for (int i = c.tid; i < n; i += c.nt) mul_inert_vec(s.cvel[i + 1], s.crb[i + 1], s.cdof[i]);
+  bsync(c);
+  for (int e = c.tid; e < (n * (n + 1)) / 2; e += c.nt) {
+    const unsigned t = m.tri[e]; const int i = t >> 8, j = t & 255u;
     T v = 0;
     if (m.anc_mask[i + 1] & (1u << j)) {
-      T buf[6]; mul_inert_vec(buf, s.crb[i + 1], s.cdof[i]);
+      const T* buf = s.cvel[i + 1];
       for (int k = 0; k < 6; k++) v += s.cdof[j][k] * buf[k];
       if (i == j) v += m.dof_armature[i];
     }
-    s.Mt[tri_idx(i, j)] = v; s.Larm[tri_idx(i, j)] = v;
+    s.Mt[e] = v; s.Larm[e] = v;
   }
   for (int d = c.tid; d < m.nv; d += c.nt) {
     if (d < n) {
