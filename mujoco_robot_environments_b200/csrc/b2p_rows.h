@@ -179,50 +179,56 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
     // body_p / pt_p / seg_p get +ax, body_n / pt_n / seg_n get -ax (both skipped for the scalar rows, which write their entries directly)
     int body_p = 0, body_n = 0, seg_p = 0, seg_n = 0; bool rot = false;
     T pt_p[3] = {0, 0, 0}, pt_n[3] = {0, 0, 0}, ax[3] = {0, 0, 0};
-    T K = 0, B = 0, imp = 0, R = 1, posterm = 0;
+    // per-kind inputs of the ONE mj_makeImpedance evaluation below (the kinds only differ in which parameters they hand it)
+    T posterm = 0, pos_imp = 0, margin = 0, diag = 1, rscale = 1; bool fric = false; int mu_of = -1;
+    const T* solref = m.eq_solref[0]; const T* solimp = m.eq_solimp[0]; PairMix<T> mx;
     if (kind == ROW_EQ && m.eq_type[id] == B2P_EQ_CONNECT) {
       const int q = r - s.eq_row0[id];
       const int b1 = m.eq_obj1[id], b2 = m.eq_obj2[id]; T res[3];
       mulmv(pt_p, s.xmat[b1], m.eq_data[id]); mulmv(pt_n, s.xmat[b2], m.eq_data[id] + 3);
       for (int k = 0; k < 3; k++) { pt_p[k] += s.xpos[b1][k]; pt_n[k] += s.xpos[b2][k]; res[k] = pt_p[k] - pt_n[k]; }
-      const T diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0], nrm = norm3(res);
+      diag = m.tb_invweight0[b1][0] + m.tb_invweight0[b2][0]; pos_imp = norm3(res);
       ax[0] = T(q == 0); ax[1] = T(q == 1); ax[2] = T(q == 2);
       body_p = b1; body_n = b2;
-      row_params(m, m.eq_solref[id], m.eq_solimp[id], nrm, T(0), diag, false, K, B, imp, R);
+      solref = m.eq_solref[id]; solimp = m.eq_solimp[id];
       posterm = q == 0 ? res[0] : (q == 1 ? res[1] : res[2]);
     } else if (kind == ROW_EQ) {
       const int j1 = m.eq_obj1[id], j2 = m.eq_obj2[id]; const T* cf = m.eq_data[id];
       const T x = s.qpos[j2] - m.qpos0[j2];
       posterm = s.qpos[j1] - m.qpos0[j1] - (cf[0] + cf[1] * x);
       J0[j1] = 1; J0[j2] = -cf[1];
-      row_params(m, m.eq_solref[id], m.eq_solimp[id], posterm, T(0), m.dof_invweight0[j1] + m.dof_invweight0[j2], false, K, B, imp, R);
+      solref = m.eq_solref[id]; solimp = m.eq_solimp[id]; pos_imp = posterm; diag = m.dof_invweight0[j1] + m.dof_invweight0[j2];
     } else if (kind == ROW_LIMIT) {
       const int j = id >> 1, side = (id & 1) ? 1 : -1;
       const T dist = side * (m.jnt_range[j][(side + 1) / 2] - s.qpos[j]);
       J0[j] = T(-side);
-      row_params(m, m.jnt_solref[j], m.jnt_solimp[j], dist, m.jnt_margin[j], m.dof_invweight0[j], false, K, B, imp, R);
-      posterm = dist - m.jnt_margin[j];
+      solref = m.jnt_solref[j]; solimp = m.jnt_solimp[j]; pos_imp = dist; margin = m.jnt_margin[j]; diag = m.dof_invweight0[j];
+      posterm = dist - margin;
     } else {
       const int q = r - s.c_row[id];
       const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
-      PairMix<T> mx;
       if (!C || !s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
-      const PairParam<T>& pp = mx.pp;
       // segment of each body inside the packed row: the tree (or the first prop) heads it, a second block follows
       seg_n = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0; seg_p = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
       const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
-      T R0;
-      row_params(m, pp.solref, pp.solimp, s.c_dist[id], s.c_incl[id], iw1 + iw2, false, K, B, imp, R0);
-      const T mv = Num<T>::minval(), R1 = R0 / (m.impratio > mv ? m.impratio : mv);
-      if (q == 0) s.c_mu[id] = s.c_fric[id] * sqrt(R1 / R0);
+      solref = mx.pp.solref; solimp = mx.pp.solimp; pos_imp = s.c_dist[id]; margin = s.c_incl[id]; diag = iw1 + iw2;
       cp3(ax, s.c_frame[id] + 3 * (q < 3 ? q : q - 3)); cp3(pt_p, s.c_pos[id]); cp3(pt_n, s.c_pos[id]);
       body_p = b2; body_n = b1; rot = C && q >= 3;
-      if (q == 0) { R = R0; posterm = s.c_dist[id] - s.c_incl[id]; }
-      else if (!C || q < 3) { R = R1; K = 0; }
-      else {   // App. B item 9: R_k = R_1 mu_0^2 / mu_k^2 for the torsional (k = 3) and rolling (k = 4, 5) rows
-        const T fk = s.w6[id * W6_STRIDE + (q == 3 ? 21 : 22)], f0 = s.c_fric[id];
-        R = R1 * f0 * f0 / (fk * fk); K = 0;
+      if (q == 0) { posterm = s.c_dist[id] - s.c_incl[id]; mu_of = id; }
+      else {
+        fric = true;
+        if (C && q >= 3) {   // App. B item 9: R_k = R_1 mu_0^2 / mu_k^2 for the torsional (k = 3) and rolling (k = 4, 5) rows
+          const T fk = s.w6[id * W6_STRIDE + (q == 3 ? 21 : 22)], f0 = s.c_fric[id];
+          rscale = f0 * f0 / (fk * fk);
+        }
       }
+    }
+    T K, B, imp, R;
+    row_params(m, solref, solimp, pos_imp, margin, diag, false, K, B, imp, R);
+    {
+      const T mv = Num<T>::minval(), R1 = R / (m.impratio > mv ? m.impratio : mv);
+      if (mu_of >= 0) s.c_mu[mu_of] = s.c_fric[mu_of] * sqrt(R1 / R);
+      if (fric) { K = 0; R = (C && rot) ? R1 * rscale : R1; }
     }
     if (C && rot) { add_jac_rot(m, s, J0, seg_p, body_p, ax, T(1)); add_jac_rot(m, s, J0, seg_n, body_n, ax, T(-1)); }
     else { add_jac(m, s, J0, seg_p, body_p, pt_p, ax, T(1)); add_jac(m, s, J0, seg_n, body_n, pt_n, ax, T(-1)); }   // body 0: nothing to add
