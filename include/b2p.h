@@ -97,6 +97,23 @@ int b2p_set_full_contacts(b2p_handle h, int full);
 int b2p_set_env_mask(b2p_handle h, const uint8_t* env_mask);
 
 int b2p_step_physics(b2p_handle h, const void* ctrl /* [n_env][nu] */, int n_steps, void* stream);
+/* b2p_step_physics for callers that must not allocate (code under CUDA graph capture, tight serving loops, harnesses that forbid
+ * cudaMalloc).  NO COUNTERPART IN THE REFERENCE.
+ * Same kernel, same results as b2p_step_physics on the same state.  The kernel's global-memory scratch (one Jacobian overflow area
+ * per resident warp + the scene-queue counter) is a file-scope `static __device__` array of csrc/b2p_api.cu instead of the handle's
+ * cudaMalloc'd pools: about 3.3 MB that every GPU which loads libb2p.so holds until the process exits.  Its device address is
+ * resolved once per device by b2p_create (cudaGetSymbolAddress, that device current); this call itself makes no cudaMalloc /
+ * cudaFree / allocating library call -- a cudaMemsetAsync of the queue counter and the kernel launch on `stream`, nothing else.
+ *   state : device [n_env][B2P_Q_STATE_STRIDE] reals, 16-byte aligned, advanced in place (passed here, not taken from b2p_bind_state)
+ *   ctrl  : device [n_env][nu] reals, or NULL for zero controls
+ * Limits: the handle holds at most B2P_NOALLOC_MAX_ENV scenes (B2P_ERR_ARG otherwise, b2p_last_error says so), Newton solver,
+ * box props only (no b2p_set_env_prop_types).  Status words, derived outputs (b2p_get), env mask and env params are the handle's.
+ * The scene queue is not re-ordered by work and the handle's work figures are not touched (pure scheduling: results do not depend on it).
+ * EVERY call on a device shares the one array, which keeps the previous call's contents (the counter is cleared by each call; the
+ * overflow areas need no clearing, a row is written before it is read): calls that overlap on the GPU -- two streams, two handles,
+ * two host threads -- RACE.  Serialise them on one stream or with events. */
+enum { B2P_NOALLOC_MAX_ENV = 128 };
+int b2p_step_physics_noalloc(b2p_handle h, void* state, const void* ctrl /* [n_env][nu] or NULL */, int n_steps, void* stream);
 int b2p_step_osc(b2p_handle h, const void* target13 /* [n_env][13] pos vel quat angvel */, const uint8_t* grip /* [n_env] */,
                  int n_ticks, int control_steps, uint8_t* converged /* [n_env] or NULL */, void* stream);
 int b2p_settle(b2p_handle h, const uint8_t* env_mask /* NULL = all */, int max_steps, int min_steps, double qvel_tol,

@@ -4,6 +4,7 @@
 
 #include <cstdio>
 #include <cstdlib>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -52,6 +53,34 @@ __global__ void __launch_bounds__(1024) b2p_order_kernel(const int* __restrict__
   if (threadIdx.x == 0) { int acc = 0; for (int b = 255; b >= 0; b--) { const int k = hist[b]; hist[b] = acc; acc += k; } }
   __syncthreads();
   for (int e = threadIdx.x; e < n; e += blockDim.x) order[atomicAdd(&hist[bucket(e)], 1)] = e;
+}
+
+// ------------------------------------------------------------------------------------------ scratch of the no-allocation step (b2p_step_physics_noalloc)
+// The step kernel's per-warp scratch in global memory is the Jacobian overflow area (rows beyond the shared-memory pool) and the
+// scene-queue counter.  Handles get theirs from cudaMalloc in b2p_create; the no-allocation entry point uses THIS array instead:
+// one per GPU that loads the library, held until exit, shared by every call (calls that overlap on the GPU race).
+// Size: one overflow area per resident warp, at most B2P_NOALLOC_MAX_ENV scenes rounded up to whole CTAs, in the wider dtype.
+constexpr size_t NOALLOC_WARPS = B2P_NOALLOC_MAX_ENV + 12;                                    // ceil(n / warps per CTA) CTAs of <= 12 warps
+constexpr size_t NOALLOC_AREA = sizeof(double) * Pool<double>::JP > sizeof(float) * Pool<float>::JP ? sizeof(double) * Pool<double>::JP : sizeof(float) * Pool<float>::JP;
+constexpr size_t NOALLOC_JOVF_OFF = 256;                                                       // [0, 4): queue counter; the areas start on the next 256-byte line
+constexpr size_t NOALLOC_BYTES = NOALLOC_JOVF_OFF + NOALLOC_WARPS * NOALLOC_AREA + 16 * sizeof(double);   // + 16 reals: row_dot's guarded slots
+static_assert(NOALLOC_BYTES <= (4u << 20), "the static scratch is meant to stay modest (4 MiB)");
+static __device__ __align__(256) unsigned char g_noalloc_scratch[NOALLOC_BYTES];
+
+// In host code `g_noalloc_scratch` is only a stand-in for the symbol: its device address has to be asked for, once per device, with
+// that device current (b2p_create does, after its cudaSetDevice).
+constexpr int NOALLOC_MAXDEV = 64;
+static std::mutex g_noalloc_mutex;
+static void* g_noalloc_ptr[NOALLOC_MAXDEV];
+static int noalloc_resolve(int device) {
+  if (device < 0 || device >= NOALLOC_MAXDEV) return B2P_OK;             // such a device simply has no no-allocation step
+  std::lock_guard<std::mutex> lock(g_noalloc_mutex);
+  if (g_noalloc_ptr[device]) return B2P_OK;
+  void* p = nullptr;
+  cudaError_t e = cudaGetSymbolAddress(&p, g_noalloc_scratch);
+  if (e != cudaSuccess || !p) return fail(B2P_ERR_CUDA, std::string("cudaGetSymbolAddress(g_noalloc_scratch): ") + cudaGetErrorString(e));
+  g_noalloc_ptr[device] = p;
+  return B2P_OK;
 }
 
 // ------------------------------------------------------------------------------------------ handle
@@ -159,6 +188,26 @@ static int place_mode(b2p_handle h, const int32_t* prop, const void* box, const 
   a.place_prop = prop; a.place_box = (const T*)box; a.place_dist = (T)dist; a.place_table = table_geom; a.place_seed = seed; a.place_out = (T*)out; a.place_yaw = yaw; a.place_quat = (T*)quat_out;
   return launch<T>(h, a, (cudaStream_t)stream);
 }
+// the step launch of b2p_step_physics with the kernel's scratch taken from g_noalloc_scratch: no queue ordering (its work figures
+// belong to the handle's own launches), no handle field is modified
+template <typename T>
+static int launch_noalloc(b2p_handle_s* h, void* scratch, void* state, const void* ctrl, int n_steps, cudaStream_t st) {
+  StepArgs<T> a; std::memset(&a, 0, sizeof a);
+  { const char* ls = getenv("B2P_LOCKSTEP"); a.lockstep = ls ? atoi(ls) : LK_DEFAULT; }
+  { const char* lg = getenv("B2P_LOCKGROUP"); a.lock_group = lg ? atoi(lg) : 0; }
+  a.mode = MODE_PHYSICS; a.n_steps = n_steps; a.control_steps = 1; a.full_contacts = h->full_contacts;
+  a.ctrl = (const T*)(ctrl ? ctrl : h->d_zero_ctrl); a.env_mask = h->env_mask;
+  a.n_env = h->n_env; a.state = (T*)state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = nullptr;
+  a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
+  a.work = nullptr; a.order = nullptr; a.solver = B2P_SOLVER_NEWTON;
+  int* next_env = (int*)scratch;                                                     // cleared by the launch itself (cudaMemsetAsync on the stream)
+  T* jovf = (T*)((unsigned char*)scratch + NOALLOC_JOVF_OFF);                         // no need to clear: a row is written before it is read
+  Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, jovf, nullptr, nullptr, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};
+  if constexpr (sizeof(T) == 8) CK(launch_f64(h->lg, h->d_model, g, a, next_env, st));
+  else CK(launch_f32(h->lg, h->d_model, g, a, next_env, st));
+  return B2P_OK;
+}
+
 extern "C" {
 
 const char* b2p_last_error(void) { return g_err.c_str(); }
@@ -172,6 +221,7 @@ int b2p_create(const void* blob, size_t nbytes, int n_env, int dtype, int device
   h->out_mask = OUT_ALL;
   h->dtype = dtype; h->device = device; h->n_env = n_env; h->nq = h->hmodel.nq; h->nv = h->hmodel.nv; h->nu = h->hmodel.nu; h->nprop = h->hmodel.nprop; h->ngeom = h->hmodel.ngeom;
   CK(cudaSetDevice(device));
+  { const int rc0 = noalloc_resolve(device); if (rc0 != B2P_OK) { delete h; return rc0; } }
   CK(cudaMalloc(&h->d_status, (size_t)n_env * 4)); CK(cudaMemset(h->d_status, 0, (size_t)n_env * 4));
   int rc = dtype == B2P_F64 ? upload<double>(h, ht) : upload<float>(h, ht);
   if (rc != B2P_OK) { delete h; return rc; }
@@ -249,6 +299,19 @@ int b2p_osc_config(b2p_handle h, const double g[6], const double q0[7], double p
 int b2p_step_physics(b2p_handle h, const void* ctrl, int n_steps, void* stream) {
   if (!h || n_steps < 0) return fail(B2P_ERR_ARG, "b2p_step_physics: bad argument");
   return DISPATCH(h, MODE_PHYSICS, n_steps, 1, h->full_contacts, ctrl, nullptr, nullptr, h->env_mask, nullptr, nullptr, 0, 0, 0, stream);
+}
+int b2p_step_physics_noalloc(b2p_handle h, void* state, const void* ctrl, int n_steps, void* stream) {
+  if (!h || !state || n_steps < 0) return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: bad argument");
+  if (((uintptr_t)state) % 16) return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: state must be 16-byte aligned (TMA)");
+  if (h->n_env > B2P_NOALLOC_MAX_ENV)
+    return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: the handle holds " + std::to_string(h->n_env) + " scenes, the static scratch covers at most " + std::to_string((int)B2P_NOALLOC_MAX_ENV) + " (B2P_NOALLOC_MAX_ENV); use b2p_step_physics");
+  if ((size_t)h->lg.grid * h->lg.warps_per_cta > NOALLOC_WARPS) return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: more resident warps than the static scratch has areas for");
+  if (h->solver != B2P_SOLVER_NEWTON) return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: Newton only (the PGS solver's pool is allocated on demand)");
+  if (h->prop_type) return fail(B2P_ERR_ARG, "b2p_step_physics_noalloc: box props only (no prop classes bound)");
+  void* scratch = h->device >= 0 && h->device < NOALLOC_MAXDEV ? g_noalloc_ptr[h->device] : nullptr;      // resolved by b2p_create on this device
+  if (!scratch) return fail(B2P_ERR_STATE, "b2p_step_physics_noalloc: the scratch address was not resolved for this device");
+  return h->dtype == B2P_F64 ? launch_noalloc<double>(h, scratch, state, ctrl, n_steps, (cudaStream_t)stream)
+                             : launch_noalloc<float>(h, scratch, state, ctrl, n_steps, (cudaStream_t)stream);
 }
 int b2p_step_osc(b2p_handle h, const void* target13, const uint8_t* grip, int n_ticks, int control_steps, uint8_t* converged, void* stream) {
   if (!h || !target13 || n_ticks < 0 || control_steps < 1) return fail(B2P_ERR_ARG, "b2p_step_osc: bad argument");

@@ -28,7 +28,7 @@ O = dict(SITE_XPOS=0, SITE_XMAT=1, QACC=2, QFRC_BIAS=3, CTRL=4, NCON=5, NEFC=6, 
          GEOM_XMAT=11, QACC_SMOOTH=12, EFC_FORCE=13)
 SYMBOLS = ["b2p_create", "b2p_destroy", "b2p_query", "b2p_out_offset", "b2p_bind_state", "b2p_bind_out", "b2p_set_env_params", "b2p_set_out_mask", "b2p_set_solver", "b2p_set_env_prop_types",
            "b2p_osc_config", "b2p_set_env_gains", "b2p_set_env_mask", "b2p_set_full_contacts", "b2p_step_physics", "b2p_step_osc", "b2p_settle", "b2p_forward", "b2p_place_search", "b2p_place_props", "b2p_get",
-           "b2p_status", "b2p_status_set", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error",
+           "b2p_status", "b2p_status_set", "b2p_prof_read", "b2p_fma_peak", "b2p_last_error", "b2p_step_physics_noalloc",
            "b2p_render_create", "b2p_render_destroy", "b2p_render_query", "b2p_render"]          # include/b2p_render.h
 GEOM = dict(box=6, sphere=2, cylinder=5)            # B2P_GEOM_* of include/b2p_model_layout.h (MuJoCo's mjtGeom numbering)
 SOLVER = dict(newton=0, pgs=1)
@@ -88,6 +88,7 @@ def lib() -> C.CDLL:
     L.b2p_set_env_gains.argtypes = [vp, vp]
     L.b2p_set_env_mask.argtypes = [vp, vp]
     L.b2p_step_physics.argtypes = [vp, vp, i32, vp]
+    L.b2p_step_physics_noalloc.argtypes = [vp, vp, vp, i32, vp]
     L.b2p_step_osc.argtypes = [vp, vp, u8p, i32, i32, u8p, vp]
     L.b2p_settle.argtypes = [vp, u8p, i32, i32, C.c_double, C.c_double, vp, vp]
     L.b2p_forward.argtypes = [vp, i32, vp]
