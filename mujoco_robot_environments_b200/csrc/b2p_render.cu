@@ -24,6 +24,7 @@
 
 #include "../../include/b2p.h"
 #include "../../include/b2p_render.h"
+#include "b2p_render_cull.h"
 
 namespace b2p { int api_fail(int code, const char* msg); }
 #define RCK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) return b2p::api_fail(B2P_ERR_CUDA, (std::string(#x) + ": " + cudaGetErrorString(e_)).c_str()); } while (0)
@@ -33,6 +34,8 @@ namespace {
 constexpr int TW = 32, TH = 8, NT = 256, NW = NT / 32, RMAXG = 32, RMAXZ = 8;
 constexpr int GEOM_PLANE = 0, GEOM_BOX = 6, GEOM_MESH = 7;
 constexpr unsigned MAGIC = 0x52503242u;
+constexpr int PL_CAP = 1024, PL_ROUNDS = 4;      // per-warp pool of listed plane indices; hulls of up to 32 * PL_ROUNDS planes get a list
+using b2p_render::Plane4;
 
 struct RGeom { int type, padr, pnum, prop, is_static, pad_i[3]; float rgba[4], size[3], cen[3], rbound, spos[3], smat[9], pad_f; };
 struct RZone { float pos[3], half[3], rgba[4], pad[2]; };
@@ -122,7 +125,7 @@ __device__ __forceinline__ bool ray_box(const float* o, const float* d, const fl
 }
 
 __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const float* pos, const float* mat, const float* cen, const float* half,
-                                         const float4* __restrict__ planes, int np, float t_max, float* t_out, float* n_out) {
+                                         const Plane4* __restrict__ planes, int np, const unsigned char* list, int nlist, float t_max, float* t_out, float* n_out) {
   float ol[3], dl[3];
   const float w0 = o[0] - pos[0], w1 = o[1] - pos[1], w2 = o[2] - pos[2];
   for (int k = 0; k < 3; k++) { ol[k] = mat[k] * w0 + mat[3 + k] * w1 + mat[6 + k] * w2; dl[k] = mat[k] * d[0] + mat[3 + k] * d[1] + mat[6 + k] * d[2]; }
@@ -142,23 +145,10 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
     if (tn > tf || tf <= 0.0f) return false;
     if (tn > t_max) return false;      // the hull lies inside the box: it cannot beat (or tie) a hit nearer than the box's entry
   }
-  // Entry / exit parameters are kept as fractions num / den (entry: den < 0, exit: den > 0) and compared by cross
-  // multiplication, so the loop has no division and no data-dependent branch besides its exit; one division at the end.
-  float tn_n = 1e30f, tn_d = -1.0f, tf_n = 1e30f, tf_d = 1.0f; int best = -1;
-  for (int i = 0; i < np; i++) {
-    const float4 P = __ldg(planes + i);
-    // explicit fused multiply-adds (the oracle calls C99 fmaf at the same places; everything else in this file is unfused)
-    const float den = __fmaf_rn(P.z, dl[2], __fmaf_rn(P.y, dl[1], P.x * dl[0]));
-    const float dist = P.w - __fmaf_rn(P.z, ol[2], __fmaf_rn(P.y, ol[1], P.x * ol[0]));
-    if (den == 0.0f) { if (dist < 0.0f) return false; continue; }
-    if (den < 0.0f) { if (dist * tn_d > tn_n * den) { tn_n = dist; tn_d = den; best = i; } }      // dist / den > tn
-    else if (dist * tf_d < tf_n * den) { tf_n = dist; tf_d = den; }                              // dist / den < tf
-    if (tn_n * tf_d < tf_n * tn_d) return false;                                                 // tn > tf
-  }
-  if (best < 0) return false;
-  const float tn = tn_n / tn_d;
-  if (tn <= 0.0f) return false;
-  const float4 P = __ldg(planes + best);
+  // the clip loop (b2p_render_cull.h): over the tile's plane list when there is one, over all np planes otherwise
+  float tn; int best;
+  if (!b2p_render::hull_clip(ol, dl, planes, list, list ? nlist : np, &tn, &best)) return false;
+  const Plane4 P = b2p_render::ld_plane(planes + best);
   *t_out = tn;
   for (int k = 0; k < 3; k++) n_out[k] = mat[3 * k] * P.x + mat[3 * k + 1] * P.y + mat[3 * k + 2] * P.z;
   return true;
@@ -189,10 +179,14 @@ __device__ __forceinline__ float shade_factor(const RCam& C, const float* p, con
 }
 __device__ __forceinline__ float clamp01(float x) { return fminf(1.0f, fmaxf(0.0f, x)); }
 
-struct TileGeoms { float pos[RMAXG][3], mat[RMAXG][9], size[RMAXG][3], rgb[RMAXG][3]; unsigned char order[RMAXG]; int n_order; };
+struct TileGeoms {
+  float pos[RMAXG][3], mat[RMAXG][9], size[RMAXG][3], rgb[RMAXG][3]; unsigned char order[RMAXG]; int n_order;
+  short pl_off[RMAXG], pl_cnt[RMAXG];            // per hull geom: its plane list inside plist (cnt < 0: none, use every plane)
+  unsigned char plist[PL_CAP];
+};
 
 // one pixel: nearest opaque geom among the static geoms and the listed moving geoms, then the nearest translucent zone in front
-__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const float4* __restrict__ planes, int u, int v,
+__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const Plane4* __restrict__ planes, int u, int v,
                            unsigned char* rgb_out, float* depth_out, int* seg_out) {
   const RCam& C = M.cam;
   const float dc0 = ((float)u - C.cx) / C.f, dc1 = (C.cy - (float)v) / C.f;             // camera-frame direction (x, y, -1): t is the axial depth
@@ -211,7 +205,7 @@ __device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const float4* _
     float t, n[3], rgb[3];
     bool hit;
     if (G.type == GEOM_BOX) { hit = ray_box(o, d, pos, mat, (dyn && G.prop >= 0) ? tg.size[g] : G.size, &t, n); }
-    else if (G.type == GEOM_MESH) { hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, best_t, &t, n); }
+    else if (G.type == GEOM_MESH) { const int lc = tg.pl_cnt[g]; hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, lc >= 0 ? tg.plist + tg.pl_off[g] : nullptr, lc, best_t, &t, n); }
     else if (G.type == GEOM_PLANE) { hit = ray_ground(o, d, pos, mat, G.size, C.check, G.rgba, C.rgb2, &t, n, rgb); }
     else hit = false;
     if (hit && (t < best_t || (t == best_t && g < best_id))) {
@@ -305,9 +299,56 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
         if (lane == 0) S.tg.n_order = __popc(mask);
       }
       __syncwarp();
+      {   // plane lists of the hulls this tile's rays are tested against (b2p_render_cull.h): lanes across planes
+        int used = 0;
+        const int n_items = S.tg.n_order + M.n_static;
+        for (int it = 0; it < n_items; it++) {
+          const int g = it < S.tg.n_order ? S.tg.order[it] : M.static_ids[it - S.tg.n_order];
+          const RGeom& G = M.geom[g];
+          if (G.type != GEOM_MESH) continue;
+          const int np = G.pnum;
+          int total = -1;
+          if (np <= 32 * PL_ROUNDS) {
+            const bool dyn = !G.is_static;
+            b2p_render::TileRays R;
+            b2p_render::tile_rays(M.cam.pos, M.cam.mat, M.cam.f, M.cam.cx, M.cam.cy, tx0, ty0, TW, TH, dyn ? S.tg.pos[g] : G.spos, dyn ? S.tg.mat[g] : G.smat, R);
+            const Plane4* pl = reinterpret_cast<const Plane4*>(a.planes) + G.padr;
+            int cls[PL_ROUNDS]; float tmn[PL_ROUNDS], tmx[PL_ROUNDS];
+            float e_lo = -3.0e38f, x_hi = 3.0e38f;
+#pragma unroll
+            for (int r = 0; r < PL_ROUNDS; r++) {
+              const int i = r * 32 + lane; cls[r] = -1; tmn[r] = tmx[r] = 0.0f;
+              if (i < np) {
+                cls[r] = b2p_render::plane_class(b2p_render::ld_plane(pl + i), R, &tmn[r], &tmx[r]);
+                if (cls[r] == b2p_render::PL_ENTRY) e_lo = fmaxf(e_lo, tmn[r]);
+                if (cls[r] == b2p_render::PL_EXIT) x_hi = fminf(x_hi, tmx[r]);
+              }
+            }
+            for (int o = 16; o; o >>= 1) { e_lo = fmaxf(e_lo, __shfl_xor_sync(0xffffffffu, e_lo, o)); x_hi = fminf(x_hi, __shfl_xor_sync(0xffffffffu, x_hi, o)); }
+            unsigned keep[PL_ROUNDS]; total = 0;
+#pragma unroll
+            for (int r = 0; r < PL_ROUNDS; r++) {
+              keep[r] = __ballot_sync(0xffffffffu, cls[r] >= 0 && b2p_render::plane_keep(cls[r], tmn[r], tmx[r], e_lo, x_hi));
+              total += __popc(keep[r]);
+            }
+            if (used + total > PL_CAP) total = -1;      // pool full: this hull keeps the full loop
+            else {
+              int at = used;
+#pragma unroll
+              for (int r = 0; r < PL_ROUNDS; r++) {
+                if ((keep[r] >> lane) & 1u) S.tg.plist[at + __popc(keep[r] & ((1u << lane) - 1u))] = (unsigned char)(r * 32 + lane);
+                at += __popc(keep[r]);
+              }
+            }
+          }
+          if (lane == 0) { S.tg.pl_off[g] = (short)used; S.tg.pl_cnt[g] = (short)total; }
+          if (total > 0) used += total;
+        }
+      }
+      __syncwarp();
       for (int ly = 0; ly < TH; ly++) {
         float dep; int sg;
-        cast_pixel(M, S.tg, a.planes, tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
+        cast_pixel(M, S.tg, reinterpret_cast<const Plane4*>(a.planes), tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
         const size_t off = (size_t)(ty0 + ly) * M.W + tx0 + lane;
         if (a.depth) a.depth[img + off] = dep;
         if (a.seg) a.seg[img + off] = sg;
