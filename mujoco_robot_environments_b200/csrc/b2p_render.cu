@@ -35,7 +35,7 @@ constexpr int TW = 32, TH = 8, NT = 256, NW = NT / 32, RMAXG = 32, RMAXZ = 8;
 constexpr int GEOM_PLANE = 0, GEOM_BOX = 6, GEOM_MESH = 7;
 constexpr unsigned MAGIC = 0x52503242u;
 constexpr int PL_CAP = 1024, PL_ROUNDS = 4;      // per-warp pool of listed plane indices; hulls of up to 32 * PL_ROUNDS planes get a list
-using b2p_render::Plane4;
+using b2p_rcull::Plane4;
 
 struct RGeom { int type, padr, pnum, prop, is_static, pad_i[3]; float rgba[4], size[3], cen[3], rbound, spos[3], smat[9], pad_f; };
 struct RZone { float pos[3], half[3], rgba[4], pad[2]; };
@@ -47,7 +47,7 @@ struct FrameArgs {
   int n_env, pose_stride, dtype, background;
   const void* xpos; const void* xmat; const float* prop_rgba; const void* prop_size; const unsigned char* prop_active;
   const short4* rects;
-  const uint8_t* bg_rgb; const float* bg_depth; const int* bg_seg;
+  const uint8_t* bg_rgb; const float* bg_depth; const int* bg_seg; float* layers;      // layers: [NLAYER][H * W], see cast_pixel
   uint8_t* rgb; float* depth; int* seg;
   const float4* planes;
   unsigned long long* queue; unsigned long long* tile_stats;
@@ -147,8 +147,8 @@ __device__ __forceinline__ bool ray_hull(const float* o, const float* d, const f
   }
   // the clip loop (b2p_render_cull.h): over the tile's plane list when there is one, over all np planes otherwise
   float tn; int best;
-  if (!b2p_render::hull_clip(ol, dl, planes, list, list ? nlist : np, &tn, &best)) return false;
-  const Plane4 P = b2p_render::ld_plane(planes + best);
+  if (!b2p_rcull::hull_clip(ol, dl, planes, list, list ? nlist : np, &tn, &best)) return false;
+  const Plane4 P = b2p_rcull::ld_plane(planes + best);
   *t_out = tn;
   for (int k = 0; k < 3; k++) n_out[k] = mat[3 * k] * P.x + mat[3 * k + 1] * P.y + mat[3 * k + 2] * P.z;
   return true;
@@ -185,19 +185,30 @@ struct TileGeoms {
   unsigned char plist[PL_CAP];
 };
 
-// one pixel: nearest opaque geom among the static geoms and the listed moving geoms, then the nearest translucent zone in front
-__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const Plane4* __restrict__ planes, int u, int v,
+// Background layers (written once with the static image, read by every ray-cast tile): what a pixel's ray finds among the things
+// that never move.  [0] depth of the nearest static opaque hit (zfar: none), [1] its geom id, [2..4] its shaded colour,
+// [5] depth of the nearest zone in front of it, [6] that zone's index (-1: none), [7..9] alpha * the zone's shaded colour.
+// A frame's ray then only has to be tested against the MOVING geoms listed for its tile: the nearest opaque hit is the nearer of
+// that and layer 0 (ties: smaller geom id), and the zone of layer 6 is blended in when it lies in front of the winner -- the
+// floats the one-pass formulation computes, in the same operations, so every pixel keeps its bits.
+constexpr int NLAYER = 10;
+
+// one pixel.  BG: the static geoms and the zones (writes the layers); otherwise the listed moving geoms against the layers
+template <bool BG>
+__device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const Plane4* __restrict__ planes, int u, int v, float* __restrict__ lay, size_t lstride,
                            unsigned char* rgb_out, float* depth_out, int* seg_out) {
   const RCam& C = M.cam;
   const float dc0 = ((float)u - C.cx) / C.f, dc1 = (C.cy - (float)v) / C.f;             // camera-frame direction (x, y, -1): t is the axial depth
   float d[3], o[3] = {C.pos[0], C.pos[1], C.pos[2]};
   for (int k = 0; k < 3; k++) d[k] = C.mat[3 * k] * dc0 + C.mat[3 * k + 1] * dc1 - C.mat[3 * k + 2];
   float best_t = C.zfar; int best_id = -1; float bn[3] = {0, 0, 0}, brgb[3] = {0, 0, 0};
-  // Moving geoms first, nearest first (tg.order), then the static ones: a hull whose bounding box starts behind the current hit
-  // is skipped without touching its planes.  The winner is order independent: smallest t, then smallest geom id.
-  const int n_items = tg.n_order + M.n_static;
+  bool won = false;
+  if (!BG) { best_t = lay[0]; best_id = __float_as_int(lay[lstride]); }
+  // Listed geoms nearest first (tg.order): a hull whose bounding box starts behind the current hit is skipped without touching its
+  // planes.  The winner is order independent: smallest t, then smallest geom id.
+  const int n_items = BG ? M.n_static : tg.n_order;
   for (int it = 0; it < n_items; it++) {
-    const int g = it < tg.n_order ? tg.order[it] : M.static_ids[it - tg.n_order];
+    const int g = BG ? M.static_ids[it] : tg.order[it];
     const RGeom& G = M.geom[g];
     const bool dyn = !G.is_static;
     const float* pos = dyn ? tg.pos[g] : G.spos;
@@ -205,32 +216,52 @@ __device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const Plane4* _
     float t, n[3], rgb[3];
     bool hit;
     if (G.type == GEOM_BOX) { hit = ray_box(o, d, pos, mat, (dyn && G.prop >= 0) ? tg.size[g] : G.size, &t, n); }
-    else if (G.type == GEOM_MESH) { const int lc = tg.pl_cnt[g]; hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, lc >= 0 ? tg.plist + tg.pl_off[g] : nullptr, lc, best_t, &t, n); }
+    else if (G.type == GEOM_MESH) {
+      const int lc = tg.pl_cnt[g];
+      if (lc == 0) continue;                                                           // no ray of this tile meets the hull
+      hit = ray_hull(o, d, pos, mat, G.cen, G.size, planes + G.padr, G.pnum, lc > 0 ? tg.plist + tg.pl_off[g] : nullptr, lc, best_t, &t, n);
+    }
     else if (G.type == GEOM_PLANE) { hit = ray_ground(o, d, pos, mat, G.size, C.check, G.rgba, C.rgb2, &t, n, rgb); }
     else hit = false;
     if (hit && (t < best_t || (t == best_t && g < best_id))) {
-      best_t = t; best_id = g; bn[0] = n[0]; bn[1] = n[1]; bn[2] = n[2];
+      best_t = t; best_id = g; bn[0] = n[0]; bn[1] = n[1]; bn[2] = n[2]; won = true;
       if (G.type != GEOM_PLANE) { const float* c = (dyn && G.prop >= 0) ? tg.rgb[g] : G.rgba; rgb[0] = c[0]; rgb[1] = c[1]; rgb[2] = c[2]; }
       brgb[0] = rgb[0]; brgb[1] = rgb[1]; brgb[2] = rgb[2];
     }
   }
   float col[3] = {0.0f, 0.0f, 0.0f};
-  if (best_id >= 0) {
-    const float p[3] = {o[0] + best_t * d[0], o[1] + best_t * d[1], o[2] + best_t * d[2]};
-    const float s = shade_factor(C, p, bn);
-    for (int k = 0; k < 3; k++) col[k] = clamp01(clamp01(brgb[k]) * s);
-  }
-  const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
-  float zt = best_t; int zid = -1; float zn[3] = {0, 0, 0};
-  for (int z = 0; z < M.nzone; z++) {
-    float t, n[3];
-    if (ray_box(o, d, M.zone[z].pos, ident, M.zone[z].half, &t, n) && t < zt) { zt = t; zid = z; zn[0] = n[0]; zn[1] = n[1]; zn[2] = n[2]; }
-  }
-  if (zid >= 0) {
-    const float p[3] = {o[0] + zt * d[0], o[1] + zt * d[1], o[2] + zt * d[2]};
-    const float s = shade_factor(C, p, zn), al = M.zone[zid].rgba[3];
-    for (int k = 0; k < 3; k++) col[k] = al * clamp01(M.zone[zid].rgba[k] * s) + (1.0f - al) * col[k];
-    best_t = zt; best_id = M.ngeom + zid;
+  if (BG || won) {
+    if (best_id >= 0) {
+      const float p[3] = {o[0] + best_t * d[0], o[1] + best_t * d[1], o[2] + best_t * d[2]};
+      const float s = shade_factor(C, p, bn);
+      for (int k = 0; k < 3; k++) col[k] = clamp01(clamp01(brgb[k]) * s);
+    }
+  } else { for (int k = 0; k < 3; k++) col[k] = lay[(2 + k) * lstride]; }                 // the static hit stands: its colour was shaded once
+  if (BG) {
+    lay[0] = best_t; lay[lstride] = __int_as_float(best_id);
+    for (int k = 0; k < 3; k++) lay[(2 + k) * lstride] = col[k];
+    const float ident[9] = {1, 0, 0, 0, 1, 0, 0, 0, 1};
+    float zt = best_t; int zid = -1; float zn[3] = {0, 0, 0}, zterm[3] = {0, 0, 0};
+    for (int z = 0; z < M.nzone; z++) {
+      float t, n[3];
+      if (ray_box(o, d, M.zone[z].pos, ident, M.zone[z].half, &t, n) && t < zt) { zt = t; zid = z; zn[0] = n[0]; zn[1] = n[1]; zn[2] = n[2]; }
+    }
+    if (zid >= 0) {
+      const float p[3] = {o[0] + zt * d[0], o[1] + zt * d[1], o[2] + zt * d[2]};
+      const float s = shade_factor(C, p, zn), al = M.zone[zid].rgba[3];
+      for (int k = 0; k < 3; k++) { zterm[k] = al * clamp01(M.zone[zid].rgba[k] * s); col[k] = zterm[k] + (1.0f - al) * col[k]; }
+      best_t = zt; best_id = M.ngeom + zid;
+    }
+    lay[5 * lstride] = zt; lay[6 * lstride] = __int_as_float(zid);
+    for (int k = 0; k < 3; k++) lay[(7 + k) * lstride] = zterm[k];
+  } else {
+    // the nearest zone in front of the static hit is the nearest zone in front of any nearer hit too, if it is in front of it at all
+    const float zt = lay[5 * lstride]; const int zid = __float_as_int(lay[6 * lstride]);
+    if (zid >= 0 && zt < best_t) {
+      const float al = M.zone[zid].rgba[3];
+      for (int k = 0; k < 3; k++) col[k] = lay[(7 + k) * lstride] + (1.0f - al) * col[k];
+      best_t = zt; best_id = M.ngeom + zid;
+    }
   }
   for (int k = 0; k < 3; k++) rgb_out[k] = (unsigned char)(col[k] * 255.0f + 0.5f);
   *depth_out = best_t; *seg_out = best_id;
@@ -240,6 +271,7 @@ __device__ void cast_pixel(const RModel& M, const TileGeoms& tg, const Plane4* _
 // One WARP per work item (scene, 32x8 tile); warps never synchronise with each other after the model is staged.
 struct WarpScratch { TileGeoms tg; __align__(16) unsigned char rgb[TH][TW * 3]; };
 
+template <bool BG>
 __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restrict__ gm, FrameArgs a) {
   __shared__ RModel M;
   __shared__ WarpScratch ws[NW];
@@ -257,24 +289,11 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
     if (item >= total) break;
     const int env = (int)(item / ntile), tile = (int)(item % ntile), tx0 = (tile % tiles_x) * TW, ty0 = (tile / tiles_x) * TH;
     bool hit = false;
-    if (!a.background) { const short4 r = a.rects[(size_t)env * RMAXG + lane]; hit = r.x <= r.z && r.x <= tx0 + TW - 1 && r.z >= tx0 && r.y <= ty0 + TH - 1 && r.w >= ty0; }
+    if (!BG) { const short4 r = a.rects[(size_t)env * RMAXG + lane]; hit = r.x <= r.z && r.x <= tx0 + TW - 1 && r.z >= tx0 && r.y <= ty0 + TH - 1 && r.w >= ty0; }
     const unsigned mask = __ballot_sync(0xffffffffu, hit);
     const size_t img = (size_t)env * M.H * M.W;
-    if (mask == 0 && !a.background) {
-      // background tile: 16-byte vector copies L2 -> HBM
-      if (a.rgb) for (int i = lane; i < TH * (TW * 3 / 16); i += 32) {
-        const int row = i / (TW * 3 / 16), c = i % (TW * 3 / 16);
-        const size_t off = ((size_t)(ty0 + row) * M.W + tx0) * 3 + (size_t)c * 16;
-        *reinterpret_cast<uint4*>(a.rgb + img * 3 + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_rgb + off));
-      }
-      for (int i = lane; i < TH * (TW / 4); i += 32) {
-        const int row = i / (TW / 4), c = i % (TW / 4);
-        const size_t off = (size_t)(ty0 + row) * M.W + tx0 + (size_t)c * 4;
-        if (a.depth) *reinterpret_cast<uint4*>(a.depth + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_depth + off));
-        if (a.seg) *reinterpret_cast<uint4*>(a.seg + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_seg + off));
-      }
-      n_copy++;
-    } else {
+    bool cast = BG || mask != 0;
+    if (cast) {
       __syncwarp();
       if ((mask >> lane) & 1u) {
         const int g = lane; const size_t pb = (size_t)env * a.pose_stride;
@@ -300,18 +319,18 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
       }
       __syncwarp();
       {   // plane lists of the hulls this tile's rays are tested against (b2p_render_cull.h): lanes across planes
-        int used = 0;
-        const int n_items = S.tg.n_order + M.n_static;
+        int used = 0, alive = 0;
+        const int n_items = BG ? M.n_static : S.tg.n_order;
         for (int it = 0; it < n_items; it++) {
-          const int g = it < S.tg.n_order ? S.tg.order[it] : M.static_ids[it - S.tg.n_order];
+          const int g = BG ? M.static_ids[it] : S.tg.order[it];
           const RGeom& G = M.geom[g];
-          if (G.type != GEOM_MESH) continue;
+          if (G.type != GEOM_MESH) { alive++; continue; }
           const int np = G.pnum;
           int total = -1;
           if (np <= 32 * PL_ROUNDS) {
             const bool dyn = !G.is_static;
-            b2p_render::TileRays R;
-            b2p_render::tile_rays(M.cam.pos, M.cam.mat, M.cam.f, M.cam.cx, M.cam.cy, tx0, ty0, TW, TH, dyn ? S.tg.pos[g] : G.spos, dyn ? S.tg.mat[g] : G.smat, R);
+            b2p_rcull::TileRays R;
+            b2p_rcull::tile_rays(M.cam.pos, M.cam.mat, M.cam.f, M.cam.cx, M.cam.cy, tx0, ty0, TW, TH, dyn ? S.tg.pos[g] : G.spos, dyn ? S.tg.mat[g] : G.smat, R);
             const Plane4* pl = reinterpret_cast<const Plane4*>(a.planes) + G.padr;
             int cls[PL_ROUNDS]; float tmn[PL_ROUNDS], tmx[PL_ROUNDS];
             float e_lo = -3.0e38f, x_hi = 3.0e38f;
@@ -319,37 +338,59 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
             for (int r = 0; r < PL_ROUNDS; r++) {
               const int i = r * 32 + lane; cls[r] = -1; tmn[r] = tmx[r] = 0.0f;
               if (i < np) {
-                cls[r] = b2p_render::plane_class(b2p_render::ld_plane(pl + i), R, &tmn[r], &tmx[r]);
-                if (cls[r] == b2p_render::PL_ENTRY) e_lo = fmaxf(e_lo, tmn[r]);
-                if (cls[r] == b2p_render::PL_EXIT) x_hi = fminf(x_hi, tmx[r]);
+                cls[r] = b2p_rcull::plane_class(b2p_rcull::ld_plane(pl + i), R, &tmn[r], &tmx[r]);
+                if (cls[r] == b2p_rcull::PL_ENTRY) e_lo = fmaxf(e_lo, tmn[r]);
+                if (cls[r] == b2p_rcull::PL_EXIT) x_hi = fminf(x_hi, tmx[r]);
               }
             }
             for (int o = 16; o; o >>= 1) { e_lo = fmaxf(e_lo, __shfl_xor_sync(0xffffffffu, e_lo, o)); x_hi = fminf(x_hi, __shfl_xor_sync(0xffffffffu, x_hi, o)); }
-            unsigned keep[PL_ROUNDS]; total = 0;
-#pragma unroll
-            for (int r = 0; r < PL_ROUNDS; r++) {
-              keep[r] = __ballot_sync(0xffffffffu, cls[r] >= 0 && b2p_render::plane_keep(cls[r], tmn[r], tmx[r], e_lo, x_hi));
-              total += __popc(keep[r]);
-            }
-            if (used + total > PL_CAP) total = -1;      // pool full: this hull keeps the full loop
+            if (b2p_rcull::tile_misses(e_lo, x_hi)) total = 0;       // the hull is not in this tile at all
             else {
-              int at = used;
+              unsigned keep[PL_ROUNDS]; total = 0;
 #pragma unroll
               for (int r = 0; r < PL_ROUNDS; r++) {
-                if ((keep[r] >> lane) & 1u) S.tg.plist[at + __popc(keep[r] & ((1u << lane) - 1u))] = (unsigned char)(r * 32 + lane);
-                at += __popc(keep[r]);
+                keep[r] = __ballot_sync(0xffffffffu, cls[r] >= 0 && b2p_rcull::plane_keep(cls[r], tmn[r], tmx[r], e_lo, x_hi));
+                total += __popc(keep[r]);
+              }
+              if (total == 0 || used + total > PL_CAP) total = -1;      // pool full (or nothing to leave out a list for): this hull keeps the full loop
+              else {
+                int at = used;
+#pragma unroll
+                for (int r = 0; r < PL_ROUNDS; r++) {
+                  if ((keep[r] >> lane) & 1u) S.tg.plist[at + __popc(keep[r] & ((1u << lane) - 1u))] = (unsigned char)(r * 32 + lane);
+                  at += __popc(keep[r]);
+                }
               }
             }
           }
           if (lane == 0) { S.tg.pl_off[g] = (short)used; S.tg.pl_cnt[g] = (short)total; }
           if (total > 0) used += total;
+          if (total != 0) alive++;
         }
+        if (!BG && alive == 0) cast = false;       // every listed geom was a hull that no ray of the tile meets: a background tile after all
       }
       __syncwarp();
+    }
+    if (!cast) {
+      // background tile: 16-byte vector copies L2 -> HBM
+      if (a.rgb) for (int i = lane; i < TH * (TW * 3 / 16); i += 32) {
+        const int row = i / (TW * 3 / 16), c = i % (TW * 3 / 16);
+        const size_t off = ((size_t)(ty0 + row) * M.W + tx0) * 3 + (size_t)c * 16;
+        *reinterpret_cast<uint4*>(a.rgb + img * 3 + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_rgb + off));
+      }
+      for (int i = lane; i < TH * (TW / 4); i += 32) {
+        const int row = i / (TW / 4), c = i % (TW / 4);
+        const size_t off = (size_t)(ty0 + row) * M.W + tx0 + (size_t)c * 4;
+        if (a.depth) *reinterpret_cast<uint4*>(a.depth + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_depth + off));
+        if (a.seg) *reinterpret_cast<uint4*>(a.seg + img + off) = __ldg(reinterpret_cast<const uint4*>(a.bg_seg + off));
+      }
+      n_copy++;
+    } else {
+      const size_t lstride = (size_t)M.W * M.H;
       for (int ly = 0; ly < TH; ly++) {
         float dep; int sg;
-        cast_pixel(M, S.tg, reinterpret_cast<const Plane4*>(a.planes), tx0 + lane, ty0 + ly, &S.rgb[ly][lane * 3], &dep, &sg);
         const size_t off = (size_t)(ty0 + ly) * M.W + tx0 + lane;
+        cast_pixel<BG>(M, S.tg, reinterpret_cast<const Plane4*>(a.planes), tx0 + lane, ty0 + ly, a.layers + off, lstride, &S.rgb[ly][lane * 3], &dep, &sg);
         if (a.depth) a.depth[img + off] = dep;
         if (a.seg) a.seg[img + off] = sg;
       }
@@ -370,17 +411,18 @@ __global__ void __launch_bounds__(NT) render_frame_kernel(const RModel* __restri
 struct b2p_render_s {
   int device, sms; long long launches;
   RModel hm; RModel* d_model; float4* d_planes; short4* d_rects; int rect_cap;
-  uint8_t* bg_rgb; float* bg_depth; int* bg_seg; unsigned long long* d_queue; unsigned long long* d_stats;
+  uint8_t* bg_rgb; float* bg_depth; int* bg_seg; float* d_layers; unsigned long long* d_queue; unsigned long long* d_stats;
 };
 
 static int launch_frame(b2p_render_s* h, FrameArgs& a, cudaStream_t st) {
   a.planes = h->d_planes; a.queue = h->d_queue; a.tile_stats = h->d_stats;
-  a.bg_rgb = h->bg_rgb; a.bg_depth = h->bg_depth; a.bg_seg = h->bg_seg;
+  a.bg_rgb = h->bg_rgb; a.bg_depth = h->bg_depth; a.bg_seg = h->bg_seg; a.layers = h->d_layers;
   RCK(cudaMemsetAsync(h->d_queue, 0, sizeof(unsigned long long), st));
   const long long total = (long long)a.n_env * (h->hm.W / TW) * (h->hm.H / TH);
   long long grid = (long long)h->sms * 3;
   if (grid > (total + NW - 1) / NW) grid = (total + NW - 1) / NW;
-  render_frame_kernel<<<(int)grid, NT, 0, st>>>(h->d_model, a);
+  if (a.background) render_frame_kernel<true><<<(int)grid, NT, 0, st>>>(h->d_model, a);
+  else render_frame_kernel<false><<<(int)grid, NT, 0, st>>>(h->d_model, a);
   RCK(cudaGetLastError());
   h->launches++;
   return B2P_OK;
@@ -414,7 +456,7 @@ int b2p_render_create(const void* blob, size_t nbytes, int device, b2p_render_ha
   RCK(cudaMalloc(&h->d_model, sizeof(RModel))); RCK(cudaMemcpy(h->d_model, &M, sizeof(RModel), cudaMemcpyHostToDevice));
   RCK(cudaMalloc(&h->d_planes, (size_t)(np + 1) * 16)); RCK(cudaMemcpy(h->d_planes, p, (size_t)np * 16, cudaMemcpyHostToDevice));
   const size_t px = (size_t)W * H;
-  RCK(cudaMalloc(&h->bg_rgb, px * 3)); RCK(cudaMalloc(&h->bg_depth, px * 4)); RCK(cudaMalloc(&h->bg_seg, px * 4));
+  RCK(cudaMalloc(&h->bg_rgb, px * 3)); RCK(cudaMalloc(&h->bg_depth, px * 4)); RCK(cudaMalloc(&h->bg_seg, px * 4)); RCK(cudaMalloc(&h->d_layers, px * 4 * NLAYER));
   RCK(cudaMalloc(&h->d_queue, sizeof(unsigned long long))); RCK(cudaMalloc(&h->d_stats, 16)); RCK(cudaMemset(h->d_stats, 0, 16));
   // static layer: ground, table, arm base, zones -- ray-cast once, then L2-resident
   FrameArgs a; memset(&a, 0, sizeof a);
@@ -430,7 +472,7 @@ int b2p_render_create(const void* blob, size_t nbytes, int device, b2p_render_ha
 int b2p_render_destroy(b2p_render_handle h) {
   if (!h) return B2P_OK;
   cudaSetDevice(h->device);
-  cudaFree(h->d_model); cudaFree(h->d_planes); cudaFree(h->d_rects); cudaFree(h->bg_rgb); cudaFree(h->bg_depth); cudaFree(h->bg_seg); cudaFree(h->d_queue); cudaFree(h->d_stats);
+  cudaFree(h->d_model); cudaFree(h->d_planes); cudaFree(h->d_rects); cudaFree(h->bg_rgb); cudaFree(h->bg_depth); cudaFree(h->bg_seg); cudaFree(h->d_layers); cudaFree(h->d_queue); cudaFree(h->d_stats);
   delete h;
   return B2P_OK;
 }

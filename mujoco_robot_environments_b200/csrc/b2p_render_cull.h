@@ -21,7 +21,7 @@
 #define RHD inline
 #endif
 
-namespace b2p_render {
+namespace b2p_rcull {
 
 struct Plane4 { float x, y, z, w; };     // outward unit normal (geom frame), offset: inside is n . p <= w
 
@@ -90,6 +90,9 @@ RHD int plane_class(const Plane4& P, const TileRays& R, float* tmin, float* tmax
   return den_hi < 0.0f ? PL_ENTRY : PL_EXIT;
 }
 RHD float cull_margin(float bound) { return 1e-4f * (1.0f + fabsf(bound)); }
+// every ray of the tile enters later than it leaves: the hull is not in this tile (the oriented-box rectangle that listed it is loose
+// for elongated links seen at an angle)
+RHD bool tile_misses(float entry_lo, float exit_hi) { return entry_lo > exit_hi + cull_margin(entry_lo) + cull_margin(exit_hi); }
 // entry_lo: max over the tile's entry planes of tmin (lower bound of every ray's entry parameter); exit_hi: min over its exit
 // planes of tmax (upper bound of every ray's exit parameter)
 RHD bool plane_keep(int cls, float tmin, float tmax, float entry_lo, float exit_hi) {
@@ -98,4 +101,4 @@ RHD bool plane_keep(int cls, float tmin, float tmax, float entry_lo, float exit_
   return true;
 }
 
-}  // namespace b2p_render
+}  // namespace b2p_rcull
