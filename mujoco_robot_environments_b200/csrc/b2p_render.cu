@@ -7,8 +7,9 @@
 //   * Per frame, a tiny bounds kernel projects the oriented bounding box of every moving geom (arm links, gripper, props) of
 //     every scene to a pixel rectangle.  The persistent frame kernel (148 x k CTAs, work items = (scene, 32x8 tile) pulled
 //     by one warp each from an atomic queue) then either COPIES the background tile with 16-byte vector loads / stores -- ~85 % of the tiles
-//     of a typical frame: pure HBM write streaming -- or ray-casts the tile against the static geoms plus the moving geoms
-//     whose rectangle overlaps it.
+//     of a typical frame: pure HBM write streaming -- or ray-casts the tile against the moving geoms whose rectangle overlaps
+//     it; what the ray finds among the static geoms and the zones comes from per-pixel background layers written with the
+//     static image (see cast_pixel), and every listed hull gets a per-tile list of the planes that can matter (b2p_render_cull.h).
 //   * The render model (<= 32 geoms, 6 zones, camera, lights: 5 kB) is staged once per CTA in shared memory; hull planes
 //     stay in global memory (L2).  RGB is staged per tile in shared memory so every global store is a full 16-byte vector.
 // The algorithmic HBM traffic is the output itself: 3 + 4 + 4 bytes per pixel.
