@@ -125,23 +125,31 @@ B2P_HD bool sp_dense_tail(const SpStruct& st, int b) { return b == st.nblk - 1 &
 #ifdef __CUDA_ARCH__
 // Branch-free on purpose: entries above the diagonal (j > i) hold don't-care values that are never read, so every lane
 // executes the same FMA stream and the row stays in registers (predicated updates made ptxas demote it to local memory).
+// Two lanes per row: lane = 16 h + i owns row i's columns j = 2 q + h (q = 0..7), so a column's rank-1 update is 8 - k/2 shuffle +
+// FMA pairs instead of 15 - k, and a row is loaded / stored in 8 steps instead of 16.  Every element sees the same operations in the
+// same order as with one lane per row (a_ij -= L_ik L_jk for k ascending, then the scaling by the pivot): the same bits.
 template <typename T>
 __device__ __forceinline__ void chol16_warp(T* A, int s0, int n, int lane) {
-  T a[16], fl = Num<T>::minval();
-  const int i = lane;
+  T a[8];
+  const int i = lane & 15, h = lane >> 4, rb = tri_idx(s0 + i, s0);
 #pragma unroll
-  for (int j = 0; j < 16; j++) { const bool in = i < n && j <= i; const T v = A[in ? tri_idx(s0 + i, s0 + j) : 0]; a[j] = in ? v : (j == i ? T(1) : T(0)); if (j == i) fl = pivot_floor(a[j]); }
+  for (int q = 0; q < 8; q++) { const int j = 2 * q + h; const bool in = i < n && j <= i; const T v = A[in ? rb + j : 0]; a[q] = in ? v : (j == i ? T(1) : T(0)); }
+  const T fl = pivot_floor(i < n ? A[rb + i] : T(1));               // relative to the row's ORIGINAL diagonal entry
 #pragma unroll
   for (int k = 0; k < 16; k++) {
-    const T akk = __shfl_sync(0xffffffffu, a[k] > fl ? a[k] : fl, k);   // lane k: its pivot, floored relative to its original diagonal
+    const int hk = k & 1, qk = k >> 1;
+    const T akk = __shfl_sync(0xffffffffu, a[qk] > fl ? a[qk] : fl, k + 16 * hk);   // lane (k, hk): its pivot, floored
     const T d = sqrt(akk);
     const T id = 1 / d;
-    a[k] = i == k ? d : a[k] * id;
+    T lik = __shfl_sync(0xffffffffu, a[qk], i + 16 * hk);                            // a_ik of my row, from the half that owns column k
+    lik = i == k ? d : lik * id;
+    a[qk] = h == hk ? lik : a[qk];
+    if (hk == 0) { const T ljk = __shfl_sync(0xffffffffu, lik, 2 * qk + h); a[qk] = h == 1 ? a[qk] - lik * ljk : a[qk]; }   // column k + 1 (the odd half's)
 #pragma unroll
-    for (int j = k + 1; j < 16; j++) a[j] -= a[k] * __shfl_sync(0xffffffffu, a[k], j);
+    for (int q = qk + 1; q < 8; q++) a[q] -= lik * __shfl_sync(0xffffffffu, lik, 2 * q + h);
   }
 #pragma unroll
-  for (int j = 0; j < 16; j++) if (i < n && j <= i) A[tri_idx(s0 + i, s0 + j)] = a[j];
+  for (int q = 0; q < 8; q++) { const int j = 2 * q + h; if (i < n && j <= i) A[rb + j] = a[q]; }
 }
 // x_tail <- (L L')^-1 x_tail for the dense tail block; also applies the backward updates to the np coupled earlier columns
 template <typename T>
