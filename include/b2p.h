@@ -73,7 +73,8 @@ int b2p_set_out_mask(b2p_handle h, int mask);
 /* Constraint solver of the stepping calls (mjOption.solver; the reference never sets it, tasks/rearrangement.py:77-78, so MuJoCo's
  * default -- Newton -- is this library's default too).  PGS is MuJoCo's projected Gauss-Seidel on the dual problem (elliptic cones),
  * offered as the independent minimiser of the same objective and because BASELINE.json names it; it runs as its own kernel
- * instantiation and is several times slower than Newton on this model class. */
+ * instantiation and is several times slower than Newton on this model class.  Refused (B2P_ERR_ARG) for a model with a pyramidal cone or
+ * a sphere / cylinder geom on the tree (the drawing scene of tasks/lasa_draw.py): those run in the class-capable Newton kernels only. */
 enum { B2P_SOLVER_NEWTON = 0, B2P_SOLVER_PGS = 1 };
 int b2p_set_solver(b2p_handle h, int solver);
 /* prop_size: [n_env][MAXPROP][3] half sizes (NULL = model default); prop_active: [n_env][MAXPROP] (NULL = all) */

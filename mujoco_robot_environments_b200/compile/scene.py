@@ -75,6 +75,44 @@ def build_scene(prop_half_sizes: Sequence[Sequence[float]], menagerie: str = DEF
     return arena
 
 
+# actuator_config/position.yaml: <general biastype="affine"> position servos, per joint (ctrlrange, forcerange, kp, kv)
+POSITION_ACTUATORS = [("-2.8973 2.8973", "-87 87", 4500, 450), ("-1.7628 1.7628", "-87 87", 4500, 450), ("-2.8973 2.8973", "-87 87", 3500, 350),
+                      ("-3.0718 -0.0698", "-87 87", 3500, 350), ("-2.8973 2.8973", "-12 12", 2000, 200), ("-0.0175 3.7525", "-12 12", 2000, 200),
+                      ("-2.8973 2.8973", "-12 12", 2000, 200)]
+
+
+def build_draw_scene(menagerie: str = DEFAULT_MENAGERIE, physics_dt=0.01, gravity=(0.0, 0.0, -9.8), actuators="motor",
+                     arm_ctrlrange=((-87, 87),) * 4 + ((-12, 12),) * 3, arm_xml="franka_emika_panda/panda_nohand.xml") -> Model:
+    """LasaDrawEnv.__init__ step by step (reference tasks/lasa_draw.py:60-176; config/lasa.yaml: physics_dt 0.01): empty arena ->
+    1 x 1 x 0.2 table at (0.4, 0, 0.2) -> the arm WITHOUT a gripper, a cylinder tool piece (radius 0.015, half height 0.05) on the
+    attachment body -> base at (0, 0, 0.4).  Without the gripper's XML nothing sets ``cone``, so the scene runs MuJoCo's default
+    pyramidal cone.  The mocap target and the draw plane have contype = conaffinity = 0 and no mass: they do not enter the physics
+    and are left out.  ``actuators``: "motor" (generate_default_config) or "position" (generate_deployment_config:
+    robots/arm/actuator_config=position)."""
+    arena = Model("arena")
+    arena.option.update(timestep=repr(physics_dt), gravity=_fmt(float(g) for g in gravity))
+    arena.world.geoms.append(dict(name="ground", type="plane", size="2 2 2", friction="0.4"))
+    arena.world.sites.append(dict(name="table_center", pos="0.4 0.0 0.2"))
+    arena.attach(_rectangle("table", (1.0, 1.0, 0.2), 10, 0.0, 0.0), "table_center")          # lasa_draw.py:91-108
+    arm = Model.from_path(os.path.join(menagerie, arm_xml))
+    arm.actuators = []
+    for i, j in enumerate(arm.all_joints()):                                                   # franka_emika.py:66-103
+        if actuators == "motor":
+            lo, hi = arm_ctrlrange[i]
+            arm.actuators.append(dict(type="motor", name="actuator%d" % (i + 1), joint=j["name"], ctrlrange=_fmt((lo, hi))))
+        else:
+            cr, fr, kp, kv = POSITION_ACTUATORS[i]
+            arm.actuators.append(dict(type="general", name="actuator%d" % (i + 1), joint=j["name"], dyntype="none", biastype="affine",
+                                      ctrlrange=cr, forcerange=fr, gainprm=repr(float(kp)), biasprm="0 %r %r" % (-float(kp), -float(kv))))
+    body, _ = arm.find_site("attachment_site")
+    body.geoms.append(dict(name="tool", type="cylinder", size="0.015 0.05", pos="0 0 0.05"))   # lasa_draw.py:113-120 (MuJoCo's geom defaults)
+    arena.world.sites.append(dict(name="robot_base", pos="0.0 0.0 0.4"))
+    arena.attach(arm, "robot_base")
+    arena.nprop = 0
+    arena.autolimits = True
+    return arena
+
+
 # ----------------------------------------------------------------------------- compiler
 _GEOM_TYPES = {"plane": B.GEOM_PLANE, "sphere": B.GEOM_SPHERE, "cylinder": B.GEOM_CYLINDER,
                "box": B.GEOM_BOX, "mesh": B.GEOM_MESH}
@@ -145,11 +183,17 @@ def _body_inertial(b: Body, meshes: _MeshCache):
             gm = float(g["mass"]) if "mass" in g else float(g.get("density", 1000)) * mi["vol"]
             Ig = R @ (mi["inertia"] * gm / mi["vol"]) @ R.T
             c = gpos + R @ mi["com"]
+        elif gtype == "cylinder":   # size = (radius, half height), axis z
+            s = _floats(g["size"])
+            vol = np.pi * s[0] ** 2 * 2 * s[1]
+            gm = float(g["mass"]) if "mass" in g else float(g.get("density", 1000)) * vol
+            Ig = gm * np.diag([s[0] ** 2 / 4 + s[1] ** 2 / 3, s[0] ** 2 / 4 + s[1] ** 2 / 3, s[0] ** 2 / 2])
+            c = gpos
         elif gtype == "plane":
             continue
         else:
             raise NotImplementedError("inertia of geom type " + gtype)
-        if gtype == "box":
+        if gtype in ("box", "cylinder"):
             Ig = R @ Ig @ R.T
         if gm <= 0:
             continue
@@ -340,6 +384,9 @@ def _flatten(model: Model, meshes: _MeshCache, geom_order: Optional[List[str]] =
             aabb = np.concatenate([np.zeros(3), size]); rbound = np.linalg.norm(size)
         elif gtype == "plane":
             aabb = np.zeros(6); rbound = 0.0
+        elif gtype == "cylinder":   # size = (radius, half height, 0) as in MuJoCo
+            half = np.array([size[0], size[0], size[1]])
+            aabb = np.concatenate([np.zeros(3), half]); rbound = np.hypot(size[0], size[1])
         else:
             raise NotImplementedError("collision geom type " + gtype)
         A["geom_type"].append(_GEOM_TYPES[gtype]); A["geom_bodyid"].append(bi)
@@ -544,7 +591,8 @@ def compile_model(model: Model, fuse: bool = True):
     first_prop_dof = A["prop_dofadr"][0] if nprop else counts["nv"]
     counts["narm"] = 7; counts["ngrip"] = first_prop_dof - 7
     counts["site_attachment"] = names["site"].index("panda nohand/attachment_site")
-    counts["site_pinch"] = names["site"].index("panda nohand/robotiq_2f85/pinch")
+    pinch = "panda nohand/robotiq_2f85/pinch"
+    counts["site_pinch"] = names["site"].index(pinch) if pinch in names["site"] else counts["site_attachment"]   # no gripper: the arm's own site
     counts["geom_table"] = names["geom"].index("table/table"); counts["geom_plane"] = names["geom"].index("ground")
     o = model.option
     grav = _floats(o.get("gravity"), 3, [0, 0, -9.81])
@@ -563,5 +611,12 @@ def compile_rearrangement(n_props=4, prop_half_size=0.0155, fuse=True, **scene_k
     """Canonical padded scene: ``n_props`` cube props (per-env sizes override the blob's)."""
     sizes = [[prop_half_size] * 3 for _ in range(n_props)]
     model = build_scene(sizes, **scene_kw)
+    counts, opts, A, names = compile_model(model, fuse=fuse)
+    return B.pack(counts, opts, A), names
+
+
+def compile_lasa_draw(fuse=True, **scene_kw):
+    """The drawing scene of tasks/lasa_draw.py: 7 arm dofs, no gripper, no props, one cylinder tool piece, pyramidal cone."""
+    model = build_draw_scene(**scene_kw)
     counts, opts, A, names = compile_model(model, fuse=fuse)
     return B.pack(counts, opts, A), names

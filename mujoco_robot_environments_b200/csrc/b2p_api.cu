@@ -156,7 +156,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = h->prop_type;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (T*)h->d_w6pool, (T*)h->d_xpool, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};
-  a.work = h->d_work; a.order = nullptr; a.solver = h->solver;
+  a.work = h->d_work; a.order = nullptr; a.solver = h->solver; a.pyramidal = model_needs_classes(h->hmodel);
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
     CK(cudaGetLastError());
@@ -199,7 +199,7 @@ static int launch_noalloc(b2p_handle_s* h, void* scratch, void* state, const voi
   a.ctrl = (const T*)(ctrl ? ctrl : h->d_zero_ctrl); a.env_mask = h->env_mask;
   a.n_env = h->n_env; a.state = (T*)state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = nullptr;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
-  a.work = nullptr; a.order = nullptr; a.solver = B2P_SOLVER_NEWTON;
+  a.work = nullptr; a.order = nullptr; a.solver = B2P_SOLVER_NEWTON; a.pyramidal = model_needs_classes(h->hmodel);
   int* next_env = (int*)scratch;                                                     // cleared by the launch itself (cudaMemsetAsync on the stream)
   T* jovf = (T*)((unsigned char*)scratch + NOALLOC_JOVF_OFF);                         // no need to clear: a row is written before it is read
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, jovf, nullptr, nullptr, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};
@@ -266,6 +266,7 @@ int b2p_bind_out(b2p_handle h, void* out) { if (!h) return B2P_ERR_ARG; h->out =
 int b2p_set_out_mask(b2p_handle h, int mask) { if (!h || mask < 0 || mask > OUT_ALL) return fail(B2P_ERR_ARG, "b2p_set_out_mask: bad argument"); h->out_mask = mask; return B2P_OK; }
 int b2p_set_solver(b2p_handle h, int solver) {
   if (!h || (solver != B2P_SOLVER_NEWTON && solver != B2P_SOLVER_PGS)) return fail(B2P_ERR_ARG, "b2p_set_solver: bad argument");
+  if (solver == B2P_SOLVER_PGS && model_needs_classes(h->hmodel)) return fail(B2P_ERR_ARG, "b2p_set_solver: the PGS instantiation covers the elliptic cone and box / hull geoms only");
   if (solver == B2P_SOLVER_PGS && h->prop_type) return fail(B2P_ERR_ARG, "b2p_set_solver: PGS covers condim 1 and 3; it is not offered while prop classes are bound (b2p_set_env_prop_types)");
   if (solver == B2P_SOLVER_PGS && !h->d_xpool) {   // M^-1 J' per resident warp, J's packed layout
     CK(cudaSetDevice(h->device));
@@ -277,6 +278,7 @@ int b2p_set_solver(b2p_handle h, int solver) {
 int b2p_set_env_params(b2p_handle h, const void* prop_size, const uint8_t* prop_active) { if (!h) return B2P_ERR_ARG; h->prop_size = prop_size; h->prop_active = prop_active; return B2P_OK; }
 int b2p_set_env_prop_types(b2p_handle h, const uint8_t* prop_type) {
   if (!h) return B2P_ERR_ARG;
+  if (prop_type && h->hmodel.cone == B2P_CONE_PYRAMIDAL) return fail(B2P_ERR_ARG, "b2p_set_env_prop_types: prop classes (condim-6 contacts) are not offered with a pyramidal cone");
   if (prop_type && h->solver == B2P_SOLVER_PGS) return fail(B2P_ERR_ARG, "b2p_set_env_prop_types: not offered with the PGS solver (condim 1 and 3 only)");
   h->prop_type = prop_type; return B2P_OK;
 }

@@ -662,8 +662,8 @@ B2P_HDN void collide(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>& s
       const unsigned pk = m.pair_pk[p]; const int g1 = pk & 255u, g2 = pk >> 8, t1 = s.gtype[g1], t2 = s.gtype[g2];
       md = pair_md(m, g, s, p, g1, g2, full_contacts);
       const int pr1 = m.geom_prop[g1], pr2 = m.geom_prop[g2];
-      const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1];
-      const T* sz2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2];
+      const T* sz1 = pr1 >= 0 ? s.psize[pr1] : m.geom_size[g1] + (C && t1 == B2P_GEOM_CYLINDER);    // tree cylinder: (r, r, h) in the model, (r, h) from + 1
+      const T* sz2 = pr2 >= 0 ? s.psize[pr2] : m.geom_size[g2] + (C && t2 == B2P_GEOM_CYLINDER);
 #if defined(B2P_PROF_NARROW) && defined(__CUDA_ARCH__)
       const long long nt0_ = clock64(); int nkind_ = 0;
 #endif

@@ -11,7 +11,7 @@
 
 namespace b2p {
 
-enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2 };
+enum { ROW_EQ = 0, ROW_LIMIT = 1, ROW_CONTACT = 2, ROW_PYR = 3 };   // ROW_PYR: one edge of a pyramidal friction cone -- a scalar inequality row like a limit (the solver only tells EQ and CONTACT apart)
 enum { ST_SATISFIED = 0, ST_QUADRATIC = 1, ST_CONE = 2 };
 enum { FLAG_BADQPOS = 1, FLAG_BADQVEL = 2, FLAG_BADQACC = 4, FLAG_CONTACTFULL = 8, FLAG_EFCFULL = 16, FLAG_CANDFULL = 32, FLAG_SOLVER_MAXITER = 64 };
 enum { MODE_PHYSICS = 0, MODE_OSC = 1, MODE_SETTLE = 2, MODE_FORWARD = 3, MODE_PLACE = 4 };

@@ -79,7 +79,7 @@ constexpr int NPCLASS = 2;       // re-classable prop colliders beyond the box: 
 template <typename T>
 struct alignas(16) DevModel {
   int nv, nq, ntd, ntb, nprop, ngeom, npair, neq, nu, nlevel;
-  int iterations, ls_iterations, integrator, ccd_iterations, site_body[2], fk_rounds, pad_[1];   // fk_rounds = ceil(log2(tree depth))
+  int iterations, ls_iterations, integrator, ccd_iterations, site_body[2], fk_rounds, cone;   // fk_rounds = ceil(log2(tree depth))
   T timestep, gravity[3], impratio, tolerance, ls_tolerance, ccd_tolerance, meaninertia, ref[3];
   // tree
   int tb_parent[MAXTB], level_start[MAXLEVEL + 1], level_body[MAXTB], child_start[MAXTB + 1], child_list[MAXTB];
@@ -116,6 +116,13 @@ struct alignas(16) DevModel {
 };
 
 // ------------------------------------------------------------------------------------------ host builder
+// A model whose rows or geoms only the class-capable instantiations (C = true) carry: a pyramidal cone, or a sphere / cylinder geom on
+// the tree.  Such a model is always launched with them, whether or not prop classes are bound (step_launch, tests/hostemu).
+template <typename M> inline bool model_needs_classes(const M& m) {
+  if (m.cone == B2P_CONE_PYRAMIDAL) return true;
+  for (int g = 0; g < m.ngeom; g++) if (m.geom_type[g] == B2P_GEOM_SPHERE || m.geom_type[g] == B2P_GEOM_CYLINDER) return true;
+  return false;
+}
 struct HostTables {              // global-memory tables, always fp64 on host; converted on upload
   std::vector<double> mesh_vert, geom_dop; std::vector<int> mesh_nbradr, mesh_nbrnum, mesh_nbr, geom_start;
   std::vector<int> pair_g1, pair_g2; std::vector<double> pair_param;  // 12 doubles per pair
@@ -142,12 +149,12 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
   if (nprop > MAXP || ntd > MAXTD - 1 || ntb > MAXTB || ngeom > MAXG || nv != ntd + 6 * nprop) return "model exceeds kernel maxima";
   if (b.C(B2PM_C_NEQ) > MAXEQ || b.C(B2PM_C_NU) > MAXU) return "too many equalities / actuators";
   if (b.C(B2PM_C_NPAIR) > MAXPAIR) return "too many geom pairs";
-  if ((int)b.opt[B2PM_O_CONE] != B2P_CONE_ELLIPTIC) return "only elliptic cones are implemented";
+  if ((int)b.opt[B2PM_O_CONE] != B2P_CONE_ELLIPTIC && (int)b.opt[B2PM_O_CONE] != B2P_CONE_PYRAMIDAL) return "unknown friction cone";
   m.nv = nv; m.nq = b.C(B2PM_C_NQ); m.ntd = ntd; m.ntb = ntb; m.nprop = nprop; m.ngeom = ngeom; m.npair = b.C(B2PM_C_NPAIR);
   m.neq = b.C(B2PM_C_NEQ); m.nu = b.C(B2PM_C_NU);
   m.timestep = b.opt[B2PM_O_TIMESTEP]; m.gravity[0] = b.opt[B2PM_O_GRAVITY_X]; m.gravity[1] = b.opt[B2PM_O_GRAVITY_Y]; m.gravity[2] = b.opt[B2PM_O_GRAVITY_Z];
   m.impratio = b.opt[B2PM_O_IMPRATIO]; m.tolerance = b.opt[B2PM_O_TOLERANCE]; m.ls_tolerance = b.opt[B2PM_O_LS_TOLERANCE];
-  m.iterations = (int)b.opt[B2PM_O_ITERATIONS]; m.ls_iterations = (int)b.opt[B2PM_O_LS_ITERATIONS]; m.integrator = (int)b.opt[B2PM_O_INTEGRATOR];
+  m.iterations = (int)b.opt[B2PM_O_ITERATIONS]; m.ls_iterations = (int)b.opt[B2PM_O_LS_ITERATIONS]; m.integrator = (int)b.opt[B2PM_O_INTEGRATOR]; m.cone = (int)b.opt[B2PM_O_CONE];
   m.ccd_iterations = (int)b.opt[B2PM_O_CCD_ITERATIONS]; m.ccd_tolerance = b.opt[B2PM_O_CCD_TOLERANCE]; m.meaninertia = b.opt[B2PM_O_MEANINERTIA];
   const int *par = b.I(B2PM_F_BODY_PARENTID), *jnum = b.I(B2PM_F_BODY_JNTNUM), *jadr = b.I(B2PM_F_BODY_JNTADR), *jtype = b.I(B2PM_F_JNT_TYPE);
   const int *dadr = b.I(B2PM_F_BODY_DOFADR), *bprop = b.I(B2PM_F_BODY_PROPID);
@@ -219,6 +226,9 @@ inline std::string build_model(const void* blob, size_t nbytes, DevModel<double>
     cp(m.geom_size[g], b.D(B2PM_F_GEOM_SIZE) + 3 * g, 3); cp(m.geom_pos[g], b.D(B2PM_F_GEOM_POS) + 3 * g, 3); cp(m.geom_quat[g], b.D(B2PM_F_GEOM_QUAT) + 4 * g, 4);
     m.geom_rbound[g] = b.D(B2PM_F_GEOM_RBOUND)[g]; cp(m.geom_invweight0[g], b.D(B2PM_F_GEOM_INVWEIGHT0) + 2 * g, 2);
     cp(m.geom_aabb_c[g], b.D(B2PM_F_GEOM_AABB) + 6 * g, 3);
+    // a cylinder on the tree (the drawing scene's tool piece): MuJoCo's size is (radius, half height, 0); stored here as (r, r, h) so that
+    // the bounding-box tests read their half extents from geom_size like a box or a hull, and the narrow phase reads (r, h) at geom_size + 1
+    if (gt[g] == B2P_GEOM_CYLINDER && gp[g] < 0) { m.geom_size[g][2] = m.geom_size[g][1]; m.geom_size[g][1] = m.geom_size[g][0]; }
     if (gt[g] == B2P_GEOM_MESH) for (int k = 0; k < 3; k++) if (std::fabs(b.D(B2PM_F_GEOM_AABB)[6 * g + 3 + k] - m.geom_size[g][k]) > 1e-9) return "mesh geom_size must equal its bounding-box half extents";
   }
   const int sid[2] = {b.C(B2PM_C_SITE_ATTACHMENT), b.C(B2PM_C_SITE_PINCH)};
@@ -342,7 +352,7 @@ inline void convert_model(const DevModel<double>& s, DevModel<T>& d) {
 #define CI(f) std::memcpy(&d.f, &s.f, sizeof d.f)
 #define CR(f) do { const double* a = (const double*)&s.f; T* o = (T*)&d.f; for (size_t i = 0; i < sizeof(s.f) / sizeof(double); i++) o[i] = (T)a[i]; } while (0)
   CI(nv); CI(nq); CI(ntd); CI(ntb); CI(nprop); CI(ngeom); CI(npair); CI(neq); CI(nu); CI(nlevel);
-  CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body); CI(fk_rounds);
+  CI(iterations); CI(ls_iterations); CI(integrator); CI(ccd_iterations); CI(site_body); CI(fk_rounds); CI(cone);
   CR(timestep); CR(gravity); CR(impratio); CR(tolerance); CR(ls_tolerance); CR(ccd_tolerance); CR(meaninertia); CR(ref);
   CI(tb_parent); CI(level_start); CI(level_body); CI(child_start); CI(child_list); CI(anc_mask);
   CR(tb_pos); CR(tb_quat); CR(tb_ipos); CR(tb_iquat); CR(tb_mass); CR(tb_inertia); CR(tb_invweight0); CR(tb_anchor); CR(tb_axis);

@@ -70,8 +70,10 @@ B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T, C>& s, int r, const T* x
   if (a == 0) {
 #pragma unroll
     for (int k = 0; k < MAXTD; k += 4) {
-      v0 += (k < wa ? j[k] : T(0)) * x[k]; v1 += (k + 1 < wa ? j[k + 1] : T(0)) * x[k + 1];
-      v2 += (k + 2 < wa ? j[k + 2] : T(0)) * x[k + 2]; v3 += (k + 3 < wa ? j[k + 3] : T(0)) * x[k + 3];
+      // the whole product is guarded, not just the Jacobian entry: with fewer than 16 dofs in the model (the drawing scene has 7) x[k]
+      // past the row is whatever the shared memory held, and 0 * NaN is NaN
+      v0 += (k < wa ? j[k] * x[k] : T(0)); v1 += (k + 1 < wa ? j[k + 1] * x[k + 1] : T(0));
+      v2 += (k + 2 < wa ? j[k + 2] * x[k + 2] : T(0)); v3 += (k + 3 < wa ? j[k + 3] * x[k + 3] : T(0));
     }
   } else {
     v0 = j[0] * x[sa] + j[4] * x[sa + 4]; v1 = j[1] * x[sa + 1] + j[5] * x[sa + 5]; v2 = j[2] * x[sa + 2]; v3 = j[3] * x[sa + 3];
@@ -116,6 +118,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
         id = it - m.neq - nlim;
         if (s.c_dist[id] < s.c_incl[id]) {
           kind = ROW_CONTACT; nr = C ? s.c_dim[id] : 3;
+          if (C && m.cone == B2P_CONE_PYRAMIDAL) { kind = ROW_PYR; nr = 4; }      // 2 (condim - 1) pyramid edges, condim 3
           // segment assignment: tree -> A; a prop -> B if A is taken (by the tree or by the other prop)
           const int p = s.c_pair[id], b1 = m.geom_body[g.pair_g1[p]], b2 = m.geom_body[g.pair_g2[p]];
           const bool t1 = b1 > 0 && b1 < PROP_BODY0, t2 = b2 > 0 && b2 < PROP_BODY0;
@@ -131,22 +134,36 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
     const int r0 = base + ofs, j0 = jbase + jofs;
     if (nr > 0 && (r0 + nr > Pool<T>::EFC || j0 + nr * w > Pool<T>::JP)) {   // dropped items always form a suffix (offsets include dropped ones)
       if (r0 < first_drop) first_drop = r0;
-      if (kind == ROW_CONTACT) s.c_row[id] = -1;
+      if (kind == ROW_CONTACT || kind == ROW_PYR) s.c_row[id] = -1;
       s.flags |= FLAG_EFCFULL; nr = 0;
     }
     if (nr > 0) {
       const bool in_smem = j0 + nr * w <= Pool<T>::JPS;   // an item's rows never straddle the two pools
       for (int q = 0; q < nr; q++) {
-        s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)id; s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
+        s.row_type[r0 + q] = (signed char)kind; s.row_id[r0 + q] = (short)((C && kind == ROW_PYR) ? 4 * id + q : id); s.row_a[r0 + q] = (signed char)ba; s.row_b[r0 + q] = (signed char)bb;
         s.joff[r0 + q] = (short)(in_smem ? j0 + q * w : -(j0 + q * w) - 1);
       }
       if (kind == ROW_CONTACT) s.c_row[id] = (short)r0;
+      else if (C && kind == ROW_PYR) s.c_row[id] = -1;      // no cone block: the edges are scalar rows of their own
       else if (kind == ROW_EQ) s.eq_row0[id] = (short)r0;
       if (bb >= 0) {   // solver blocks: prop p -> p, tree -> nprop
         const int sa = ba == 0 ? m.nprop : ba - 1, sb = bb - 1, hi = sa > sb ? sa : sb, lo = sa > sb ? sb : sa;
         pairs |= 1u << (hi * SP_MAXBLK + lo);
       }
     }
+    if (C && m.cone == B2P_CONE_PYRAMIDAL) {   // a pyramid edge is an item of its own in the lists: an item's walkers take a non-contact row for one row
+      for (int b = 0; b < nblk; b++) {
+        const bool f = nr > 0 && (ba == b || bb == b); const int cnt = f ? (kind == ROW_PYR ? nr : 1) : 0;
+        int nt; const int rk = block_scan(c, cnt, nt);
+        const int cap = b == 0 ? Pool<T>::EFC : MAXCON;
+        for (int q = 0; q < cnt; q++) {
+          const int at = nb[b] + rk + q;
+          if (at >= cap) { s.flags |= FLAG_EFCFULL; continue; }
+          if (b == 0) s.brow0[at] = (unsigned char)(r0 + q); else s.browp[b - 1][at] = (unsigned char)(r0 + q);
+        }
+        nb[b] += nt; if (nb[b] > cap) nb[b] = cap;
+      }
+    } else
     for (int b = 0; b < nblk; b++) {   // per-block item lists, in row order
       int nt; const bool f = nr > 0 && (ba == b || bb == b); const int rk = block_rank(c, f, nt);
       if (f) { if (b == 0) s.brow0[nb[0] + rk] = (unsigned char)r0; else s.browp[b - 1][nb[b] + rk] = (unsigned char)r0; }
@@ -204,6 +221,25 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
       J0[j] = T(-side);
       solref = m.jnt_solref[j]; solimp = m.jnt_solimp[j]; pos_imp = dist; margin = m.jnt_margin[j]; diag = m.dof_invweight0[j];
       posterm = dist - margin;
+    } else if (C && kind == ROW_PYR) {
+      // One edge of MuJoCo's pyramidal cone (mj_instantiateContact / mj_makeImpedance): J = J_normal +- mu J_tangent_k -- the point
+      // Jacobian is linear in the axis, so the edge is a "normal row" along n +- mu t_k; it carries the contact's distance, so K, B and
+      // the impedance are the normal's; diagApprox = tran (1 + mu^2); every edge then gets R_py = 2 mu_reg^2 R_first (below).
+      const int cid = id >> 2, q = id & 3, k = 1 + (q >> 1);
+      const int p = s.c_pair[cid], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
+      if (!s.reclassed) mx.pp = g.pair_param[p]; else pair_mix(m, g, s, p, g1, g2, mx);
+      seg_n = (b1 >= PROP_BODY0 && 1 + b1 - PROP_BODY0 == bb) ? block_width(m, ba) : 0; seg_p = (b2 >= PROP_BODY0 && 1 + b2 - PROP_BODY0 == bb) ? block_width(m, ba) : 0;
+      const T iw1 = b1 >= PROP_BODY0 ? s.pinvw[b1 - PROP_BODY0][0] : m.geom_invweight0[g1][0], iw2 = b2 >= PROP_BODY0 ? s.pinvw[b2 - PROP_BODY0][0] : m.geom_invweight0[g2][0];
+      const T mu = s.c_fric[cid], sg = (q & 1) ? T(-1) : T(1);
+      solref = mx.pp.solref; solimp = mx.pp.solimp; pos_imp = s.c_dist[cid]; margin = s.c_incl[cid];
+      diag = (iw1 + iw2) + mu * mu * (iw1 + iw2);                                   // of the FIRST edge (all edges of a condim-3 contact have this value)
+      const T* fr = s.c_frame[cid];
+      for (int e = 0; e < 3; e++) ax[e] = fr[e] + sg * mu * fr[3 * k + e];
+      cp3(pt_p, s.c_pos[cid]); cp3(pt_n, s.c_pos[cid]);
+      body_p = b2; body_n = b1;
+      posterm = s.c_dist[cid] - s.c_incl[cid];
+      rscale = T(-1);                                                               // marks the edge for the R_py step below
+      mu_of = -1 - cid;
     } else {
       const int q = r - s.c_row[id];
       const int p = s.c_pair[id], g1 = g.pair_g1[p], g2 = g.pair_g2[p], b1 = m.geom_body[g1], b2 = m.geom_body[g2];
@@ -229,6 +265,7 @@ B2P_HDN void make_rows(const DevModel<T>& m, const Globals<T>& g, Scratch<T, C>&
       const T mv = Num<T>::minval(), R1 = R / (m.impratio > mv ? m.impratio : mv);
       if (mu_of >= 0) s.c_mu[mu_of] = s.c_fric[mu_of] * sqrt(R1 / R);
       if (fric) { K = 0; R = (C && rot) ? R1 * rscale : R1; }
+      if (C && rscale < 0) { const T mur = s.c_fric[-1 - mu_of] * sqrt(R1 / R); R = 2 * mur * mur * R; }      // pyramid edge
     }
     if (C && rot) { add_jac_rot(m, s, J0, seg_p, body_p, ax, T(1)); add_jac_rot(m, s, J0, seg_n, body_n, ax, T(-1)); }
     else { add_jac(m, s, J0, seg_p, body_p, pt_p, ax, T(1)); add_jac(m, s, J0, seg_n, body_n, pt_n, ax, T(-1)); }   // body 0: nothing to add

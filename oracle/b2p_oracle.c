@@ -1007,7 +1007,7 @@ static void make_constraint(orc_t* o) {
       }
     }
   }
-  /* contacts (elliptic cones) */
+  /* contacts (elliptic cones; pyramidal below) */
   const int* gb = FI(o, B2PM_F_GEOM_BODYID);
   for (int ci = 0; ci < o->ncon; ci++) {
     contact_t* c = &o->con[ci];
@@ -1017,6 +1017,29 @@ static void make_constraint(orc_t* o) {
     double tran = o->geom_invweight0[2 * c->geom1] + o->geom_invweight0[2 * c->geom2];
     double rot = o->geom_invweight0[2 * c->geom1 + 1] + o->geom_invweight0[2 * c->geom2 + 1];
     c->efc_address = o->nefc;
+    if (o->cone == B2P_CONE_PYRAMIDAL && c->dim > 1) {
+      /* MuJoCo's pyramidal cone (mj_instantiateContact / mj_makeImpedance, restated from the published algorithm): 2 (dim - 1) scalar
+       * inequality rows per contact, one per pyramid edge, J = J_normal +- mu_k J_tangent_k; every edge carries the contact's
+       * distance (so K, B and the impedance are the normal row's); diagApprox = tran + mu_k^2 (tran | rot); and after the impedance
+       * pass all edges share R_py = 2 mu_reg^2 R_first with mu_reg = mu_1 / sqrt(impratio).  In the solver an edge is an ordinary
+       * inequality row (force >= 0), which is what ROW_LIMIT means there. */
+      if (o->nefc + 2 * (c->dim - 1) > ORC_MAXEFC) { c->efc_address = -1; c->exclude = 2; continue; }
+      int r0 = o->nefc;
+      for (int k = 1; k < c->dim; k++) for (int sgn = 1; sgn >= -1; sgn -= 2) {
+        const double mu = c->friction[k - 1];
+        int r = add_row(o, ROW_LIMIT, ci, c->dist, c->includemargin, tran + mu * mu * (k < 3 ? tran : rot));
+        const double* n = c->frame; const double* ax = c->frame + 3 * (k % 3);
+        const double *ja = k < 3 ? jp1 : jr1, *jb = k < 3 ? jp2 : jr2;
+        for (int i = 0; i < nv; i++)
+          o->efc_J[(size_t)r * nv + i] = n[0] * (jp2[i] - jp1[i]) + n[1] * (jp2[nv + i] - jp1[nv + i]) + n[2] * (jp2[2 * nv + i] - jp1[2 * nv + i])
+                                         + sgn * mu * (ax[0] * (jb[i] - ja[i]) + ax[1] * (jb[nv + i] - ja[nv + i]) + ax[2] * (jb[2 * nv + i] - ja[2 * nv + i]));
+        finish_row(o, r, c->solref, c->solimp, 0);
+      }
+      { const double R1 = o->efc_R[r0] / fmax(MINVAL, o->impratio); c->mu = c->friction[0] * sqrt(R1 / o->efc_R[r0]);
+        const double Rpy = 2 * c->mu * c->mu * o->efc_R[r0];
+        for (int r = r0; r < o->nefc; r++) o->efc_R[r] = Rpy; }
+      continue;
+    }
     int r0 = -1;
     for (int k = 0; k < c->dim; k++) {
       int r = add_row(o, ROW_CONTACT, ci, k == 0 ? c->dist : 0, c->includemargin, k < 3 ? tran : rot);

@@ -75,7 +75,7 @@ static int run(Emu<T>* e, const EmuArgs* a) {
   Ctx c = {0, 1};
   for (int env = 0; env < a->n_env; env++) {
     if (s.env_mask && !s.env_mask[env]) continue;
-    if (a->prop_type) run_env<T, VAR_STEP>(e->model, e->g, *e->sc, s, env, c, false);
+    if (a->prop_type || model_needs_classes(e->model)) run_env<T, VAR_STEP>(e->model, e->g, *e->sc, s, env, c, false);      // as step_launch chooses
     else if (a->solver == 1) run_env<T, VAR_PGS>(e->model, e->g, *e->s, s, env, c, false);
     else run_env<T, VAR_STEP>(e->model, e->g, *e->s, s, env, c, false);
   }

@@ -32,3 +32,9 @@ for tag, fuse in (("rearrangement_n4", True), ("rearrangement_n4_unfused", False
         rb = render.build_render_blob(blob, names["geom"], cfglib.CAMERAS[0], cfglib.TASK_GROUPS["rearrangement_w_targets"]["target_locations"])
         open(os.path.join(out, tag + ".b2pr"), "wb").write(rb)
         print(tag + ".b2pr", len(rb), "bytes")
+# the drawing scenes of tasks/lasa_draw.py (arm without the gripper, cylinder tool piece, pyramidal cone): torque motors / position servos
+for tag, kw in (("lasa_draw", {}), ("lasa_draw_position", {"actuators": "position"})):
+    blob, names = scene.compile_lasa_draw(menagerie=args.menagerie, **kw)
+    open(os.path.join(out, tag + ".b2pm"), "wb").write(blob)
+    json.dump(names, open(os.path.join(out, tag + ".names.json"), "w"), indent=0)
+    print(tag, len(blob), "bytes")
