@@ -70,10 +70,11 @@ B2P_HD T row_dot(const DevModel<T>& m, const Scratch<T, C>& s, int r, const T* x
   if (a == 0) {
 #pragma unroll
     for (int k = 0; k < MAXTD; k += 4) {
-      // the whole product is guarded, not just the Jacobian entry: with fewer than 16 dofs in the model (the drawing scene has 7) x[k]
-      // past the row is whatever the shared memory held, and 0 * NaN is NaN
-      v0 += (k < wa ? j[k] * x[k] : T(0)); v1 += (k + 1 < wa ? j[k + 1] * x[k + 1] : T(0));
-      v2 += (k + 2 < wa ? j[k + 2] * x[k + 2] : T(0)); v3 += (k + 3 < wa ? j[k + 3] * x[k + 3] : T(0));
+      // both factors are guarded, not just the Jacobian entry: with fewer than 16 dofs in the model (the drawing scene has 7) x[k] past
+      // the row is whatever the shared memory held, and 0 * NaN is NaN.  (Selecting each factor keeps the fused multiply-add, i.e. the
+      // bits, of the one-guard form; selecting the product would round it separately.)
+      v0 += (k < wa ? j[k] : T(0)) * (k < wa ? x[k] : T(0)); v1 += (k + 1 < wa ? j[k + 1] : T(0)) * (k + 1 < wa ? x[k + 1] : T(0));
+      v2 += (k + 2 < wa ? j[k + 2] : T(0)) * (k + 2 < wa ? x[k + 2] : T(0)); v3 += (k + 3 < wa ? j[k + 3] : T(0)) * (k + 3 < wa ? x[k + 3] : T(0));
     }
   } else {
     v0 = j[0] * x[sa] + j[4] * x[sa + 4]; v1 = j[1] * x[sa + 1] + j[5] * x[sa + 5]; v2 = j[2] * x[sa + 2]; v3 = j[3] * x[sa + 3];
