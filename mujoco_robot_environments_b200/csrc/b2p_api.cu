@@ -156,7 +156,7 @@ static int launch(b2p_handle_s* h, StepArgs<T>& a, cudaStream_t st) {
   a.n_env = h->n_env; a.state = (T*)h->state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = h->prop_type;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, (T*)h->d_jovf, (T*)h->d_w6pool, (T*)h->d_xpool, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};
-  a.work = h->d_work; a.order = nullptr; a.solver = h->solver; a.pyramidal = model_needs_classes(h->hmodel);
+  a.work = h->d_work; a.order = nullptr; a.solver = h->solver; a.need_classes = model_needs_classes(h->hmodel);
   if (h->sort_queue && h->work_steps > 0) {
     b2p_order_kernel<<<1, 1024, 0, st>>>(h->d_work, h->n_env, h->d_order);
     CK(cudaGetLastError());
@@ -199,7 +199,7 @@ static int launch_noalloc(b2p_handle_s* h, void* scratch, void* state, const voi
   a.ctrl = (const T*)(ctrl ? ctrl : h->d_zero_ctrl); a.env_mask = h->env_mask;
   a.n_env = h->n_env; a.state = (T*)state; a.state_stride = REC_SIZE; a.prop_size = (const T*)h->prop_size; a.prop_active = h->prop_active; a.prop_type = nullptr;
   a.status = h->d_status; a.out = (T*)h->out; a.out_stride = OutLayout::SIZE; a.out_mask = h->out_mask; a.gains = (const T*)h->env_gains;
-  a.work = nullptr; a.order = nullptr; a.solver = B2P_SOLVER_NEWTON; a.pyramidal = model_needs_classes(h->hmodel);
+  a.work = nullptr; a.order = nullptr; a.solver = B2P_SOLVER_NEWTON; a.need_classes = model_needs_classes(h->hmodel);
   int* next_env = (int*)scratch;                                                     // cleared by the launch itself (cudaMemsetAsync on the stream)
   T* jovf = (T*)((unsigned char*)scratch + NOALLOC_JOVF_OFF);                         // no need to clear: a row is written before it is read
   Globals<T> g = {(const T*)h->d_mesh_vert, h->d_nbradr, h->d_nbrnum, h->d_nbr, h->d_g1, h->d_g2, (const PairParam<T>*)h->d_pair_param, h->d_geom_start, (const NbrPt<T>*)h->d_nbr_pt, (const NbrSpan*)h->d_nbr_span, jovf, nullptr, nullptr, (const GeomRaw<T>*)h->d_geom_raw, (const T*)h->d_geom_dop};

@@ -161,7 +161,7 @@ static cudaError_t step_launch(const LaunchGeom& lg, const void* d_model, const 
   if (e != cudaSuccess) return e;
   // five instantiations: {step, place} x {box props only, prop classes} + PGS (box props only).  The box-only step kernel is the
   // throughput path; a handle with prop classes bound (b2p_set_env_prop_types) launches the class-capable ones.
-  const bool cls = a.prop_type != nullptr || a.pyramidal != 0;      // pyramidal-cone rows live in the class-capable instantiations only
+  const bool cls = a.prop_type != nullptr || a.need_classes != 0;      // pyramidal-cone rows and tree cylinders live in the class-capable instantiations only
   const DevModel<T>* dm = (const DevModel<T>*)d_model;
   if (a.mode == MODE_PLACE) { if (cls) b2p_step_kernel<T, VAR_PLACE, true><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env); else b2p_step_kernel<T, VAR_PLACE, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env); }
   else if (a.solver == 1 && !cls) b2p_step_kernel<T, VAR_PGS, false><<<lg.grid, lg.threads, lg.smem_bytes, st>>>(dm, g, a, next_env);

@@ -103,7 +103,7 @@ template <typename T, bool C> B2P_HD const unsigned char* block_rows(const Scrat
 // launch parameters shared by kernel and host emulation
 template <typename T>
 struct StepArgs {
-  int mode, n_env, n_steps, control_steps, state_stride, full_contacts, lockstep, lock_group, solver, pyramidal;   // solver: 0 Newton, 1 PGS; pyramidal: model_needs_classes() -- a pyramidal cone or a sphere / cylinder on the tree: launch the class-capable instantiations   // lock_group: warps per lockstep group (0 = whole CTA)
+  int mode, n_env, n_steps, control_steps, state_stride, full_contacts, lockstep, lock_group, solver, need_classes;   // solver: 0 Newton, 1 PGS; need_classes: model_needs_classes() -- a pyramidal cone or a sphere / cylinder on the tree: launch the class-capable instantiations   // lock_group: warps per lockstep group (0 = whole CTA)
   T* state;                  // [n_env][state_stride]: qpos | qvel | qacc_warmstart | time
   const T* ctrl;             // MODE_PHYSICS / SETTLE: [n_env][nu]
   const T* target;           // MODE_OSC: [n_env][13] pos3 vel3 quat4(wxyz) angvel3
