@@ -9,12 +9,19 @@
  *                         (OSC.compute_control_output  mujoco_controllers/osc.py:180-238,
  *                          MinMax.compute_control_output  mujoco_controllers/min_max.py:14-19,
  *                          OSC.is_converged  osc.py:240-247)
+ *                         LasaDrawEnv.move_to_draw_target / interactive_tuning (one tick)   tasks/lasa_draw.py:300-349
+ *                         (b2p_step_physics on the position-servo scene: move_to_joint_position_target  tasks/lasa_draw.py:351-368)
  *   b2p_settle         <- PropPlacer settle loop under JointStaticIsolator    environment/prop_initializer.py:245-257
  *   b2p_forward        <- physics.forward() + reads of data.site_xpos / contact / qacc
  *                                                                           prop_initializer.py:190,221 ; tasks/rearrangement.py:653
  *   b2p_osc_config     <- config/robots/arm/controller_config/osc.yaml gains / nullspace / convergence
  *   b2p_set_env_params <- per-scene prop sizes drawn in environment/props.py:277-291 and the per-prop
  *                         contype/conaffinity toggling of prop_initializer.py:142-162
+ *
+ * Model class (b2p_create refuses anything else with B2P_ERR_MODEL and a message): one hinge-jointed tree of <= 15 dofs (the arm, with
+ * or without the gripper's four-bar) under unit-gear joint actuators, <= 4 free box props (sphere / cylinder colliders per scene through
+ * b2p_set_env_prop_types), static boxes / planes / convex hulls, a cylinder on the tree (the drawing scene's tool piece), condim 3,
+ * Newton solver, elliptic or pyramidal friction cone, implicitfast or Euler integrator.
  *
  * Conventions (after the reference's own raw C boundary, madrona_mjx src/bindings.cpp:219-250): the caller owns
  * every I/O buffer (device pointers, e.g. torch tensors), the handle owns scratch, work is enqueued on the
