@@ -78,8 +78,22 @@ def hull_planes(verts: np.ndarray, max_planes="auto") -> np.ndarray:
     return pl[_spread(len(pl))]
 
 
-def build_render_blob(model_blob: bytes, geom_names: Sequence[str], camera: dict, zones: Optional[dict] = None) -> bytes:
+CYLINDER_SIDES = 64     # a cylinder geom is rendered as the circumscribed 64-gon prism (66 planes; sticks out by r (1 / cos(pi/64) - 1) = 0.02 mm at r = 15 mm)
+
+
+def cylinder_prism(radius: float, half_height: float, sides: int = CYLINDER_SIDES) -> np.ndarray:
+    """Vertices of the prism whose side faces are tangent to the cylinder (axis z)."""
+    ang = 2 * np.pi * (np.arange(sides) + 0.5) / sides
+    rc = radius / np.cos(np.pi / sides)
+    ring = np.stack([rc * np.cos(ang), rc * np.sin(ang)], 1)
+    return np.concatenate([np.concatenate([ring, np.full((sides, 1), z)], 1) for z in (-half_height, half_height)], 0)
+
+
+def build_render_blob(model_blob: bytes, geom_names: Sequence[str], camera: dict, zones: Optional[dict] = None,
+                      colours: Optional[Sequence] = None) -> bytes:
+    """``colours``: (name fragment, rgb) pairs looked up before the rearrangement scene's table of materials."""
     counts, _, A = B.unpack(model_blob)
+    palette = list(colours or []) + _COLOURS
     ng = counts["ngeom"]
     geoms = np.zeros((ng, GEOM_WORDS), np.float32)
     gi = geoms.view(np.int32)
@@ -95,11 +109,17 @@ def build_render_blob(model_blob: bytes, geom_names: Sequence[str], camera: dict
                 mesh_planes[mid] = (sum(len(p) for p in planes), len(pl))
                 planes.append(pl)
             adr, num = mesh_planes[mid]
-        static = int(A["geom_bodyid"][g]) == 0
-        gi[g, 0:8] = (t, adr, num, prop_of.get(g, -1), 1 if static else 0, 0, 0, 0)
-        rgb = next(c for k, c in _COLOURS if k in geom_names[g])
         aabb = np.asarray(A["geom_aabb"][g], np.float64)
         size = np.asarray(A["geom_size"][g], np.float64)
+        if t == B.GEOM_CYLINDER:      # no cylinder primitive in the ray-caster: a convex polytope like the link hulls
+            pl = hull_planes(cylinder_prism(size[0], size[1]), max_planes=None)
+            adr, num = sum(len(p) for p in planes), len(pl)
+            planes.append(pl)
+            t = B.GEOM_MESH
+            aabb = np.array([0, 0, 0, size[0] / np.cos(np.pi / CYLINDER_SIDES), size[0] / np.cos(np.pi / CYLINDER_SIDES), size[1]])
+        static = int(A["geom_bodyid"][g]) == 0
+        gi[g, 0:8] = (t, adr, num, prop_of.get(g, -1), 1 if static else 0, 0, 0, 0)
+        rgb = next(c for k, c in palette if k in geom_names[g])
         f = geoms[g]
         f[8:11] = rgb; f[11] = 1.0
         f[12:15] = size if t != B.GEOM_MESH else aabb[3:6] + AABB_PAD

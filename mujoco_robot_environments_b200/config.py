@@ -61,6 +61,12 @@ TASK_GROUPS: Dict[str, Dict[str, Any]] = {
 }
 
 # config/arena/cameras/transporter_data_collection.yaml:1-6 (the `rearrangement_table` arena's camera list)
+# config/arena/cameras/lasa.yaml:1-6 (the drawing task's observation camera)
+LASA_CAMERAS = [dict(name="main_camera", pos=[0.363, -0.919, 1.663], quat=[0.94215352, 0.3349722, -0.00401909, -0.01114498], height=640, width=640, fovy=61)]
+# the drawing task's visual-only geoms: the draw plane (tasks/lasa_draw.py:147-163: box half (0.3, 0.4, 0.001) at (0.4, 0, 0.55), rgba
+# (0, 0, 1, 0.05), contype = conaffinity = 0) is a translucent zone for the ray-caster; the tool piece and the table carry their rgba
+LASA_ZONES = {"draw_plane": dict(location=[0.4, 0.0, 0.55], size=[0.3, 0.4, 0.001], rgba=[0.0, 0.0, 1.0, 0.05])}
+LASA_COLOURS = [("panda nohand/tool", (0.02, 0.302, 0.4)), ("table/table", (1.0, 1.0, 1.0))]      # lasa_draw.py:118, :97
 CAMERAS = [dict(name="overhead_camera", pos=[0.7, 0.0, 1.3], quat=[0.707, 0.0, 0.0, -0.707], height=480, width=640, fovy=61)]
 # config/dataset/default.yaml
 DATASET = dict(num_episodes=1000, max_steps=10, max_episodes_per_file=10)

@@ -15,8 +15,12 @@ Mirrored methods (same names, argument meaning and return values, every argument
 
 ``config/lasa.yaml`` sets ``physics_dt: 0.01`` and the ticks hold a command for 5 steps: with the OSC gains of
 ``controller_config/osc.yaml`` that sample-and-hold loop is not stable (orientation kd 100 x 0.05 s); ``physics_dt`` is therefore a
-compile-time argument of ``compile_lasa_draw`` and the committed blobs keep the reference's value.  The observations
-(``main_camera`` rgb / depth) are the reference's OpenGL renderer: unavailable on this box, and this scene has no render model yet.
+compile-time argument of ``compile_lasa_draw`` and the committed blobs keep the reference's value.
+
+Observations (``_compute_observation``, lasa_draw.py:281-298: ``main_camera`` rgb + depth, 640 x 640): the reference's OpenGL
+renderer is unavailable on this box; the frames come from the CUDA ray-caster (``render.BatchedRenderer``) on the scene's own render
+model ``assets/lasa_draw.b2pr`` -- camera of config/arena/cameras/lasa.yaml, the arm's collision hulls, the tool piece as a 64-gon
+prism, the translucent draw plane (lasa_draw.py:147-163) as a blended zone.
 """
 from __future__ import annotations
 
@@ -25,6 +29,7 @@ from typing import Optional
 import torch
 
 from .physics import ARM_HOME, BatchedPhysics, load_default_blob
+from .render import BatchedRenderer, load_default_render_blob
 
 TOOL_OFFSET = (0.0, 0.0, 0.1)          # "account for height of toolpiece" (lasa_draw.py:312,334)
 CONTROL_STEPS = 5                      # lasa_draw.py:320,343,361: for _ in range(5)
@@ -38,7 +43,8 @@ class BatchedLasaDrawEnv:
         self.actuators = actuators
         self.physics = BatchedPhysics(num_envs, dtype=dtype, device=device, blob=blob, names=names)
         self.num_envs, self.device, self.dtype = num_envs, self.physics.device, dtype
-        self.physics.set_out_fields("SITE", "DYN")          # the eef site and the controller's torque command
+        self.physics.set_out_fields("SITE", "DYN", "GEOM")  # the eef site, the controller's torque command, the geom poses the renderer reads
+        self._renderer = None
         self._grip = torch.zeros(num_envs, device=self.device, dtype=torch.uint8)      # no gripper: the OSC's gripper bit is ignored (nu = 7)
         self.mocap_quat = torch.tensor([0.0, 0.0, 1.0, 0.0], device=self.device, dtype=dtype).repeat(num_envs, 1)   # R.from_euler('xyz', [180, 180, 0]) as MuJoCo reads it (lasa_draw.py:137)
         self.reset()
@@ -87,3 +93,21 @@ class BatchedLasaDrawEnv:
         p.set_control(torch.as_tensor(target_position, device=self.device, dtype=self.dtype).expand(self.num_envs, 7))
         p.step(CONTROL_STEPS)          # xfrc_applied: the reference draws it with scale = 0 (lasa_draw.py:355-358), i.e. nothing is applied
         return p.qpos[:, :7].clone()
+
+    # ---------------------------------------------------------------------------------------------- lasa_draw.py:245-298
+    def observation_spec(self):
+        r = self._get_renderer()
+        return {"main_camera/depth": ((self.num_envs, r.height, r.width), torch.float32), "main_camera/rgb": ((self.num_envs, r.height, r.width, 3), torch.uint8)}
+
+    def _get_renderer(self) -> BatchedRenderer:
+        if self._renderer is None:
+            self._renderer = BatchedRenderer(self.device, blob=load_default_render_blob("lasa_draw"))
+        return self._renderer
+
+    def _compute_observation(self):
+        out = self._get_renderer().render(self.physics, seg=False)
+        return {"main_camera/rgb": out["rgb"], "main_camera/depth": out["depth"]}
+
+    def step(self, action_dict=None):
+        """lasa_draw.py:245-257: the reference's step only observes (the motion goes through move_to_draw_target)."""
+        return self._compute_observation()

@@ -87,3 +87,28 @@ def test_move_to_joint_position_target_with_the_tool_on_the_table(dtype, tol):
     assert np.abs(q.cpu().numpy().astype(np.float64) - o.qpos[:7]).max() < tol
     with pytest.raises(RuntimeError):
         env.move_to_draw_target(torch.zeros(n, 3), torch.zeros(n, 3))
+
+
+def test_main_camera_observation_bit_exact_vs_render_oracle():
+    """lasa_draw.py:281-298 on the CUDA ray-caster: rgb bytes and depth floats of the drawing scene's own render model (tool piece as a
+    64-gon prism, draw plane as a blended zone) against the plain-C restatement, on a window around the arm and on a full frame."""
+    import rnd
+    from mujoco_robot_environments_b200.lasa_draw import BatchedLasaDrawEnv
+    from mujoco_robot_environments_b200.render import load_default_render_blob
+    n = 2
+    env = BatchedLasaDrawEnv(n, dtype=torch.float32)
+    env.physics.qpos[1, :7] = torch.tensor(TOUCH, device=env.device)
+    env.physics.forward(full_contacts=False)
+    obs = env.step()
+    torch.cuda.synchronize()
+    assert obs["main_camera/rgb"].shape == (n, 640, 640, 3) and obs["main_camera/depth"].shape == (n, 640, 640)
+    xp, xm = env.physics.data.geom_xpos.cpu().numpy().astype(np.float64), env.physics.data.geom_xmat.cpu().numpy().astype(np.float64)
+    blob = load_default_render_blob("lasa_draw")
+    for e, win in ((0, None), (1, (160, 96, 544, 480))):
+        rgb, depth, seg = rnd.render(blob, xp[e], xm[e], None, None, None, window=win)
+        x0, y0, x1, y1 = win if win else (0, 0, 640, 640)
+        g_rgb, g_d = obs["main_camera/rgb"][e].cpu().numpy()[y0:y1, x0:x1], obs["main_camera/depth"][e].cpu().numpy()[y0:y1, x0:x1]
+        assert np.array_equal(g_d.view(np.uint32), depth[y0:y1, x0:x1].view(np.uint32)), ("depth", e)
+        assert np.array_equal(g_rgb, rgb[y0:y1, x0:x1]), ("rgb", e)
+        assert (seg[y0:y1, x0:x1] == 1).any() and ((seg[y0:y1, x0:x1] >= 3) & (seg[y0:y1, x0:x1] <= 12)).any()      # table and arm in view
+    assert not torch.equal(obs["main_camera/rgb"][0], obs["main_camera/rgb"][1])

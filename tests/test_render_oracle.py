@@ -102,3 +102,50 @@ def test_oracle_known_answers():
     assert arm.sum() > 10000 and len(np.unique(seg[256:][arm])) >= 6
     assert depth[256:][arm].max() < 0.9 and depth[256:][arm].min() > 0.2
     assert rgb[256:][seg[256:] == 10].mean() > 150            # link6 hull: white panda material, lit from above
+
+
+# ---------------------------------------------------------------------------------------------- the drawing scene's render model
+def _draw_assets():
+    root = os.path.join(os.path.dirname(os.path.dirname(os.path.abspath(__file__))), "mujoco_robot_environments_b200", "assets")
+    with open(os.path.join(root, "lasa_draw.b2pm"), "rb") as f:
+        pb = f.read()
+    with open(os.path.join(root, "lasa_draw.b2pr"), "rb") as f:
+        rb = f.read()
+    with open(os.path.join(root, "lasa_draw.names.json")) as f:
+        names = json.load(f)
+    return pb, rb, names
+
+
+def test_draw_render_blob_is_reproducible_and_the_tool_piece_is_a_tight_prism():
+    pb, rb, names = _draw_assets()
+    assert R.build_render_blob(pb, names["geom"], C.LASA_CAMERAS[0], C.LASA_ZONES, colours=C.LASA_COLOURS) == rb
+    assert rnd.header(rb) == dict(ngeom=13, nplane=rnd.header(rb)["nplane"], nzone=1, W=640, H=640, nprop=0)
+    pl = R.hull_planes(R.cylinder_prism(0.015, 0.05), max_planes=None)
+    assert len(pl) == R.CYLINDER_SIDES + 2
+    ang = np.linspace(0, 2 * np.pi, 1000)
+    surf = np.concatenate([np.stack([0.015 * np.cos(ang), 0.015 * np.sin(ang), np.full_like(ang, z)], 1) for z in (-0.05, 0.0, 0.05)], 0)
+    slackness = (surf @ pl[:, :3].T - pl[:, 3]).max(1)           # how far outside the polytope a cylinder point lies (<= 0: inside)
+    assert slackness.max() <= 1e-12 and slackness.min() > -2.5e-5  # circumscribed: the cylinder touches every side face, sticks in by < 0.02 mm
+
+
+def test_draw_scene_known_answers():
+    """main_camera (config/arena/cameras/lasa.yaml) at the arm's home pose: a table pixel's depth is the ray / plane z = 0.4 answer of
+    the pinhole model; the tool piece, the links and the draw plane's zone are in view."""
+    pb, rb, names = _draw_assets()
+    o = Oracle(pb); o.reset(); o.qpos[:7] = [0, -0.785, 0, -2.356, 0, 1.571, 0.785]; o.forward()
+    rgb, depth, seg = rnd.render(rb, np.array(o.geom_xpos), np.array(o.geom_xmat), None, None, None)
+    tool, table = names["geom"].index("panda nohand/tool"), names["geom"].index("table/table")
+    assert (seg == tool).sum() > 50 and (seg == table).sum() > 100000 and (seg == 13).sum() > 10000      # 13 = ngeom + zone 0
+    cam = C.LASA_CAMERAS[0]
+    q = np.asarray(cam["quat"], float); q /= np.linalg.norm(q)
+    w, x, y, z = q
+    M = np.array([[1 - 2 * (y * y + z * z), 2 * (x * y - w * z), 2 * (x * z + w * y)], [2 * (x * y + w * z), 1 - 2 * (x * x + z * z), 2 * (y * z - w * x)],
+                  [2 * (x * z - w * y), 2 * (y * z + w * x), 1 - 2 * (x * x + y * y)]])
+    f = (1 / np.tan(np.deg2rad(cam["fovy"]) / 2)) * cam["height"] / 2
+    vs, us = np.nonzero(seg == table)
+    for k in (0, len(vs) // 2, len(vs) - 1):
+        u, v = us[k], vs[k]
+        d = M[:, 0] * ((u - (cam["width"] - 1) / 2) / f) + M[:, 1] * (((cam["height"] - 1) / 2 - v) / f) - M[:, 2]
+        t = (0.4 - cam["pos"][2]) / d[2]                                                               # axial depth: the direction has -1 along the view axis
+        assert abs(depth[v, u] - t) < 2e-5 * t, (u, v, depth[v, u], t)
+    assert tuple(rgb[vs[0], us[0]]) != tuple(rgb[(seg == tool)][0])                                    # white table, petrol tool piece

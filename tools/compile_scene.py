@@ -38,3 +38,9 @@ for tag, kw in (("lasa_draw", {}), ("lasa_draw_position", {"actuators": "positio
     open(os.path.join(out, tag + ".b2pm"), "wb").write(blob)
     json.dump(names, open(os.path.join(out, tag + ".names.json"), "w"), indent=0)
     print(tag, len(blob), "bytes")
+    if tag == "lasa_draw":      # render model: main_camera, the draw plane as a translucent zone, the tool piece as a 64-gon prism
+        from mujoco_robot_environments_b200 import config as cfglib
+        from mujoco_robot_environments_b200.compile import render
+        rb = render.build_render_blob(blob, names["geom"], cfglib.LASA_CAMERAS[0], cfglib.LASA_ZONES, colours=cfglib.LASA_COLOURS)
+        open(os.path.join(out, tag + ".b2pr"), "wb").write(rb)
+        print(tag + ".b2pr", len(rb), "bytes")
